@@ -1,0 +1,75 @@
+"""Build libfi_b200.so (the C-ABI extension) in-tree with nvcc for sm_100a.
+
+No JIT, no torch cpp_extension: one explicit nvcc invocation per translation unit
+(`-gencode arch=compute_100a,code=sm_100a -lineinfo`), linked into
+flashinfer_b200/libfi_b200.so with the static CUDA runtime.  The reference instead
+JIT-compiles per (dtype, head_dim, variant) through ninja (flashinfer/jit/core.py:250-263).
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+CSRC = HERE / "csrc"
+OUT = HERE / "libfi_b200.so"
+OBJ = HERE / "build"
+SOURCES = ["plan.cu", "decode.cu", "merge.cu"]
+NVCC = os.environ.get("FI_B200_NVCC", "/usr/local/cuda/bin/nvcc")
+FLAGS = [
+    "-std=c++17", "-O3", "-lineinfo", "--expt-relaxed-constexpr",
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
+    "-DFI_B200_BUILD",
+]
+
+
+def _digest() -> str:
+    h = hashlib.sha256()
+    for p in sorted(list(CSRC.glob("*")) + [HERE.parent / "include" / "fi_b200.h", Path(__file__)]):
+        if p.is_file():
+            h.update(p.name.encode())
+            h.update(p.read_bytes())
+    h.update(" ".join(FLAGS).encode())
+    return h.hexdigest()
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    stamp = OBJ / "stamp.txt"
+    dig = _digest()
+    if not force and OUT.exists() and stamp.exists() and stamp.read_text() == dig:
+        return OUT
+    if not Path(NVCC).exists():
+        raise RuntimeError(f"nvcc not found at {NVCC}; cannot build libfi_b200.so")
+    OBJ.mkdir(exist_ok=True)
+
+    def cc(src: str) -> Path:
+        obj = OBJ / (src + ".o")
+        cmd = [NVCC, *FLAGS, "-c", str(CSRC / src), "-o", str(obj)]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+        if verbose:
+            print(r.stderr)
+        return obj
+
+    with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
+        objs = list(ex.map(cc, SOURCES))
+    cmd = [NVCC, "-shared", "-o", str(OUT), *map(str, objs), "-cudart", "static",
+           "-gencode", "arch=compute_100a,code=sm_100a"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    stamp.write_text(dig)
+    return OUT
+
+
+if __name__ == "__main__":
+    p = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    print(p)

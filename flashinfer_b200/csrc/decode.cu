@@ -1,0 +1,350 @@
+// decode.cu — launchers and C-ABI entry points for batch / single decode.
+// Replaces BatchDecodeWithPagedKVCacheRun (reference csrc/batch_decode.cu:81-191),
+// BatchDecodeWithPagedKVCacheDispatched (include/flashinfer/attention/decode.cuh:739-825),
+// single_decode_with_kv_cache (csrc/single_decode.cu:33-104) and
+// SingleDecodeWithKVCacheDispatched (decode.cuh:658-737).
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <string.h>
+
+#include <mutex>
+#include <utility>
+
+#include "decode_kernel.cuh"
+#include "host_common.h"
+#include "merge_kernels.cuh"
+
+namespace fib200 {
+
+// ---- TMA descriptor ------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 4-D map over one of K / V: dims (D, n, h, page) — or (D, h, n, page) when the head
+// stride is the smaller one (NHD), so that strides grow with the dimension index.
+static int make_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int head_dim,
+                       int64_t dim_n, int64_t dim_h, int64_t dim_page, int64_t stride_n,
+                       int64_t stride_h, int64_t stride_page, int rows_per_box) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (enc == nullptr) return fail(FI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  const int es = dtype_size(kv_dtype);
+  CUtensorMapDataType dt = es == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                   : (kv_dtype == FI_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                                                : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
+  cuuint64_t dims[4] = {(cuuint64_t)head_dim, (cuuint64_t)dim_n, (cuuint64_t)dim_h,
+                        (cuuint64_t)dim_page};
+  cuuint64_t strides[3] = {(cuuint64_t)(stride_n * es), (cuuint64_t)(stride_h * es),
+                           (cuuint64_t)(stride_page * es)};
+  cuuint32_t box[4] = {(cuuint32_t)(128 / es), (cuuint32_t)rows_per_box, 1, 1};
+  if (stride_h < stride_n) {
+    std::swap(dims[1], dims[2]);
+    std::swap(strides[0], strides[1]);
+    std::swap(box[1], box[2]);
+  }
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(map, dt, 4, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(FI_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
+  return FI_OK;
+}
+
+static bool is_pow2(int64_t x) { return x > 0 && (x & (x - 1)) == 0; }
+static int ilog2(int64_t x) { int s = 0; while ((int64_t(1) << s) < x) ++s; return s; }
+
+static bool tma_eligible(const void* k, const void* v, int es, int64_t sn, int64_t sh, int64_t sp,
+                         int page_size, bool contiguous, int64_t kv_len) {
+  if (tuning().loader == 2) return false;
+  if ((reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15) return false;
+  if ((sn * es) % 16 || (sh * es) % 16 || (sp * es) % 16) return false;
+  if (contiguous) return kv_len >= kTileTokens;
+  return is_pow2(page_size) && page_size >= 8;
+}
+
+// ---- kernel launch ---------------------------------------------------------------
+template <int QT, int KVF, int HD, int LOADER>
+static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
+                      int grid, cudaStream_t stream) {
+  auto kern = paged_decode_kernel<QT, KVF, HD, LOADER>;
+  const int smem = SmemLayout<KVF, HD>::total(p.num_stages);
+  FI_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(BlockDim<LOADER>::kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.enable_pdl ? 1 : 0;
+  FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p, km, vm));
+  return FI_OK;
+}
+
+template <int QT, int KVF, int HD>
+static int launch_loader(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
+                         int grid, bool tma, cudaStream_t stream) {
+  return tma ? launch_one<QT, KVF, HD, 0>(p, km, vm, grid, stream)
+             : launch_one<QT, KVF, HD, 1>(p, km, vm, grid, stream);
+}
+
+template <int QT, int KVF>
+static int launch_hd(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
+                     int head_dim, int grid, bool tma, cudaStream_t stream) {
+  switch (head_dim) {
+    case 128: return launch_loader<QT, KVF, 128>(p, km, vm, grid, tma, stream);
+    case 256: return launch_loader<QT, KVF, 256>(p, km, vm, grid, tma, stream);
+    case 64:
+      if constexpr (KVF == 0) return launch_loader<QT, KVF, 64>(p, km, vm, grid, tma, stream);
+    default: break;
+  }
+  return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
+}
+
+static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
+                         int q_dtype, int kvf, int head_dim, int grid, bool tma,
+                         cudaStream_t stream) {
+  const bool bf = q_dtype == FI_DTYPE_BF16;
+  switch (kvf) {
+    case 0: return bf ? launch_hd<1, 0>(p, km, vm, head_dim, grid, tma, stream)
+                      : launch_hd<0, 0>(p, km, vm, head_dim, grid, tma, stream);
+    case 1: return bf ? launch_hd<1, 1>(p, km, vm, head_dim, grid, tma, stream)
+                      : launch_hd<0, 1>(p, km, vm, head_dim, grid, tma, stream);
+    case 2: return bf ? launch_hd<1, 2>(p, km, vm, head_dim, grid, tma, stream)
+                      : launch_hd<0, 2>(p, km, vm, head_dim, grid, tma, stream);
+    default: break;
+  }
+  return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
+}
+
+static int launch_merge(const MergeParams& mp, int grid, cudaStream_t stream) {
+  if (grid <= 0) return FI_OK;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(128);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = mp.enable_pdl ? 1 : 0;
+  if (mp.out_dtype == FI_DTYPE_BF16) FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, decode_merge_kernel<1>, mp));
+  else FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, decode_merge_kernel<0>, mp));
+  return FI_OK;
+}
+
+static int g_last_loader = -1;  // 0 TMA, 1 cp.async: what the last run() launched (for tests)
+static long long g_launch_count = 0;
+
+}  // namespace fib200
+
+using namespace fib200;
+
+extern "C" {
+
+int fi_last_loader(void) { return g_last_loader; }
+long long fi_launch_count(void) { return g_launch_count; }
+
+int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, const void* q,
+                        int64_t q_stride_n, int64_t q_stride_h, const void* k_cache,
+                        const void* v_cache, int64_t num_pages, int64_t kv_stride_page,
+                        int64_t kv_stride_n, int64_t kv_stride_h, const int32_t* kv_indices,
+                        const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
+                        float v_scale, float logits_soft_cap, int enable_pdl, int device,
+                        void* stream_) {
+  if (plan_info == nullptr || plan_info[kPiMagic] != kPlanMagic)
+    return fail(FI_ERR_INVALID_ARGUMENT, "plan info is not initialized");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int bs = (int)plan_info[kPiBatchSize];
+  if (bs == 0) return FI_OK;
+  const int q_dtype = (int)plan_info[kPiQDtype], kv_dtype = (int)plan_info[kPiKvDtype];
+  const int kvf = kv_format(q_dtype, kv_dtype);
+  const int es = dtype_size(kv_dtype);
+  const int head_dim = (int)plan_info[kPiHeadDim];
+  const int page_size = (int)plan_info[kPiPageSize];
+  const int Hq = (int)plan_info[kPiNumQoHeads], Hkv = (int)plan_info[kPiNumKvHeads];
+  if ((q_stride_n % 4) || (q_stride_h % 4) || (reinterpret_cast<uintptr_t>(q) & 7))
+    return fail(FI_ERR_INVALID_ARGUMENT, "q rows must be 8-byte aligned");
+  if ((kv_stride_n * es) % 16 || (kv_stride_h * es) % 16 || (kv_stride_page * es) % 16 ||
+      ((reinterpret_cast<uintptr_t>(k_cache) | reinterpret_cast<uintptr_t>(v_cache)) & 15))
+    return fail(FI_ERR_INVALID_ARGUMENT, "k/v cache rows must be 16-byte aligned");
+  FI_CUDA_TRY(cudaSetDevice(device));
+
+  char* iw = static_cast<char*>(int_ws);
+  char* fw = static_cast<char*>(float_ws);
+  DecodeParams p;
+  memset(&p, 0, sizeof(p));
+  p.q = q; p.q_stride_n = q_stride_n; p.q_stride_h = q_stride_h;
+  p.o = o; p.lse = lse;
+  p.k = k_cache; p.v = v_cache;
+  p.kv_stride_page = kv_stride_page; p.kv_stride_n = kv_stride_n; p.kv_stride_h = kv_stride_h;
+  p.kv_indices = kv_indices; p.kv_indptr = kv_indptr;
+  p.page_size = page_size;
+  p.page_shift = is_pow2(page_size) ? ilog2(page_size) : -1;
+  p.page_mask = is_pow2(page_size) ? page_size - 1 : 0;
+  p.rows_per_box = page_size < kTileTokens ? page_size : kTileTokens;
+  p.tma_h_first = kv_stride_h < kv_stride_n;
+  p.header = reinterpret_cast<const PlanHeader*>(iw + plan_info[kPiOffHeader]);
+  p.cta_seg_indptr = reinterpret_cast<const int32_t*>(iw + plan_info[kPiOffCtaIndptr]);
+  p.segments = reinterpret_cast<const Segment*>(iw + plan_info[kPiOffSegments]);
+  p.tmp_o = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpO]);
+  p.tmp_lse = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpLse]);
+  p.num_qo_heads = Hq;
+  p.group_size = Hq / Hkv;
+  p.num_stages = (int)plan_info[kPiStages];
+  p.sm_scale = sm_scale;
+  p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
+  p.v_scale = v_scale;
+  p.soft_cap = logits_soft_cap;
+  p.enable_pdl = enable_pdl;
+
+  const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
+                                page_size, false, 0);
+  if (!tma && tuning().loader == 1)
+    return fail(FI_ERR_UNSUPPORTED, "TMA loader forced but page geometry is not eligible");
+  CUtensorMap km, vm;
+  memset(&km, 0, sizeof(km));
+  memset(&vm, 0, sizeof(vm));
+  if (tma) {
+    int rc = make_kv_map(&km, k_cache, kv_dtype, head_dim, page_size, Hkv, num_pages, kv_stride_n,
+                         kv_stride_h, kv_stride_page, p.rows_per_box);
+    if (rc != FI_OK) return rc;
+    rc = make_kv_map(&vm, v_cache, kv_dtype, head_dim, page_size, Hkv, num_pages, kv_stride_n,
+                     kv_stride_h, kv_stride_page, p.rows_per_box);
+    if (rc != FI_OK) return rc;
+  }
+  int rc = launch_decode(p, km, vm, q_dtype, kvf, head_dim, (int)plan_info[kPiNumCtas], tma, stream);
+  if (rc != FI_OK) return rc;
+  g_last_loader = tma ? 0 : 1;
+  ++g_launch_count;
+
+  const int merge_grid = (int)plan_info[kPiMergeGrid];
+  if (merge_grid > 0) {
+    MergeParams mp;
+    memset(&mp, 0, sizeof(mp));
+    mp.header = p.header;
+    mp.units = reinterpret_cast<const MergeUnit*>(iw + plan_info[kPiOffMerge]);
+    mp.tmp_o = p.tmp_o; mp.tmp_lse = p.tmp_lse;
+    mp.o = o; mp.lse = lse;
+    mp.num_qo_heads = Hq; mp.group_size = p.group_size; mp.head_dim = head_dim;
+    mp.out_scale = v_scale;
+    mp.out_dtype = q_dtype;
+    mp.enable_pdl = enable_pdl;
+    rc = launch_merge(mp, merge_grid, stream);
+    if (rc != FI_OK) return rc;
+    ++g_launch_count;
+  }
+  return FI_OK;
+}
+
+size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int head_dim, int device) {
+  int sms = 148;
+  if (device >= 0) device_sm_count(device, &sms);
+  const size_t slots = (size_t)sms * 2 + num_kv_heads;
+  const size_t g = num_qo_heads / (num_kv_heads > 0 ? num_kv_heads : 1);
+  return slots * g * (head_dim + 1) * 4 + 64;
+}
+
+int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp, size_t tmp_bytes,
+                         void* o, float* lse, int num_qo_heads, int num_kv_heads, int head_dim,
+                         int kv_len, int q_dtype, int kv_dtype, int kv_layout, int window_left,
+                         float sm_scale, float v_scale, float logits_soft_cap, int device,
+                         void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (num_kv_heads <= 0 || num_qo_heads % num_kv_heads)
+    return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads must be a multiple of num_kv_heads");
+  const int group = num_qo_heads / num_kv_heads;
+  if (group > kMaxGroup) return fail(FI_ERR_UNSUPPORTED, "Unsupported group_size: %d", group);
+  const int kvf = kv_format(q_dtype, kv_dtype);
+  if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair");
+  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256) || (kvf != 0 && head_dim == 64))
+    return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
+  if (kv_len < 0) return fail(FI_ERR_INVALID_ARGUMENT, "negative kv_len");
+  const int es = dtype_size(kv_dtype);
+  FI_CUDA_TRY(cudaSetDevice(device));
+  int sms = 0;
+  int rc = device_sm_count(device, &sms);
+  if (rc != FI_OK) return rc;
+  const KernelConfig cfg = choose_config(kvf, head_dim);
+
+  const int tok_lo = window_left >= 0 ? (kv_len - 1 - window_left > 0 ? kv_len - 1 - window_left : 0) : 0;
+  const int tiles = kv_len == 0 ? 0 : (kv_len + kTileTokens - 1) / kTileTokens - tok_lo / kTileTokens;
+  const long long T = (long long)tiles * num_kv_heads;
+  const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
+  long long grid = T / min_tiles;
+  if (grid < 1) grid = 1;
+  if (grid > (long long)sms * cfg.ctas_per_sm) grid = (long long)sms * cfg.ctas_per_sm;
+
+  const size_t slots = (size_t)grid + num_kv_heads;
+  const size_t tmp_o_bytes = ((slots * group * head_dim * 4) + 15) & ~size_t(15);
+  if (tmp_o_bytes + slots * group * 4 > tmp_bytes)
+    return fail(FI_ERR_WORKSPACE, "single decode tmp buffer too small");
+
+  DecodeParams p;
+  memset(&p, 0, sizeof(p));
+  p.q = q; p.q_stride_n = 0; p.q_stride_h = head_dim;
+  p.o = o; p.lse = lse; p.k = k; p.v = v;
+  if (kv_layout == FI_LAYOUT_NHD) { p.kv_stride_n = (int64_t)num_kv_heads * head_dim; p.kv_stride_h = head_dim; }
+  else { p.kv_stride_n = head_dim; p.kv_stride_h = (int64_t)kv_len * head_dim; }
+  p.kv_stride_page = 0;
+  p.page_size = kv_len > 0 ? kv_len : 1;
+  p.page_shift = 31; p.page_mask = 0x7fffffff;
+  p.rows_per_box = kTileTokens;
+  p.tma_h_first = p.kv_stride_h < p.kv_stride_n;
+  p.header = nullptr;
+  p.imp_units = num_kv_heads; p.imp_tiles = tiles; p.imp_tok_lo = tok_lo; p.imp_tok_hi = kv_len;
+  p.tmp_o = static_cast<float*>(tmp);
+  p.tmp_lse = reinterpret_cast<float*>(static_cast<char*>(tmp) + tmp_o_bytes);
+  p.num_qo_heads = num_qo_heads; p.group_size = group;
+  p.num_stages = cfg.stages;
+  p.sm_scale = sm_scale; p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
+  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0;
+
+  const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len);
+  CUtensorMap km, vm;
+  memset(&km, 0, sizeof(km));
+  memset(&vm, 0, sizeof(vm));
+  if (tma) {
+    const int64_t sp = (int64_t)kv_len * num_kv_heads * head_dim;  // single "page"
+    rc = make_kv_map(&km, k, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, kTileTokens);
+    if (rc != FI_OK) return rc;
+    rc = make_kv_map(&vm, v, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, kTileTokens);
+    if (rc != FI_OK) return rc;
+  }
+  rc = launch_decode(p, km, vm, q_dtype, kvf, head_dim, (int)grid, tma, stream);
+  if (rc != FI_OK) return rc;
+  g_last_loader = tma ? 0 : 1;
+  ++g_launch_count;
+  if (grid > 1 && T > 0) {
+    MergeParams mp;
+    memset(&mp, 0, sizeof(mp));
+    mp.header = nullptr;
+    mp.imp_units = num_kv_heads; mp.imp_tiles = tiles; mp.imp_ctas = (int)grid;
+    mp.tmp_o = p.tmp_o; mp.tmp_lse = p.tmp_lse; mp.o = o; mp.lse = lse;
+    mp.num_qo_heads = num_qo_heads; mp.group_size = group; mp.head_dim = head_dim;
+    mp.out_scale = v_scale; mp.out_dtype = q_dtype; mp.enable_pdl = 0;
+    rc = launch_merge(mp, num_kv_heads, stream);
+    if (rc != FI_OK) return rc;
+    ++g_launch_count;
+  }
+  return FI_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,141 @@
+// decode_params.h — work-list records and kernel parameter block shared by the
+// host planner (plan.cu), the launchers (decode.cu) and the kernels.
+//
+// Reference counterparts: DecodePlanInfo (include/flashinfer/attention/scheduler.cuh:366-422),
+// Params (csrc/batch_decode_customize_config.jinja:28-60), paged_kv_t
+// (include/flashinfer/page.cuh:37-210).  The design differs on purpose: instead of a
+// (request, uniform-chunk) grid the planner cuts the flattened (request, kv-head, tile)
+// stream into one contiguous range per persistent CTA ("stream-K" over KV tiles).
+#pragma once
+#include <stdint.h>
+
+namespace fib200 {
+
+constexpr int kTileTokens = 64;       // KV tokens per pipeline stage
+constexpr int kConsumerWarps = 4;     // 16 tokens per warp per stage (MMA M = 16)
+constexpr int kMaxStages = 12;
+constexpr int kSegCache = 32;         // segment records cached in smem per CTA
+constexpr float kNegInf = -5e4f;      // finite "-inf", reference math.cuh:32
+constexpr int kMaxGroup = 8;          // GQA group size handled by one MMA N tile
+
+// One unit of work for a CTA: tiles [tile_begin, tile_end) (absolute tile index on the
+// request's token axis, tile t covers tokens [64 t, 64 t + 64)) of KV head `kv_head`
+// of request `request`.  Only tokens in [tok_lo, tok_hi) are attended.
+// slot < 0: the segment covers the whole unit, write o/lse directly;
+// slot >= 0: write a normalised partial (o fp32, lse) into partial slot `slot`.
+struct alignas(16) Segment {
+  int32_t request;
+  int32_t kv_head;
+  int32_t tile_begin;
+  int32_t tile_end;
+  int32_t slot;
+  int32_t tok_lo;
+  int32_t tok_hi;
+  int32_t pad;
+};
+static_assert(sizeof(Segment) == 32, "Segment must be 32 bytes");
+
+// A (request, kv_head) unit whose KV range was split over several CTAs: partial
+// slots [slot_begin, slot_begin + count) are merged into o[request, kv_head*G ..].
+struct alignas(16) MergeUnit {
+  int32_t request;
+  int32_t kv_head;
+  int32_t slot_begin;
+  int32_t count;
+};
+
+// Device-resident header (first bytes of the int workspace), rewritten by every plan()
+// so that CUDA-graph replays pick up new counts without new launch geometry.
+struct PlanHeader {
+  int32_t num_ctas_used;
+  int32_t num_segments;
+  int32_t num_merge_units;
+  int32_t num_slots;
+  int32_t total_tiles;
+  int32_t pad[3];
+};
+
+// indices into the int64 plan-info vector handed to Python (opaque there)
+enum PlanInfoSlot {
+  kPiMagic = 0,
+  kPiNumCtas,       // launch grid of the decode kernel
+  kPiNumSegments,
+  kPiNumMergeUnits,
+  kPiNumSlots,
+  kPiOffHeader,
+  kPiOffCtaIndptr,
+  kPiOffSegments,
+  kPiOffMerge,
+  kPiOffTmpO,
+  kPiOffTmpLse,
+  kPiBatchSize,
+  kPiNumQoHeads,
+  kPiNumKvHeads,
+  kPiHeadDim,
+  kPiPageSize,
+  kPiQDtype,
+  kPiKvDtype,
+  kPiCudaGraph,
+  kPiMergeGrid,     // launch grid of the merge kernel (0: no merge launch)
+  kPiTotalTiles,
+  kPiWindowLeft,
+  kPiStages,
+  kPiIntBytesUsed,
+  kPiLen
+};
+constexpr int64_t kPlanMagic = 0xF1B2000001LL;
+
+struct DecodeParams {
+  // q / o
+  const void* q;
+  int64_t q_stride_n, q_stride_h;  // elements
+  void* o;                         // [bs, Hq, D] contiguous, q dtype
+  float* lse;                      // [bs, Hq] or null
+  // kv (element strides; used by the cp.async loader, TMA uses the tensor maps)
+  const void* k;
+  const void* v;
+  int64_t kv_stride_page, kv_stride_n, kv_stride_h;
+  const int32_t* kv_indices;  // null: identity page table
+  const int32_t* kv_indptr;   // null: page base 0 (contiguous single request)
+  int32_t page_size;
+  int32_t page_shift;  // log2(page_size) when a power of two, else -1 (31: one giant page)
+  int32_t page_mask;   // page_size - 1 when a power of two (0x7fffffff: one giant page)
+  int32_t rows_per_box;  // TMA: min(page_size, 64)
+  int32_t tma_h_first;   // TMA map dim order: 1 = (D, h, n, page), 0 = (D, n, h, page)
+  // work list (explicit) ...
+  const PlanHeader* header;
+  const int32_t* cta_seg_indptr;
+  const Segment* segments;
+  // ... or implicit uniform mode (single request, contiguous KV): segments are
+  // derived in closed form from these (header == nullptr).
+  int32_t imp_units;      // number of kv heads
+  int32_t imp_tiles;      // tiles per unit
+  int32_t imp_tok_lo, imp_tok_hi;
+  // partial outputs
+  float* tmp_o;    // [slots, G, D]
+  float* tmp_lse;  // [slots, G]
+  int32_t num_qo_heads;
+  int32_t group_size;
+  int32_t num_stages;
+  float sm_scale_log2;     // sm_scale * log2(e)
+  float v_scale;
+  float soft_cap;          // <= 0 disabled
+  float sm_scale;          // plain sm_scale (soft-cap path)
+  int32_t enable_pdl;
+};
+
+struct MergeParams {
+  const PlanHeader* header;     // null in implicit mode
+  const MergeUnit* units;
+  int32_t imp_units, imp_tiles, imp_ctas;  // implicit mode
+  const float* tmp_o;
+  const float* tmp_lse;
+  void* o;
+  float* lse;
+  int32_t num_qo_heads, group_size, head_dim;
+  float out_scale;
+  int32_t out_dtype;
+  int32_t enable_pdl;
+};
+
+}  // namespace fib200

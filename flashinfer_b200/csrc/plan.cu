@@ -1,0 +1,293 @@
+// plan.cu — host-side decode scheduler (C++), the replacement for the reference's
+// DecodePlan (include/flashinfer/attention/scheduler.cuh:424-493) and its helpers
+// PartitionPagedKVCacheBinarySearchMinNumPagePerBatch (:73-99) and DecodeSplitKVIndptr
+// (:348-364).
+//
+// The reference picks ONE uniform chunk size for all requests and launches a
+// (work item, kv_head) grid.  Here the KV tiles (64 tokens) of all (request, kv_head)
+// units are laid out as one stream, request-major / head-minor, and the stream is cut
+// into `num_ctas` equal contiguous ranges — one per persistent CTA — so every CTA reads
+// the same number of KV bytes (+-1 tile) whatever the length distribution.  A unit cut
+// by a range boundary becomes several partial segments (consecutive partial slots) plus
+// one MergeUnit; a unit inside one range is written directly.
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <vector>
+
+#include "host_common.h"
+
+namespace fib200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+Tuning& tuning() {
+  static Tuning t = {0, 0, 0, 0};
+  return t;
+}
+
+KernelConfig choose_config(int kvf, int head_dim) {
+  const int es = kvf == 0 ? 2 : 1;
+  const int stage = 2 * kTileTokens * head_dim * es;
+  const int fixed = 1024 + (kConsumerWarps - 1) * head_dim * 32 /*scratch o*/ +
+                    kConsumerWarps * kMaxGroup * 8 + kSegCache * (int)sizeof(Segment) +
+                    2 * kMaxStages * 8;
+  const int sm_total = 233472;  // 228 KiB per SM, each resident CTA reserves 1 KiB
+  KernelConfig c;
+  c.ctas_per_sm = tuning().ctas_per_sm;
+  if (c.ctas_per_sm <= 0) {
+    const int avail2 = sm_total / 2 - 1024 - fixed;
+    c.ctas_per_sm = (avail2 / stage >= 3) ? 2 : 1;
+  }
+  const int avail = sm_total / c.ctas_per_sm - 1024 - fixed;
+  int stages = std::min(kMaxStages, avail / stage);
+  if (tuning().stages > 0) stages = std::min(stages, tuning().stages);
+  c.stages = std::max(stages, 1);
+  c.smem_bytes = fixed + c.stages * stage;
+  return c;
+}
+
+int device_sm_count(int device, int* out) {
+  static std::mutex mu;
+  static int cache[64];
+  std::lock_guard<std::mutex> lk(mu);
+  if (device < 0 || device >= 64) return fail(FI_ERR_INVALID_ARGUMENT, "bad device %d", device);
+  if (cache[device] == 0) {
+    int n = 0;
+    FI_CUDA_TRY(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device));
+    cache[device] = n;
+  }
+  *out = cache[device];
+  return FI_OK;
+}
+
+static inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
+
+}  // namespace fib200
+
+using namespace fib200;
+
+extern "C" {
+
+const char* fi_last_error(void) { return g_err; }
+int fi_version(void) { return 100; }
+int fi_plan_info_len(void) { return FI_PLAN_INFO_LEN; }
+
+void fi_set_tuning(int stages, int ctas_per_sm, int loader, int min_tiles_per_cta) {
+  Tuning& t = tuning();
+  t.stages = stages;
+  t.ctas_per_sm = ctas_per_sm;
+  t.loader = loader;
+  t.min_tiles_per_cta = min_tiles_per_cta;
+}
+
+int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, void* pinned_int_ws,
+                         size_t int_ws_bytes, const int32_t* indptr_host,
+                         const int32_t* last_page_len_host, const int32_t* kv_len_host,
+                         int batch_size, int num_qo_heads, int num_kv_heads, int head_dim,
+                         int page_size, int q_dtype, int kv_dtype, int window_left,
+                         int cuda_graph, int device, int num_ctas_override, void* stream,
+                         int64_t* plan_info_out) {
+  static_assert(kPiLen <= FI_PLAN_INFO_LEN, "plan info vector too short");
+  (void)float_ws;
+  if (batch_size < 0 || num_qo_heads <= 0 || num_kv_heads <= 0 || page_size <= 0)
+    return fail(FI_ERR_INVALID_ARGUMENT, "invalid problem shape");
+  if (num_qo_heads % num_kv_heads != 0)
+    return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads %d is not a multiple of num_kv_heads %d",
+                num_qo_heads, num_kv_heads);
+  const int group = num_qo_heads / num_kv_heads;
+  if (group > kMaxGroup)
+    return fail(FI_ERR_UNSUPPORTED, "Unsupported group_size: %d (max %d)", group, kMaxGroup);
+  const int kvf = kv_format(q_dtype, kv_dtype);
+  if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair (%d, %d)", q_dtype, kv_dtype);
+  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256) || (kvf != 0 && head_dim == 64))
+    return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d for this dtype", head_dim);
+  if (indptr_host == nullptr || (last_page_len_host == nullptr && kv_len_host == nullptr))
+    return fail(FI_ERR_INVALID_ARGUMENT, "indptr / last_page_len must be host pointers");
+  if (pinned_int_ws == nullptr || int_ws == nullptr)
+    return fail(FI_ERR_INVALID_ARGUMENT, "int workspaces must not be null");
+
+  const KernelConfig cfg = choose_config(kvf, head_dim);
+  int num_ctas = num_ctas_override;
+  if (num_ctas <= 0) {
+    int sms = 0;
+    int rc = device_sm_count(device, &sms);
+    if (rc != FI_OK) return rc;
+    num_ctas = sms * cfg.ctas_per_sm;
+  }
+
+  // ---- per-request token / tile ranges --------------------------------------
+  std::vector<int32_t> tok_lo(batch_size), tok_hi(batch_size), tile_b(batch_size), ntile(batch_size);
+  int64_t total_tiles = 0;
+  for (int b = 0; b < batch_size; ++b) {
+    const int64_t npages = (int64_t)indptr_host[b + 1] - indptr_host[b];
+    if (npages < 0) return fail(FI_ERR_INVALID_ARGUMENT, "indptr must be non-decreasing");
+    int64_t len;
+    if (kv_len_host != nullptr) {
+      len = kv_len_host[b];
+      if (len < 0 || len > npages * page_size)
+        return fail(FI_ERR_INVALID_ARGUMENT, "kv_len[%d]=%lld exceeds its pages", b, (long long)len);
+    } else {
+      const int lpl = last_page_len_host[b];
+      if (npages > 0 && (lpl < 0 || lpl > page_size))
+        return fail(FI_ERR_INVALID_ARGUMENT, "last_page_len[%d]=%d out of range", b, lpl);
+      len = npages == 0 ? 0 : (npages - 1) * page_size + lpl;
+    }
+    if (len > 0x7fffff00LL) return fail(FI_ERR_INVALID_ARGUMENT, "kv_len too large");
+    int64_t lo = 0;
+    if (window_left >= 0) lo = std::max<int64_t>(0, len - 1 - window_left);
+    tok_lo[b] = (int32_t)lo;
+    tok_hi[b] = (int32_t)len;
+    tile_b[b] = (int32_t)(lo / kTileTokens);
+    ntile[b] = len == 0 ? 0 : (int32_t)((len + kTileTokens - 1) / kTileTokens - tile_b[b]);
+    total_tiles += (int64_t)ntile[b] * num_kv_heads;
+  }
+  if (total_tiles > 0x7fffffffLL) return fail(FI_ERR_INVALID_ARGUMENT, "too many KV tiles");
+
+  // ---- fixed (worst-case) layout: offsets depend only on (bs, heads, num_ctas) -------
+  const int64_t units = (int64_t)batch_size * num_kv_heads;
+  const int64_t max_segs = units + num_ctas;
+  const int64_t max_merge = num_ctas;
+  const int64_t max_slots = 2 * (int64_t)num_ctas;
+  size_t off = 0;
+  const size_t off_header = off; off = align16(off + sizeof(PlanHeader));
+  const size_t off_indptr = off; off = align16(off + (size_t)(num_ctas + 1) * 4);
+  const size_t off_segs = off;   off = align16(off + (size_t)max_segs * sizeof(Segment));
+  const size_t off_merge = off;  off = align16(off + (size_t)max_merge * sizeof(MergeUnit));
+  const size_t int_need = off;
+  if (int_need > int_ws_bytes)
+    return fail(FI_ERR_WORKSPACE,
+                "Buffer overflow when allocating the decode work list: need %zu bytes of int "
+                "workspace, have %zu. Increase the workspace buffer size.", int_need, int_ws_bytes);
+  const size_t off_tmp_o = 0;
+  const size_t tmp_o_bytes = align16((size_t)max_slots * group * head_dim * 4);
+  const size_t off_tmp_lse = off_tmp_o + tmp_o_bytes;
+  const size_t float_need = off_tmp_lse + align16((size_t)max_slots * group * 4);
+  if (float_need > float_ws_bytes)
+    return fail(FI_ERR_WORKSPACE,
+                "Buffer overflow when allocating split-KV partials: need %zu bytes of float "
+                "workspace, have %zu. Increase the workspace buffer size.", float_need, float_ws_bytes);
+
+  char* host = static_cast<char*>(pinned_int_ws);
+  PlanHeader* hdr = reinterpret_cast<PlanHeader*>(host + off_header);
+  int32_t* cta_indptr = reinterpret_cast<int32_t*>(host + off_indptr);
+  Segment* segs = reinterpret_cast<Segment*>(host + off_segs);
+  MergeUnit* merges = reinterpret_cast<MergeUnit*>(host + off_merge);
+
+  // ---- cut the tile stream into per-CTA ranges ---------------------------------
+  const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
+  int64_t ctas_used = std::min<int64_t>(num_ctas, std::max<int64_t>(1, total_tiles / min_tiles));
+  auto bound = [&](int64_t i) { return (i * total_tiles) / ctas_used; };  // start of CTA i
+
+  int64_t nseg = 0, nmerge = 0, nslot = 0;
+  int64_t cta = 0;       // CTA currently being filled
+  int64_t cta_end = bound(1);
+  cta_indptr[0] = 0;
+  int64_t pos = 0;       // stream position (tiles)
+  for (int b = 0; b < batch_size; ++b) {
+    for (int h = 0; h < num_kv_heads; ++h) {
+      const int64_t nt = ntile[b];
+      Segment s;
+      s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b]; s.pad = 0;
+      if (nt == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
+        s.tile_begin = s.tile_end = 0; s.slot = -1;
+        segs[nseg++] = s;
+        continue;
+      }
+      int64_t cur = pos;
+      const int64_t end = pos + nt;
+      bool split_open = false;
+      while (cur < end) {
+        while (cta_end <= cur) {  // advance to the CTA that owns `cur`
+          ++cta;
+          cta_indptr[cta] = (int32_t)nseg;
+          cta_end = bound(cta + 1);
+        }
+        const int64_t e = std::min(end, cta_end);
+        const bool whole = (cur == pos && e == end);
+        s.tile_begin = tile_b[b] + (int32_t)(cur - pos);
+        s.tile_end = tile_b[b] + (int32_t)(e - pos);
+        if (whole) {
+          s.slot = -1;
+        } else {
+          s.slot = (int32_t)nslot++;
+          if (!split_open) {
+            MergeUnit mu = {b, h, s.slot, 0};
+            merges[nmerge++] = mu;
+            split_open = true;
+          }
+          merges[nmerge - 1].count++;
+        }
+        segs[nseg++] = s;
+        cur = e;
+      }
+      pos = end;
+    }
+  }
+  for (int64_t i = cta + 1; i <= num_ctas; ++i) cta_indptr[i] = (int32_t)nseg;
+  if (nseg > max_segs || nmerge > max_merge || nslot > max_slots)
+    return fail(FI_ERR_WORKSPACE, "internal planner overflow (%lld segs, %lld merges, %lld slots)",
+                (long long)nseg, (long long)nmerge, (long long)nslot);
+  hdr->num_ctas_used = (int32_t)num_ctas;  // every CTA has a (possibly empty) indptr entry
+  hdr->num_segments = (int32_t)nseg;
+  hdr->num_merge_units = (int32_t)nmerge;
+  hdr->num_slots = (int32_t)nslot;
+  hdr->total_tiles = (int32_t)total_tiles;
+  hdr->pad[0] = hdr->pad[1] = hdr->pad[2] = 0;
+
+  // ---- one H2D copy of the used prefix (header .. merge list) -------------------
+  const size_t used = off_merge + (size_t)std::max<int64_t>(nmerge, 1) * sizeof(MergeUnit);
+  if (device >= 0) {
+    FI_CUDA_TRY(cudaSetDevice(device));
+    FI_CUDA_TRY(cudaMemcpyAsync(int_ws, pinned_int_ws, used, cudaMemcpyHostToDevice,
+                                static_cast<cudaStream_t>(stream)));
+  } else {
+    if (int_ws != pinned_int_ws) memcpy(int_ws, pinned_int_ws, used);  // CPU-only test mode
+  }
+
+  int64_t* pi = plan_info_out;
+  for (int i = 0; i < FI_PLAN_INFO_LEN; ++i) pi[i] = 0;
+  pi[kPiMagic] = kPlanMagic;
+  pi[kPiNumCtas] = num_ctas;
+  pi[kPiNumSegments] = nseg;
+  pi[kPiNumMergeUnits] = nmerge;
+  pi[kPiNumSlots] = nslot;
+  pi[kPiOffHeader] = (int64_t)off_header;
+  pi[kPiOffCtaIndptr] = (int64_t)off_indptr;
+  pi[kPiOffSegments] = (int64_t)off_segs;
+  pi[kPiOffMerge] = (int64_t)off_merge;
+  pi[kPiOffTmpO] = (int64_t)off_tmp_o;
+  pi[kPiOffTmpLse] = (int64_t)off_tmp_lse;
+  pi[kPiBatchSize] = batch_size;
+  pi[kPiNumQoHeads] = num_qo_heads;
+  pi[kPiNumKvHeads] = num_kv_heads;
+  pi[kPiHeadDim] = head_dim;
+  pi[kPiPageSize] = page_size;
+  pi[kPiQDtype] = q_dtype;
+  pi[kPiKvDtype] = kv_dtype;
+  pi[kPiCudaGraph] = cuda_graph;
+  // graph mode: the merge launch must exist in every replay; its grid is the upper bound
+  pi[kPiMergeGrid] = cuda_graph ? max_merge : nmerge;
+  pi[kPiTotalTiles] = total_tiles;
+  pi[kPiWindowLeft] = window_left;
+  pi[kPiStages] = cfg.stages;
+  pi[kPiIntBytesUsed] = (int64_t)used;
+  return FI_OK;
+}
+
+}  // extern "C"

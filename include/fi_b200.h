@@ -1,0 +1,193 @@
+/*
+ * fi_b200.h — C-ABI boundary of the B200-native paged-KV batch decode path.
+ *
+ * Every entry point replaces one tvm-ffi typed function of the reference
+ * (happierpig/flashinfer-ai, FlashInfer 0.3.1).  Plain pointers and sizes only:
+ * no torch / DLPack / tvm types cross this boundary.  All device memory is
+ * caller-owned; the library never allocates device memory.
+ *
+ * Return value: 0 on success, non-zero FI_ERR_* otherwise; fi_last_error()
+ * returns a thread-local human-readable message for the last failure.
+ *
+ * LSE values are base-2 (m + log2(d) with logits pre-multiplied by
+ * sm_scale*log2(e)), as in the reference (include/flashinfer/attention/state.cuh:45).
+ */
+#ifndef FI_B200_H_
+#define FI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define FI_API __attribute__((visibility("default")))
+#else
+#define FI_API
+#endif
+
+/* ---- status codes ------------------------------------------------------- */
+#define FI_OK 0
+#define FI_ERR_INVALID_ARGUMENT 1 /* maps to Python ValueError            */
+#define FI_ERR_WORKSPACE 2        /* workspace too small -> RuntimeError  */
+#define FI_ERR_CUDA 3             /* CUDA runtime failure -> RuntimeError */
+#define FI_ERR_UNSUPPORTED 4      /* shape / dtype not built -> RuntimeError */
+
+/* ---- dtype codes -------------------------------------------------------- */
+#define FI_DTYPE_F16 0
+#define FI_DTYPE_BF16 1
+#define FI_DTYPE_E4M3 2
+#define FI_DTYPE_E5M2 3
+#define FI_DTYPE_F32 4 /* merge operators only */
+
+/* ---- kv layout codes (reference: flashinfer/utils.py:35-38 TensorLayout) - */
+#define FI_LAYOUT_NHD 0
+#define FI_LAYOUT_HND 1
+
+/* number of int64 slots in the plan-info vector (reference DecodePlanInfo has
+ * 10, include/flashinfer/attention/scheduler.cuh:366-422; ours carries the
+ * persistent-grid work list offsets instead and is opaque to Python). */
+#define FI_PLAN_INFO_LEN 24
+
+FI_API const char* fi_last_error(void);
+FI_API int fi_version(void);
+
+/* Number of int64 plan-info slots (== FI_PLAN_INFO_LEN). */
+FI_API int fi_plan_info_len(void);
+
+/*
+ * Process-wide tuning overrides used by benchmarks / tests (0 = automatic):
+ *  stages             cap on the shared-memory ring depth
+ *  ctas_per_sm        persistent CTAs per SM (1 or 2)
+ *  loader             0 auto, 1 force per-page TMA boxes, 2 force cp.async gathers
+ *  min_tiles_per_cta  smallest per-CTA share (64-token tiles) before CTAs are left idle
+ * No reference counterpart (the reference fixes these at JIT time,
+ * include/flashinfer/attention/decode.cuh:752-772).
+ */
+FI_API void fi_set_tuning(int stages, int ctas_per_sm, int loader, int min_tiles_per_cta);
+/* loader used by the last decode launch: 0 = TMA, 1 = cp.async, -1 = none yet */
+FI_API int fi_last_loader(void);
+/* number of kernels launched by this library so far (decode + merge + merge ops) */
+FI_API long long fi_launch_count(void);
+
+/*
+ * fi_batch_decode_plan — host-side scheduler.
+ * Replaces: BatchDecodeWithPagedKVCachePlan (csrc/batch_decode.cu:39-79) ->
+ *           DecodePlan (include/flashinfer/attention/scheduler.cuh:424-493).
+ *
+ * Cuts the flattened (request, kv-head, 64-token tile) stream into `num_ctas` equal
+ * contiguous ranges (one per persistent CTA), emits per-CTA segments and the
+ * split-KV merge metadata into `pinned_int_ws` (host) and issues ONE async H2D
+ * copy into `int_ws` (device) on `stream`.
+ *
+ *  float_ws/float_ws_bytes   device scratch for split-KV partials (caller-owned)
+ *  int_ws/pinned_int_ws      device / page-locked host mirrors, int_ws_bytes each
+ *  indptr_host[bs+1]         page indptr (host)
+ *  last_page_len_host[bs]    host; may be NULL iff kv_len_host != NULL
+ *  kv_len_host[bs]           optional explicit token lengths (host) or NULL
+ *  window_left               <0: none; else only the last window_left+1 tokens
+ *  cuda_graph                1: grid and all array extents are fixed by
+ *                            (bs, num_ctas) only, so re-plans are graph-safe
+ *  num_ctas_override         >0: use this many CTAs along x instead of querying
+ *                            the device (used by CPU-only tests; then `device`
+ *                            may be -1 and no CUDA call is made: the H2D copy
+ *                            becomes a memcpy into int_ws)
+ *  plan_info_out[FI_PLAN_INFO_LEN]
+ */
+FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws,
+                         void* pinned_int_ws, size_t int_ws_bytes,
+                         const int32_t* indptr_host,
+                         const int32_t* last_page_len_host,
+                         const int32_t* kv_len_host, int batch_size,
+                         int num_qo_heads, int num_kv_heads, int head_dim,
+                         int page_size, int q_dtype, int kv_dtype,
+                         int window_left, int cuda_graph, int device,
+                         int num_ctas_override, void* stream,
+                         int64_t* plan_info_out);
+
+/*
+ * fi_batch_decode_run — launches the decode kernel (+ merge kernel if any
+ * request was split).
+ * Replaces: BatchDecodeWithPagedKVCacheRun (csrc/batch_decode.cu:81-191) ->
+ *           BatchDecodeWithPagedKVCacheDispatched
+ *           (include/flashinfer/attention/decode.cuh:739-825).
+ *
+ *  q            [bs, Hq, D], element strides q_stride_n / q_stride_h, unit on D
+ *  k_cache/v_cache  page pools of num_pages pages sharing element strides
+ *                   (page, n, h), unit on D (reference constraint
+ *                   csrc/batch_decode.cu:123-128)
+ *  kv_indices   device int32 page table; NULL = identity (page id == position)
+ *  kv_indptr    device int32 [bs+1]
+ *  o            [bs, Hq, D] contiguous, q dtype
+ *  lse          [bs, Hq] f32 base-2 or NULL
+ *  sm_scale     already multiplied by q_scale*k_scale (decode.py:1250-1256)
+ *  v_scale      multiplies the output (fused; reference: decode.py:1367-1372)
+ *  logits_soft_cap  <=0: disabled
+ */
+FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info,
+                        const void* q, int64_t q_stride_n, int64_t q_stride_h,
+                        const void* k_cache, const void* v_cache,
+                        int64_t num_pages, int64_t kv_stride_page, int64_t kv_stride_n,
+                        int64_t kv_stride_h, const int32_t* kv_indices,
+                        const int32_t* kv_indptr, void* o, float* lse,
+                        float sm_scale, float v_scale, float logits_soft_cap,
+                        int enable_pdl, int device, void* stream);
+
+/*
+ * fi_single_decode_run — one request, contiguous K/V.
+ * Replaces: single_decode_with_kv_cache FFI (csrc/single_decode.cu:33-104) ->
+ *           SingleDecodeWithKVCacheDispatched (decode.cuh:658-737).
+ *  k, v   NHD [L, Hkv, D] or HND [Hkv, L, D], contiguous
+ *  tmp    device scratch (>= fi_single_decode_tmp_bytes) for split-KV partials
+ *         and the work list; int_host_scratch is not needed: the plan for a
+ *         single request is closed-form and computed on the device.
+ */
+FI_API int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
+                         size_t tmp_bytes, void* o, float* lse, int num_qo_heads,
+                         int num_kv_heads, int head_dim, int kv_len,
+                         int q_dtype, int kv_dtype, int kv_layout,
+                         int window_left, float sm_scale, float v_scale,
+                         float logits_soft_cap, int device, void* stream);
+FI_API size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int head_dim,
+                                  int device);
+
+/*
+ * State-merge operators.  Replaces csrc/cascade.cu:23 / :59 / :102 ->
+ * MergeState / MergeStateInPlace / MergeStates
+ * (include/flashinfer/attention/cascade.cuh:573 / :605 / :638).
+ *  v_*  [seq, H, D] contiguous, dtype in {F16, BF16} (or F32 accepted too)
+ *  s_*  [seq, H] f32 base-2 LSE
+ */
+FI_API int fi_merge_state(const void* v_a, const float* s_a, const void* v_b,
+                   const float* s_b, void* v_merged, float* s_merged,
+                   int seq_len, int num_heads, int head_dim, int dtype,
+                   int device, void* stream);
+FI_API int fi_merge_state_in_place(void* v, float* s, const void* v_other,
+                            const float* s_other, const uint8_t* mask_or_null,
+                            int seq_len, int num_heads, int head_dim, int dtype,
+                            int device, void* stream);
+/* v [seq, n, H, D], s [seq, n, H] -> v_merged [seq, H, D], s_merged [seq, H] */
+FI_API int fi_merge_states(const void* v, const float* s, void* v_merged,
+                    float* s_merged, int seq_len, int num_index_sets,
+                    int num_heads, int head_dim, int dtype, int device,
+                    void* stream);
+/*
+ * Variable-length merge used after split-KV decode.
+ * Replaces VariableLengthMergeStates (cascade.cuh:686-736).
+ *  v [total, H, D] (dtype_in), s [total, H]; indptr device int32 [seq+1];
+ *  rows with indptr[i+1]-indptr[i]==0 are left untouched if skip_empty!=0,
+ *  else written as zeros / lse=-5e4 (reference cascade.cuh:397-405).
+ */
+FI_API int fi_variable_length_merge_states(const void* v, const float* s,
+                                    const int32_t* indptr, void* v_merged,
+                                    float* s_merged, int seq_len, int num_heads,
+                                    int head_dim, int dtype_in, int dtype_out,
+                                    int skip_empty, float out_scale, int device,
+                                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FI_B200_H_ */
