@@ -1,0 +1,93 @@
+"""ctypes binding of libfi_b200.so — the thin C-ABI boundary (include/fi_b200.h).
+
+The reference loads one tvm-ffi module per (dtype, head_dim, variant) through its JIT
+(flashinfer/jit/core.py:247-263, flashinfer/decode.py:208-302).  Here there is ONE
+prebuilt shared library with plain-C entry points; this module declares their
+prototypes and converts non-zero status codes into the Python exceptions the
+reference raises (ValueError for argument errors, RuntimeError otherwise).
+
+There is deliberately no fallback: if the library is missing, importing the ops
+raises, it never reroutes to a CPU / PyTorch path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "libfi_b200.so"
+
+FI_OK = 0
+FI_ERR_INVALID_ARGUMENT = 1
+FI_ERR_WORKSPACE = 2
+FI_ERR_CUDA = 3
+FI_ERR_UNSUPPORTED = 4
+
+DTYPE_F16, DTYPE_BF16, DTYPE_E4M3, DTYPE_E5M2, DTYPE_F32 = 0, 1, 2, 3, 4
+LAYOUT_NHD, LAYOUT_HND = 0, 1
+
+_vp, _i, _i64, _f, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/fi_b200.h declares
+PROTOTYPES = {
+    "fi_last_error": (C.c_char_p, []),
+    "fi_version": (_i, []),
+    "fi_plan_info_len": (_i, []),
+    "fi_set_tuning": (None, [_i, _i, _i, _i]),
+    "fi_last_loader": (_i, []),
+    "fi_launch_count": (C.c_longlong, []),
+    "fi_batch_decode_plan": (_i, [_vp, _sz, _vp, _vp, _sz, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
+                                  _i, _i, _i, _i, _i, _vp, _vp]),
+    "fi_batch_decode_run": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _i64,
+                                 _vp, _vp, _vp, _vp, _f, _f, _f, _i, _i, _vp]),
+    "fi_single_decode_run": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,
+                                  _i, _f, _f, _f, _i, _vp]),
+    "fi_single_decode_tmp_bytes": (_sz, [_i, _i, _i, _i]),
+    "fi_merge_state": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "fi_merge_state_in_place": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "fi_merge_states": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "fi_variable_length_merge_states": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f,
+                                             _i, _vp]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load libfi_b200.so (building it first if FI_B200_AUTOBUILD=1 and it is absent)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        if os.environ.get("FI_B200_AUTOBUILD", "0") == "1":
+            from .build import build
+
+            build()
+        else:
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m flashinfer_b200.build` "
+                "(there is no CPU / PyTorch fallback for the decode path)"
+            )
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so does not export it
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    msg = load().fi_last_error()
+    return msg.decode("utf-8", "replace") if msg else ""
+
+
+def check(status: int) -> None:
+    """Map a C status code to the reference's exception classes."""
+    if status == FI_OK:
+        return
+    msg = last_error()
+    if status == FI_ERR_INVALID_ARGUMENT:
+        raise ValueError(msg)
+    raise RuntimeError(msg)

@@ -1,0 +1,612 @@
+"""Decode attention API — same public names, signatures and error behaviour as the
+reference's flashinfer/decode.py (single_decode_with_kv_cache :389-578,
+BatchDecodeWithPagedKVCacheWrapper :581-1410, CUDAGraphBatchDecodeWithPagedKVCacheWrapper
+:1413-1480, fast_decode_plan :2416-2579), backed by the prebuilt sm_100a C-ABI library
+(include/fi_b200.h) instead of per-configuration JIT modules.
+
+Host code is Python/PyTorch (device memory, streams); all arithmetic happens in the CUDA
+kernels behind libfi_b200.so.  There is no CPU path: tensors must live on a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import functools
+import math
+from typing import Any, List, Optional, Tuple, Union
+
+import torch
+
+from . import _lib
+from .page import get_seq_lens
+from .utils import (
+    _check_cached_qkv_data_type,
+    _check_kv_layout,
+    _check_pos_encoding_mode,
+    _get_cache_buf,
+    _get_range_buf,
+    _unpack_paged_kv_cache,
+    canonicalize_torch_dtype,
+    check_shape_dtype_device,
+    current_stream_ptr,
+    device_index,
+    device_support_pdl,
+    dtype_code,
+    is_float8,
+    TensorLayout,
+)
+
+_INT_WORKSPACE_BYTES = 8 * 1024 * 1024
+
+
+def _host_i32_ptr(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
+    """Contiguous CPU int32 copy of `t` and its address (kept alive by the caller)."""
+    h = t.detach().to("cpu", torch.int32).contiguous()
+    return h, h.data_ptr()
+
+
+def _unsupported_variant(pos_encoding_mode: str) -> None:
+    _check_pos_encoding_mode(pos_encoding_mode)
+    if pos_encoding_mode != "NONE":
+        # in-kernel RoPE / ALiBi are "next" rows, not built yet.
+        raise NotImplementedError(
+            f"pos_encoding_mode={pos_encoding_mode!r} is not implemented by flashinfer_b200 "
+            "(apply RoPE to q/k before the call)"
+        )
+
+
+def single_decode_with_kv_cache(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    kv_layout: str = "NHD",
+    pos_encoding_mode: str = "NONE",
+    use_tensor_cores: bool = False,
+    q_scale: Optional[float] = None,
+    k_scale: Optional[float] = None,
+    v_scale: Optional[float] = None,
+    window_left: int = -1,
+    logits_soft_cap: Optional[float] = None,
+    sm_scale: Optional[float] = None,
+    rope_scale: Optional[float] = None,
+    rope_theta: Optional[float] = None,
+    return_lse: bool = False,
+) -> Union[torch.Tensor, Tuple[torch.Tensor, torch.Tensor]]:
+    r"""Decode attention with KV cache for a single request (reference decode.py:389-578).
+
+    q ``[num_qo_heads, head_dim]``; k, v ``[kv_len, num_kv_heads, head_dim]`` (NHD) or
+    ``[num_kv_heads, kv_len, head_dim]`` (HND), contiguous (csrc/single_decode.cu:36-39).
+    Returns o ``[num_qo_heads, head_dim]`` (and base-2 lse ``[num_qo_heads]``).
+    ``use_tensor_cores`` is accepted and ignored: the sm_100a kernel always runs its
+    MMA path.
+    """
+    _check_kv_layout(kv_layout)
+    _unsupported_variant(pos_encoding_mode)
+    if q.dim() != 2 or k.dim() != 3 or v.dim() != 3:
+        raise ValueError("q must be 2-D and k / v 3-D")
+    if k.shape != v.shape:
+        raise ValueError("k and v must have the same shape")
+    if k.dtype != v.dtype:
+        raise ValueError("k and v must have the same dtype")
+    for t, name in ((q, "q"), (k, "k"), (v, "v")):
+        if not t.is_contiguous():
+            raise ValueError(f"{name} must be contiguous")
+    dev = q.device
+    dev_idx = device_index(dev)
+    if k.device != dev or v.device != dev:
+        raise ValueError("q, k, v must be on the same device")
+    num_qo_heads, head_dim = q.shape
+    if kv_layout == "NHD":
+        kv_len, num_kv_heads = k.shape[0], k.shape[1]
+    else:
+        num_kv_heads, kv_len = k.shape[0], k.shape[1]
+    if k.shape[2] != head_dim:
+        raise ValueError("head_dim of q and k/v must match")
+    if logits_soft_cap is None:
+        logits_soft_cap = 0.0
+    if sm_scale is None:
+        sm_scale = 1.0 / math.sqrt(head_dim)
+    if q_scale is not None:
+        sm_scale *= q_scale
+    if k_scale is not None:
+        sm_scale *= k_scale
+
+    lib = _lib.load()
+    tmp_bytes = lib.fi_single_decode_tmp_bytes(num_qo_heads, num_kv_heads, head_dim, dev_idx)
+    tmp = _get_cache_buf("single_decode_with_kv_cache_tmp", max(tmp_bytes, 32 * 1024 * 1024), dev)
+    o = torch.empty_like(q)
+    lse = torch.empty((num_qo_heads,), dtype=torch.float32, device=dev) if return_lse else None
+    _lib.check(
+        lib.fi_single_decode_run(
+            q.data_ptr(), k.data_ptr(), v.data_ptr(), tmp.data_ptr(), tmp.numel(),
+            o.data_ptr(), lse.data_ptr() if lse is not None else None,
+            num_qo_heads, num_kv_heads, head_dim, kv_len,
+            dtype_code(q.dtype), dtype_code(k.dtype), TensorLayout[kv_layout].value,
+            window_left, float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
+            float(logits_soft_cap), dev_idx, current_stream_ptr(dev),
+        )
+    )
+    return (o, lse) if return_lse else o
+
+
+class BatchDecodeWithPagedKVCacheWrapper:
+    r"""Batch decode over a paged KV cache (reference decode.py:581-1410).
+
+    >>> wrapper = BatchDecodeWithPagedKVCacheWrapper(workspace, "NHD")
+    >>> wrapper.plan(indptr, indices, last_page_len, Hq, Hkv, D, page_size,
+    ...              q_data_type=torch.bfloat16, kv_data_type=torch.bfloat16)
+    >>> o = wrapper.run(q, paged_kv_cache)
+
+    ``plan`` runs the host scheduler (C++, csrc/plan.cu) once per decode step;
+    ``run`` launches the persistent sm_100a kernel (+ the split-KV merge) per layer and
+    never synchronises, so it can be captured in a CUDA graph.
+    """
+
+    def __init__(
+        self,
+        float_workspace_buffer: torch.Tensor,
+        kv_layout: str = "NHD",
+        use_cuda_graph: bool = False,
+        use_tensor_cores: bool = False,
+        paged_kv_indptr_buffer: Optional[torch.Tensor] = None,
+        paged_kv_indices_buffer: Optional[torch.Tensor] = None,
+        paged_kv_last_page_len_buffer: Optional[torch.Tensor] = None,
+        backend: str = "auto",
+        jit_args: Optional[List[Any]] = None,
+    ) -> None:
+        _check_kv_layout(kv_layout)
+        if jit_args is not None:
+            # custom JIT attention variants are out of scope (no JIT here)
+            raise NotImplementedError("jit_args (custom JIT variants) are not supported")
+        self._jit_module = None
+        self._kv_layout = kv_layout
+        self._float_workspace_buffer = float_workspace_buffer
+        self.device = float_workspace_buffer.device
+        device_index(self.device)  # raises on non-CUDA devices: no CPU fallback
+        self._int_workspace_buffer = torch.empty(
+            (_INT_WORKSPACE_BYTES,), dtype=torch.uint8, device=self.device
+        )
+        self._pin_memory_int_workspace_buffer = torch.empty(
+            (_INT_WORKSPACE_BYTES,), dtype=torch.uint8, pin_memory=True, device="cpu"
+        )
+        if use_cuda_graph:
+            if not torch.is_tensor(paged_kv_indptr_buffer):
+                raise ValueError("paged_kv_indptr_buffer should be a torch.Tensor in cudagraph mode")
+            if not torch.is_tensor(paged_kv_indices_buffer):
+                raise ValueError("paged_kv_indices_buffer should be a torch.Tensor in cudagraph mode")
+            if not torch.is_tensor(paged_kv_last_page_len_buffer):
+                raise ValueError(
+                    "paged_kv_last_page_len_buffer should be a torch.Tensor in cudagraph mode"
+                )
+            self._fixed_batch_size = len(paged_kv_last_page_len_buffer)
+            if len(paged_kv_indptr_buffer) != self._fixed_batch_size + 1:
+                raise ValueError("The size of paged_kv_indptr_buffer should be batch_size + 1")
+        else:
+            self._fixed_batch_size = 0
+        self._paged_kv_indptr_buf = paged_kv_indptr_buffer
+        self._paged_kv_indices_buf = paged_kv_indices_buffer
+        self._paged_kv_last_page_len_buf = paged_kv_last_page_len_buffer
+        # both flags select the same kernel here: the MMA path is the only path
+        self._use_tensor_cores = use_tensor_cores or backend == "trtllm-gen"
+        self._use_cuda_graph = use_cuda_graph
+        self._backend = backend
+        self._plan_info: Optional[torch.Tensor] = None
+
+    @property
+    def use_tensor_cores(self) -> bool:
+        return self._use_tensor_cores
+
+    @property
+    def is_cuda_graph_enabled(self) -> bool:
+        return self._use_cuda_graph
+
+    def reset_workspace_buffer(
+        self, float_workspace_buffer: torch.Tensor, int_workspace_buffer: torch.Tensor
+    ) -> None:
+        self._float_workspace_buffer = float_workspace_buffer
+        self._int_workspace_buffer = int_workspace_buffer
+        self._pin_memory_int_workspace_buffer = torch.empty(
+            self._int_workspace_buffer.shape,
+            dtype=self._int_workspace_buffer.dtype,
+            device="cpu",
+            pin_memory=True,
+        )
+
+    # ------------------------------------------------------------------ plan
+    def plan(
+        self,
+        indptr: torch.Tensor,
+        indices: torch.Tensor,
+        last_page_len: torch.Tensor,
+        num_qo_heads: int,
+        num_kv_heads: int,
+        head_dim: int,
+        page_size: int,
+        pos_encoding_mode: str = "NONE",
+        window_left: int = -1,
+        logits_soft_cap: Optional[float] = None,
+        q_data_type: Optional[Union[str, torch.dtype]] = "float16",
+        kv_data_type: Optional[Union[str, torch.dtype]] = None,
+        data_type: Optional[Union[str, torch.dtype]] = None,
+        sm_scale: Optional[float] = None,
+        rope_scale: Optional[float] = None,
+        rope_theta: Optional[float] = None,
+        non_blocking: bool = True,
+        block_tables: Optional[torch.Tensor] = None,
+        seq_lens: Optional[torch.Tensor] = None,
+        fixed_split_size: Optional[int] = None,
+        disable_split_kv: bool = False,
+    ) -> None:
+        r"""Plan batch decode for a page table (reference decode.py:810-1102).
+
+        Cannot be captured in a CUDA graph (it reads indptr / last_page_len on the host).
+        """
+        for tensor, name in [(indptr, "indptr"), (indices, "indices"), (last_page_len, "last_page_len")]:
+            if tensor.dtype != torch.int32:
+                raise ValueError(f"{name} must have dtype torch.int32, got {tensor.dtype}")
+        _unsupported_variant(pos_encoding_mode)
+        self._workspace_size = (
+            self._float_workspace_buffer.numel() * self._float_workspace_buffer.element_size()
+        )
+        batch_size = len(last_page_len)
+        if logits_soft_cap is None:
+            logits_soft_cap = 0.0
+
+        if self.is_cuda_graph_enabled:
+            if batch_size != self._fixed_batch_size:
+                raise ValueError(
+                    "The batch size should be fixed in cudagraph mode, the runtime batch size {} "
+                    " mismatches the batch size set during initialization {}".format(
+                        batch_size, self._fixed_batch_size
+                    )
+                )
+            if len(indices) > len(self._paged_kv_indices_buf):
+                raise ValueError(
+                    "The size of indices should be less than or equal to the allocated buffer"
+                )
+            self._paged_kv_indptr_buf.copy_(indptr, non_blocking=non_blocking)
+            self._paged_kv_last_page_len_buf.copy_(last_page_len, non_blocking=non_blocking)
+            self._paged_kv_indices_buf[: len(indices)].copy_(
+                indices, non_blocking=(indices.device == self.device) and non_blocking
+            )
+        else:
+            self._paged_kv_indptr_buf = indptr.to(self.device, non_blocking=non_blocking)
+            self._paged_kv_indices_buf = indices.to(self.device, non_blocking=non_blocking)
+            self._paged_kv_last_page_len_buf = last_page_len.to(self.device, non_blocking=non_blocking)
+
+        indptr_host, indptr_ptr = _host_i32_ptr(indptr)
+        last_page_len_host, lpl_ptr = _host_i32_ptr(last_page_len)
+        if len(indptr_host) != batch_size + 1:
+            raise ValueError("indptr must have batch_size + 1 entries")
+
+        if data_type is not None:
+            if q_data_type is None:
+                q_data_type = data_type
+            if kv_data_type is None:
+                kv_data_type = data_type
+        q_data_type = canonicalize_torch_dtype(q_data_type)
+        if kv_data_type is None:
+            kv_data_type = q_data_type
+        kv_data_type = canonicalize_torch_dtype(kv_data_type)
+        if fixed_split_size is not None and not self.use_tensor_cores:
+            raise ValueError("fixed_split_size is only supported by tensor core decode for now.")
+
+        self._cached_q_data_type = q_data_type
+        self._cached_kv_data_type = kv_data_type
+        self._batch_size = batch_size
+        self._num_qo_heads = num_qo_heads
+        self._num_kv_heads = num_kv_heads
+        self._block_tables = block_tables
+        self._max_kv_len = None
+
+        kv_len_host, kv_len_ptr = (None, None)
+        if seq_lens is not None:
+            kv_len_host, kv_len_ptr = _host_i32_ptr(seq_lens)
+            if len(kv_len_host) != batch_size:
+                raise ValueError("seq_lens must have batch_size entries")
+
+        self._run_plan(
+            indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads, head_dim,
+            page_size, q_data_type, kv_data_type, window_left,
+        )
+        del indptr_host, last_page_len_host, kv_len_host  # only needed during the call
+
+        self._pos_encoding_mode = pos_encoding_mode
+        self._window_left = window_left
+        self._logits_soft_cap = logits_soft_cap
+        self._sm_scale = sm_scale
+        self._rope_scale = rope_scale
+        self._rope_theta = rope_theta
+
+    begin_forward = plan
+
+    def _run_plan(self, indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
+                  head_dim, page_size, q_data_type, kv_data_type, window_left) -> None:
+        lib = _lib.load()
+        info = torch.zeros(lib.fi_plan_info_len(), dtype=torch.int64)
+        dev_idx = device_index(self.device)
+        fws = self._float_workspace_buffer
+        with torch.cuda.device(self.device):
+            _lib.check(
+                lib.fi_batch_decode_plan(
+                    fws.data_ptr(), fws.numel() * fws.element_size(),
+                    self._int_workspace_buffer.data_ptr(),
+                    self._pin_memory_int_workspace_buffer.data_ptr(),
+                    min(self._int_workspace_buffer.numel() * self._int_workspace_buffer.element_size(),
+                        self._pin_memory_int_workspace_buffer.numel()
+                        * self._pin_memory_int_workspace_buffer.element_size()),
+                    indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
+                    head_dim, page_size, dtype_code(q_data_type), dtype_code(kv_data_type),
+                    int(window_left), int(self.is_cuda_graph_enabled), dev_idx, 0,
+                    current_stream_ptr(self.device), info.data_ptr(),
+                )
+            )
+        self._plan_info = info
+        self._head_dim = head_dim
+        self._page_size = page_size
+
+    # ------------------------------------------------------------------- run
+    def forward(
+        self,
+        q: torch.Tensor,
+        paged_kv_cache: Union[torch.Tensor, Tuple[torch.Tensor, torch.Tensor]],
+        pos_encoding_mode: str = "NONE",
+        q_scale: Optional[float] = None,
+        k_scale: Optional[float] = None,
+        v_scale: Optional[float] = None,
+        window_left: int = -1,
+        logits_soft_cap: Optional[float] = None,
+        sm_scale: Optional[float] = None,
+        rope_scale: Optional[float] = None,
+        rope_theta: Optional[float] = None,
+    ) -> torch.Tensor:
+        r"""Deprecated alias of :meth:`run` (reference decode.py:1106-1133)."""
+        self._pos_encoding_mode = pos_encoding_mode
+        self._window_left = window_left
+        self._logits_soft_cap = logits_soft_cap
+        self._sm_scale = sm_scale
+        self._rope_scale = rope_scale
+        self._rope_theta = rope_theta
+        return self.run(q, paged_kv_cache, q_scale=q_scale, k_scale=k_scale, v_scale=v_scale)
+
+    def run(
+        self,
+        q: torch.Tensor,
+        paged_kv_cache: Union[torch.Tensor, Tuple[torch.Tensor, torch.Tensor]],
+        *args,
+        q_scale: Optional[float] = None,
+        k_scale: Optional[float] = None,
+        v_scale: Optional[float] = None,
+        out: Optional[torch.Tensor] = None,
+        lse: Optional[torch.Tensor] = None,
+        return_lse: bool = False,
+        enable_pdl: Optional[bool] = None,
+        window_left: Optional[int] = None,
+        sinks: Optional[torch.Tensor] = None,
+        q_len_per_req: Optional[int] = 1,
+    ) -> Union[torch.Tensor, Tuple[torch.Tensor, torch.Tensor]]:
+        r"""Batch decode attention (reference decode.py:1163-1374).
+
+        q ``[batch_size, num_qo_heads, head_dim]`` (may be a strided view, unit stride on
+        head_dim); paged_kv_cache a 5-D tensor ``[pages, 2, page_size, Hkv, D]`` (NHD) /
+        ``[pages, 2, Hkv, page_size, D]`` (HND) or a ``(k_cache, v_cache)`` tuple of 4-D
+        tensors.  Returns o (q's dtype and shape) and, if ``return_lse``, the base-2
+        log-sum-exp ``[batch_size, num_qo_heads]`` (float32).
+        """
+        if self._plan_info is None:
+            raise RuntimeError("plan() must be called before run()")
+        if sinks is not None:
+            raise NotImplementedError("attention sinks are not supported")
+        if q_len_per_req not in (None, 1):
+            raise NotImplementedError("q_len_per_req > 1 is not supported")
+        if enable_pdl is None:
+            enable_pdl = device_support_pdl(q.device)
+        k_cache, v_cache = _unpack_paged_kv_cache(paged_kv_cache, self._kv_layout)
+        _check_cached_qkv_data_type(q, k_cache, self._cached_q_data_type, self._cached_kv_data_type)
+        if v_cache.dtype != k_cache.dtype:
+            raise ValueError("k_cache and v_cache must have the same dtype")
+        if self._kv_layout == "NHD":
+            page_size, num_kv_heads = k_cache.shape[1], k_cache.shape[2]
+            stride_n, stride_h = k_cache.stride(1), k_cache.stride(2)
+        else:
+            num_kv_heads, page_size = k_cache.shape[1], k_cache.shape[2]
+            stride_h, stride_n = k_cache.stride(1), k_cache.stride(2)
+        if page_size != self._page_size or num_kv_heads != self._num_kv_heads:
+            raise ValueError(
+                "paged_kv_cache shape does not match the (page_size, num_kv_heads) given to plan()"
+            )
+        if k_cache.stride() != v_cache.stride():
+            raise ValueError("k/v strides must be identical")
+        if k_cache.stride(-1) != 1 or q.stride(-1) != 1:
+            raise ValueError("the last dimension of q / k / v must be contiguous")
+        if q.dim() != 3 or q.shape[0] != self._batch_size or q.shape[1] != self._num_qo_heads \
+                or q.shape[2] != self._head_dim:
+            raise ValueError(
+                f"q must have shape [{self._batch_size}, {self._num_qo_heads}, {self._head_dim}], "
+                f"got {list(q.shape)}"
+            )
+        dev = q.device
+        if dev != self.device or k_cache.device != dev:
+            raise ValueError("q / paged_kv_cache must be on the wrapper's device")
+
+        window_left = self._window_left if window_left is None else window_left
+        assert window_left == self._window_left, "window_left must equal the planned one"
+        logits_soft_cap = self._logits_soft_cap
+        sm_scale = self._sm_scale
+        if logits_soft_cap is None:
+            logits_soft_cap = 0.0
+        if sm_scale is None:
+            sm_scale = 1.0 / math.sqrt(q.shape[-1])
+        if q_scale is not None:
+            sm_scale *= q_scale
+        if k_scale is not None:
+            sm_scale *= k_scale
+
+        if return_lse:
+            if lse is None:
+                lse = torch.empty((q.size(0), q.size(1)), dtype=torch.float32, device=dev)
+            else:
+                check_shape_dtype_device(lse, (q.size(0), q.size(1)), torch.float32, dev, "lse")
+                if not lse.is_contiguous():
+                    raise ValueError("lse must be contiguous")
+        if out is None:
+            out = torch.empty(q.shape, dtype=q.dtype, device=dev)
+        else:
+            check_shape_dtype_device(out, q.shape, q.dtype, dev, "out")
+            if not out.is_contiguous():
+                raise ValueError("out must be contiguous")
+
+        lib = _lib.load()
+        _lib.check(
+            lib.fi_batch_decode_run(
+                self._float_workspace_buffer.data_ptr(), self._int_workspace_buffer.data_ptr(),
+                self._plan_info.data_ptr(),
+                q.data_ptr(), q.stride(0), q.stride(1),
+                k_cache.data_ptr(), v_cache.data_ptr(), k_cache.shape[0],
+                k_cache.stride(0), stride_n, stride_h,
+                self._paged_kv_indices_buf.data_ptr(), self._paged_kv_indptr_buf.data_ptr(),
+                out.data_ptr(), lse.data_ptr() if return_lse else None,
+                float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
+                float(logits_soft_cap), int(bool(enable_pdl)), device_index(dev),
+                current_stream_ptr(dev),
+            )
+        )
+        # v_scale is fused into the kernel epilogue (the reference multiplies afterwards,
+        # decode.py:1367-1372)
+        return (out, lse) if return_lse else out
+
+    def forward_return_lse(
+        self,
+        q: torch.Tensor,
+        paged_kv_cache: torch.Tensor,
+        pos_encoding_mode: str = "NONE",
+        q_scale: Optional[float] = None,
+        k_scale: Optional[float] = None,
+        v_scale: Optional[float] = None,
+        window_left: int = -1,
+        logits_soft_cap: Optional[float] = None,
+        sm_scale: Optional[float] = None,
+        rope_scale: Optional[float] = None,
+        rope_theta: Optional[float] = None,
+    ) -> Tuple[torch.Tensor, torch.Tensor]:
+        r"""Deprecated alias of :meth:`run_return_lse` (reference decode.py:1376-1403)."""
+        self._pos_encoding_mode = pos_encoding_mode
+        self._window_left = window_left
+        self._logits_soft_cap = logits_soft_cap
+        self._sm_scale = sm_scale
+        self._rope_scale = rope_scale
+        self._rope_theta = rope_theta
+        return self.run(q, paged_kv_cache, q_scale=q_scale, k_scale=k_scale, v_scale=v_scale,
+                        return_lse=True)
+
+    run_return_lse = functools.partialmethod(run, return_lse=True)
+
+    def end_forward(self) -> None:
+        r"""Deprecated, no effect (reference decode.py:1407-1409)."""
+        pass
+
+
+class CUDAGraphBatchDecodeWithPagedKVCacheWrapper(BatchDecodeWithPagedKVCacheWrapper):
+    r"""CUDA-graph flavour with user-owned index buffers (reference decode.py:1413-1480)."""
+
+    def __init__(
+        self,
+        workspace_buffer: torch.Tensor,
+        indptr_buffer: torch.Tensor,
+        indices_buffer: torch.Tensor,
+        last_page_len_buffer: torch.Tensor,
+        kv_layout: str = "NHD",
+        use_tensor_cores: bool = False,
+    ) -> None:
+        super().__init__(
+            workspace_buffer,
+            kv_layout,
+            use_cuda_graph=True,
+            use_tensor_cores=use_tensor_cores,
+            paged_kv_indptr_buffer=indptr_buffer,
+            paged_kv_indices_buffer=indices_buffer,
+            paged_kv_last_page_len_buffer=last_page_len_buffer,
+        )
+
+
+def fast_decode_plan(
+    self: BatchDecodeWithPagedKVCacheWrapper,
+    indptr: torch.Tensor,
+    indices: torch.Tensor,
+    last_page_len: torch.Tensor,
+    num_qo_heads: int,
+    num_kv_heads: int,
+    head_dim: int,
+    page_size: int,
+    pos_encoding_mode: str = "NONE",
+    window_left: int = -1,
+    logits_soft_cap: Optional[float] = None,
+    q_data_type: Optional[Union[str, torch.dtype]] = None,
+    kv_data_type: Optional[Union[str, torch.dtype]] = None,
+    data_type: Optional[Union[str, torch.dtype]] = None,
+    sm_scale: Optional[float] = None,
+    rope_scale: Optional[float] = None,
+    rope_theta: Optional[float] = None,
+    non_blocking: bool = True,
+    fixed_split_size: Optional[int] = None,
+    disable_split_kv: bool = False,
+    global_override_indptr_cpu: Optional[torch.Tensor] = None,
+) -> None:
+    r"""Lighter ``plan`` that adopts the caller's device index tensors without copying
+    (reference decode.py:2416-2579).  ``global_override_indptr_cpu`` avoids the D2H read of
+    ``indptr``; ``last_page_len`` is read on the host unless ``page_size == 1``.
+    """
+    batch_size = len(last_page_len)
+    if logits_soft_cap is None:
+        logits_soft_cap = 0.0
+    _unsupported_variant(pos_encoding_mode)
+    if data_type is not None:
+        if q_data_type is None:
+            q_data_type = data_type
+        if kv_data_type is None:
+            kv_data_type = data_type
+    if q_data_type is None:
+        q_data_type = getattr(self, "_cached_q_data_type", None) or torch.float16
+    q_data_type = canonicalize_torch_dtype(q_data_type)
+    if kv_data_type is None:
+        kv_data_type = q_data_type
+    kv_data_type = canonicalize_torch_dtype(kv_data_type)
+
+    if self.is_cuda_graph_enabled:
+        if batch_size != self._fixed_batch_size:
+            raise ValueError(
+                "The batch size should be fixed in cudagraph mode, the runtime batch size {} "
+                " mismatches the batch size set during initialization {}".format(
+                    batch_size, self._fixed_batch_size
+                )
+            )
+        if len(indices) > len(self._paged_kv_indices_buf):
+            raise ValueError(
+                "The size of indices should be less than or equal to the allocated buffer"
+            )
+    else:
+        self._paged_kv_indptr_buf = indptr
+        self._paged_kv_indices_buf = indices
+        self._paged_kv_last_page_len_buf = last_page_len
+
+    indptr_src = global_override_indptr_cpu if global_override_indptr_cpu is not None else indptr
+    indptr_host, indptr_ptr = _host_i32_ptr(indptr_src)
+    if page_size == 1:
+        last_page_len_host = torch.ones((batch_size,), dtype=torch.int32)
+    else:
+        last_page_len_host = last_page_len.detach().to("cpu", torch.int32).contiguous()
+    self._cached_q_data_type = q_data_type
+    self._cached_kv_data_type = kv_data_type
+    self._batch_size = batch_size
+    self._num_qo_heads = num_qo_heads
+    self._num_kv_heads = num_kv_heads
+    try:
+        self._run_plan(indptr_ptr, last_page_len_host.data_ptr(), None, batch_size, num_qo_heads,
+                       num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left)
+    except Exception as e:
+        raise RuntimeError(f"Error in standard plan: {e}") from e
+    self._pos_encoding_mode = pos_encoding_mode
+    self._window_left = window_left
+    self._logits_soft_cap = logits_soft_cap
+    self._sm_scale = sm_scale
+    self._rope_scale = rope_scale
+    self._rope_theta = rope_theta

@@ -1,0 +1,171 @@
+"""Shared test helpers: golden fixtures, synthetic paged caches, plan replay."""
+from __future__ import annotations
+
+import ctypes as C
+import hashlib
+from pathlib import Path
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+GOLDEN = Path(__file__).resolve().parent / "golden" / "decode_golden.npz"
+
+
+# ---------------------------------------------------------------- golden fixtures
+def golden_cases():
+    z = np.load(GOLDEN)
+    return z, [str(n) for n in z["names"]]
+
+
+def golden_inputs(z, name):
+    Hq, Hkv, D, L, is_bf16, seed, stored = [int(x) for x in z[f"{name}/meta"]]
+    dtype = torch.bfloat16 if is_bf16 else torch.float16
+    if stored:
+        q = torch.from_numpy(z[f"{name}/q"].copy()).view(dtype)
+        k = torch.from_numpy(z[f"{name}/k"].copy()).view(dtype)
+        v = torch.from_numpy(z[f"{name}/v"].copy()).view(dtype)
+    else:
+        g = torch.Generator().manual_seed(seed)
+        q = torch.randn(Hq, D, generator=g).to(dtype)
+        k = torch.randn(L, Hkv, D, generator=g).to(dtype)
+        v = torch.randn(L, Hkv, D, generator=g).to(dtype)
+    h = hashlib.sha256()
+    for t in (q, k, v):
+        h.update(t.view(torch.int16).numpy().tobytes())
+    ok = h.digest() == z[f"{name}/hash"].tobytes()
+    return q, k, v, ok
+
+
+# ---------------------------------------------------------------- synthetic paged caches
+def make_paged_case(
+    kv_lens: Sequence[int],
+    num_kv_heads: int,
+    head_dim: int,
+    page_size: int,
+    kv_layout: str = "NHD",
+    dtype: torch.dtype = torch.float16,
+    seed: int = 0,
+    extra_pages: int = 3,
+    shuffle: bool = True,
+    device: str = "cpu",
+):
+    """Random 5-D paged cache with a shuffled page table (values ~ N(0,1)
+    generated in fp32 then cast, test_batch_decode_kernels.py:109-110)."""
+    g = torch.Generator().manual_seed(seed)
+    pages_per = [(-(-l // page_size)) for l in kv_lens]
+    total = sum(pages_per)
+    num_pages = total + extra_pages
+    if kv_layout == "NHD":
+        shape = (num_pages, 2, page_size, num_kv_heads, head_dim)
+    else:
+        shape = (num_pages, 2, num_kv_heads, page_size, head_dim)
+    cache32 = torch.randn(*shape, generator=g)
+    perm = torch.randperm(num_pages, generator=g) if shuffle else torch.arange(num_pages)
+    indices = perm[:total].to(torch.int32)
+    indptr = torch.zeros(len(kv_lens) + 1, dtype=torch.int32)
+    indptr[1:] = torch.cumsum(torch.tensor(pages_per, dtype=torch.int32), 0)
+    last = torch.tensor([((l - 1) % page_size + 1) if l > 0 else 0 for l in kv_lens], dtype=torch.int32)
+    if dtype in (torch.float8_e4m3fn, torch.float8_e5m2):
+        cache = cache32.to(dtype)
+    else:
+        cache = cache32.to(dtype)
+    return cache.to(device), indptr, indices, last
+
+
+def make_q(bs, num_qo_heads, head_dim, dtype, seed=1, device="cpu"):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(bs, num_qo_heads, head_dim, generator=g).to(dtype).to(device)
+
+
+# ---------------------------------------------------------------- plan through the C-ABI (host only)
+class Segment(C.Structure):
+    _fields_ = [("request", C.c_int32), ("kv_head", C.c_int32), ("tile_begin", C.c_int32),
+                ("tile_end", C.c_int32), ("slot", C.c_int32), ("tok_lo", C.c_int32),
+                ("tok_hi", C.c_int32), ("pad", C.c_int32)]
+
+
+class MergeUnit(C.Structure):
+    _fields_ = [("request", C.c_int32), ("kv_head", C.c_int32), ("slot_begin", C.c_int32),
+                ("count", C.c_int32)]
+
+
+# plan-info slots (flashinfer_b200/csrc/decode_params.h PlanInfoSlot)
+PI = dict(magic=0, num_ctas=1, num_segments=2, num_merge=3, num_slots=4, off_header=5,
+          off_cta_indptr=6, off_segments=7, off_merge=8, off_tmp_o=9, off_tmp_lse=10,
+          batch_size=11, hq=12, hkv=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
+          cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23)
+TILE = 64
+
+
+def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size,
+              num_ctas, q_dtype=1, kv_dtype=1, window_left=-1, cuda_graph=0,
+              kv_len=None, int_bytes=8 << 20, float_bytes=128 << 20):
+    """Run fi_batch_decode_plan in host-only mode (device = -1) and decode the work list."""
+    from flashinfer_b200 import _lib
+
+    lib = _lib.load()
+    ws = np.zeros(int_bytes, dtype=np.uint8)
+    ip = np.ascontiguousarray(np.asarray(indptr, dtype=np.int32))
+    lp = np.ascontiguousarray(np.asarray(last_page_len, dtype=np.int32))
+    kl = None if kv_len is None else np.ascontiguousarray(np.asarray(kv_len, dtype=np.int32))
+    info = np.zeros(lib.fi_plan_info_len(), dtype=np.int64)
+    rc = lib.fi_batch_decode_plan(
+        None, float_bytes, ws.ctypes.data, ws.ctypes.data, int_bytes, ip.ctypes.data,
+        lp.ctypes.data, None if kl is None else kl.ctypes.data, len(lp), num_qo_heads,
+        num_kv_heads, head_dim, page_size, q_dtype, kv_dtype, window_left, cuda_graph, -1,
+        num_ctas, None, info.ctypes.data)
+    if rc != 0:
+        return rc, _lib.last_error(), None
+    hdr = ws[info[PI["off_header"]]:info[PI["off_header"]] + 32].view(np.int32)
+    ncta = int(info[PI["num_ctas"]])
+    cta_indptr = ws[info[PI["off_cta_indptr"]]:info[PI["off_cta_indptr"]] + 4 * (ncta + 1)].view(np.int32).copy()
+    nseg = int(hdr[1])
+    segs = ws[info[PI["off_segments"]]:info[PI["off_segments"]] + 32 * nseg].view(np.int32).reshape(nseg, 8).copy()
+    nm = int(hdr[2])
+    merges = ws[info[PI["off_merge"]]:info[PI["off_merge"]] + 16 * nm].view(np.int32).reshape(nm, 4).copy()
+    return 0, "", dict(info=info, header=hdr.copy(), cta_indptr=cta_indptr, segments=segs, merges=merges)
+
+
+def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1):
+    """Pure-Python replay of the work list: returns per-(request, head) token visit counts
+    and checks the structural invariants.  Raises AssertionError on any inconsistency."""
+    segs, merges, cta_indptr, hdr = plan["segments"], plan["merges"], plan["cta_indptr"], plan["header"]
+    bs = len(kv_lens)
+    visits = [np.zeros(max(l, 0), dtype=np.int32) for l in kv_lens for _ in range(num_kv_heads)]
+    direct = np.zeros((bs, num_kv_heads), dtype=np.int32)
+    slot_owner = {}
+    assert cta_indptr[0] == 0 and np.all(np.diff(cta_indptr) >= 0)
+    assert cta_indptr[-1] == len(segs) == hdr[1]
+    for r, h, tb, te, slot, lo, hi, _ in segs:
+        assert 0 <= r < bs and 0 <= h < num_kv_heads
+        L = kv_lens[r]
+        exp_lo = max(0, L - 1 - window_left) if window_left >= 0 else 0
+        assert lo == exp_lo and hi == L, (lo, hi, exp_lo, L)
+        assert tb <= te
+        a, b = max(tb * TILE, lo), min(te * TILE, hi)
+        if b > a:
+            visits[r * num_kv_heads + h][a:b] += 1
+        if slot < 0:
+            direct[r, h] += 1
+        else:
+            assert slot not in slot_owner, "partial slot written twice"
+            slot_owner[slot] = (r, h)
+    merged = np.zeros((bs, num_kv_heads), dtype=np.int32)
+    for r, h, sb, cnt in merges:
+        assert cnt >= 2, "a merge unit must have at least two partials"
+        merged[r, h] += 1
+        for s in range(sb, sb + cnt):
+            assert slot_owner.get(s) == (r, h), "merge unit reads a slot it does not own"
+            del slot_owner[s]
+    assert not slot_owner, "partial slots never merged"
+    # every unit is written exactly once: directly or through exactly one merge
+    assert np.all(direct + merged == 1), "unit written != once"
+    for r in range(bs):
+        L = kv_lens[r]
+        lo = max(0, L - 1 - window_left) if window_left >= 0 else 0
+        for h in range(num_kv_heads):
+            v = visits[r * num_kv_heads + h]
+            assert np.all(v[lo:] == 1), f"tokens of request {r} head {h} not visited exactly once"
+            assert np.all(v[:lo] == 0)
+    return visits

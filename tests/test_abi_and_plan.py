@@ -1,0 +1,125 @@
+"""CPU: the C-ABI library loads and exports every symbol include/fi_b200.h declares, and the
+host planner (csrc/plan.cu) is self-consistent: every KV token of every (request, kv head)
+is visited exactly once, every unit is written exactly once, work is balanced over CTAs
+(north_star: "plan metadata must be bit-exact self-consistent")."""
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from helpers import PI, TILE, host_plan, replay_plan
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_library_exports_every_declared_symbol():
+    from flashinfer_b200 import _lib
+
+    lib = _lib.load()
+    header = (ROOT / "include" / "fi_b200.h").read_text()
+    declared = set(re.findall(r"FI_API\s+[\w\s\*]+?\b(fi_\w+)\s*\(", header))
+    assert declared, "no FI_API declarations found"
+    for name in declared:
+        assert hasattr(lib, name), f"libfi_b200.so does not export {name}"
+    assert declared == set(_lib.PROTOTYPES), "ctypes prototypes out of sync with the header"
+    assert lib.fi_version() >= 100
+    assert lib.fi_plan_info_len() == 24
+
+
+def lens_to_table(kv_lens, page_size):
+    pages = [-(-l // page_size) for l in kv_lens]
+    indptr = np.concatenate([[0], np.cumsum(pages)]).astype(np.int32)
+    last = np.array([((l - 1) % page_size + 1) if l > 0 else 0 for l in kv_lens], dtype=np.int32)
+    return indptr, last
+
+
+CASES = [
+    # (kv_lens, Hq, Hkv, page_size, num_ctas)
+    ([4096] * 64, 32, 8, 16, 296),                       # C2
+    ([8192] * 128, 8, 1, 16, 296),                       # C3 per rank
+    ([131072] * 16, 8, 1, 16, 148),                      # C5 per rank
+    ([1, 54, 97, 512, 2048, 0, 16384, 63, 64, 65], 32, 4, 8, 296),
+    ([0, 9], 4, 1, 16, 148),                             # empty-request regression case
+    ([0, 0, 0], 8, 2, 16, 148),
+    ([7] * 17, 4, 4, 1, 148),
+    ([5, 11, 130], 8, 8, 5, 31),                         # non-power-of-two page size
+]
+
+
+@pytest.mark.parametrize("kv_lens,hq,hkv,page,nctas", CASES)
+def test_plan_visits_every_token_once(kv_lens, hq, hkv, page, nctas):
+    indptr, last = lens_to_table(kv_lens, page)
+    rc, err, plan = host_plan(indptr, last, hq, hkv, 128, page, nctas)
+    assert rc == 0, err
+    replay_plan(plan, kv_lens, hkv)
+    # balance: per-CTA tile counts differ by at most one (+ the floor of min tiles per CTA)
+    segs, cip = plan["segments"], plan["cta_indptr"]
+    loads = np.array([sum(int(s[3] - s[2]) for s in segs[cip[i]:cip[i + 1]]) for i in range(nctas)])
+    total = sum((-(-l // TILE)) * hkv for l in kv_lens)
+    assert loads.sum() == total
+    used = loads[loads > 0]
+    if len(used):
+        assert used.max() - used.min() <= 1
+    assert plan["info"][PI["total_tiles"]] == total
+
+
+def test_plan_log_uniform_c4_balance():
+    rng = np.random.default_rng(0)
+    kv_lens = np.exp(rng.uniform(np.log(512), np.log(32768), 256)).round().astype(int).tolist()
+    indptr, last = lens_to_table(kv_lens, 16)
+    rc, err, plan = host_plan(indptr, last, 32, 8, 128, 16, 296)
+    assert rc == 0, err
+    replay_plan(plan, kv_lens, 8)
+    assert len(plan["merges"]) <= 296
+
+
+def test_plan_is_deterministic():
+    kv_lens = [100, 2000, 31, 977]
+    indptr, last = lens_to_table(kv_lens, 16)
+    a = host_plan(indptr, last, 32, 8, 128, 16, 296)[2]
+    b = host_plan(indptr, last, 32, 8, 128, 16, 296)[2]
+    for key in ("segments", "merges", "cta_indptr", "header"):
+        assert np.array_equal(a[key], b[key])
+    assert np.array_equal(a["info"], b["info"])
+
+
+def test_plan_window_left():
+    kv_lens = [300, 10, 1000]
+    indptr, last = lens_to_table(kv_lens, 16)
+    rc, err, plan = host_plan(indptr, last, 8, 2, 128, 16, 148, window_left=99)
+    assert rc == 0, err
+    replay_plan(plan, kv_lens, 2, window_left=99)
+
+
+def test_plan_explicit_seq_lens():
+    indptr = np.array([0, 4, 10], dtype=np.int32)
+    rc, err, plan = host_plan(indptr, [16, 16], 8, 2, 128, 16, 148, kv_len=[50, 96])
+    assert rc == 0, err
+    replay_plan(plan, [50, 96], 2)
+
+
+def test_plan_graph_mode_layout_is_shape_independent():
+    """CUDA-graph contract: offsets and launch grids depend only on (bs, heads, num_ctas)."""
+    a = host_plan(*lens_to_table([100] * 8, 16), 32, 8, 128, 16, 296, cuda_graph=1)[2]["info"]
+    b = host_plan(*lens_to_table([5000, 3, 77, 0, 12000, 640, 64, 1], 16), 32, 8, 128, 16, 296,
+                  cuda_graph=1)[2]["info"]
+    for key in ("num_ctas", "off_header", "off_cta_indptr", "off_segments", "off_merge",
+                "off_tmp_o", "off_tmp_lse", "merge_grid", "stages"):
+        assert a[PI[key]] == b[PI[key]], key
+
+
+def test_plan_errors():
+    indptr, last = lens_to_table([100], 16)
+    rc, err, _ = host_plan(indptr, last, 30, 8, 128, 16, 148)
+    assert rc == 1 and "multiple" in err
+    rc, err, _ = host_plan(indptr, last, 32, 2, 128, 16, 148)
+    assert rc == 4 and "group_size" in err
+    rc, err, _ = host_plan(indptr, last, 8, 2, 96, 16, 148)
+    assert rc == 4 and "head_dim" in err
+    rc, err, _ = host_plan(indptr, [17], 8, 2, 128, 16, 148)
+    assert rc == 1 and "last_page_len" in err
+    rc, err, _ = host_plan(indptr, last, 8, 2, 128, 16, 148, float_bytes=1024)
+    assert rc == 2 and "workspace" in err.lower()
+    rc, err, _ = host_plan(*lens_to_table([64] * 4096, 16), 8, 8, 128, 16, 148, int_bytes=4096)
+    assert rc == 2 and "Increase the workspace buffer size" in err
