@@ -1,0 +1,272 @@
+// oracle/ref_shim.cu — TEST INFRASTRUCTURE, NOT PRODUCT.
+//
+// Plain extern "C" entry points over the REFERENCE's own header-only implementation of the
+// hot path, compiled where the headers lie (-I /root/reference/include, see oracle/Makefile)
+// into oracle/_ref/liboracle_ref.so.  No reference source is copied into this repo: this file
+// only instantiates the reference templates
+//   DecodePlan                             include/flashinfer/attention/scheduler.cuh:424-493
+//   BatchDecodeWithPagedKVCacheDispatched  include/flashinfer/attention/decode.cuh:739-825
+//   SingleDecodeWithKVCacheDispatched      include/flashinfer/attention/decode.cuh:658-737
+//   MergeState / MergeStateInPlace / MergeStates / VariableLengthMergeStates
+//                                          include/flashinfer/attention/cascade.cuh:573-736
+// with parameter structs carrying the fields those templates read (the reference renders the
+// same structs from csrc/batch_decode_customize_config.jinja and
+// csrc/single_decode_customize_config.jinja at JIT time).
+// Only tests/ and bench.py's comparator leg load the resulting library.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
+
+#include <flashinfer/attention/cascade.cuh>
+#include <flashinfer/attention/decode.cuh>
+#include <flashinfer/attention/scheduler.cuh>
+#include <flashinfer/attention/variants.cuh>
+#include <flashinfer/page.cuh>
+#include <flashinfer/pos_enc.cuh>
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+using namespace flashinfer;
+
+namespace refshim {
+
+thread_local std::string g_err;
+
+template <typename Q, typename KV>
+struct BatchParams {
+  using DTypeQ = Q;
+  using DTypeKV = KV;
+  using DTypeO = Q;
+  using IdType = int32_t;
+  DTypeQ* q;
+  paged_kv_t<DTypeKV, IdType> paged_kv;
+  DTypeO* o;
+  float* lse;
+  float* maybe_alibi_slopes;
+  float logits_soft_cap, sm_scale, rope_rcp_scale, rope_rcp_theta;
+  uint32_t padded_batch_size, num_qo_heads;
+  IdType q_stride_n, q_stride_h;
+  int32_t window_left;
+  bool enable_pdl;
+  IdType *request_indices, *kv_tile_indices, *o_indptr, *kv_chunk_size_ptr;
+  bool* block_valid_mask;
+  bool partition_kv;
+  __host__ __device__ __forceinline__ int32_t get_qo_len(int32_t) const { return 1; }
+  __host__ __device__ __forceinline__ int32_t get_kv_len(int32_t b) const {
+    return paged_kv.get_length(b);
+  }
+};
+
+template <typename Q, typename KV>
+struct SingleParams {
+  using DTypeQ = Q;
+  using DTypeKV = KV;
+  using DTypeO = Q;
+  using IdType = int32_t;
+  DTypeQ* q;
+  DTypeKV *k, *v;
+  DTypeO* o;
+  float* lse;
+  float* maybe_alibi_slopes;
+  float logits_soft_cap, sm_scale, rope_rcp_scale, rope_rcp_theta;
+  uint32_t kv_len, num_qo_heads, num_kv_heads, q_stride_n, q_stride_h, kv_stride_n, kv_stride_h;
+  int32_t window_left;
+  uint32_t kv_chunk_size;
+  __host__ __device__ __forceinline__ uint32_t get_qo_len(uint32_t) const { return 1; }
+  __host__ __device__ __forceinline__ uint32_t get_kv_len(uint32_t) const { return kv_len; }
+};
+
+using Variant = DefaultAttention</*custom_mask=*/false, /*swa=*/false, /*softcap=*/false, /*alibi=*/false>;
+
+struct BatchArgs {
+  void *float_ws, *int_ws, *pinned_ws;
+  size_t float_bytes, int_bytes;
+  int32_t* indptr_h;
+  int bs, hq, hkv, page_size, layout, cuda_graph;
+  void *q, *k, *v, *o;
+  float* lse;
+  int64_t q_stride_n, q_stride_h, kv_strides[3];
+  int32_t *indices, *indptr, *last_page_len;
+  float sm_scale;
+  cudaStream_t stream;
+  int64_t* info_out;  // 10 x int64 DecodePlanInfo + [10] = launches (1 or 2)
+};
+
+template <typename Q, typename KV, uint32_t HD>
+int batch_impl(const BatchArgs& a) {
+  using P = BatchParams<Q, KV>;
+  DecodePlanInfo info;
+  cudaError_t st = cudaSuccess;
+  bool ok = false;
+  DISPATCH_GQA_GROUP_SIZE(a.hq / a.hkv, GROUP_SIZE, {
+    auto est = BatchDecodeWithPagedKVCacheWorkEstimationDispatched<GROUP_SIZE, HD, PosEncodingMode::kNone,
+                                                                   Variant, P>;
+    st = DecodePlan<HD, PosEncodingMode::kNone, Variant, P>(a.float_ws, a.float_bytes, a.int_ws,
+                                                            a.pinned_ws, a.int_bytes, info, a.indptr_h,
+                                                            a.bs, a.hq, a.page_size, a.cuda_graph != 0,
+                                                            a.stream, est);
+    ok = true;
+  });
+  if (!ok) { g_err = "unsupported group size"; return 4; }
+  if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
+  paged_kv_t<KV, int32_t> kv(a.hkv, a.page_size, HD, a.bs, static_cast<QKVLayout>(a.layout),
+                             static_cast<KV*>(a.k), static_cast<KV*>(a.v), a.kv_strides, a.indices,
+                             a.indptr, a.last_page_len);
+  P p;
+  p.q = static_cast<Q*>(a.q);
+  p.paged_kv = kv;
+  p.o = static_cast<Q*>(a.o);
+  p.lse = a.lse;
+  p.maybe_alibi_slopes = nullptr;
+  p.logits_soft_cap = 0.f;
+  p.sm_scale = a.sm_scale;
+  p.rope_rcp_scale = 1.f;
+  p.rope_rcp_theta = 1e-4f;
+  p.padded_batch_size = info.padded_batch_size;
+  p.num_qo_heads = a.hq;
+  p.q_stride_n = a.q_stride_n;
+  p.q_stride_h = a.q_stride_h;
+  p.window_left = -1;
+  p.enable_pdl = false;
+  char* ib = static_cast<char*>(a.int_ws);
+  p.request_indices = reinterpret_cast<int32_t*>(ib + info.request_indices_offset);
+  p.kv_tile_indices = reinterpret_cast<int32_t*>(ib + info.kv_tile_indices_offset);
+  p.o_indptr = reinterpret_cast<int32_t*>(ib + info.o_indptr_offset);
+  p.kv_chunk_size_ptr = reinterpret_cast<int32_t*>(ib + info.kv_chunk_size_ptr_offset);
+  p.block_valid_mask = nullptr;
+  p.partition_kv = false;
+  Q* tmp_v = nullptr;
+  float* tmp_s = nullptr;
+  if (info.split_kv) {
+    tmp_v = reinterpret_cast<Q*>(static_cast<char*>(a.float_ws) + info.v_offset);
+    tmp_s = reinterpret_cast<float*>(static_cast<char*>(a.float_ws) + info.s_offset);
+    if (info.enable_cuda_graph)
+      p.block_valid_mask = reinterpret_cast<bool*>(ib + info.block_valid_mask_offset);
+  }
+  st = BatchDecodeWithPagedKVCacheDispatched<HD, PosEncodingMode::kNone, Variant>(p, tmp_v, tmp_s,
+                                                                                 false, a.stream);
+  if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
+  if (a.info_out) {
+    auto v = info.ToVector();
+    for (int i = 0; i < 10; ++i) a.info_out[i] = v[i];
+    a.info_out[10] = info.split_kv ? 2 : 1;
+  }
+  return 0;
+}
+
+template <typename Q, typename KV, uint32_t HD>
+int single_impl(void* q, void* k, void* v, void* tmp, void* o, float* lse, int hq, int hkv, int kv_len,
+                int layout, float sm_scale, cudaStream_t stream) {
+  SingleParams<Q, KV> p;
+  p.q = static_cast<Q*>(q);
+  p.k = static_cast<KV*>(k);
+  p.v = static_cast<KV*>(v);
+  p.o = static_cast<Q*>(o);
+  p.lse = lse;
+  p.maybe_alibi_slopes = nullptr;
+  p.logits_soft_cap = 0.f;
+  p.sm_scale = sm_scale;
+  p.rope_rcp_scale = 1.f;
+  p.rope_rcp_theta = 1e-4f;
+  p.kv_len = kv_len;
+  p.num_qo_heads = hq;
+  p.num_kv_heads = hkv;
+  p.q_stride_n = hq * HD;
+  p.q_stride_h = HD;
+  p.kv_stride_n = layout == 0 ? hkv * HD : HD;
+  p.kv_stride_h = layout == 0 ? HD : kv_len * HD;
+  p.window_left = -1;
+  p.kv_chunk_size = 0;
+  cudaError_t st = SingleDecodeWithKVCacheDispatched<HD, PosEncodingMode::kNone, Variant>(
+      p, static_cast<Q*>(tmp), stream);
+  if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
+  return 0;
+}
+
+}  // namespace refshim
+using namespace refshim;
+
+// dtype codes as in include/fi_b200.h: 0 f16, 1 bf16, 2 e4m3
+#define REF_DISPATCH(qd, kvd, ...)                                                                  \
+  if (qd == 0 && kvd == 0) { using Q = half; using KV = half; __VA_ARGS__; }                        \
+  else if (qd == 1 && kvd == 1) { using Q = nv_bfloat16; using KV = nv_bfloat16; __VA_ARGS__; }     \
+  else if (qd == 0 && kvd == 2) { using Q = half; using KV = __nv_fp8_e4m3; __VA_ARGS__; }          \
+  else if (qd == 1 && kvd == 2) { using Q = nv_bfloat16; using KV = __nv_fp8_e4m3; __VA_ARGS__; }   \
+  else { g_err = "unsupported dtype pair"; return 4; }
+
+extern "C" {
+
+__attribute__((visibility("default"))) const char* ref_last_error() { return g_err.c_str(); }
+
+// plan (reference DecodePlan) + run (reference kernel [+ reference merge]); head_dim 128 only
+__attribute__((visibility("default"))) int ref_batch_decode(
+    void* float_ws, size_t float_bytes, void* int_ws, void* pinned_ws, size_t int_bytes,
+    int32_t* indptr_h, int bs, int hq, int hkv, int head_dim, int page_size, int q_dtype,
+    int kv_dtype, int layout, int cuda_graph, void* q, int64_t q_stride_n, int64_t q_stride_h,
+    void* k, void* v, int64_t s0, int64_t s1, int64_t s2, int32_t* indices, int32_t* indptr,
+    int32_t* last_page_len, void* o, float* lse, float sm_scale, void* stream, int64_t* info_out) {
+  if (head_dim != 128) { g_err = "ref shim is built for head_dim 128"; return 4; }
+  BatchArgs a{float_ws, int_ws, pinned_ws, float_bytes, int_bytes, indptr_h, bs, hq, hkv, page_size,
+              layout, cuda_graph, q, k, v, o, lse, q_stride_n, q_stride_h, {s0, s1, s2}, indices,
+              indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), info_out};
+  try {
+    REF_DISPATCH(q_dtype, kv_dtype, return (batch_impl<Q, KV, 128>(a)));
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return 2;
+  }
+}
+
+__attribute__((visibility("default"))) int ref_single_decode(void* q, void* k, void* v, void* tmp,
+                                                            void* o, float* lse, int hq, int hkv,
+                                                            int head_dim, int kv_len, int q_dtype,
+                                                            int kv_dtype, int layout, float sm_scale,
+                                                            void* stream) {
+  if (head_dim != 128) { g_err = "ref shim is built for head_dim 128"; return 4; }
+  try {
+    REF_DISPATCH(q_dtype, kv_dtype, return (single_impl<Q, KV, 128>(q, k, v, tmp, o, lse, hq, hkv, kv_len, layout, sm_scale, static_cast<cudaStream_t>(stream))));
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return 2;
+  }
+}
+
+#define REF_DT(dt, ...)                                       \
+  if (dt == 0) { using T = half; __VA_ARGS__; }               \
+  else if (dt == 1) { using T = nv_bfloat16; __VA_ARGS__; }   \
+  else { g_err = "unsupported dtype"; return 4; }
+
+__attribute__((visibility("default"))) int ref_merge_state(void* va, float* sa, void* vb, float* sb,
+                                                          void* vm, float* sm, int seq, int heads,
+                                                          int d, int dt, void* stream) {
+  cudaError_t st;
+  REF_DT(dt, st = MergeState(static_cast<T*>(va), sa, static_cast<T*>(vb), sb, static_cast<T*>(vm), sm,
+                             seq, heads, d, static_cast<cudaStream_t>(stream)));
+  if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
+  return 0;
+}
+
+__attribute__((visibility("default"))) int ref_merge_state_in_place(void* v, float* s, void* vo,
+                                                                   float* so, uint8_t* mask, int seq,
+                                                                   int heads, int d, int dt,
+                                                                   void* stream) {
+  cudaError_t st;
+  REF_DT(dt, st = MergeStateInPlace(static_cast<T*>(v), s, static_cast<T*>(vo), so, seq, heads, d, mask,
+                                    static_cast<cudaStream_t>(stream)));
+  if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
+  return 0;
+}
+
+__attribute__((visibility("default"))) int ref_merge_states(void* v, float* s, void* vm, float* sm,
+                                                           int n, int seq, int heads, int d, int dt,
+                                                           void* stream) {
+  cudaError_t st;
+  REF_DT(dt, st = MergeStates(static_cast<T*>(v), s, static_cast<T*>(vm), sm, n, seq, heads, d,
+                              static_cast<cudaStream_t>(stream)));
+  if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
+  return 0;
+}
+
+}  // extern "C"

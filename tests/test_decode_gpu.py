@@ -1,0 +1,263 @@
+"""GPU parity tests of the decode path — through the public API, i.e. through the C-ABI.
+
+Oracle: oracle/attention_ref.py (fp32 CPU restatement pinned to the reference's test oracle).
+Gates (BASELINE.json north_star): o max-abs <= 1e-2 (fp16/bf16 KV), <= 3e-2 (fp8 KV);
+base-2 lse within 1e-3.  Cases follow the reference's matrix
+(tests/attention/test_batch_decode_kernels.py:58-188, test_decode_prefill_lse.py:22-71,
+test_non_contiguous_decode.py:46-118, test_decode_fp8_calibration_scale.py:74-153)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import golden_cases, golden_inputs, make_paged_case, make_q
+from oracle import attention_ref as orc
+
+pytestmark = pytest.mark.gpu
+
+O_TOL = 1e-2
+O_TOL_FP8 = 3e-2
+LSE_TOL = 1e-3
+DEV = "cuda:0"
+
+
+def _fi():
+    import flashinfer_b200 as fi
+
+    return fi
+
+
+def _workspace(nbytes=128 << 20):
+    return torch.zeros(nbytes, dtype=torch.uint8, device=DEV)
+
+
+def run_batch(kv_lens, hq, hkv, d, page, layout, q_dtype, kv_dtype=None, seed=0, tuple_cache=False,
+              loader=0, window_left=-1, soft_cap=None, ws=None, check_requests=None):
+    fi = _fi()
+    from flashinfer_b200 import _lib
+
+    kv_dtype = kv_dtype or q_dtype
+    is8 = kv_dtype in (torch.float8_e4m3fn, torch.float8_e5m2)
+    cache, indptr, indices, last = make_paged_case(kv_lens, hkv, d, page, layout,
+                                                   torch.float32, seed=seed)
+    k_scale = v_scale = None
+    if is8:
+        # test_decode_fp8_calibration_scale.py:131-137: scale = amax / 256
+        k_scale = float(cache[:, 0].abs().amax() / 256)
+        v_scale = float(cache[:, 1].abs().amax() / 256)
+        cache[:, 0] /= k_scale
+        cache[:, 1] /= v_scale
+    cache = cache.to(kv_dtype)
+    q = make_q(len(kv_lens), hq, d, q_dtype, seed=seed + 1)
+    cache_d, q_d = cache.to(DEV), q.to(DEV)
+    wrapper = fi.BatchDecodeWithPagedKVCacheWrapper(ws if ws is not None else _workspace(), layout)
+    _lib.load().fi_set_tuning(0, 0, loader, 0)
+    try:
+        wrapper.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=q_dtype,
+                     kv_data_type=kv_dtype, window_left=window_left, logits_soft_cap=soft_cap)
+        pkv = (cache_d[:, 0], cache_d[:, 1]) if tuple_cache else cache_d
+        o, lse = wrapper.run(q_d, pkv, k_scale=k_scale, v_scale=v_scale, return_lse=True)
+        torch.cuda.synchronize()
+    finally:
+        _lib.load().fi_set_tuning(0, 0, 0, 0)
+    o_ref, lse_ref = orc.batch_decode_ref(
+        q, cache, indptr, indices, last, layout, k_scale=k_scale or 1.0, v_scale=v_scale or 1.0,
+        logits_soft_cap=soft_cap or 0.0, window_left=window_left, requests=check_requests)
+    o_c, lse_c = o.float().cpu(), lse.cpu()
+    if check_requests is not None:
+        o_c, lse_c = o_c[list(check_requests)], lse_c[list(check_requests)]
+    tol = O_TOL_FP8 if is8 else O_TOL
+    assert (o_c - o_ref).abs().max().item() <= tol, (o_c - o_ref).abs().max().item()
+    assert (lse_c - lse_ref).abs().max().item() <= LSE_TOL, (lse_c - lse_ref).abs().max().item()
+    return o, lse
+
+
+@pytest.mark.parametrize("loader", [1, 2])  # 1 = TMA boxes, 2 = cp.async gathers
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("q_dtype", [torch.float16, torch.bfloat16])
+def test_batch_decode_minimum_slice(loader, layout, q_dtype):
+    # bs in {1, 12, 17}, kv_len in {1, 54, 97, 512, 2048}, shuffled pages
+    run_batch([1, 54, 97, 512, 2048, 33, 64, 65, 128, 1000, 17, 3], 32, 8, 128, 16, layout,
+              q_dtype, loader=loader)
+
+
+@pytest.mark.parametrize("page", [1, 5, 8, 16, 32])
+@pytest.mark.parametrize("group", [1, 2, 4, 8])
+def test_batch_decode_page_sizes_and_groups(page, group):
+    hkv = 4
+    run_batch([54, 97, 512, 1, 2048, 130], hkv * group, hkv, 128, page, "NHD", torch.float16,
+              seed=page * 10 + group)
+
+
+@pytest.mark.parametrize("d", [64, 128, 256])
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+def test_batch_decode_head_dims(d, layout):
+    run_batch([97, 512, 54, 2047], 8, 2, d, 8, layout, torch.bfloat16, seed=d)
+
+
+@pytest.mark.parametrize("bs,kv_len", [(12, 54), (17, 97), (128, 512), (12, 2048), (3, 16384)])
+def test_batch_decode_reference_matrix(bs, kv_len):
+    # test_batch_decode_kernels.py:58-66 (uniform lengths)
+    run_batch([kv_len] * bs, 32, 4, 128, 16, "NHD", torch.float16, seed=bs,
+              check_requests=range(min(bs, 6)))
+
+
+def test_batch_decode_tuple_cache_and_user_buffers():
+    fi = _fi()
+    kv_lens = [100, 7, 300]
+    run_batch(kv_lens, 8, 2, 128, 16, "HND", torch.float16, tuple_cache=True)
+    cache, indptr, indices, last = make_paged_case(kv_lens, 2, 128, 16, "NHD", torch.float16)
+    q = make_q(3, 8, 128, torch.float16).to(DEV)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, 8, 2, 128, 16, q_data_type=torch.float16)
+    o = w.run(q, cache.to(DEV))
+    out = torch.empty_like(q)
+    lse = torch.empty(3, 8, dtype=torch.float32, device=DEV)
+    o2, lse2 = w.run(q, cache.to(DEV), out=out, lse=lse, return_lse=True)
+    assert o2.data_ptr() == out.data_ptr() and torch.equal(o, out)
+    with pytest.raises(ValueError):
+        w.run(q.to(torch.bfloat16), cache.to(DEV))
+    with pytest.raises(ValueError):
+        w.run(q, cache.to(DEV), out=torch.empty(3, 8, 64, dtype=torch.float16, device=DEV))
+    with pytest.raises(ValueError):
+        w.plan(indptr.long(), indices, last, 8, 2, 128, 16)
+
+
+def test_empty_request_regression():
+    # tests/attention/test_decode_prefill_lse.py:24-26: indptr=[0,0,9], last_page_len=[0,1], HND
+    fi = _fi()
+    hq, hkv, d, page = 8, 2, 128, 16
+    g = torch.Generator().manual_seed(0)
+    cache = torch.randn(9, 2, hkv, page, d, generator=g).half()
+    indptr = torch.tensor([0, 0, 9], dtype=torch.int32)
+    indices = torch.arange(9, dtype=torch.int32)
+    last = torch.tensor([0, 1], dtype=torch.int32)
+    q = make_q(2, hq, d, torch.float16)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "HND")
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16)
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True)
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, "HND")
+    assert torch.all(o[0] == 0) and torch.all(lse[0] == -5e4)
+    assert (o.float().cpu() - o_ref).abs().max() <= O_TOL
+    assert (lse.cpu() - lse_ref).abs().max() <= LSE_TOL
+
+
+@pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("loader", [1, 2])
+def test_batch_decode_fp8_kv(kv_dtype, layout, loader):
+    run_batch([54, 97, 512, 2048, 1, 77], 32, 4, 128, 16, layout, torch.float16, kv_dtype,
+              loader=loader)
+    run_batch([300, 5000], 8, 1, 128, 16, layout, torch.bfloat16, kv_dtype, loader=loader)
+
+
+def test_non_contiguous_q_and_cache():
+    # test_non_contiguous_decode.py:100-118: q sliced out of a packed QKV projection
+    fi = _fi()
+    hq, hkv, d, page = 8, 2, 128, 16
+    kv_lens = [70, 200, 5]
+    cache, indptr, indices, last = make_paged_case(kv_lens, hkv, d, page, "NHD", torch.float16)
+    g = torch.Generator().manual_seed(5)
+    qkv = torch.randn(3, (hq + 2 * hkv) * d, generator=g).half().to(DEV)
+    q = qkv[:, : hq * d].view(3, hq, d)
+    assert not q.is_contiguous()
+    # cache rows padded: strided view on the head_dim-major storage
+    big = torch.zeros(cache.shape[0], 2, page, hkv, 2 * d, dtype=torch.float16, device=DEV)
+    big[..., :d] = cache.to(DEV)
+    view = big[..., :d]
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16)
+    o, lse = w.run(q, view, return_lse=True)
+    o_ref, lse_ref = orc.batch_decode_ref(q.cpu(), cache, indptr, indices, last, "NHD")
+    assert (o.float().cpu() - o_ref).abs().max() <= O_TOL
+    assert (lse.cpu() - lse_ref).abs().max() <= LSE_TOL
+
+
+def test_window_left_and_soft_cap():
+    run_batch([300, 10, 1000, 64], 8, 2, 128, 16, "NHD", torch.float16, window_left=99)
+    run_batch([300, 10, 1000, 64], 8, 2, 128, 16, "NHD", torch.float16, soft_cap=30.0)
+
+
+def test_split_kv_long_single_request_and_determinism():
+    # one long request: every CTA gets a slice, one merge unit per head
+    o1, l1 = run_batch([50000], 32, 8, 128, 16, "NHD", torch.bfloat16)
+    o2, l2 = run_batch([50000], 32, 8, 128, 16, "NHD", torch.bfloat16)
+    assert torch.equal(o1, o2) and torch.equal(l1, l2)  # fixed inputs + plan => bit-identical
+
+
+def test_cuda_graph_replay_with_replan():
+    # test_batch_decode_kernels.py:492-676: capture run, re-plan between replays
+    fi = _fi()
+    hq, hkv, d, page, bs = 32, 8, 128, 16, 4
+    max_pages = 4096
+    indptr_buf = torch.zeros(bs + 1, dtype=torch.int32, device=DEV)
+    indices_buf = torch.zeros(max_pages, dtype=torch.int32, device=DEV)
+    last_buf = torch.zeros(bs, dtype=torch.int32, device=DEV)
+    w = fi.CUDAGraphBatchDecodeWithPagedKVCacheWrapper(_workspace(), indptr_buf, indices_buf,
+                                                       last_buf, "NHD")
+    lens_a, lens_b = [100, 2000, 31, 977], [4000, 1, 64, 15000]
+    cache, ip_b, ix_b, lp_b = make_paged_case(lens_b, hkv, d, page, "NHD", torch.float16, seed=2)
+    cache_d = cache.to(DEV)
+    # plan A uses a page table that is valid inside the same pool
+    _, ip_a, ix_a, lp_a = make_paged_case(lens_a, hkv, d, page, "NHD", torch.float16, seed=3)
+    q = make_q(bs, hq, d, torch.float16).to(DEV)
+    out = torch.empty_like(q)
+    w.plan(ip_a, ix_a, lp_a, hq, hkv, d, page, q_data_type=torch.float16)
+    w.run(q, cache_d, out=out)  # warm-up outside the graph
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        w.run(q, cache_d, out=out)
+    for ip, ix, lp in ((ip_a, ix_a, lp_a), (ip_b, ix_b, lp_b), (ip_a, ix_a, lp_a)):
+        w.plan(ip, ix, lp, hq, hkv, d, page, q_data_type=torch.float16)
+        graph.replay()
+        torch.cuda.synchronize()
+        o_ref, _ = orc.batch_decode_ref(q.cpu(), cache, ip, ix, lp, "NHD")
+        assert (out.float().cpu() - o_ref).abs().max() <= O_TOL
+
+
+Z, NAMES = golden_cases()
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_single_decode_against_reference_golden(name):
+    fi = _fi()
+    q, k, v, ok = golden_inputs(Z, name)
+    if not ok:
+        pytest.skip("un-stored golden inputs not reproducible on this machine")
+    o, lse = fi.single_decode_with_kv_cache(q.to(DEV), k.to(DEV), v.to(DEV), return_lse=True)
+    assert np.abs(o.float().cpu().numpy() - Z[f"{name}/o_fp32"]).max() <= O_TOL
+    assert np.abs(lse.cpu().numpy() - Z[f"{name}/lse2"]).max() <= LSE_TOL
+    # HND layout gives the same answer
+    o2 = fi.single_decode_with_kv_cache(q.to(DEV), k.transpose(0, 1).contiguous().to(DEV),
+                                        v.transpose(0, 1).contiguous().to(DEV), kv_layout="HND")
+    assert (o2.float() - o.float()).abs().max() <= 2e-3
+
+
+@pytest.mark.parametrize("kv_len", [0, 1, 63, 64, 65, 255, 256, 257, 4099, 33001])
+def test_single_decode_lengths(kv_len):
+    fi = _fi()
+    g = torch.Generator().manual_seed(kv_len)
+    q = torch.randn(32, 128, generator=g).half()
+    k = torch.randn(kv_len, 8, 128, generator=g).half()
+    v = torch.randn(kv_len, 8, 128, generator=g).half()
+    o, lse = fi.single_decode_with_kv_cache(q.to(DEV), k.to(DEV), v.to(DEV), return_lse=True)
+    o_ref, lse_ref = orc.decode_attention_ref(q, k, v)
+    assert (o.float().cpu() - o_ref).abs().max() <= O_TOL
+    assert (lse.cpu() - lse_ref).abs().max() <= LSE_TOL
+
+
+def test_batch_equals_single():
+    # the reference's own chain: batch paged decode == single decode per request, 1e-3
+    fi = _fi()
+    kv_lens = [54, 512, 2048]
+    cache, indptr, indices, last = make_paged_case(kv_lens, 4, 128, 16, "NHD", torch.float16)
+    q = make_q(3, 32, 128, torch.float16)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, 32, 4, 128, 16, q_data_type=torch.float16)
+    o = w.run(q.to(DEV), cache.to(DEV))
+    for i in range(3):
+        k, v = orc.gather_paged_kv(cache[:, 0], cache[:, 1], indptr, indices, last, i, "NHD")
+        oi = fi.single_decode_with_kv_cache(q[i].to(DEV), k.contiguous().to(DEV), v.contiguous().to(DEV))
+        torch.testing.assert_close(o[i], oi, rtol=1e-3, atol=1e-3)
