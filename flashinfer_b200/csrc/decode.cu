@@ -58,9 +58,17 @@ static int make_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int hea
     std::swap(box[1], box[2]);
   }
   cuuint32_t estr[4] = {1, 1, 1, 1};
+  // L2 promotion must not exceed the contiguous run of one (token, head) row: a 128-byte row
+  // (fp8 D=128, 16-bit D=64) inside an NHD page has another head's row next to it, and
+  // promoting to 256 B would drag that row through DRAM for nothing (measured 1.49x traffic).
+  const int64_t row_bytes = (int64_t)head_dim * es;
+  const bool rows_adjacent = stride_n * es == row_bytes;
+  const CUtensorMapL2promotion promo = (row_bytes >= 256 || rows_adjacent)
+                                           ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+                                           : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
   CUresult r = enc(map, dt, 4, const_cast<void*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(FI_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
   return FI_OK;
 }
@@ -69,11 +77,11 @@ static bool is_pow2(int64_t x) { return x > 0 && (x & (x - 1)) == 0; }
 static int ilog2(int64_t x) { int s = 0; while ((int64_t(1) << s) < x) ++s; return s; }
 
 static bool tma_eligible(const void* k, const void* v, int es, int64_t sn, int64_t sh, int64_t sp,
-                         int page_size, bool contiguous, int64_t kv_len) {
+                         int page_size, bool contiguous, int64_t kv_len, int tile) {
   if (tuning().loader == 2) return false;
   if ((reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15) return false;
   if ((sn * es) % 16 || (sh * es) % 16 || (sp * es) % 16) return false;
-  if (contiguous) return kv_len >= kTileTokens;
+  if (contiguous) return kv_len >= tile;
   return is_pow2(page_size) && page_size >= 8;
 }
 
@@ -199,13 +207,16 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.page_size = page_size;
   p.page_shift = is_pow2(page_size) ? ilog2(page_size) : -1;
   p.page_mask = is_pow2(page_size) ? page_size - 1 : 0;
-  p.rows_per_box = page_size < kTileTokens ? page_size : kTileTokens;
+  const int TT = tile_tokens(kvf);
+  p.rows_per_box = page_size < TT ? page_size : TT;
   p.tma_h_first = kv_stride_h < kv_stride_n;
   p.header = reinterpret_cast<const PlanHeader*>(iw + plan_info[kPiOffHeader]);
   p.cta_seg_indptr = reinterpret_cast<const int32_t*>(iw + plan_info[kPiOffCtaIndptr]);
   p.segments = reinterpret_cast<const Segment*>(iw + plan_info[kPiOffSegments]);
   p.tmp_o = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpO]);
   p.tmp_lse = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpLse]);
+  p.merge_units = reinterpret_cast<const MergeUnit*>(iw + plan_info[kPiOffMerge]);
+  p.merge_counters = reinterpret_cast<int32_t*>(iw + plan_info[kPiOffCounters]);
   p.num_qo_heads = Hq;
   p.group_size = Hq / Hkv;
   p.num_stages = (int)plan_info[kPiStages];
@@ -216,7 +227,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.enable_pdl = enable_pdl;
 
   const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
-                                page_size, false, 0);
+                                page_size, false, 0, TT);
   if (!tma && tuning().loader == 1)
     return fail(FI_ERR_UNSUPPORTED, "TMA loader forced but page geometry is not eligible");
   CUtensorMap km, vm;
@@ -285,7 +296,8 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   const KernelConfig cfg = choose_config(kvf, head_dim);
 
   const int tok_lo = window_left >= 0 ? (kv_len - 1 - window_left > 0 ? kv_len - 1 - window_left : 0) : 0;
-  const int tiles = kv_len == 0 ? 0 : (kv_len + kTileTokens - 1) / kTileTokens - tok_lo / kTileTokens;
+  const int TT = tile_tokens(kvf);
+  const int tiles = kv_len == 0 ? 0 : (kv_len + TT - 1) / TT - tok_lo / TT;
   const long long T = (long long)tiles * num_kv_heads;
   const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
   long long grid = T / min_tiles;
@@ -306,7 +318,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.kv_stride_page = 0;
   p.page_size = kv_len > 0 ? kv_len : 1;
   p.page_shift = 31; p.page_mask = 0x7fffffff;
-  p.rows_per_box = kTileTokens;
+  p.rows_per_box = TT;
   p.tma_h_first = p.kv_stride_h < p.kv_stride_n;
   p.header = nullptr;
   p.imp_units = num_kv_heads; p.imp_tiles = tiles; p.imp_tok_lo = tok_lo; p.imp_tok_hi = kv_len;
@@ -317,15 +329,15 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.sm_scale = sm_scale; p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
   p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0;
 
-  const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len);
+  const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
   CUtensorMap km, vm;
   memset(&km, 0, sizeof(km));
   memset(&vm, 0, sizeof(vm));
   if (tma) {
     const int64_t sp = (int64_t)kv_len * num_kv_heads * head_dim;  // single "page"
-    rc = make_kv_map(&km, k, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, kTileTokens);
+    rc = make_kv_map(&km, k, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, TT);
     if (rc != FI_OK) return rc;
-    rc = make_kv_map(&vm, v, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, kTileTokens);
+    rc = make_kv_map(&vm, v, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, TT);
     if (rc != FI_OK) return rc;
   }
   rc = launch_decode(p, km, vm, q_dtype, kvf, head_dim, (int)grid, tma, stream);

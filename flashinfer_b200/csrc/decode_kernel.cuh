@@ -26,13 +26,19 @@
 
 namespace fib200 {
 
+// cp.async gather loader: 2 producer warps keep the CTA at 192 threads so that two CTAs per SM
+// fit the register file next to the 4 consumer warps
+constexpr int kCpAsyncProducerThreads = 64;
+
 template <int KVF, int HD>
 struct TileGeom {
   static constexpr int ES = (KVF == 0) ? 2 : 1;          // bytes per KV element
+  static constexpr int TT = tile_tokens(KVF);            // tokens per stage
+  static constexpr int TPW = TT / kConsumerWarps;        // tokens per consumer warp per stage
   static constexpr int ROW_BYTES = HD * ES;              // one token row of K (or V)
   static constexpr int NP = ROW_BYTES / 128;             // 128-byte swizzle panels per row
   static constexpr int CHUNKS = ROW_BYTES / 16;          // 16-byte chunks per row
-  static constexpr int PANEL_BYTES = kTileTokens * 128;  // 8 KiB
+  static constexpr int PANEL_BYTES = TT * 128;           // 8 / 16 KiB
   static constexpr int KV_BYTES = NP * PANEL_BYTES;      // K part of one stage
   static constexpr int STAGE_BYTES = 2 * KV_BYTES;       // K + V
   static constexpr int KSTEPS = HD / 16;                 // mma k-steps for QK == m-tiles for PV
@@ -44,7 +50,7 @@ template <int KVF, int HD>
 struct SmemLayout {
   using G = TileGeom<KVF, HD>;
   static constexpr int SCRATCH_O = (kConsumerWarps - 1) * G::KSTEPS * 4 * 32 * 4;
-  static constexpr int SCRATCH_ML = kConsumerWarps * kMaxGroup * 2 * 4;
+  static constexpr int SCRATCH_ML = kConsumerWarps * kMaxGroup * 2 * 4 + 16;  // + merge flag
   static constexpr int SEG_BYTES = kSegCache * (int)sizeof(Segment);
   static constexpr int BAR_BYTES = 2 * kMaxStages * 8;
   __host__ __device__ static constexpr int ring(int stages) { return stages * G::STAGE_BYTES; }
@@ -54,8 +60,9 @@ struct SmemLayout {
 };
 
 // byte offset of (row, 16B-chunk) inside the K (or V) part of a stage, 128B swizzle
+template <int TT>
 __device__ __forceinline__ uint32_t swz(int row, int chunk) {
-  return (uint32_t)((chunk >> 3) * (kTileTokens * 128) + row * 128 +
+  return (uint32_t)((chunk >> 3) * (TT * 128) + row * 128 +
                     (((chunk & 7) ^ (row & 7)) << 4));
 }
 
@@ -65,11 +72,13 @@ struct SegSource {
   int first;  // explicit: index of this CTA's first segment
   int count;
   long long imp_begin, imp_end;  // implicit: stream range of this CTA
+  int tt;                        // tokens per tile
 };
 
-__device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p) {
+__device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int tt) {
   SegSource s;
   s.p = &p;
+  s.tt = tt;
   s.first = 0;
   s.count = 0;
   s.imp_begin = s.imp_end = 0;
@@ -100,15 +109,15 @@ __device__ __forceinline__ Segment seg_make(const SegSource& s, int k) {
     const int4* src = reinterpret_cast<const int4*>(p.segments + s.first + k);
     int4 a = __ldg(src), b = __ldg(src + 1);
     g.request = a.x; g.kv_head = a.y; g.tile_begin = a.z; g.tile_end = a.w;
-    g.slot = b.x; g.tok_lo = b.y; g.tok_hi = b.z; g.pad = 0;
+    g.slot = b.x; g.tok_lo = b.y; g.tok_hi = b.z; g.merge_unit = b.w;
   } else {
-    g.request = 0; g.pad = 0;
+    g.request = 0; g.merge_unit = -1;
     g.tok_lo = p.imp_tok_lo; g.tok_hi = p.imp_tok_hi;
     const int nt = p.imp_tiles;
     if (nt == 0) {
       g.kv_head = k; g.tile_begin = g.tile_end = 0; g.slot = -1;
     } else {
-      const int tb0 = p.imp_tok_lo / kTileTokens;  // first tile of the window
+      const int tb0 = p.imp_tok_lo / s.tt;  // first tile of the window
       const long long u = s.imp_begin / nt + k;
       const long long ub = u * nt, ue = ub + nt;
       const long long b = s.imp_begin > ub ? s.imp_begin : ub;
@@ -139,7 +148,7 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   using G = TileGeom<KVF, HD>;
   const int lane = threadIdx.x & 31;
   const int rpb = p.rows_per_box;
-  const int bpt = kTileTokens / rpb;  // boxes per tile along tokens: 1, 2, 4 or 8
+  const int bpt = G::TT / rpb;  // boxes per tile along tokens: a power of two <= 16
   const int nbox = 2 * G::NP * bpt;
   const int j = lane % bpt;  // same j for every i = lane + 32 k since bpt | 32
   const uint32_t box_bytes = (uint32_t)rpb * 128u;
@@ -149,9 +158,9 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
     const Segment sg = seg_get(src, seg_cache, k);
     const int page_base = p.kv_indptr ? __ldg(p.kv_indptr + sg.request) : 0;
     for (int t = sg.tile_begin; t < sg.tile_end; ++t) {
-      const int tok0 = t * kTileTokens;
+      const int tok0 = t * G::TT;
       const int rem = sg.tok_hi - tok0;  // > 0 by construction
-      const int nvb = rem >= kTileTokens ? bpt : (rem + rpb - 1) / rpb;
+      const int nvb = rem >= G::TT ? bpt : (rem + rpb - 1) / rpb;
       const int tok = tok0 + j * rpb;
       int page = 0;
       if (j < nvb) {
@@ -179,7 +188,7 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
 }
 
 // ---- producer: 16-byte cp.async gathers (any page size / stride) -------------
-// Runs in 4 warps (128 threads, ptid = 0..127).  Rows past tok_hi are zero-filled.
+// Runs in kCpAsyncProducerThreads threads (ptid = 0 ..).  Rows past tok_hi are zero-filled.
 template <int KVF, int HD>
 __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const SegSource& src,
                                                 const Segment* seg_cache, int ptid,
@@ -187,9 +196,9 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
                                                 uint32_t empty_bar) {
   using G = TileGeom<KVF, HD>;
   constexpr int CPR = G::CHUNKS;
-  constexpr int RPP = 128 / CPR;             // rows per pass
-  constexpr int PASSES = kTileTokens / RPP;
-  static_assert(128 % CPR == 0 && kTileTokens % RPP == 0, "bad cp.async geometry");
+  constexpr int RPP = kCpAsyncProducerThreads / CPR;  // rows per pass
+  constexpr int PASSES = G::TT / RPP;
+  static_assert(kCpAsyncProducerThreads % CPR == 0 && G::TT % RPP == 0, "bad cp.async geometry");
   const int c = ptid % CPR;
   const int r0 = ptid / CPR;
   const char* kb = static_cast<const char*>(p.k);
@@ -206,7 +215,7 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
 #pragma unroll 4
       for (int ps = 0; ps < PASSES; ++ps) {
         const int row = ps * RPP + r0;
-        const int tok = t * kTileTokens + row;
+        const int tok = t * G::TT + row;
         const bool valid = tok < sg.tok_hi;
         int64_t off = 0;
         if (valid) {
@@ -217,7 +226,7 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
           off = ((int64_t)page * p.kv_stride_page + (int64_t)rip * p.kv_stride_n + head_off) *
                 G::ES;
         }
-        const uint32_t d = sk + swz(row, c);
+        const uint32_t d = sk + swz<G::TT>(row, c);
         cp_async_16(d, kb + off, valid ? 16u : 0u);
         cp_async_16(d + G::KV_BYTES, vb + off, valid ? 16u : 0u);
       }
@@ -227,136 +236,162 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
   }
 }
 
-// ---- consumer helpers ---------------------------------------------------------
-// Query fragments (B operand of S^T = K Q^T): lane (g = lane/4, t = lane%4) holds head g.
-//   16-bit KV: k-step ks covers d in [16ks, 16ks+16): b0 = q[16ks+2t..+1], b1 = q[16ks+8+2t..+1]
-//   fp8 KV   : k-step c  covers d in [16c, 16c+16) with the k-slots permuted to match the
-//              4-byte fp8 groups ldmatrix hands out: b0 = q[16c+4t..+1], b1 = q[16c+4t+2..+3]
-template <int QT, int KVF, int HD>
-__device__ __forceinline__ void load_q_frags(uint32_t (&qf)[HD / 16][2], const void* qrow,
-                                             bool head_valid, int t) {
+// ---- consumer helpers: 16-bit KV ----------------------------------------------
+// Query fragments (B operand of S^T = K Q^T): lane (g = lane/4, t = lane%4) holds head g;
+// k-step ks covers d in [16ks, 16ks+16): b0 = q[16ks+2t..+1], b1 = q[16ks+8+2t..+1].
+template <int HD>
+__device__ __forceinline__ void load_q_frags16(uint32_t (&qf)[HD / 16][2], const void* qrow,
+                                               bool head_valid, int t) {
   constexpr int KS = HD / 16;
   if (!head_valid) {
 #pragma unroll
     for (int i = 0; i < KS; ++i) qf[i][0] = qf[i][1] = 0u;
     return;
   }
-  if constexpr (KVF == 0) {
-    const uint32_t* q32 = static_cast<const uint32_t*>(qrow);
+  const uint32_t* q32 = static_cast<const uint32_t*>(qrow);
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      qf[ks][0] = __ldg(q32 + 8 * ks + t);
-      qf[ks][1] = __ldg(q32 + 8 * ks + 4 + t);
-    }
-  } else {
-    const uint2* q64 = static_cast<const uint2*>(qrow);
-#pragma unroll
-    for (int c = 0; c < KS; ++c) {
-      uint2 v = __ldg(q64 + 4 * c + t);  // q[16c + 4t .. 16c + 4t + 3]
-      if constexpr (QT == 1) {           // bf16 -> f16 (MMA runs in f16 for fp8 KV)
-        float a = __uint_as_float(v.x << 16), b = __uint_as_float(v.x & 0xffff0000u);
-        float cc = __uint_as_float(v.y << 16), d = __uint_as_float(v.y & 0xffff0000u);
-        v.x = pack2<false>(a, b);
-        v.y = pack2<false>(cc, d);
-      }
-      qf[c][0] = v.x;
-      qf[c][1] = v.y;
-    }
+  for (int ks = 0; ks < KS; ++ks) {
+    qf[ks][0] = __ldg(q32 + 8 * ks + t);
+    qf[ks][1] = __ldg(q32 + 8 * ks + 4 + t);
   }
 }
 
-// per-lane row/chunk offsets of the ldmatrix.x4 address patterns
-//   K (non-trans) and fp8 V : row = (lane&7) + 8*((lane>>3)&1), chunk += lane>>4
-//   16-bit V (trans)         : row = (lane&7) + 8*(lane>>4),     chunk += (lane>>3)&1
-struct LaneAddr {
-  int krow, kch;  // K pattern
-  int vrow, vch;  // V pattern
-};
-template <int KVF>
-__device__ __forceinline__ LaneAddr lane_addr(int warp, int lane) {
-  LaneAddr a;
-  a.krow = warp * 16 + (lane & 7) + 8 * ((lane >> 3) & 1);
-  a.kch = lane >> 4;
-  if constexpr (KVF == 0) {
-    a.vrow = warp * 16 + (lane & 7) + 8 * (lane >> 4);
-    a.vch = (lane >> 3) & 1;
-  } else {
-    a.vrow = a.krow;
-    a.vch = a.kch;
-  }
-  return a;
-}
-
-// S^T(16 tokens x 8 heads) for this warp's token slice
-template <int QT, int KVF, int HD>
-__device__ __forceinline__ void qk_tile(float (&s)[4], uint32_t kbase, const LaneAddr& la,
-                                        const uint32_t (&qf)[HD / 16][2]) {
-  constexpr bool BF = (QT == 1 && KVF == 0);
+// S^T(16 tokens x 8 heads) for this warp's token slice (rows row0 .. row0+15 of the stage)
+template <int QT, int HD>
+__device__ __forceinline__ void qk_tile16(float (&s)[4], uint32_t kbase, int row0, int lane,
+                                          const uint32_t (&qf)[HD / 16][2]) {
+  constexpr bool BF = (QT == 1);
   constexpr int KS = HD / 16;
+  // ldmatrix.x4 address pattern: row = (lane&7) + 8*((lane>>3)&1), chunk += lane>>4
+  const int krow = row0 + (lane & 7) + 8 * ((lane >> 3) & 1), kch = lane >> 4;
   float s1[4] = {0.f, 0.f, 0.f, 0.f};
   s[0] = s[1] = s[2] = s[3] = 0.f;
-  if constexpr (KVF == 0) {
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      uint32_t a[4];
-      ldmatrix_x4(a, kbase + swz(la.krow, 2 * ks + la.kch));
-      if (ks & 1) mma_16816<BF>(s1, a, qf[ks][0], qf[ks][1]);
-      else mma_16816<BF>(s, a, qf[ks][0], qf[ks][1]);
-    }
-  } else {
-#pragma unroll
-    for (int kp = 0; kp < KS / 2; ++kp) {
-      uint32_t r[4];
-      ldmatrix_x4(r, kbase + swz(la.krow, 2 * kp + la.kch));
-      uint32_t a[4], b[4];
-      a[0] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[0] & 0xffffu));
-      a[1] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[1] & 0xffffu));
-      a[2] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[0] >> 16));
-      a[3] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[1] >> 16));
-      b[0] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[2] & 0xffffu));
-      b[1] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[3] & 0xffffu));
-      b[2] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[2] >> 16));
-      b[3] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(r[3] >> 16));
-      mma_16816<false>(s, a, qf[2 * kp][0], qf[2 * kp][1]);
-      mma_16816<false>(s1, b, qf[2 * kp + 1][0], qf[2 * kp + 1][1]);
-    }
+  for (int ks = 0; ks < KS; ++ks) {
+    uint32_t a[4];
+    ldmatrix_x4(a, kbase + swz<64>(krow, 2 * ks + kch));
+    if (ks & 1) mma_16816<BF>(s1, a, qf[ks][0], qf[ks][1]);
+    else mma_16816<BF>(s, a, qf[ks][0], qf[ks][1]);
   }
 #pragma unroll
   for (int i = 0; i < 4; ++i) s[i] += s1[i];
 }
 
 // O^T(HD x 8 heads) += V^T . P^T for this warp's 16 tokens; (pb0, pb1) = B fragments of P^T
-template <int QT, int KVF, int HD>
-__device__ __forceinline__ void pv_tile(float (&o)[HD / 16][4], uint32_t vbase,
-                                        const LaneAddr& la, uint32_t pb0, uint32_t pb1) {
-  constexpr bool BF = (QT == 1 && KVF == 0);
-  constexpr int MT = HD / 16;
-  if constexpr (KVF == 0) {
+template <int QT, int HD>
+__device__ __forceinline__ void pv_tile16(float (&o)[HD / 16][4], uint32_t vbase, int row0,
+                                          int lane, uint32_t pb0, uint32_t pb1) {
+  constexpr bool BF = (QT == 1);
+  // ldmatrix.x4.trans pattern: row = (lane&7) + 8*(lane>>4), chunk += (lane>>3)&1
+  const int vrow = row0 + (lane & 7) + 8 * (lane >> 4), vch = (lane >> 3) & 1;
 #pragma unroll
-    for (int mt = 0; mt < MT; ++mt) {
-      uint32_t a[4];
-      ldmatrix_x4_trans(a, vbase + swz(la.vrow, 2 * mt + la.vch));
-      mma_16816<BF>(o[mt], a, pb0, pb1);
-    }
-  } else {
+  for (int mt = 0; mt < HD / 16; ++mt) {
+    uint32_t a[4];
+    ldmatrix_x4_trans(a, vbase + swz<64>(vrow, 2 * mt + vch));
+    mma_16816<BF>(o[mt], a, pb0, pb1);
+  }
+}
+
+// ---- consumer helpers: fp8 KV (native fp8 MMA, no dequantisation) ---------------
+// K and V bytes feed mma.m16n8k32 directly as the A operand; the 16-bit query (and later
+// the probabilities) are split into an e4m3 "hi" part and an e4m3 residual "lo" part and
+// each product is two MMAs into the same accumulator (~8 significant bits, like bf16).
+// Query fragments: lane (g, t) holds head g; k-block c covers d in [32c, 32c+32):
+//   b0 = q[32c+4t .. +3], b1 = q[32c+16+4t .. +3] (4 e4m3 bytes each).
+// The query row is scaled so that its amax maps to 256; `dq` is the inverse scale.
+template <int QT, int HD>
+__device__ __forceinline__ void load_q_frags8(uint32_t (&qhi)[HD / 32][2],
+                                              uint32_t (&qlo)[HD / 32][2],
+                                              uint32_t (&ql2)[HD / 32][2], float& dq,
+                                              const void* qrow, bool head_valid, int t) {
+  constexpr int KB = HD / 32;
+  float x[KB][2][4];
+  float amax = 0.f;
+  const uint2* q64 = static_cast<const uint2*>(qrow);
 #pragma unroll
-    for (int mp = 0; mp < MT / 2; ++mp) {
-      uint32_t r[4];
-      ldmatrix_x4_trans(r, vbase + swz(la.vrow, 2 * mp + la.vch));
+  for (int c = 0; c < KB; ++c)
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        // r[2h]: tokens 0-7, r[2h+1]: tokens 8-15 of chunk 2mp+h; bytes
-        // [tok 2t:d 2g, d 2g+1 | tok 2t+1: d 2g, d 2g+1] -> group by d
-        const uint32_t x = prmt(r[2 * h], 0u, 0x3120u);
-        const uint32_t y = prmt(r[2 * h + 1], 0u, 0x3120u);
-        uint32_t a[4];
-        a[0] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(x & 0xffffu));  // row g   <-> d = 2g
-        a[1] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(x >> 16));      // row g+8 <-> d = 2g+1
-        a[2] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(y & 0xffffu));
-        a[3] = fp8x2_to_f16x2<KVF == 2>((uint16_t)(y >> 16));
-        mma_16816<false>(o[2 * mp + h], a, pb0, pb1);
+    for (int h = 0; h < 2; ++h) {
+      uint2 v = make_uint2(0u, 0u);
+      if (head_valid) v = __ldg(q64 + 8 * c + 4 * h + t);
+      if constexpr (QT == 1) {
+        x[c][h][0] = __uint_as_float(v.x << 16); x[c][h][1] = __uint_as_float(v.x & 0xffff0000u);
+        x[c][h][2] = __uint_as_float(v.y << 16); x[c][h][3] = __uint_as_float(v.y & 0xffff0000u);
+      } else {
+        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+        const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+        x[c][h][0] = a.x; x[c][h][1] = a.y; x[c][h][2] = b.x; x[c][h][3] = b.y;
       }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) amax = fmaxf(amax, fabsf(x[c][h][i]));
     }
+  amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+  amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+  const bool nz = amax > 0.f && amax < 3.0e38f;
+  const float sq = nz ? 256.f / amax : 1.f;
+  dq = nz ? amax * (1.f / 256.f) : 1.f;
+#pragma unroll
+  for (int c = 0; c < KB; ++c)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      // three e4m3 terms (~12 significant bits): the base-2 LSE must hold to 1e-3
+      uint32_t t01[3], t23[3];
+      split3_e4m3x2(t01, x[c][h][0] * sq, x[c][h][1] * sq);
+      split3_e4m3x2(t23, x[c][h][2] * sq, x[c][h][3] * sq);
+      qhi[c][h] = t01[0] | (t23[0] << 16);
+      qlo[c][h] = t01[1] | (t23[1] << 16);
+      ql2[c][h] = t01[2] | (t23[2] << 16);
+    }
+}
+
+// S^T for this warp's 32 tokens (two 16-token M tiles) at stage rows row0 .. row0+31
+template <int KVF, int HD>
+__device__ __forceinline__ void qk_tile8(float (&s)[2][4], uint32_t kbase, int row0, int lane,
+                                         const uint32_t (&qhi)[HD / 32][2],
+                                         const uint32_t (&qlo)[HD / 32][2],
+                                         const uint32_t (&ql2)[HD / 32][2]) {
+  constexpr int KB = HD / 32;
+  const int krow = row0 + (lane & 7) + 8 * ((lane >> 3) & 1), kch = lane >> 4;
+  float s2[2][4];
+#pragma unroll
+  for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s[mb][i] = s2[mb][i] = 0.f;
+#pragma unroll
+  for (int c = 0; c < KB; ++c)
+#pragma unroll
+    for (int mb = 0; mb < 2; ++mb) {
+      uint32_t a[4];
+      ldmatrix_x4(a, kbase + swz<128>(krow + 16 * mb, 2 * c + kch));
+      mma_16832_fp8<KVF == 2>(s[mb], a, qhi[c][0], qhi[c][1]);
+      mma_16832_fp8<KVF == 2>(s2[mb], a, qlo[c][0], qlo[c][1]);
+      mma_16832_fp8<KVF == 2>(s2[mb], a, ql2[c][0], ql2[c][1]);
+    }
+#pragma unroll
+  for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s[mb][i] += s2[mb][i];
+}
+
+// O^T += V^T . P^T over this warp's 32 tokens.  ldmatrix.trans hands out byte pairs
+// [tok 2t: d 2g, d 2g+1 | tok 2t+1: d 2g, d 2g+1] per 8-token group; prmt regroups them by d so
+// that MMA row g <-> d = 16c + 2g, row g+8 <-> d = 16c + 2g + 1 and the k slots 4t..4t+3 of
+// each half <-> tokens {2t, 2t+1, 8+2t, 9+2t} (+16).  bh/bl: hi / lo B fragments of P^T in the
+// same token order.
+template <int KVF, int HD>
+__device__ __forceinline__ void pv_tile8(float (&o)[HD / 16][4], uint32_t vbase, int row0, int lane,
+                                         const uint32_t (&bh)[2], const uint32_t (&bl)[2]) {
+  const int vrow = row0 + lane;  // matrix j = lane>>3 covers tokens 8j .. 8j+7
+#pragma unroll
+  for (int c = 0; c < HD / 16; ++c) {
+    uint32_t r[4], a[4];
+    ldmatrix_x4_trans(r, vbase + swz<128>(vrow, c));
+    a[0] = prmt(r[0], r[1], 0x6420u);
+    a[1] = prmt(r[0], r[1], 0x7531u);
+    a[2] = prmt(r[2], r[3], 0x6420u);
+    a[3] = prmt(r[2], r[3], 0x7531u);
+    mma_16832_fp8<KVF == 2>(o[c], a, bh[0], bh[1]);
+    mma_16832_fp8<KVF == 2>(o[c], a, bl[0], bl[1]);
   }
 }
 
@@ -367,99 +402,240 @@ __device__ __forceinline__ int o_dim(int mt, int hi, int g) {
   else return 16 * mt + 2 * g + hi;
 }
 
+// ---- fused split-KV merge ---------------------------------------------------------
+// Run by ONE warp of the CTA whose partial arrived last at a split unit: combines the unit's
+// `count` normalised f32 partials (written by this and other CTAs, hence .cg loads) into the
+// final o / lse.  Same operator as the reference's merge (cascade.cuh:366-467, state.cuh:53-62).
+__device__ __forceinline__ float ldcg_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float4 ldcg_f32x4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+// ctid: 0 .. 127 (the four consumer warps).  One item = (head, 4 dims); loads are issued in
+// batches of four independent .cg reads so that the unit costs ~two L2 round trips.
+template <int QT, int HD>
+__device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int request, int kv_head,
+                                               int slot_begin, int count, int ctid) {
+  const int GS = p.group_size;
+  constexpr int CPH = HD / 4;  // float4 chunks per head row
+  for (int item = ctid; item < GS * CPH; item += kConsumerWarps * 32) {
+    const int h = item / CPH, c = item - h * CPH;
+    const float* lse = p.tmp_lse + (int64_t)slot_begin * GS + h;
+    const float* row = p.tmp_o + ((int64_t)slot_begin * GS + h) * HD + 4 * c;
+    float mx = kNegInf;
+    for (int k0 = 0; k0 < count; k0 += 4) {
+      float s4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) s4[j] = k0 + j < count ? __ldcg(lse + (int64_t)(k0 + j) * GS) : kNegInf;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mx = fmaxf(mx, s4[j]);
+    }
+    float d = 0.f;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k0 = 0; k0 < count; k0 += 4) {
+      float s4[4];
+      float4 x4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const bool ok = k0 + j < count;
+        s4[j] = ok ? __ldcg(lse + (int64_t)(k0 + j) * GS) : kNegInf;
+        x4[j] = ok ? __ldcg(reinterpret_cast<const float4*>(row + (int64_t)(k0 + j) * GS * HD))
+                   : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float w = k0 + j < count ? ex2f(s4[j] - mx) : 0.f;
+        d += w;
+        acc.x += w * x4[j].x; acc.y += w * x4[j].y; acc.z += w * x4[j].z; acc.w += w * x4[j].w;
+      }
+    }
+    const int64_t hq = (int64_t)request * p.num_qo_heads + kv_head * GS + h;
+    const float inv = p.v_scale / d;
+    uint2 u;
+    u.x = pack2<QT == 1>(acc.x * inv, acc.y * inv);
+    u.y = pack2<QT == 1>(acc.z * inv, acc.w * inv);
+    *reinterpret_cast<uint2*>(static_cast<uint16_t*>(p.o) + hq * HD + 4 * c) = u;
+    // all partials empty: weights are 1 and o stays 0; clamp lse to the sentinel
+    if (c == 0 && p.lse != nullptr) p.lse[hq] = mx > kNegInf ? mx + lg2f(d) : kNegInf;
+  }
+}
+
 // ---- consumer: 4 warps, online softmax + MMA ---------------------------------
+// Per-warp running state per query head j (two heads per lane: 2t, 2t+1):
+//   m[j]  reference exponent of o / l (16-bit KV: the running max; fp8 KV: max(block max,
+//         running max - 20), so that probabilities quantised to e4m3 are scaled by their own
+//         32-token block's maximum and nothing within 2^-18 of it is flushed),
+//   l[j]  sum of exp2(x - m[j]),  o[..] = sum of exp2(x - m[j]) v  (x 256 for fp8 KV).
 template <int QT, int KVF, int HD, int LOADER>
 __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& src,
                                         const Segment* seg_cache, uint32_t ring,
                                         uint32_t full_bar, uint32_t empty_bar, float* scratch_o,
                                         float* scratch_ml) {
   using G = TileGeom<KVF, HD>;
-  constexpr bool BF = (QT == 1 && KVF == 0);  // operand type of P
+  constexpr bool BF = (QT == 1);  // operand type of P (16-bit KV path)
   constexpr int MT = HD / 16;
+  constexpr int TPW = G::TPW;
+  constexpr int NQ = (KVF == 0) ? HD / 16 : HD / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t = lane & 3;
-  const LaneAddr la = lane_addr<KVF>(warp, lane);
   const int GS = p.group_size;
   const bool use_cap = p.soft_cap > 0.f;
   const float cap_pre = use_cap ? p.sm_scale / p.soft_cap : 0.f;
   const float cap_post = use_cap ? p.soft_cap * 1.4426950408889634f : 0.f;
+  const int row0 = warp * TPW;
 
   int stage = 0;
   uint32_t phase = 0;
   for (int k = 0; k < src.count; ++k) {
     const Segment sg = seg_get(src, seg_cache, k);
-    uint32_t qf[MT][2];
+    uint32_t qf[NQ][2];
+    uint32_t ql[KVF == 0 ? 1 : NQ][2], ql2[KVF == 0 ? 1 : NQ][2];  // fp8: residual query terms
+    float mul[2], pre[2];               // logit scale per head column (2t, 2t+1)
     {
       const char* qrow = static_cast<const char*>(p.q) +
                          ((int64_t)sg.request * p.q_stride_n +
                           (int64_t)(sg.kv_head * GS + g) * p.q_stride_h) * 2;
-      load_q_frags<QT, KVF, HD>(qf, qrow, g < GS, t);
+      if constexpr (KVF == 0) {
+        load_q_frags16<HD>(qf, qrow, g < GS, t);
+        ql[0][0] = ql[0][1] = ql2[0][0] = ql2[0][1] = 0u;
+        mul[0] = mul[1] = p.sm_scale_log2;
+        pre[0] = pre[1] = cap_pre;
+      } else {
+        float dq;
+        load_q_frags8<QT, HD>(qf, ql, ql2, dq, qrow, g < GS, t);
+        const float d0 = __shfl_sync(0xffffffffu, dq, 8 * t);      // head 2t lives in lanes 8t..8t+3
+        const float d1 = __shfl_sync(0xffffffffu, dq, 8 * t + 4);  // head 2t+1
+        mul[0] = d0 * p.sm_scale_log2; mul[1] = d1 * p.sm_scale_log2;
+        pre[0] = d0 * cap_pre; pre[1] = d1 * cap_pre;
+      }
     }
     float o[MT][4];
 #pragma unroll
     for (int i = 0; i < MT; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
     float m[2] = {kNegInf, kNegInf}, l[2] = {0.f, 0.f};
+    float mrun[2] = {kNegInf, kNegInf};  // fp8 only: true running max
 
     for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
       mbar_wait(full_bar + 8 * stage, phase);
-      const int tok0 = tile * kTileTokens + warp * 16;
-      const int vcount = min(16, sg.tok_hi - tok0);
-      if (vcount > 0 && tok0 + 16 > sg.tok_lo) {  // warp-uniform
+      const int tok0 = tile * G::TT + row0;
+      const int vcount = min(TPW, sg.tok_hi - tok0);
+      if (vcount > 0 && tok0 + TPW > sg.tok_lo) {  // warp-uniform
         const uint32_t kbase = ring + stage * G::STAGE_BYTES;
         const uint32_t vbase = kbase + G::KV_BYTES;
         if constexpr (LOADER == 0) {
-          if (vcount < 16) {  // rows the TMA did not (validly) fill: zero V so 0 * junk != NaN
-            for (int i = lane; i < (16 - vcount) * G::CHUNKS; i += 32) {
-              const int row = warp * 16 + vcount + i / G::CHUNKS;
-              const uint32_t a = vbase + swz(row, i % G::CHUNKS);
+          if (vcount < TPW) {  // rows the TMA did not (validly) fill: zero V so 0 * junk != NaN
+            for (int i = lane; i < (TPW - vcount) * G::CHUNKS; i += 32) {
+              const int row = row0 + vcount + i / G::CHUNKS;
+              const uint32_t a = vbase + swz<G::TT>(row, i % G::CHUNKS);
               asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(a), "r"(0u) : "memory");
             }
             __syncwarp();
           }
         }
-        float s[4];
-        qk_tile<QT, KVF, HD>(s, kbase, la, qf);
-        // s[0],s[1]: token g, heads 2t,2t+1;  s[2],s[3]: token g+8
-        const int ta = tok0 + g, tb = ta + 8;
-        const bool va = ta >= sg.tok_lo && ta < sg.tok_hi;
-        const bool vb = tb >= sg.tok_lo && tb < sg.tok_hi;
-        float x[4];
+        if constexpr (KVF == 0) {
+          float s[4];
+          qk_tile16<QT, HD>(s, kbase, row0, lane, qf);
+          // s[0],s[1]: token g, heads 2t,2t+1;  s[2],s[3]: token g+8
+          const int ta = tok0 + g, tb = ta + 8;
+          const bool va = ta >= sg.tok_lo && ta < sg.tok_hi;
+          const bool vb = tb >= sg.tok_lo && tb < sg.tok_hi;
+          float x[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          x[i] = use_cap ? cap_post * tanhf_approx(s[i] * cap_pre) : s[i] * p.sm_scale_log2;
-        }
-        x[0] = va ? x[0] : kNegInf; x[1] = va ? x[1] : kNegInf;
-        x[2] = vb ? x[2] : kNegInf; x[3] = vb ? x[3] : kNegInf;
-        float mx[2] = {fmaxf(x[0], x[2]), fmaxf(x[1], x[3])};
+          for (int i = 0; i < 4; ++i)
+            x[i] = use_cap ? cap_post * tanhf_approx(s[i] * pre[i & 1]) : s[i] * mul[i & 1];
+          x[0] = va ? x[0] : kNegInf; x[1] = va ? x[1] : kNegInf;
+          x[2] = vb ? x[2] : kNegInf; x[3] = vb ? x[3] : kNegInf;
+          float mx[2] = {fmaxf(x[0], x[2]), fmaxf(x[1], x[3])};
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 4));
-          mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 8));
-          mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 16));
-        }
-        float sc[2];
+          for (int j = 0; j < 2; ++j) {
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 4));
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 8));
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 16));
+          }
+          float sc[2];
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const float mn = fmaxf(m[j], mx[j]);
-          sc[j] = ex2f(m[j] - mn);
-          m[j] = mn;
-        }
-        float pr[4];
-        pr[0] = va ? ex2f(x[0] - m[0]) : 0.f;
-        pr[1] = va ? ex2f(x[1] - m[1]) : 0.f;
-        pr[2] = vb ? ex2f(x[2] - m[0]) : 0.f;
-        pr[3] = vb ? ex2f(x[3] - m[1]) : 0.f;
-        l[0] = l[0] * sc[0] + pr[0] + pr[2];
-        l[1] = l[1] * sc[1] + pr[1] + pr[3];
+          for (int j = 0; j < 2; ++j) {
+            const float mn = fmaxf(m[j], mx[j]);
+            sc[j] = ex2f(m[j] - mn);
+            m[j] = mn;
+          }
+          float pr[4];
+          pr[0] = va ? ex2f(x[0] - m[0]) : 0.f;
+          pr[1] = va ? ex2f(x[1] - m[1]) : 0.f;
+          pr[2] = vb ? ex2f(x[2] - m[0]) : 0.f;
+          pr[3] = vb ? ex2f(x[3] - m[1]) : 0.f;
+          l[0] = l[0] * sc[0] + pr[0] + pr[2];
+          l[1] = l[1] * sc[1] + pr[1] + pr[3];
 #pragma unroll
-        for (int i = 0; i < MT; ++i) {
-          o[i][0] *= sc[0]; o[i][1] *= sc[1]; o[i][2] *= sc[0]; o[i][3] *= sc[1];
+          for (int i = 0; i < MT; ++i) {
+            o[i][0] *= sc[0]; o[i][1] *= sc[1]; o[i][2] *= sc[0]; o[i][3] *= sc[1];
+          }
+          const uint32_t pb0 = movmatrix_trans(pack2<BF>(pr[0], pr[1]));
+          const uint32_t pb1 = movmatrix_trans(pack2<BF>(pr[2], pr[3]));
+          pv_tile16<QT, HD>(o, vbase, row0, lane, pb0, pb1);
+        } else {
+          float s[2][4];
+          qk_tile8<KVF, HD>(s, kbase, row0, lane, qf, ql, ql2);
+          // s[mb][0..1]: token 16mb+g, heads 2t,2t+1;  s[mb][2..3]: token 16mb+g+8
+          bool valid[2][2];
+          float mx[2] = {kNegInf, kNegInf};
+#pragma unroll
+          for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int tk = tok0 + 16 * mb + 8 * h + g;
+              valid[mb][h] = tk >= sg.tok_lo && tk < sg.tok_hi;
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                float& x = s[mb][2 * h + j];
+                x = use_cap ? cap_post * tanhf_approx(x * pre[j]) : x * mul[j];
+                x = valid[mb][h] ? x : kNegInf;
+                mx[j] = fmaxf(mx[j], x);
+              }
+            }
+          float sc[2];
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 4));
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 8));
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 16));
+            mrun[j] = fmaxf(mrun[j], mx[j]);
+            const float mn = fmaxf(mx[j], mrun[j] - 20.f);
+            sc[j] = ex2f(m[j] - mn);  // <= 2^20
+            m[j] = mn;
+          }
+          uint32_t tq[4];  // tq[2mb+h]: transposed (hi, lo) byte pairs of token group 8(2mb+h)..+7
+          float ls[2] = {0.f, 0.f};
+#pragma unroll
+          for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const float p0 = valid[mb][h] ? ex2f(s[mb][2 * h] - m[0]) : 0.f;
+              const float p1 = valid[mb][h] ? ex2f(s[mb][2 * h + 1] - m[1]) : 0.f;
+              ls[0] += p0; ls[1] += p1;
+              // [hi(h0), hi(h1), lo(h0), lo(h1)] -> [hi(h0), lo(h0), hi(h1), lo(h1)]
+              const uint32_t w = prmt(split_e4m3x2(p0 * 256.f, p1 * 256.f), 0u, 0x3120u);
+              tq[2 * mb + h] = movmatrix_trans(w);
+            }
+          l[0] = l[0] * sc[0] + ls[0];
+          l[1] = l[1] * sc[1] + ls[1];
+#pragma unroll
+          for (int i = 0; i < MT; ++i) {
+            o[i][0] *= sc[0]; o[i][1] *= sc[1]; o[i][2] *= sc[0]; o[i][3] *= sc[1];
+          }
+          // after the transpose lane (g, t) holds, for head g, [tok 2t: hi, lo | tok 2t+1: hi, lo]
+          const uint32_t bh[2] = {prmt(tq[0], tq[1], 0x6420u), prmt(tq[2], tq[3], 0x6420u)};
+          const uint32_t bl[2] = {prmt(tq[0], tq[1], 0x7531u), prmt(tq[2], tq[3], 0x7531u)};
+          pv_tile8<KVF, HD>(o, vbase, row0, lane, bh, bl);
         }
-        const uint32_t pb0 = movmatrix_trans(pack2<BF>(pr[0], pr[1]));
-        const uint32_t pb1 = movmatrix_trans(pack2<BF>(pr[2], pr[3]));
-        pv_tile<QT, KVF, HD>(o, vbase, la, pb0, pb1);
         if constexpr (LOADER == 0) {
-          if (vcount < 16) fence_proxy_async_smem();  // generic zero-fill before next TMA write
+          if (vcount < TPW) fence_proxy_async_smem();  // generic zero-fill before next TMA write
         }
       }
       __syncwarp();
@@ -522,7 +698,8 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         const bool any = L[j] > 0.f;
-        inv[j] = any ? (direct ? p.v_scale : 1.f) / L[j] : 0.f;
+        // fp8 KV: the accumulator carries the x256 scale of the quantised probabilities
+        inv[j] = any ? (direct ? p.v_scale : 1.f) * (KVF == 0 ? 1.f : 1.f / 256.f) / L[j] : 0.f;
         lse2[j] = any ? M[j] + lg2f(L[j]) : kNegInf;
       }
       const int h0 = 2 * t;
@@ -562,6 +739,26 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
             if (g == 0) p.tmp_lse[(int64_t)sg.slot * GS + h0 + j] = lse2[j];
           }
         }
+        if (sg.merge_unit >= 0) {
+          // publish the partial, then count arrivals; the CTA whose partial arrives last
+          // merges the unit and returns the counter to zero for the next run()
+          __threadfence();
+          __syncwarp();
+          if (lane == 0) {
+            const int cnt = __ldg(&p.merge_units[sg.merge_unit].count);
+            const int last = atomicAdd(p.merge_counters + sg.merge_unit, 1) == cnt - 1;
+            if (last) p.merge_counters[sg.merge_unit] = 0;
+            reinterpret_cast<volatile int*>(scratch_ml)[kConsumerWarps * kMaxGroup * 2] = last;
+          }
+        }
+      }
+    }
+    if (sg.merge_unit >= 0) {  // CTA-uniform
+      named_bar_sync(3, kConsumerWarps * 32);
+      if (reinterpret_cast<volatile int*>(scratch_ml)[kConsumerWarps * kMaxGroup * 2]) {
+        __threadfence();
+        const int4 mu = __ldg(reinterpret_cast<const int4*>(p.merge_units + sg.merge_unit));
+        merge_unit_cta<QT, HD>(p, mu.x, mu.y, mu.z, mu.w, threadIdx.x);
       }
     }
   }
@@ -570,14 +767,14 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 // threads per CTA: 4 consumer warps + 1 (TMA) or 4 (cp.async) producer warps
 template <int LOADER>
 struct BlockDim {
-  static constexpr int kProducerWarps = (LOADER == 0) ? 1 : 4;
+  static constexpr int kProducerWarps = (LOADER == 0) ? 1 : kCpAsyncProducerThreads / 32;
   static constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 };
 
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 0 = KV has q's dtype, 1 = e4m3, 2 = e5m2.
 // LOADER: 0 = TMA boxes, 1 = cp.async gathers.
 template <int QT, int KVF, int HD, int LOADER>
-__global__ void __launch_bounds__(BlockDim<LOADER>::kThreads)
+__global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
     paged_decode_kernel(const __grid_constant__ DecodeParams p,
                         const __grid_constant__ CUtensorMap kmap,
                         const __grid_constant__ CUtensorMap vmap) {
@@ -610,7 +807,7 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads)
   }
   // the work list was written by plan() (a memcpy), not by the preceding kernel, so it
   // may be read before the PDL dependency resolves
-  const SegSource src = seg_source_init(p);
+  const SegSource src = seg_source_init(p, G::TT);
   for (int i = tid; i < min(src.count, kSegCache); i += blockDim.x) seg_cache[i] = seg_make(src, i);
   __syncthreads();
   if (src.count == 0) return;

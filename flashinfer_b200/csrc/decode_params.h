@@ -11,15 +11,18 @@
 
 namespace fib200 {
 
-constexpr int kTileTokens = 64;       // KV tokens per pipeline stage
-constexpr int kConsumerWarps = 4;     // 16 tokens per warp per stage (MMA M = 16)
+constexpr int kConsumerWarps = 4;
+// KV tokens per pipeline stage: 16 per consumer warp for 16-bit KV (one m16n8k16 M tile),
+// 32 per warp for fp8 KV (one m16n8k32 K block of the P.V product).  A stage is 32 KiB at
+// D = 128 either way.  kvf: 0 = 16-bit KV, 1 = e4m3, 2 = e5m2.
+__host__ __device__ constexpr int tile_tokens(int kvf) { return kvf == 0 ? 64 : 128; }
 constexpr int kMaxStages = 12;
 constexpr int kSegCache = 32;         // segment records cached in smem per CTA
 constexpr float kNegInf = -5e4f;      // finite "-inf", reference math.cuh:32
 constexpr int kMaxGroup = 8;          // GQA group size handled by one MMA N tile
 
 // One unit of work for a CTA: tiles [tile_begin, tile_end) (absolute tile index on the
-// request's token axis, tile t covers tokens [64 t, 64 t + 64)) of KV head `kv_head`
+// request's token axis, tile t covers tokens [TT t, TT t + TT), TT = tile_tokens(kvf)) of KV head `kv_head`
 // of request `request`.  Only tokens in [tok_lo, tok_hi) are attended.
 // slot < 0: the segment covers the whole unit, write o/lse directly;
 // slot >= 0: write a normalised partial (o fp32, lse) into partial slot `slot`.
@@ -31,7 +34,7 @@ struct alignas(16) Segment {
   int32_t slot;
   int32_t tok_lo;
   int32_t tok_hi;
-  int32_t pad;
+  int32_t merge_unit;  // index of the MergeUnit this partial belongs to (-1 when slot < 0)
 };
 static_assert(sizeof(Segment) == 32, "Segment must be 32 bytes");
 
@@ -81,6 +84,7 @@ enum PlanInfoSlot {
   kPiWindowLeft,
   kPiStages,
   kPiIntBytesUsed,
+  kPiOffCounters,   // int32 arrival counters, one per merge unit (fused split-KV merge)
   kPiLen
 };
 constexpr int64_t kPlanMagic = 0xF1B2000001LL;
@@ -114,6 +118,10 @@ struct DecodeParams {
   // partial outputs
   float* tmp_o;    // [slots, G, D]
   float* tmp_lse;  // [slots, G]
+  // fused split-KV merge (explicit work list only): the CTA whose partial arrives last at a
+  // unit merges all of the unit's partials; counters return to zero for the next run()
+  const MergeUnit* merge_units;
+  int32_t* merge_counters;
   int32_t num_qo_heads;
   int32_t group_size;
   int32_t num_stages;

@@ -10,6 +10,7 @@
 // the same number of KV bytes (+-1 tile) whatever the length distribution.  A unit cut
 // by a range boundary becomes several partial segments (consecutive partial slots) plus
 // one MergeUnit; a unit inside one range is written directly.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -43,9 +44,9 @@ Tuning& tuning() {
 
 KernelConfig choose_config(int kvf, int head_dim) {
   const int es = kvf == 0 ? 2 : 1;
-  const int stage = 2 * kTileTokens * head_dim * es;
+  const int stage = 2 * tile_tokens(kvf) * head_dim * es;
   const int fixed = 1024 + (kConsumerWarps - 1) * head_dim * 32 /*scratch o*/ +
-                    kConsumerWarps * kMaxGroup * 8 + kSegCache * (int)sizeof(Segment) +
+                    kConsumerWarps * kMaxGroup * 8 + 16 + kSegCache * (int)sizeof(Segment) +
                     2 * kMaxStages * 8;
   const int sm_total = 233472;  // 228 KiB per SM, each resident CTA reserves 1 KiB
   KernelConfig c;
@@ -132,6 +133,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   }
 
   // ---- per-request token / tile ranges --------------------------------------
+  const int TT = tile_tokens(kvf);
   std::vector<int32_t> tok_lo(batch_size), tok_hi(batch_size), tile_b(batch_size), ntile(batch_size);
   int64_t total_tiles = 0;
   for (int b = 0; b < batch_size; ++b) {
@@ -153,8 +155,8 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     if (window_left >= 0) lo = std::max<int64_t>(0, len - 1 - window_left);
     tok_lo[b] = (int32_t)lo;
     tok_hi[b] = (int32_t)len;
-    tile_b[b] = (int32_t)(lo / kTileTokens);
-    ntile[b] = len == 0 ? 0 : (int32_t)((len + kTileTokens - 1) / kTileTokens - tile_b[b]);
+    tile_b[b] = (int32_t)(lo / TT);
+    ntile[b] = len == 0 ? 0 : (int32_t)((len + TT - 1) / TT - tile_b[b]);
     total_tiles += (int64_t)ntile[b] * num_kv_heads;
   }
   if (total_tiles > 0x7fffffffLL) return fail(FI_ERR_INVALID_ARGUMENT, "too many KV tiles");
@@ -167,6 +169,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   size_t off = 0;
   const size_t off_header = off; off = align16(off + sizeof(PlanHeader));
   const size_t off_indptr = off; off = align16(off + (size_t)(num_ctas + 1) * 4);
+  const size_t off_counters = off; off = align16(off + (size_t)max_merge * 4);
   const size_t off_segs = off;   off = align16(off + (size_t)max_segs * sizeof(Segment));
   const size_t off_merge = off;  off = align16(off + (size_t)max_merge * sizeof(MergeUnit));
   const size_t int_need = off;
@@ -187,8 +190,15 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   PlanHeader* hdr = reinterpret_cast<PlanHeader*>(host + off_header);
   int32_t* cta_indptr = reinterpret_cast<int32_t*>(host + off_indptr);
   Segment* segs = reinterpret_cast<Segment*>(host + off_segs);
+  // arrival counters of the fused merge: zeroed by every plan (the workspace is not
+  // guaranteed to be zero-initialised) and returned to zero by the kernel itself
+  memset(host + off_counters, 0, (size_t)max_merge * 4);
   MergeUnit* merges = reinterpret_cast<MergeUnit*>(host + off_merge);
 
+  // split-KV merge: fused into the decode kernel (default) or a second launch
+  // (FI_B200_FUSED_MERGE=0, kept for A/B measurements)
+  const char* fm = getenv("FI_B200_FUSED_MERGE");
+  const bool fused_merge = !(fm != nullptr && fm[0] == '0');
   // ---- cut the tile stream into per-CTA ranges ---------------------------------
   const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
   int64_t ctas_used = std::min<int64_t>(num_ctas, std::max<int64_t>(1, total_tiles / min_tiles));
@@ -203,7 +213,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     for (int h = 0; h < num_kv_heads; ++h) {
       const int64_t nt = ntile[b];
       Segment s;
-      s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b]; s.pad = 0;
+      s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b]; s.merge_unit = -1;
       if (nt == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
         s.tile_begin = s.tile_end = 0; s.slot = -1;
         segs[nseg++] = s;
@@ -224,6 +234,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
         s.tile_end = tile_b[b] + (int32_t)(e - pos);
         if (whole) {
           s.slot = -1;
+          s.merge_unit = -1;
         } else {
           s.slot = (int32_t)nslot++;
           if (!split_open) {
@@ -232,6 +243,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
             split_open = true;
           }
           merges[nmerge - 1].count++;
+          s.merge_unit = fused_merge ? (int32_t)(nmerge - 1) : -1;
         }
         segs[nseg++] = s;
         cur = e;
@@ -281,8 +293,10 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   pi[kPiQDtype] = q_dtype;
   pi[kPiKvDtype] = kv_dtype;
   pi[kPiCudaGraph] = cuda_graph;
-  // graph mode: the merge launch must exist in every replay; its grid is the upper bound
-  pi[kPiMergeGrid] = cuda_graph ? max_merge : nmerge;
+  // fused: the last CTA to arrive at a unit merges it inside the decode kernel; otherwise a
+  // second launch (graph mode: fixed upper-bound grid so that replays stay valid)
+  pi[kPiMergeGrid] = fused_merge ? 0 : (cuda_graph ? max_merge : nmerge);
+  pi[kPiOffCounters] = (int64_t)off_counters;
   pi[kPiTotalTiles] = total_tiles;
   pi[kPiWindowLeft] = window_left;
   pi[kPiStages] = cfg.stages;

@@ -169,3 +169,55 @@ __device__ __forceinline__ void pdl_launch_dependents() {
 }
 
 }  // namespace fib200
+
+namespace fib200 {
+// ---- fp8 tensor-core path ---------------------------------------------------------
+// D(16x8,f32) += A(16x32, fp8) * B(32x8, e4m3).  A_E5M2 selects the KV storage type; the
+// B operand (quantised q or p) is always e4m3.
+template <bool A_E5M2>
+__device__ __forceinline__ void mma_16832_fp8(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                              uint32_t b1) {
+  if constexpr (A_E5M2) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.f32.e5m2.e4m3.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  } else {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.f32.e4m3.e4m3.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+}
+// (lo, hi) f32 -> two e4m3 bytes (lo in bits 0-7), round-to-nearest, saturating
+__device__ __forceinline__ uint32_t f32x2_to_e4m3x2(float lo, float hi) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return (uint32_t)r;
+}
+// two e4m3 bytes (low 16 bits) -> (lo, hi) f32
+__device__ __forceinline__ float2 e4m3x2_to_f32x2(uint32_t v) {
+  const uint32_t h = fp8x2_to_f16x2<false>((uint16_t)v);
+  return __half22float2(*reinterpret_cast<const __half2*>(&h));
+}
+// Split (x0, x1) into e4m3 "hi" parts and e4m3 residual "lo" parts: x ~= hi + lo with ~8
+// significant bits.  Returns hi in bits 0-15 and lo in bits 16-31 (byte order x0, x1).
+__device__ __forceinline__ uint32_t split_e4m3x2(float x0, float x1) {
+  const uint32_t hi = f32x2_to_e4m3x2(x0, x1);
+  const float2 back = e4m3x2_to_f32x2(hi);
+  const uint32_t lo = f32x2_to_e4m3x2(x0 - back.x, x1 - back.y);
+  return hi | (lo << 16);
+}
+// Three-term split: x ~= t[0] + t[1] + t[2] (each two e4m3 bytes in bits 0-15, byte order x0, x1)
+__device__ __forceinline__ void split3_e4m3x2(uint32_t (&t)[3], float x0, float x1) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    t[i] = f32x2_to_e4m3x2(x0, x1);
+    const float2 back = e4m3x2_to_f32x2(t[i]);
+    x0 -= back.x;
+    x1 -= back.y;
+  }
+}
+}  // namespace fib200

@@ -49,7 +49,7 @@ extern "C" {
 /* number of int64 slots in the plan-info vector (reference DecodePlanInfo has
  * 10, include/flashinfer/attention/scheduler.cuh:366-422; ours carries the
  * persistent-grid work list offsets instead and is opaque to Python). */
-#define FI_PLAN_INFO_LEN 24
+#define FI_PLAN_INFO_LEN 32
 
 FI_API const char* fi_last_error(void);
 FI_API int fi_version(void);

@@ -95,7 +95,8 @@ PI = dict(magic=0, num_ctas=1, num_segments=2, num_merge=3, num_slots=4, off_hea
           off_cta_indptr=6, off_segments=7, off_merge=8, off_tmp_o=9, off_tmp_lse=10,
           batch_size=11, hq=12, hkv=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
           cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23)
-TILE = 64
+TILE = 64        # tokens per tile for 16-bit KV (csrc/decode_params.h tile_tokens)
+TILE_FP8 = 128   # ... and for fp8 KV
 
 
 def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size,
@@ -127,7 +128,7 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
     return 0, "", dict(info=info, header=hdr.copy(), cta_indptr=cta_indptr, segments=segs, merges=merges)
 
 
-def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1):
+def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1, tile=TILE):
     """Pure-Python replay of the work list: returns per-(request, head) token visit counts
     and checks the structural invariants.  Raises AssertionError on any inconsistency."""
     segs, merges, cta_indptr, hdr = plan["segments"], plan["merges"], plan["cta_indptr"], plan["header"]
@@ -143,7 +144,7 @@ def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1):
         exp_lo = max(0, L - 1 - window_left) if window_left >= 0 else 0
         assert lo == exp_lo and hi == L, (lo, hi, exp_lo, L)
         assert tb <= te
-        a, b = max(tb * TILE, lo), min(te * TILE, hi)
+        a, b = max(tb * tile, lo), min(te * tile, hi)
         if b > a:
             visits[r * num_kv_heads + h][a:b] += 1
         if slot < 0:

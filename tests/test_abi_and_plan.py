@@ -8,7 +8,7 @@ from pathlib import Path
 import numpy as np
 import pytest
 
-from helpers import PI, TILE, host_plan, replay_plan
+from helpers import PI, TILE, TILE_FP8, host_plan, replay_plan
 
 ROOT = Path(__file__).resolve().parent.parent
 
@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), f"libfi_b200.so does not export {name}"
     assert declared == set(_lib.PROTOTYPES), "ctypes prototypes out of sync with the header"
     assert lib.fi_version() >= 100
-    assert lib.fi_plan_info_len() == 24
+    assert lib.fi_plan_info_len() == 32
 
 
 def lens_to_table(kv_lens, page_size):
@@ -62,6 +62,15 @@ def test_plan_visits_every_token_once(kv_lens, hq, hkv, page, nctas):
     if len(used):
         assert used.max() - used.min() <= 1
     assert plan["info"][PI["total_tiles"]] == total
+
+
+def test_plan_fp8_tiles_are_128_tokens():
+    kv_lens = [8192] * 16 + [1, 127, 128, 129, 5000]
+    indptr, last = lens_to_table(kv_lens, 16)
+    rc, err, plan = host_plan(indptr, last, 8, 1, 128, 16, 296, q_dtype=1, kv_dtype=2)
+    assert rc == 0, err
+    replay_plan(plan, kv_lens, 1, tile=TILE_FP8)
+    assert plan["info"][PI["total_tiles"]] == sum(-(-l // TILE_FP8) for l in kv_lens)
 
 
 def test_plan_log_uniform_c4_balance():
