@@ -69,7 +69,8 @@ def load() -> C.CDLL:
                 f"{LIB_PATH} is missing: build it with `python -m flashinfer_b200.build` "
                 "(there is no CPU / PyTorch fallback for the decode path)"
             )
-    lib = C.CDLL(str(LIB_PATH))
+    # FI_B200_LIB: load another build of the same ABI (the -DFI_B200_TRACE one, scripts/trace_probe.py)
+    lib = C.CDLL(os.environ.get("FI_B200_LIB", str(LIB_PATH)))
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the .so does not export it
         fn.restype = res

@@ -38,18 +38,23 @@ def _digest() -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
-    stamp = OBJ / "stamp.txt"
+def build(force: bool = False, verbose: bool = False, trace: bool = False) -> Path:
+    """trace=True builds libfi_b200_trace.so (-DFI_B200_TRACE: per-CTA phase timestamps for
+    scripts/trace_probe.py); the shipped library never carries the trace code."""
+    out = HERE / "libfi_b200_trace.so" if trace else OUT
+    obj_dir = HERE / "build_trace" if trace else OBJ
+    flags = FLAGS + (["-DFI_B200_TRACE"] if trace else [])
+    stamp = obj_dir / "stamp.txt"
     dig = _digest()
-    if not force and OUT.exists() and stamp.exists() and stamp.read_text() == dig:
-        return OUT
+    if not force and out.exists() and stamp.exists() and stamp.read_text() == dig:
+        return out
     if not Path(NVCC).exists():
-        raise RuntimeError(f"nvcc not found at {NVCC}; cannot build libfi_b200.so")
-    OBJ.mkdir(exist_ok=True)
+        raise RuntimeError(f"nvcc not found at {NVCC}; cannot build {out.name}")
+    obj_dir.mkdir(exist_ok=True)
 
     def cc(src: str) -> Path:
-        obj = OBJ / (src + ".o")
-        cmd = [NVCC, *FLAGS, "-c", str(CSRC / src), "-o", str(obj)]
+        obj = obj_dir / (src + ".o")
+        cmd = [NVCC, *flags, "-c", str(CSRC / src), "-o", str(obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)
@@ -61,15 +66,15 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(cc, SOURCES))
-    cmd = [NVCC, "-shared", "-o", str(OUT), *map(str, objs), "-cudart", "static",
+    cmd = [NVCC, "-shared", "-o", str(out), *map(str, objs), "-cudart", "static",
            "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
     stamp.write_text(dig)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":
-    p = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    p = build(force="--force" in sys.argv, verbose="-v" in sys.argv, trace="--trace" in sys.argv)
     print(p)

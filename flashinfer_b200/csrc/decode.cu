@@ -5,12 +5,15 @@
 // SingleDecodeWithKVCacheDispatched (decode.cuh:658-737).
 #include <cuda.h>
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 #include <string.h>
 
+#include <map>
 #include <mutex>
 #include <utility>
 
 #include "decode_kernel.cuh"
+#include "decode_kernel_tc5.cuh"
 #include "host_common.h"
 #include "merge_kernels.cuh"
 
@@ -86,12 +89,28 @@ static bool tma_eligible(const void* k, const void* v, int es, int64_t sn, int64
 }
 
 // ---- kernel launch ---------------------------------------------------------------
+// The opt-in dynamic shared memory limit is a per-(function, device) attribute: set it when it
+// has to grow (or the device changed), not on every launch.
+template <typename K>
+static cudaError_t ensure_smem_attr(K kern, int smem) {
+  // all kernels share one pointer type, so the cache is keyed by (function, device)
+  static thread_local std::map<std::pair<const void*, int>, int> cache;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  int& cur = cache[{reinterpret_cast<const void*>(kern), dev}];
+  if (smem <= cur) return cudaSuccess;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e == cudaSuccess) cur = smem;
+  return e;
+}
+
 template <int QT, int KVF, int HD, int LOADER>
 static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                       int grid, cudaStream_t stream) {
   auto kern = paged_decode_kernel<QT, KVF, HD, LOADER>;
   const int smem = SmemLayout<KVF, HD>::total(p.num_stages);
-  FI_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  FI_CUDA_TRY(ensure_smem_attr(kern, smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(BlockDim<LOADER>::kThreads);
@@ -126,10 +145,53 @@ static int launch_hd(const DecodeParams& p, const CUtensorMap& km, const CUtenso
   return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
 }
 
+// fp8 KV, head_dim 128, TMA-eligible pages: tcgen05 / TMEM kernel (decode_kernel_tc5.cuh)
+template <int QT, int KVF>
+static int launch_tc5(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm, int grid,
+                      cudaStream_t stream) {
+  auto kern = paged_decode_tc5_kernel<QT, KVF>;
+  const int smem = SmemLayout<KVF, 128>::total(p.num_stages);
+  FI_CUDA_TRY(ensure_smem_attr(kern, smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kTc5Threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.enable_pdl ? 1 : 0;
+  FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p, km, vm));
+  return FI_OK;
+}
+
+static int use_l2_prefetch() {
+  static const int on = [] {
+    // off by default: measured on B200 it LOWERS throughput (C2 192 -> 298 us, C3 401 -> 628 us;
+    // the prefetch boxes compete with the demand boxes in the TMA / L2 request path)
+    const char* e = getenv("FI_B200_L2_PREFETCH");
+    return (e != nullptr && e[0] == '1') ? 1 : 0;
+  }();
+  return on;
+}
+
+static bool use_tc5() {
+  static const bool on = [] {
+    const char* e = getenv("FI_B200_FP8_TC5");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
+
 static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                          int q_dtype, int kvf, int head_dim, int grid, bool tma,
                          cudaStream_t stream) {
   const bool bf = q_dtype == FI_DTYPE_BF16;
+  if (kvf != 0 && head_dim == 128 && tma && use_tc5()) {
+    if (kvf == 1) return bf ? launch_tc5<1, 1>(p, km, vm, grid, stream) : launch_tc5<0, 1>(p, km, vm, grid, stream);
+    return bf ? launch_tc5<1, 2>(p, km, vm, grid, stream) : launch_tc5<0, 2>(p, km, vm, grid, stream);
+  }
   switch (kvf) {
     case 0: return bf ? launch_hd<1, 0>(p, km, vm, head_dim, grid, tma, stream)
                       : launch_hd<0, 0>(p, km, vm, head_dim, grid, tma, stream);
@@ -166,6 +228,19 @@ static long long g_launch_count = 0;
 using namespace fib200;
 
 extern "C" {
+
+#ifdef FI_B200_TRACE
+// trace build only: copy the per-CTA phase timestamps (kTraceSlots per CTA) to the host
+FI_API int fi_debug_trace(unsigned long long* dst, int n_ctas) {
+  if (n_ctas > kTraceCtas) n_ctas = kTraceCtas;
+  cudaError_t e = cudaMemcpyFromSymbol(dst, g_fi_trace, sizeof(unsigned long long) * kTraceSlots * n_ctas);
+  if (e != cudaSuccess) return fail(FI_ERR_CUDA, "trace copy failed: %s", cudaGetErrorString(e));
+  unsigned long long* sym = nullptr;
+  if (cudaGetSymbolAddress(reinterpret_cast<void**>(&sym), g_fi_trace) == cudaSuccess)
+    cudaMemset(sym, 0, sizeof(unsigned long long) * kTraceSlots * kTraceCtas);
+  return FI_OK;
+}
+#endif
 
 int fi_last_loader(void) { return g_last_loader; }
 long long fi_launch_count(void) { return g_launch_count; }
@@ -212,6 +287,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.tma_h_first = kv_stride_h < kv_stride_n;
   p.header = reinterpret_cast<const PlanHeader*>(iw + plan_info[kPiOffHeader]);
   p.cta_seg_indptr = reinterpret_cast<const int32_t*>(iw + plan_info[kPiOffCtaIndptr]);
+  p.cta_heads = reinterpret_cast<const CtaHead*>(iw + plan_info[kPiOffCtaHeads]);
   p.segments = reinterpret_cast<const Segment*>(iw + plan_info[kPiOffSegments]);
   p.tmp_o = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpO]);
   p.tmp_lse = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpLse]);
@@ -225,6 +301,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.v_scale = v_scale;
   p.soft_cap = logits_soft_cap;
   p.enable_pdl = enable_pdl;
+  p.l2_prefetch = use_l2_prefetch();
 
   const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
                                 page_size, false, 0, TT);
@@ -327,7 +404,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.num_qo_heads = num_qo_heads; p.group_size = group;
   p.num_stages = cfg.stages;
   p.sm_scale = sm_scale; p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
-  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0;
+  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0; p.l2_prefetch = use_l2_prefetch();
 
   const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
   CUtensorMap km, vm;

@@ -26,6 +26,25 @@
 
 namespace fib200 {
 
+// Phase timestamps for latency work (scripts/trace_probe.py): compiled only into the
+// -DFI_B200_TRACE build (libfi_b200_trace.so), never into the shipped library.
+#ifdef FI_B200_TRACE
+constexpr int kTraceCtas = 1024, kTraceSlots = 16;
+__device__ unsigned long long g_fi_trace[kTraceCtas * kTraceSlots];
+__device__ __forceinline__ void fi_trace(int slot) {
+  if (blockIdx.x < kTraceCtas) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_fi_trace[blockIdx.x * kTraceSlots + slot] = t;
+  }
+}
+#define FI_TRACE(slot) fi_trace(slot)
+#define FI_TRACE_IF(cond, slot) do { if (cond) fi_trace(slot); } while (0)
+#else
+#define FI_TRACE(slot)
+#define FI_TRACE_IF(cond, slot)
+#endif
+
 // cp.async gather loader: 2 producer warps keep the CTA at 192 threads so that two CTAs per SM
 // fit the register file next to the 4 consumer warps
 constexpr int kCpAsyncProducerThreads = 64;
@@ -50,9 +69,9 @@ template <int KVF, int HD>
 struct SmemLayout {
   using G = TileGeom<KVF, HD>;
   static constexpr int SCRATCH_O = (kConsumerWarps - 1) * G::KSTEPS * 4 * 32 * 4;
-  static constexpr int SCRATCH_ML = kConsumerWarps * kMaxGroup * 2 * 4 + 16;  // + merge flag
+  static constexpr int SCRATCH_ML = 768;  // warp (m, l) pairs + merge flag; tcgen05 path: more
   static constexpr int SEG_BYTES = kSegCache * (int)sizeof(Segment);
-  static constexpr int BAR_BYTES = 2 * kMaxStages * 8;
+  static constexpr int BAR_BYTES = 2 * kMaxStages * 8 + 128;  // ring + tcgen05-path barriers
   __host__ __device__ static constexpr int ring(int stages) { return stages * G::STAGE_BYTES; }
   __host__ __device__ static constexpr int total(int stages) {
     return 1024 + ring(stages) + SCRATCH_O + SCRATCH_ML + SEG_BYTES + BAR_BYTES;
@@ -82,11 +101,10 @@ __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int 
   s.first = 0;
   s.count = 0;
   s.imp_begin = s.imp_end = 0;
-  if (p.header != nullptr) {
-    if ((int)blockIdx.x < p.header->num_ctas_used) {
-      s.first = p.cta_seg_indptr[blockIdx.x];
-      s.count = p.cta_seg_indptr[blockIdx.x + 1] - s.first;
-    }
+  if (p.header != nullptr) {  // explicit work list: the grid is exactly the planned CTA count
+    const int2 h = __ldg(reinterpret_cast<const int2*>(p.cta_heads + blockIdx.x));
+    s.first = h.x;
+    s.count = h.y;
   } else {
     const long long T = (long long)p.imp_units * p.imp_tiles;
     const long long C = gridDim.x;
@@ -106,12 +124,15 @@ __device__ __forceinline__ Segment seg_make(const SegSource& s, int k) {
   const DecodeParams& p = *s.p;
   Segment g;
   if (p.header != nullptr) {
-    const int4* src = reinterpret_cast<const int4*>(p.segments + s.first + k);
-    int4 a = __ldg(src), b = __ldg(src + 1);
+    // the first kCtaInlineSegs segments sit in the CTA head (same round trip as first / count)
+    const int4* src = reinterpret_cast<const int4*>(
+        k < kCtaInlineSegs ? &p.cta_heads[blockIdx.x].seg[k] : p.segments + s.first + k);
+    int4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2);
     g.request = a.x; g.kv_head = a.y; g.tile_begin = a.z; g.tile_end = a.w;
     g.slot = b.x; g.tok_lo = b.y; g.tok_hi = b.z; g.merge_unit = b.w;
+    g.page_base = c.x;
   } else {
-    g.request = 0; g.merge_unit = -1;
+    g.request = 0; g.merge_unit = -1; g.page_base = 0;
     g.tok_lo = p.imp_tok_lo; g.tok_hi = p.imp_tok_hi;
     const int nt = p.imp_tiles;
     if (nt == 0) {
@@ -140,6 +161,17 @@ __device__ __forceinline__ Segment seg_get(const SegSource& s, const Segment* ca
 // ---- producer: per-page TMA boxes -------------------------------------------
 // Runs in one warp (all 32 lanes converged).  Box i of a tile is issued by lane i%32:
 //   i = (kv * NP + panel) * BPT + j,  j = token-block of rows_per_box rows.
+// L2 prefetch: besides the boxes that fill the shared-memory ring, the producer asks TMA to pull
+// the tiles kPrefetchTiles beyond the ring from DRAM into L2 (cp.async.bulk.prefetch.tensor), so a
+// ring slot that frees up is refilled at L2 latency instead of DRAM latency.  The bytes in flight
+// per SM are then no longer capped by the ring (Little's law at ~6.5 TB/s needs > 100 KB per SM).
+constexpr int kPrefetchTiles = 4;
+
+struct TileCursor {  // walks the CTA's (segment, tile) sequence
+  int k, t, t_end, page_base;
+  Segment sg;
+};
+
 template <int KVF, int HD>
 __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSource& src,
                                             const Segment* seg_cache, const CUtensorMap* kmap,
@@ -152,38 +184,87 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   const int nbox = 2 * G::NP * bpt;
   const int j = lane % bpt;  // same j for every i = lane + 32 k since bpt | 32
   const uint32_t box_bytes = (uint32_t)rpb * 128u;
+
+  auto cursor_load = [&](TileCursor& c) {  // position on segment c.k (skipping empty ones)
+    while (c.k < src.count) {
+      c.sg = seg_get(src, seg_cache, c.k);
+      if (c.sg.tile_end > c.sg.tile_begin) break;
+      ++c.k;
+    }
+    if (c.k < src.count) {
+      c.t = c.sg.tile_begin;
+      c.t_end = c.sg.tile_end;
+      c.page_base = c.sg.page_base;  // planned copy of kv_indptr[request]: no dependent load
+    }
+  };
+  auto cursor_next = [&](TileCursor& c) {
+    if (++c.t >= c.t_end) { ++c.k; cursor_load(c); }
+  };
+  // boxes of tile c.t: page index + first row for this lane's token block j
+  auto tile_geom = [&](const TileCursor& c, int& nvb, int& page, int& row0) {
+    const int tok0 = c.t * G::TT;
+    const int rem = c.sg.tok_hi - tok0;  // > 0 by construction
+    nvb = rem >= G::TT ? bpt : (rem + rpb - 1) / rpb;
+    const int tok = tok0 + j * rpb;
+    page = 0;
+    if (j < nvb) {
+      const int pit = tok >> p.page_shift;
+      page = p.kv_indices ? __ldg(p.kv_indices + c.page_base + pit) : c.page_base + pit;
+    }
+    row0 = tok & p.page_mask;
+  };
+
+  TileCursor cur, pf;
+  cur.k = 0;
+  cursor_load(cur);
+  pf = cur;
+  const bool do_pf = p.l2_prefetch != 0;
+  int ahead = 0;  // tiles between the load cursor and the prefetch cursor
+  if (do_pf) {
+    for (; ahead < p.num_stages && pf.k < src.count; ++ahead) cursor_next(pf);  // the ring covers these
+  }
   int stage = 0;
   uint32_t phase = 0;
-  for (int k = 0; k < src.count; ++k) {
-    const Segment sg = seg_get(src, seg_cache, k);
-    const int page_base = p.kv_indptr ? __ldg(p.kv_indptr + sg.request) : 0;
-    for (int t = sg.tile_begin; t < sg.tile_end; ++t) {
-      const int tok0 = t * G::TT;
-      const int rem = sg.tok_hi - tok0;  // > 0 by construction
-      const int nvb = rem >= G::TT ? bpt : (rem + rpb - 1) / rpb;
-      const int tok = tok0 + j * rpb;
-      int page = 0;
-      if (j < nvb) {
-        const int pit = tok >> p.page_shift;
-        page = p.kv_indices ? __ldg(p.kv_indices + page_base + pit) : page_base + pit;
-      }
-      const int row0 = tok & p.page_mask;
-      mbar_wait(empty_bar + 8 * stage, phase ^ 1);
-      if (lane == 0) mbar_arrive_expect_tx(full_bar + 8 * stage, 2u * G::NP * nvb * box_bytes);
-      __syncwarp();
-      if (j < nvb) {
-        const uint32_t sbase = ring + stage * G::STAGE_BYTES + j * box_bytes;
-        for (int i = lane; i < nbox; i += 32) {
-          const int pn = (i / bpt) % G::NP;
-          const int kv = i / (bpt * G::NP);
-          tma_load_4d(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
-                      full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? sg.kv_head : row0,
-                      p.tma_h_first ? row0 : sg.kv_head, page);
+  [[maybe_unused]] bool first_tile = true;
+  while (cur.k < src.count) {
+    if (do_pf) {
+      while (ahead < p.num_stages + kPrefetchTiles && pf.k < src.count) {
+        int nvb, page, row0;
+        tile_geom(pf, nvb, page, row0);
+        if (j < nvb) {
+          for (int i = lane; i < nbox; i += 32) {
+            const int pn = (i / bpt) % G::NP;
+            const int kv = i / (bpt * G::NP);
+            tma_prefetch_4d(kv ? vmap : kmap, pn * (128 / G::ES), p.tma_h_first ? pf.sg.kv_head : row0,
+                            p.tma_h_first ? row0 : pf.sg.kv_head, page);
+          }
         }
+        cursor_next(pf);
+        ++ahead;
       }
-      __syncwarp();
-      if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
     }
+    int nvb, page, row0;
+    tile_geom(cur, nvb, page, row0);
+    FI_TRACE_IF(lane == 0 && first_tile && page >= 0, 3);
+    mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+    if (lane == 0) mbar_arrive_expect_tx(full_bar + 8 * stage, 2u * G::NP * nvb * box_bytes);
+    __syncwarp();
+    if (j < nvb) {
+      const uint32_t sbase = ring + stage * G::STAGE_BYTES + j * box_bytes;
+      for (int i = lane; i < nbox; i += 32) {
+        const int pn = (i / bpt) % G::NP;
+        const int kv = i / (bpt * G::NP);
+        tma_load_4d(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
+                    full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? cur.sg.kv_head : row0,
+                    p.tma_h_first ? row0 : cur.sg.kv_head, page);
+      }
+    }
+    __syncwarp();
+    FI_TRACE_IF(lane == 0 && first_tile, 4);
+    first_tile = false;
+    if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+    cursor_next(cur);
+    --ahead;
   }
 }
 
@@ -207,7 +288,7 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
   uint32_t phase = 0;
   for (int k = 0; k < src.count; ++k) {
     const Segment sg = seg_get(src, seg_cache, k);
-    const int page_base = p.kv_indptr ? __ldg(p.kv_indptr + sg.request) : 0;
+    const int page_base = sg.page_base;
     const int64_t head_off = (int64_t)sg.kv_head * p.kv_stride_h + c * (16 / G::ES);
     for (int t = sg.tile_begin; t < sg.tile_end; ++t) {
       mbar_wait(empty_bar + 8 * stage, phase ^ 1);
@@ -523,6 +604,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 
     for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
       mbar_wait(full_bar + 8 * stage, phase);
+      FI_TRACE_IF(threadIdx.x == 0 && k == 0 && tile == sg.tile_begin, 5);
       const int tok0 = tile * G::TT + row0;
       const int vcount = min(TPW, sg.tok_hi - tok0);
       if (vcount > 0 && tok0 + TPW > sg.tok_lo) {  // warp-uniform
@@ -643,6 +725,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
       if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
     }
 
+    FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 6);
     // ---- segment epilogue: merge the 4 warp states, write o/lse or a partial ----
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -753,14 +836,17 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
         }
       }
     }
+    FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 7);
     if (sg.merge_unit >= 0) {  // CTA-uniform
       named_bar_sync(3, kConsumerWarps * 32);
       if (reinterpret_cast<volatile int*>(scratch_ml)[kConsumerWarps * kMaxGroup * 2]) {
         __threadfence();
         const int4 mu = __ldg(reinterpret_cast<const int4*>(p.merge_units + sg.merge_unit));
         merge_unit_cta<QT, HD>(p, mu.x, mu.y, mu.z, mu.w, threadIdx.x);
+        FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 9);
       }
     }
+    FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 8);
   }
 }
 
@@ -794,6 +880,7 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   const uint32_t empty_bar = full_bar + 8 * kMaxStages;
 
   const int tid = threadIdx.x;
+  FI_TRACE_IF(tid == 0, 0);
   if (tid == 0) {
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(full_bar + 8 * s, LOADER == 0 ? 1 : BlockDim<LOADER>::kProducerWarps * 32);
@@ -810,8 +897,10 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   const SegSource src = seg_source_init(p, G::TT);
   for (int i = tid; i < min(src.count, kSegCache); i += blockDim.x) seg_cache[i] = seg_make(src, i);
   __syncthreads();
+  FI_TRACE_IF(tid == 0, 1);
   if (src.count == 0) return;
   if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
+  FI_TRACE_IF(tid == 0, 2);
 
   if (tid < kConsumerWarps * 32) {
     consume<QT, KVF, HD, LOADER>(p, src, seg_cache, ring, full_bar, empty_bar, scratch_o,

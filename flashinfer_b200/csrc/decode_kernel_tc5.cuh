@@ -1,0 +1,499 @@
+// decode_kernel_tc5.cuh — fp8-KV paged decode on the 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// sm_100a has no native fp8 mma.sync (ptxas lowers it to F2FP conversions + HMMA), so the
+// register-level path pays one conversion per KV element and stalls near 5.3 TB/s.  Here the fp8
+// K / V bytes that TMA wrote to shared memory (128B swizzle) are consumed as they are by
+// tcgen05.mma.kind::f8f6f4 — zero per-element ALU work:
+//
+//   S[128 tokens x 32]  = K_tile[128 x 128 fp8, K-major SW128]  x  Qs^T   (4 MMAs, k = 32 each)
+//       Qs = the 16-bit query split into three e4m3 terms (rows 8t+h: term t of head h) so that
+//       q.k keeps ~12 significant bits; the three partial logits are summed after tcgen05.ld.
+//   O[128 d x 16]      += V_tile^T[128 d x 128 tokens, MN-major SW128]  x  P[128 tokens x 16]
+//       P = probabilities of the 8 heads as e4m3 hi (cols 0-7) + residual lo (cols 8-15), written
+//       by the softmax threads as one 16-byte row per token (MN-major, no swizzle).
+//
+// Roles (192 threads): warps 0-3 = softmax (thread t <-> token t of the tile, TMEM lane t),
+// warp 4 = TMA producer (same per-page boxes as the mma.sync kernel), warp 5 = MMA issuer (one
+// elected lane).  S is double-buffered in TMEM, P in shared memory; QK of tile i+1 is issued
+// before PV of tile i so the tensor pipe runs under the softmax of tile i.
+// The softmax keeps ONE reference exponent rho[h] per head for the whole CTA (the accumulator
+// in TMEM is shared): per tile the 4 warp maxima are exchanged through shared memory and rho is
+// raised only when the tile maximum exceeds it by more than 2^5; then O is rescaled in TMEM
+// (tcgen05.ld / st).  p = 2^(x - rho + 3) <= 256 fits e4m3; hi + lo keeps ~8 bits.
+// Semantics (base-2 lse, -5e4 sentinel, empty -> o = 0) as in decode_kernel.cuh.
+#pragma once
+#include "decode_kernel.cuh"
+#include "tc5.cuh"
+
+namespace fib200 {
+
+constexpr int kTc5Threads = 192;
+constexpr int kTc5TmemCols = 128;   // S: 2 x 32 columns, O: 16 columns
+constexpr int kTc5ColS = 0;         // S[b] at column 32 b
+constexpr int kTc5ColO = 64;
+constexpr float kTc5Bump = 5.f;     // raise rho when a tile max exceeds it by more than 2^5
+constexpr float kTc5PShift = 3.f;   // p = 2^(x - rho + 3): <= 2^8 right after a bump
+
+// barrier slots after the ring's full/empty arrays (SmemLayout::BAR_BYTES reserves 128 bytes)
+struct Tc5Bars {
+  uint32_t s_ready[2], s_free[2], p_ready[2], p_free[2], q_ready[2];
+};
+__device__ __forceinline__ Tc5Bars tc5_bars(uint32_t base) {
+  Tc5Bars b;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    b.s_ready[i] = base + 8 * i;
+    b.s_free[i] = base + 16 + 8 * i;
+    b.p_ready[i] = base + 32 + 8 * i;
+    b.p_free[i] = base + 48 + 8 * i;
+    b.q_ready[i] = base + 64 + 8 * i;
+  }
+  return b;
+}
+
+// ---- query preparation: 128 softmax threads write Qs (32 rows x 128 B, K-major SW128) ---------
+// thread t: head h = t / 16, dims d0 = 8 (t % 16) .. d0 + 7.  Row 8 term + h holds term `term` of
+// head h; rows 24-31 and heads >= group_size are zero.  dq[h] = amax / 256 is the inverse scale.
+template <int QT>
+__device__ __forceinline__ void tc5_prepare_q(const DecodeParams& p, const Segment& sg, uint8_t* qbuf,
+                                              float* dq_out, int tid) {
+  const int h = tid >> 4, d0 = (tid & 15) * 8;
+  const int GS = p.group_size;
+  float x[8];
+  float amax = 0.f;
+  if (h < GS) {
+    const char* qrow = static_cast<const char*>(p.q) +
+                       ((int64_t)sg.request * p.q_stride_n +
+                        (int64_t)(sg.kv_head * GS + h) * p.q_stride_h) * 2 + d0 * 2;
+    const uint2 v0 = __ldg(reinterpret_cast<const uint2*>(qrow));
+    const uint2 v1 = __ldg(reinterpret_cast<const uint2*>(qrow) + 1);
+    const uint32_t w[4] = {v0.x, v0.y, v1.x, v1.y};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (QT == 1) {
+        x[2 * i] = __uint_as_float(w[i] << 16);
+        x[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+      } else {
+        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+        x[2 * i] = f.x;
+        x[2 * i + 1] = f.y;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(x[i]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = 0.f;
+  }
+#pragma unroll
+  for (int s = 1; s < 16; s <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, s));
+  const bool nz = amax > 0.f && amax < 3.0e38f;
+  const float sq = nz ? 256.f / amax : 1.f;
+  if ((tid & 15) == 0) dq_out[h] = nz ? amax * (1.f / 256.f) : 1.f;
+  uint32_t t[4][3];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) split3_e4m3x2(t[i], x[2 * i] * sq, x[2 * i + 1] * sq);
+  const int chunk = d0 >> 4, within = d0 & 15;
+#pragma unroll
+  for (int term = 0; term < 4; ++term) {
+    const int row = 8 * term + h;
+    uint2 v = make_uint2(0u, 0u);
+    if (term < 3) {
+      v.x = t[0][term] | (t[1][term] << 16);
+      v.y = t[2][term] | (t[3][term] << 16);
+    }
+    *reinterpret_cast<uint2*>(qbuf + swz<128>(row, chunk) + within) = v;
+  }
+}
+
+// ---- MMA issuer (warp 5; one elected lane issues, the warp stays converged) ---------------------
+template <int KVF>
+__device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource& src,
+                                          const Segment* seg_cache, uint32_t ring, uint32_t qbufs,
+                                          uint32_t pbufs, uint32_t full_bar, uint32_t empty_bar,
+                                          const Tc5Bars& bars, uint32_t tmem) {
+  using G = TileGeom<KVF, 128>;
+  constexpr int AF = (KVF == 2) ? 1 : 0;  // e5m2 : e4m3 storage
+  constexpr uint32_t idesc_qk = tc5::instr_desc_f8(AF, 0, /*a K-major*/ 0, /*b K-major*/ 0, 128, 32);
+  constexpr uint32_t idesc_pv = tc5::instr_desc_f8(AF, 0, /*a MN-major*/ 1, /*b MN-major*/ 1, 128, 16);
+  const bool leader = (threadIdx.x & 31) == 0;
+  int stage = 0;
+  uint32_t phase = 0;
+  uint32_t n = 0;  // tiles issued so far by this CTA: S / P buffer = n & 1
+  // pending P.V of the previous tile
+  bool pend = false;
+  int pend_stage = 0;
+  uint32_t pend_n = 0, pend_acc = 0;
+
+  auto issue_pv = [&]() {
+    const uint32_t b = pend_n & 1u;
+    mbar_wait(bars.p_ready[b], (pend_n >> 1) & 1u);
+    tc5::fence_after_sync();
+    if (leader) {
+      const uint32_t vbase = ring + pend_stage * G::STAGE_BYTES + G::KV_BYTES;
+      const uint32_t pb = pbufs + b * 2048u;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {  // 32 tokens per MMA
+        const uint64_t ad = tc5::smem_desc(vbase + ks * 4096u, 1024u, 1024u, tc5::kLayoutSw128);
+        const uint64_t bd = tc5::smem_desc(pb + ks * 512u, 128u, 128u, tc5::kLayoutNone);
+        tc5::mma_f8(tmem + kTc5ColO, ad, bd, idesc_pv, (ks > 0) ? 1u : pend_acc);
+      }
+      tc5::commit(empty_bar + 8 * pend_stage);  // K / V stage back to the TMA producer
+      tc5::commit(bars.p_free[b]);              // P buffer reusable, O updated
+    }
+    __syncwarp();
+    pend = false;
+  };
+
+  for (int k = 0; k < src.count; ++k) {
+    const Segment sg = seg_get(src, seg_cache, k);
+    mbar_wait(bars.q_ready[k & 1], (k >> 1) & 1u);  // every segment: never lag a phase behind
+    const uint32_t qb = qbufs + (k & 1) * 4096u;
+    for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
+      const uint32_t b = n & 1u;
+      // wait for the next K tile (and a free S buffer), but serve the pending P.V the moment its
+      // probabilities arrive: that frees the K / V stage for the TMA producer as early as possible
+      {
+        const long long t0 = clock64();
+        while (true) {
+          if (pend && mbar_try_wait(bars.p_ready[pend_n & 1u], (pend_n >> 1) & 1u)) issue_pv();
+          if (mbar_try_wait(full_bar + 8 * stage, phase) &&
+              mbar_try_wait(bars.s_free[b], ((n >> 1) & 1u) ^ 1u))
+            break;
+          if (clock64() - t0 > 4000000000LL) {
+            printf("fi_b200: tcgen05 issuer timed out (block %d tile %u)\n", blockIdx.x, n);
+            __trap();
+          }
+        }
+      }
+      tc5::fence_after_sync();
+      if (leader) {
+        const uint32_t kbase = ring + stage * G::STAGE_BYTES;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {  // 32 head dims per MMA: +32 bytes inside the SW128 row
+          const uint64_t ad = tc5::smem_desc(kbase + ks * 32u, 16u, 1024u, tc5::kLayoutSw128);
+          const uint64_t bd = tc5::smem_desc(qb + ks * 32u, 16u, 1024u, tc5::kLayoutSw128);
+          tc5::mma_f8(tmem + kTc5ColS + 32u * b, ad, bd, idesc_qk, ks > 0 ? 1u : 0u);
+        }
+        tc5::commit(bars.s_ready[b]);
+      }
+      __syncwarp();
+      if (pend) issue_pv();
+      pend = true;
+      pend_stage = stage;
+      pend_n = n;
+      pend_acc = (tile != sg.tile_begin) ? 1u : 0u;
+      ++n;
+      if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+    }
+    if (pend) issue_pv();  // the softmax warps need O complete before the segment epilogue
+  }
+}
+
+
+// ---- softmax warps (0-3): thread tid <-> token tid of each tile, TMEM lane tid ------------------
+template <int QT, int KVF>
+__device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSource& src,
+                                            const Segment* seg_cache, uint8_t* smem_ring,
+                                            uint8_t* qbufs, uint8_t* pbufs, float* scratch,
+                                            const Tc5Bars& bars, uint32_t tmem, int num_stages) {
+  using G = TileGeom<KVF, 128>;
+  constexpr int HD = 128;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int GS = p.group_size;
+  const bool use_cap = p.soft_cap > 0.f;
+  const float cap_pre = use_cap ? p.sm_scale / p.soft_cap : 0.f;
+  const float cap_post = use_cap ? p.soft_cap * 1.4426950408889634f : 0.f;
+  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;  // TMEM lane field
+  // scratch (floats): wmax[2][4][8] @0, merge flag @64, dq[2][8] @72, lsum[4][8] @88
+  float* wmax = scratch;
+  volatile int* flag = reinterpret_cast<volatile int*>(scratch + 64);
+  float* dqs = scratch + 72;
+  float* lsum = scratch + 88;
+  volatile int* vote = reinterpret_cast<volatile int*>(scratch + 124);  // [2][4]
+
+  int stage = 0;
+  uint32_t n = 0;  // tiles consumed so far: S / P buffer = n & 1
+  if (src.count > 0) {
+    const Segment s0 = seg_get(src, seg_cache, 0);
+    tc5_prepare_q<QT>(p, s0, qbufs, dqs, tid);
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bars.q_ready[0]);
+  }
+  for (int k = 0; k < src.count; ++k) {
+    const Segment sg = seg_get(src, seg_cache, k);
+    named_bar_sync(1, 128);  // dq of segment k visible; scratch of segment k-1 no longer read
+    float mul[8], pre[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = dqs[(k & 1) * 8 + j];
+      mul[j] = d * p.sm_scale_log2;
+      pre[j] = d * cap_pre;
+    }
+    if (k + 1 < src.count) {  // query of the next segment, so the MMA warp can run ahead
+      const Segment sn = seg_get(src, seg_cache, k + 1);
+      tc5_prepare_q<QT>(p, sn, qbufs + ((k + 1) & 1) * 4096, dqs + ((k + 1) & 1) * 8, tid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.q_ready[(k + 1) & 1]);
+    }
+    float rho[8], l[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { rho[j] = kNegInf; l[j] = 0.f; }
+
+    for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
+      const uint32_t b = n & 1u;
+      const int tok = tile * G::TT + tid;
+      const bool valid = tok >= sg.tok_lo && tok < sg.tok_hi;
+      float x[8];
+      {
+        mbar_wait(bars.s_ready[b], (n >> 1) & 1u);
+        FI_TRACE_IF(tid == 0 && n == 0, 5);
+        tc5::fence_after_sync();
+        float c[32];
+        tc5::ld_x32(tmem + lane_base + kTc5ColS + 32u * b, c);
+        tc5::wait_ld();
+        tc5::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bars.s_free[b]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float sdot = c[j] + c[8 + j] + c[16 + j];
+          const float v = use_cap ? cap_post * tanhf_approx(sdot * pre[j]) : sdot * mul[j];
+          x[j] = valid ? v : kNegInf;
+        }
+      }
+      // Does any logit of this tile exceed rho by more than 2^kTc5Bump?  One vote per warp and one
+      // CTA barrier in the common case; the exact per-head maxima are only reduced when rho moves.
+      bool over = false;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) over |= x[j] > rho[j] + kTc5Bump;
+      const bool wover = __any_sync(0xffffffffu, over);
+      if (lane == 0) vote[b * 4 + warp] = wover ? 1 : 0;
+      named_bar_sync(2, 128);
+      const bool bump = (vote[b * 4] | vote[b * 4 + 1] | vote[b * 4 + 2] | vote[b * 4 + 3]) != 0;
+      float mt[8];
+      if (bump) {  // CTA-uniform
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float m = x[j];
+#pragma unroll
+          for (int sft = 16; sft > 0; sft >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, sft));
+          mt[j] = m;
+        }
+        float* wm = wmax + b * 32;
+        if (lane < 8) {
+          float mine = mt[0];
+#pragma unroll
+          for (int j = 1; j < 8; ++j) mine = lane == j ? mt[j] : mine;
+          wm[warp * 8 + lane] = mine;
+        }
+        named_bar_sync(3, 128);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          mt[j] = fmaxf(fmaxf(wm[j], wm[8 + j]), fmaxf(wm[16 + j], wm[24 + j]));
+      }
+      if (bump) {  // CTA-uniform: every thread sees the same maxima
+        float alpha[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float rn = mt[j] > rho[j] + kTc5Bump ? mt[j] : rho[j];
+          alpha[j] = ex2f(rho[j] - rn);
+          l[j] *= alpha[j];
+          rho[j] = rn;
+        }
+        if (tile != sg.tile_begin) {
+          // O in TMEM is relative to the old rho: wait for P.V of the previous tile, rescale
+          mbar_wait(bars.p_free[b ^ 1u], ((n - 1) >> 1) & 1u);
+          tc5::fence_after_sync();
+          float o[16];
+          tc5::ld_x16(tmem + lane_base + kTc5ColO, o);
+          tc5::wait_ld();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { o[j] *= alpha[j]; o[8 + j] *= alpha[j]; }
+          tc5::st_x16(tmem + lane_base + kTc5ColO, o);
+          tc5::wait_st();
+          tc5::fence_before_sync();
+        }
+      }
+      // probabilities -> e4m3 hi / lo, one 16-byte row per token
+      uint32_t w[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float p0 = valid ? ex2f(x[2 * i] - rho[2 * i] + kTc5PShift) : 0.f;
+        const float p1 = valid ? ex2f(x[2 * i + 1] - rho[2 * i + 1] + kTc5PShift) : 0.f;
+        l[2 * i] += p0;
+        l[2 * i + 1] += p1;
+        w[i] = split_e4m3x2(p0, p1);  // hi pair in bits 0-15, lo pair in bits 16-31
+      }
+      uint4 row;
+      row.x = (w[0] & 0xffffu) | (w[1] << 16);
+      row.y = (w[2] & 0xffffu) | (w[3] << 16);
+      row.z = (w[0] >> 16) | (w[1] & 0xffff0000u);
+      row.w = (w[2] >> 16) | (w[3] & 0xffff0000u);
+      mbar_wait(bars.p_free[b], ((n >> 1) & 1u) ^ 1u);  // P.V of tile n-2 done with this buffer
+      *reinterpret_cast<uint4*>(pbufs + b * 2048 + tid * 16) = row;
+      if (tok >= sg.tok_hi) {
+        // this token's V row was not (validly) loaded: zero it so that 0 * junk cannot be NaN
+        uint4* vrow = reinterpret_cast<uint4*>(smem_ring + stage * G::STAGE_BYTES + G::KV_BYTES +
+                                               tid * 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) vrow[i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.p_ready[b]);
+      ++n;
+      if (++stage == num_stages) stage = 0;
+    }
+
+    FI_TRACE_IF(tid == 0 && k == src.count - 1, 6);
+    // ---- segment epilogue: thread tid <-> head-dim index d = tid (TMEM lane of O) ---------------
+    float o8[8];
+    if (sg.tile_end > sg.tile_begin) {
+      mbar_wait(bars.p_free[(n - 1) & 1u], ((n - 1) >> 1) & 1u);  // P.V of the last tile complete
+      tc5::fence_after_sync();
+      float o[16];
+      tc5::ld_x16(tmem + lane_base + kTc5ColO, o);
+      tc5::wait_ld();
+      tc5::fence_before_sync();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o8[j] = o[j] + o[8 + j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o8[j] = 0.f;
+    }
+    float L[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = l[j];
+#pragma unroll
+      for (int sft = 16; sft > 0; sft >>= 1) s += __shfl_xor_sync(0xffffffffu, s, sft);
+      L[j] = s;
+    }
+    if (lane < 8) {
+      float mine = L[0];
+#pragma unroll
+      for (int j = 1; j < 8; ++j) mine = lane == j ? L[j] : mine;
+      lsum[warp * 8 + lane] = mine;
+    }
+    named_bar_sync(3, 128);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) L[j] = (lsum[j] + lsum[8 + j]) + (lsum[16 + j] + lsum[24 + j]);
+
+    const bool direct = sg.slot < 0;
+    const int64_t hq = (int64_t)sg.request * p.num_qo_heads + sg.kv_head * GS;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (j < GS) {
+        const bool any = L[j] > 0.f;
+        // numerator and denominator both carry the 2^kTc5PShift scale of p
+        const float val = any ? o8[j] * ((direct ? p.v_scale : 1.f) / L[j]) : 0.f;
+        const float lse2 = any ? rho[j] + lg2f(L[j]) - kTc5PShift : kNegInf;
+        if (direct) {
+          if (QT == 1) static_cast<__nv_bfloat16*>(p.o)[(hq + j) * HD + tid] = __float2bfloat16_rn(val);
+          else static_cast<__half*>(p.o)[(hq + j) * HD + tid] = __float2half_rn(val);
+          if (p.lse != nullptr && tid == j) p.lse[hq + j] = lse2;
+        } else {
+          p.tmp_o[((int64_t)sg.slot * GS + j) * HD + tid] = val;
+          if (tid == j) p.tmp_lse[(int64_t)sg.slot * GS + j] = lse2;
+        }
+      }
+    }
+    FI_TRACE_IF(tid == 0 && k == src.count - 1, 7);
+    if (sg.merge_unit >= 0) {  // CTA-uniform: fused split-KV merge, last arriver merges
+      __threadfence();
+      named_bar_sync(2, 128);
+      if (tid == 0) {
+        const int cnt = __ldg(&p.merge_units[sg.merge_unit].count);
+        const int last = atomicAdd(p.merge_counters + sg.merge_unit, 1) == cnt - 1;
+        if (last) p.merge_counters[sg.merge_unit] = 0;
+        *flag = last;
+      }
+      named_bar_sync(3, 128);
+      if (*flag) {
+        __threadfence();
+        const int4 mu = __ldg(reinterpret_cast<const int4*>(p.merge_units + sg.merge_unit));
+        merge_unit_cta<QT, HD>(p, mu.x, mu.y, mu.z, mu.w, tid);
+        FI_TRACE_IF(tid == 0 && k == src.count - 1, 9);
+      }
+    }
+    FI_TRACE_IF(tid == 0 && k == src.count - 1, 8);
+  }
+}
+
+// QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 1 = e4m3, 2 = e5m2 KV.  head_dim 128, TMA-eligible pages.
+template <int QT, int KVF>
+__global__ void __launch_bounds__(kTc5Threads, 2)
+    paged_decode_tc5_kernel(const __grid_constant__ DecodeParams p,
+                            const __grid_constant__ CUtensorMap kmap,
+                            const __grid_constant__ CUtensorMap vmap) {
+  using G = TileGeom<KVF, 128>;
+  using L = SmemLayout<KVF, 128>;
+  static_assert(L::SCRATCH_O >= 2 * 4096 + 2 * 2048, "Q / P buffers do not fit the scratch region");
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t pad = ((raw + 1023u) & ~1023u) - raw;
+  uint8_t* base = smem_raw + pad;
+  const uint32_t ring = raw + pad;
+  const int ring_bytes = p.num_stages * G::STAGE_BYTES;
+  uint8_t* qbufs = base + ring_bytes;            // 2 x 4 KiB, 1024-aligned
+  uint8_t* pbufs = qbufs + 2 * 4096;             // 2 x 2 KiB
+  float* scratch = reinterpret_cast<float*>(base + ring_bytes + L::SCRATCH_O);
+  Segment* seg_cache =
+      reinterpret_cast<Segment*>(base + ring_bytes + L::SCRATCH_O + L::SCRATCH_ML);
+  const uint32_t full_bar = ring + ring_bytes + L::SCRATCH_O + L::SCRATCH_ML + L::SEG_BYTES;
+  const uint32_t empty_bar = full_bar + 8 * kMaxStages;
+  const Tc5Bars bars = tc5_bars(empty_bar + 8 * kMaxStages);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(scratch + 120);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  FI_TRACE_IF(tid == 0, 0);
+  // TMEM allocation (warp 1) overlaps barrier setup (thread 0) and the work-list fetch
+  if (warp == 1) tc5::tmem_alloc(smem_u32(tmem_slot), kTc5TmemCols);
+  if (tid == 0) {
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);  // one tcgen05.commit per tile
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bars.s_ready[i], 1);
+      mbar_init(bars.s_free[i], 4);
+      mbar_init(bars.p_ready[i], 4);
+      mbar_init(bars.p_free[i], 1);
+      mbar_init(bars.q_ready[i], 4);
+    }
+    fence_mbar_init();
+    tma_prefetch_desc(&kmap);
+    tma_prefetch_desc(&vmap);
+  }
+  const SegSource src = seg_source_init(p, G::TT);
+  for (int i = tid; i < min(src.count, kSegCache); i += blockDim.x) seg_cache[i] = seg_make(src, i);
+  tc5::fence_before_sync();
+  __syncthreads();
+  tc5::fence_after_sync();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+  FI_TRACE_IF(tid == 0, 1);
+  if (src.count == 0) {
+    if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);
+    return;
+  }
+  if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
+  FI_TRACE_IF(tid == 0, 2);
+
+  if (warp < 4) {
+    tc5_softmax<QT, KVF>(p, src, seg_cache, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
+  } else if (warp == 4) {
+    produce_tma<KVF, 128>(p, src, seg_cache, &kmap, &vmap, ring, full_bar, empty_bar);
+  } else {
+    tc5_issue<KVF>(p, src, seg_cache, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar,
+                   bars, tmem);
+  }
+  if (p.enable_pdl) pdl_launch_dependents();
+  tc5::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);
+}
+
+}  // namespace fib200

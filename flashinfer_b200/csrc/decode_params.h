@@ -35,8 +35,22 @@ struct alignas(16) Segment {
   int32_t tok_lo;
   int32_t tok_hi;
   int32_t merge_unit;  // index of the MergeUnit this partial belongs to (-1 when slot < 0)
+  int32_t page_base;   // kv_indptr[request]: first entry of the request in the page table
+  int32_t pad[3];
 };
-static_assert(sizeof(Segment) == 32, "Segment must be 32 bytes");
+static_assert(sizeof(Segment) == 48, "Segment must be 48 bytes");
+
+// Per-CTA head of the work list: the CTA's segment range plus its first kCtaInlineSegs segments
+// inline, so that the kernel prologue needs ONE global round trip before the producer can look
+// up page indices (segments beyond the inline ones are read from the list).
+constexpr int kCtaInlineSegs = 3;
+struct alignas(16) CtaHead {
+  int32_t first;  // index of the CTA's first segment in the list
+  int32_t count;
+  int32_t pad[2];
+  Segment seg[kCtaInlineSegs];
+};
+static_assert(sizeof(CtaHead) == 160, "CtaHead must be 160 bytes");
 
 // A (request, kv_head) unit whose KV range was split over several CTAs: partial
 // slots [slot_begin, slot_begin + count) are merged into o[request, kv_head*G ..].
@@ -85,6 +99,7 @@ enum PlanInfoSlot {
   kPiStages,
   kPiIntBytesUsed,
   kPiOffCounters,   // int32 arrival counters, one per merge unit (fused split-KV merge)
+  kPiOffCtaHeads,
   kPiLen
 };
 constexpr int64_t kPlanMagic = 0xF1B2000001LL;
@@ -108,7 +123,8 @@ struct DecodeParams {
   int32_t tma_h_first;   // TMA map dim order: 1 = (D, h, n, page), 0 = (D, n, h, page)
   // work list (explicit) ...
   const PlanHeader* header;
-  const int32_t* cta_seg_indptr;
+  const int32_t* cta_seg_indptr;   // host-side / test view; the kernels read cta_heads
+  const CtaHead* cta_heads;
   const Segment* segments;
   // ... or implicit uniform mode (single request, contiguous KV): segments are
   // derived in closed form from these (header == nullptr).
@@ -130,6 +146,7 @@ struct DecodeParams {
   float soft_cap;          // <= 0 disabled
   float sm_scale;          // plain sm_scale (soft-cap path)
   int32_t enable_pdl;
+  int32_t l2_prefetch;     // TMA producer also prefetches tiles beyond the ring into L2
 };
 
 struct MergeParams {

@@ -46,8 +46,7 @@ KernelConfig choose_config(int kvf, int head_dim) {
   const int es = kvf == 0 ? 2 : 1;
   const int stage = 2 * tile_tokens(kvf) * head_dim * es;
   const int fixed = 1024 + (kConsumerWarps - 1) * head_dim * 32 /*scratch o*/ +
-                    kConsumerWarps * kMaxGroup * 8 + 16 + kSegCache * (int)sizeof(Segment) +
-                    2 * kMaxStages * 8;
+                    768 + kSegCache * (int)sizeof(Segment) + 2 * kMaxStages * 8 + 128;
   const int sm_total = 233472;  // 228 KiB per SM, each resident CTA reserves 1 KiB
   KernelConfig c;
   c.ctas_per_sm = tuning().ctas_per_sm;
@@ -170,6 +169,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   const size_t off_header = off; off = align16(off + sizeof(PlanHeader));
   const size_t off_indptr = off; off = align16(off + (size_t)(num_ctas + 1) * 4);
   const size_t off_counters = off; off = align16(off + (size_t)max_merge * 4);
+  const size_t off_heads = off;  off = align16(off + (size_t)num_ctas * sizeof(CtaHead));
   const size_t off_segs = off;   off = align16(off + (size_t)max_segs * sizeof(Segment));
   const size_t off_merge = off;  off = align16(off + (size_t)max_merge * sizeof(MergeUnit));
   const size_t int_need = off;
@@ -214,6 +214,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
       const int64_t nt = ntile[b];
       Segment s;
       s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b]; s.merge_unit = -1;
+      s.page_base = indptr_host[b]; s.pad[0] = s.pad[1] = s.pad[2] = 0;
       if (nt == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
         s.tile_begin = s.tile_end = 0; s.slot = -1;
         segs[nseg++] = s;
@@ -255,6 +256,18 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   if (nseg > max_segs || nmerge > max_merge || nslot > max_slots)
     return fail(FI_ERR_WORKSPACE, "internal planner overflow (%lld segs, %lld merges, %lld slots)",
                 (long long)nseg, (long long)nmerge, (long long)nslot);
+  // per-CTA heads: segment range + the first segments inline (one round trip in the prologue)
+  CtaHead* heads = reinterpret_cast<CtaHead*>(host + off_heads);
+  for (int64_t i = 0; i < num_ctas; ++i) {
+    CtaHead& hd = heads[i];
+    hd.first = cta_indptr[i];
+    hd.count = cta_indptr[i + 1] - cta_indptr[i];
+    hd.pad[0] = hd.pad[1] = 0;
+    for (int j = 0; j < kCtaInlineSegs; ++j) {
+      if (j < hd.count) hd.seg[j] = segs[hd.first + j];
+      else memset(&hd.seg[j], 0, sizeof(Segment));
+    }
+  }
   hdr->num_ctas_used = (int32_t)num_ctas;  // every CTA has a (possibly empty) indptr entry
   hdr->num_segments = (int32_t)nseg;
   hdr->num_merge_units = (int32_t)nmerge;
@@ -297,6 +310,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   // second launch (graph mode: fixed upper-bound grid so that replays stay valid)
   pi[kPiMergeGrid] = fused_merge ? 0 : (cuda_graph ? max_merge : nmerge);
   pi[kPiOffCounters] = (int64_t)off_counters;
+  pi[kPiOffCtaHeads] = (int64_t)off_heads;
   pi[kPiTotalTiles] = total_tiles;
   pi[kPiWindowLeft] = window_left;
   pi[kPiStages] = cfg.stages;

@@ -94,7 +94,11 @@ class MergeUnit(C.Structure):
 PI = dict(magic=0, num_ctas=1, num_segments=2, num_merge=3, num_slots=4, off_header=5,
           off_cta_indptr=6, off_segments=7, off_merge=8, off_tmp_o=9, off_tmp_lse=10,
           batch_size=11, hq=12, hkv=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
-          cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23)
+          cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23,
+          off_counters=24, off_cta_heads=25)
+SEG_BYTES = 48    # sizeof(Segment)
+HEAD_BYTES = 160  # sizeof(CtaHead)
+INLINE_SEGS = 3   # kCtaInlineSegs
 TILE = 64        # tokens per tile for 16-bit KV (csrc/decode_params.h tile_tokens)
 TILE_FP8 = 128   # ... and for fp8 KV
 
@@ -122,10 +126,24 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
     ncta = int(info[PI["num_ctas"]])
     cta_indptr = ws[info[PI["off_cta_indptr"]]:info[PI["off_cta_indptr"]] + 4 * (ncta + 1)].view(np.int32).copy()
     nseg = int(hdr[1])
-    segs = ws[info[PI["off_segments"]]:info[PI["off_segments"]] + 32 * nseg].view(np.int32).reshape(nseg, 8).copy()
+    # Segment records are 48 bytes (12 int32): 8 work fields, page_base, 3 pad
+    seg_full = ws[info[PI["off_segments"]]:info[PI["off_segments"]] + SEG_BYTES * nseg].view(np.int32)
+    seg_full = seg_full.reshape(nseg, SEG_BYTES // 4).copy()
+    segs = seg_full[:, :8].copy()
     nm = int(hdr[2])
     merges = ws[info[PI["off_merge"]]:info[PI["off_merge"]] + 16 * nm].view(np.int32).reshape(nm, 4).copy()
-    return 0, "", dict(info=info, header=hdr.copy(), cta_indptr=cta_indptr, segments=segs, merges=merges)
+    # per-CTA heads (160 bytes): first, count, 2 pad, then kCtaInlineSegs inline Segment records
+    heads = ws[info[PI["off_cta_heads"]]:info[PI["off_cta_heads"]] + HEAD_BYTES * ncta].view(np.int32)
+    heads = heads.reshape(ncta, HEAD_BYTES // 4).copy()
+    # structural checks that need the raw records
+    assert np.array_equal(seg_full[:, 8], ip[segs[:, 0]]), "page_base != kv_indptr[request]"
+    assert np.array_equal(heads[:, 0], cta_indptr[:-1]) and np.array_equal(heads[:, 1], np.diff(cta_indptr))
+    for c in range(ncta):
+        for k in range(min(int(heads[c, 1]), INLINE_SEGS)):
+            inl = heads[c, 4 + 12 * k:4 + 12 * (k + 1)]
+            assert np.array_equal(inl, seg_full[heads[c, 0] + k]), "inline segment != list segment"
+    return 0, "", dict(info=info, header=hdr.copy(), cta_indptr=cta_indptr, segments=segs, merges=merges,
+                       cta_heads=heads)
 
 
 def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1, tile=TILE):
