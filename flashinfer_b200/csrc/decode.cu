@@ -166,16 +166,6 @@ static int launch_tc5(const DecodeParams& p, const CUtensorMap& km, const CUtens
   return FI_OK;
 }
 
-static int use_l2_prefetch() {
-  static const int on = [] {
-    // off by default: measured on B200 it LOWERS throughput (C2 192 -> 298 us, C3 401 -> 628 us;
-    // the prefetch boxes compete with the demand boxes in the TMA / L2 request path)
-    const char* e = getenv("FI_B200_L2_PREFETCH");
-    return (e != nullptr && e[0] == '1') ? 1 : 0;
-  }();
-  return on;
-}
-
 static bool use_tc5() {
   static const bool on = [] {
     const char* e = getenv("FI_B200_FP8_TC5");
@@ -286,9 +276,9 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.rows_per_box = page_size < TT ? page_size : TT;
   p.tma_h_first = kv_stride_h < kv_stride_n;
   p.header = reinterpret_cast<const PlanHeader*>(iw + plan_info[kPiOffHeader]);
-  p.cta_seg_indptr = reinterpret_cast<const int32_t*>(iw + plan_info[kPiOffCtaIndptr]);
-  p.cta_heads = reinterpret_cast<const CtaHead*>(iw + plan_info[kPiOffCtaHeads]);
-  p.segments = reinterpret_cast<const Segment*>(iw + plan_info[kPiOffSegments]);
+  p.item_heads = reinterpret_cast<const ItemHead*>(iw + plan_info[kPiOffItemHeads]);
+  p.work_counter = reinterpret_cast<int32_t*>(iw + plan_info[kPiOffWorkCounter]);
+  p.sched_lookahead = sched_tuning().lookahead_tiles;
   p.tmp_o = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpO]);
   p.tmp_lse = reinterpret_cast<float*>(fw + plan_info[kPiOffTmpLse]);
   p.merge_units = reinterpret_cast<const MergeUnit*>(iw + plan_info[kPiOffMerge]);
@@ -301,7 +291,6 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.v_scale = v_scale;
   p.soft_cap = logits_soft_cap;
   p.enable_pdl = enable_pdl;
-  p.l2_prefetch = use_l2_prefetch();
 
   const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
                                 page_size, false, 0, TT);
@@ -404,7 +393,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.num_qo_heads = num_qo_heads; p.group_size = group;
   p.num_stages = cfg.stages;
   p.sm_scale = sm_scale; p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
-  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0; p.l2_prefetch = use_l2_prefetch();
+  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0;
 
   const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
   CUtensorMap km, vm;

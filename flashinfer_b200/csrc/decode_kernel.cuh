@@ -38,6 +38,13 @@ __device__ __forceinline__ void fi_trace(int slot) {
     g_fi_trace[blockIdx.x * kTraceSlots + slot] = t;
   }
 }
+__device__ __forceinline__ void fi_trace_smid() {
+  if (blockIdx.x < kTraceCtas) {
+    unsigned id;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(id));
+    g_fi_trace[blockIdx.x * kTraceSlots + 15] = id + 1;
+  }
+}
 #define FI_TRACE(slot) fi_trace(slot)
 #define FI_TRACE_IF(cond, slot) do { if (cond) fi_trace(slot); } while (0)
 #else
@@ -85,26 +92,82 @@ __device__ __forceinline__ uint32_t swz(int row, int chunk) {
                     (((chunk & 7) ^ (row & 7)) << 4));
 }
 
-// ---- segment source: explicit work list or closed-form uniform split --------
+// ---- segment queue ---------------------------------------------------------------
+// A CTA works through a run-time sequence of segments: those of item blockIdx.x, then those of
+// every item it draws from the plan's ticket counter.  One warp (the "feeder": the TMA producer
+// warp, or warp 0 of the cp.async producers) draws tickets, fetches item heads / list segments
+// and publishes them into a shared-memory ring of kSegCache Segment records; all other roles
+// read the ring.  Control words (ints in shared memory):
+constexpr int kQPub = 0;    // segments published so far, | kQFinal once nothing more will come
+constexpr int kQDone0 = 1;  // consumer group: ring entries below this index are no longer read
+constexpr int kQDone1 = 2;  // second reader (cp.async producer warp 1 / tcgen05 issuer)
+constexpr int kQPeek = 3;   // tcgen05 softmax: "segment k + 1 is already published" broadcast
+constexpr int kQFinal = 1 << 30;
+constexpr int kQNoReader = 0x3fffffff;
+constexpr int kQueueCtlFloat = 160;  // offset of the control words in the warp scratch (floats)
+constexpr int kMergeDescFloat = 168; // {go, request, kv_head, slot_begin, count} of a posted merge
+
+// In the implicit mode (single request, header == nullptr) the sequence is static and in closed
+// form: nothing is drawn, the ring holds the first kSegCache segments and later ones are recomputed.
 struct SegSource {
   const DecodeParams* p;
-  int first;  // explicit: index of this CTA's first segment
-  int count;
-  long long imp_begin, imp_end;  // implicit: stream range of this CTA
-  int tt;                        // tokens per tile
+  Segment* cache;
+  volatile int* ctl;
+  bool implicit;
+  int first, head_count, num_items;  // explicit: head of item blockIdx.x
+  int count;                         // implicit: segments of this CTA
+  long long imp_begin, imp_end;      // implicit: stream range of this CTA
+  int tt;                            // tokens per tile
 };
 
-__device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int tt) {
+// closed-form segment k of this CTA (implicit mode only)
+__device__ __forceinline__ Segment seg_make(const SegSource& s, int k) {
+  const DecodeParams& p = *s.p;
+  Segment g;
+  g.request = 0; g.merge_unit = -1; g.page_base = 0;
+  g.tok_lo = p.imp_tok_lo; g.tok_hi = p.imp_tok_hi;
+  const int nt = p.imp_tiles;
+  if (nt == 0) {
+    g.kv_head = k; g.tile_begin = g.tile_end = 0; g.slot = -1;
+  } else {
+    const int tb0 = p.imp_tok_lo / s.tt;  // first tile of the window
+    const long long u = s.imp_begin / nt + k;
+    const long long ub = u * nt, ue = ub + nt;
+    const long long b = s.imp_begin > ub ? s.imp_begin : ub;
+    const long long e = s.imp_end < ue ? s.imp_end : ue;
+    g.kv_head = (int)u;
+    g.tile_begin = tb0 + (int)(b - ub);
+    g.tile_end = tb0 + (int)(e - ub);
+    const bool whole = (b == ub) && (e == ue);
+    g.slot = whole ? -1 : (int)(blockIdx.x + u);
+  }
+  return g;
+}
+
+// Called by every thread of the CTA before the first __syncthreads(): reads the head of item
+// blockIdx.x (one global round trip), publishes its inline segments and sets up the control words.
+// has_reader1: the kernel has a second ring reader that reports progress in kQDone1.
+__device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int tt, Segment* cache,
+                                                     float* scratch, bool has_reader1) {
   SegSource s;
   s.p = &p;
+  s.cache = cache;
+  s.ctl = reinterpret_cast<volatile int*>(scratch + kQueueCtlFloat);
   s.tt = tt;
-  s.first = 0;
-  s.count = 0;
+  s.implicit = p.header == nullptr;
+  s.first = s.head_count = s.num_items = s.count = 0;
   s.imp_begin = s.imp_end = 0;
-  if (p.header != nullptr) {  // explicit work list: the grid is exactly the planned CTA count
-    const int2 h = __ldg(reinterpret_cast<const int2*>(p.cta_heads + blockIdx.x));
+  const int tid = threadIdx.x;
+  int pub0;
+  if (!s.implicit) {
+    const ItemHead* head = p.item_heads + blockIdx.x;  // heads exist for every launched CTA
+    const int4 h = __ldg(reinterpret_cast<const int4*>(head));
     s.first = h.x;
-    s.count = h.y;
+    s.head_count = h.y;
+    s.num_items = h.z;
+    pub0 = min(s.head_count, kItemInlineSegs);
+    if (tid < 3 * pub0)
+      reinterpret_cast<int4*>(cache)[tid] = __ldg(reinterpret_cast<const int4*>(head->seg) + tid);
   } else {
     const long long T = (long long)p.imp_units * p.imp_tiles;
     const long long C = gridDim.x;
@@ -116,67 +179,157 @@ __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int 
       if (s.imp_end > s.imp_begin)
         s.count = (int)((s.imp_end - 1) / p.imp_tiles - s.imp_begin / p.imp_tiles) + 1;
     }
+    for (int i = tid; i < min(s.count, kSegCache); i += blockDim.x) cache[i] = seg_make(s, i);
+    pub0 = s.count | kQFinal;
+  }
+  if (tid == 0) {
+    s.ctl[kQPub] = pub0;
+    s.ctl[kQDone0] = 0;
+    s.ctl[kQDone1] = has_reader1 ? 0 : kQNoReader;
+    s.ctl[kQPeek] = 0;
   }
   return s;
 }
 
-__device__ __forceinline__ Segment seg_make(const SegSource& s, int k) {
-  const DecodeParams& p = *s.p;
-  Segment g;
-  if (p.header != nullptr) {
-    // the first kCtaInlineSegs segments sit in the CTA head (same round trip as first / count)
-    const int4* src = reinterpret_cast<const int4*>(
-        k < kCtaInlineSegs ? &p.cta_heads[blockIdx.x].seg[k] : p.segments + s.first + k);
-    int4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2);
-    g.request = a.x; g.kv_head = a.y; g.tile_begin = a.z; g.tile_end = a.w;
-    g.slot = b.x; g.tok_lo = b.y; g.tok_hi = b.z; g.merge_unit = b.w;
-    g.page_base = c.x;
-  } else {
-    g.request = 0; g.merge_unit = -1; g.page_base = 0;
-    g.tok_lo = p.imp_tok_lo; g.tok_hi = p.imp_tok_hi;
-    const int nt = p.imp_tiles;
-    if (nt == 0) {
-      g.kv_head = k; g.tile_begin = g.tile_end = 0; g.slot = -1;
-    } else {
-      const int tb0 = p.imp_tok_lo / s.tt;  // first tile of the window
-      const long long u = s.imp_begin / nt + k;
-      const long long ub = u * nt, ue = ub + nt;
-      const long long b = s.imp_begin > ub ? s.imp_begin : ub;
-      const long long e = s.imp_end < ue ? s.imp_end : ue;
-      g.kv_head = (int)u;
-      g.tile_begin = tb0 + (int)(b - ub);
-      g.tile_end = tb0 + (int)(e - ub);
-      const bool whole = (b == ub) && (e == ue);
-      g.slot = whole ? -1 : (int)(blockIdx.x + u);
-    }
-  }
-  return g;
+// segment k, which the caller knows to be published
+__device__ __forceinline__ Segment seg_read(const SegSource& s, int k) {
+  if (s.implicit && k >= kSegCache) return seg_make(s, k);
+  return s.cache[k & (kSegCache - 1)];
 }
 
-__device__ __forceinline__ Segment seg_get(const SegSource& s, const Segment* cache, int k) {
-  if (k < kSegCache) return cache[k];
-  return seg_make(s, k);
+// is segment k published yet?  (non-blocking)
+__device__ __forceinline__ bool seg_peek(const SegSource& s, int k) {
+  if (s.implicit) return k < s.count;
+  const bool yes = k < (s.ctl[kQPub] & (kQFinal - 1));
+  __threadfence_block();
+  return yes;
+}
+
+// wait for segment k; false when the CTA's sequence ended before it
+__device__ __forceinline__ bool seg_fetch(const SegSource& s, int k, Segment& out) {
+  if (s.implicit) {
+    if (k >= s.count) return false;
+  } else {
+    for (;;) {
+      const int v = s.ctl[kQPub];
+      if (k < (v & (kQFinal - 1))) break;
+      if (v & kQFinal) return false;
+      __nanosleep(40);
+    }
+    __threadfence_block();
+  }
+  out = seg_read(s, k);
+  return true;
+}
+
+// ---- feeder: draws items and publishes their segments (one warp, converged) -------------
+// One latency-bound step per call — draw a ticket / load the item head or 8 list segments /
+// publish — so that called once per tile from the producer loop the global round trips hide
+// behind the tile traffic.  A new item is drawn when at most sched_lookahead published tiles
+// are still to be issued: late enough that a slow CTA does not hoard tail items.
+struct Feeder {
+  int pub, fin, item_first, item_count, item_next, num_items, tiles_pub, phase, ticket, nload;
+  int4 v;
+};
+
+__device__ __forceinline__ void feeder_init(Feeder& f, const SegSource& s) {
+  f.fin = s.implicit ? 1 : 0;
+  f.pub = s.implicit ? s.count : min(s.head_count, kItemInlineSegs);
+  f.item_first = s.first;
+  f.item_count = s.implicit ? 0 : s.head_count;
+  f.item_next = s.implicit ? 0 : f.pub;
+  f.num_items = s.num_items;
+  f.tiles_pub = 0;
+  if (!s.implicit)
+    for (int i = 0; i < f.pub; ++i) f.tiles_pub += s.cache[i].tile_end - s.cache[i].tile_begin;
+  f.phase = 0;
+  f.ticket = 0;
+  f.nload = 0;
+  f.v = make_int4(0, 0, 0, 0);
+}
+
+__device__ __forceinline__ void feeder_step(Feeder& f, const SegSource& s, int cur_k,
+                                            int tiles_issued, int lane) {
+  if (f.fin) return;
+  const DecodeParams& p = *s.p;
+  if (f.phase >= 2) {  // loaded records -> ring, publish
+    int n, base;
+    if (f.phase == 2) {  // lane 0: head, lanes 1..9: inline segments
+      f.item_first = __shfl_sync(0xffffffffu, f.v.x, 0);
+      f.item_count = __shfl_sync(0xffffffffu, f.v.y, 0);
+      n = min(f.item_count, kItemInlineSegs);
+      base = 1;
+      f.item_next = n;
+    } else {  // lanes 0..3n-1: list segments
+      n = f.nload;
+      base = 0;
+      f.item_next += n;
+    }
+    const int li = lane - base;
+    const bool mine = li >= 0 && li < 3 * n;
+    const int j = li / 3, part = li - 3 * j;
+    if (mine) reinterpret_cast<int4*>(s.cache + ((f.pub + j) & (kSegCache - 1)))[part] = f.v;
+    f.tiles_pub += __reduce_add_sync(0xffffffffu, (mine && part == 0) ? f.v.w - f.v.z : 0);
+    f.pub += n;
+    __syncwarp();
+    __threadfence_block();
+    if (lane == 0) s.ctl[kQPub] = f.pub;
+    f.phase = 0;
+    return;
+  }
+  if (f.phase == 1) {  // ticket -> item head
+    const int t = __shfl_sync(0xffffffffu, f.ticket, 0);
+    const int item = t + (int)gridDim.x;
+    // exactly num_items tickets are drawn per launch (every item past the static ones once,
+    // plus one failing draw per active CTA): the last one re-arms the counter
+    if (t == f.num_items - 1 && lane == 0) *p.work_counter = 0;
+    if (item >= f.num_items) {
+      f.fin = 1;
+      if (lane == 0) s.ctl[kQPub] = f.pub | kQFinal;
+      f.phase = 0;
+      return;
+    }
+    if (lane < 1 + 3 * kItemInlineSegs)
+      f.v = __ldg(reinterpret_cast<const int4*>(p.item_heads + item) + lane);
+    f.phase = 2;
+    return;
+  }
+  // idle: is there room in the ring, and is it time to fetch more?
+  const int done = min(s.ctl[kQDone0], s.ctl[kQDone1]);
+  const bool space = f.pub + kSegRefill <= done + kSegCache;
+  if (f.item_next < f.item_count) {  // rest of the current item, from the list
+    if (space && f.pub - cur_k < kSegRefill) {
+      const int n = min(kSegRefill, f.item_count - f.item_next);
+      const Segment* list =
+          reinterpret_cast<const Segment*>(p.item_heads + max(f.num_items, (int)gridDim.x));
+      if (lane < 3 * n)
+        f.v = __ldg(reinterpret_cast<const int4*>(list + f.item_first + f.item_next) + lane);
+      f.nload = n;
+      f.phase = 3;
+    }
+  } else if (space && f.tiles_pub - tiles_issued <= p.sched_lookahead) {
+    if (lane == 0) f.ticket = atomicAdd(p.work_counter, 1);
+    f.phase = 1;
+  }
+}
+
+// feeder-side: make sure segment k is published (false: the sequence ended before it)
+__device__ __forceinline__ bool feeder_await(Feeder& f, const SegSource& s, int k, int tiles_issued,
+                                             int lane) {
+  while (k >= f.pub && !f.fin) feeder_step(f, s, k, tiles_issued, lane);
+  return k < f.pub;
 }
 
 // ---- producer: per-page TMA boxes -------------------------------------------
 // Runs in one warp (all 32 lanes converged).  Box i of a tile is issued by lane i%32:
 //   i = (kv * NP + panel) * BPT + j,  j = token-block of rows_per_box rows.
-// L2 prefetch: besides the boxes that fill the shared-memory ring, the producer asks TMA to pull
-// the tiles kPrefetchTiles beyond the ring from DRAM into L2 (cp.async.bulk.prefetch.tensor), so a
-// ring slot that frees up is refilled at L2 latency instead of DRAM latency.  The bytes in flight
-// per SM are then no longer capped by the ring (Little's law at ~6.5 TB/s needs > 100 KB per SM).
-constexpr int kPrefetchTiles = 4;
-
-struct TileCursor {  // walks the CTA's (segment, tile) sequence
-  int k, t, t_end, page_base;
-  Segment sg;
-};
-
+// (A variant that also pulled tiles beyond the ring into L2 with cp.async.bulk.prefetch.tensor
+// was measured 1.5x SLOWER on B200 — the prefetch boxes compete with the demand boxes — and
+// was removed; see DESIGN.md.)
 template <int KVF, int HD>
 __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSource& src,
-                                            const Segment* seg_cache, const CUtensorMap* kmap,
-                                            const CUtensorMap* vmap, uint32_t ring,
-                                            uint32_t full_bar, uint32_t empty_bar) {
+                                            const CUtensorMap* kmap, const CUtensorMap* vmap,
+                                            uint32_t ring, uint32_t full_bar, uint32_t empty_bar) {
   using G = TileGeom<KVF, HD>;
   const int lane = threadIdx.x & 31;
   const int rpb = p.rows_per_box;
@@ -185,66 +338,39 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   const int j = lane % bpt;  // same j for every i = lane + 32 k since bpt | 32
   const uint32_t box_bytes = (uint32_t)rpb * 128u;
 
-  auto cursor_load = [&](TileCursor& c) {  // position on segment c.k (skipping empty ones)
-    while (c.k < src.count) {
-      c.sg = seg_get(src, seg_cache, c.k);
-      if (c.sg.tile_end > c.sg.tile_begin) break;
-      ++c.k;
-    }
-    if (c.k < src.count) {
-      c.t = c.sg.tile_begin;
-      c.t_end = c.sg.tile_end;
-      c.page_base = c.sg.page_base;  // planned copy of kv_indptr[request]: no dependent load
-    }
-  };
-  auto cursor_next = [&](TileCursor& c) {
-    if (++c.t >= c.t_end) { ++c.k; cursor_load(c); }
-  };
-  // boxes of tile c.t: page index + first row for this lane's token block j
-  auto tile_geom = [&](const TileCursor& c, int& nvb, int& page, int& row0) {
-    const int tok0 = c.t * G::TT;
-    const int rem = c.sg.tok_hi - tok0;  // > 0 by construction
-    nvb = rem >= G::TT ? bpt : (rem + rpb - 1) / rpb;
-    const int tok = tok0 + j * rpb;
-    page = 0;
-    if (j < nvb) {
-      const int pit = tok >> p.page_shift;
-      page = p.kv_indices ? __ldg(p.kv_indices + c.page_base + pit) : c.page_base + pit;
-    }
-    row0 = tok & p.page_mask;
-  };
-
-  TileCursor cur, pf;
-  cur.k = 0;
-  cursor_load(cur);
-  pf = cur;
-  const bool do_pf = p.l2_prefetch != 0;
-  int ahead = 0;  // tiles between the load cursor and the prefetch cursor
-  if (do_pf) {
-    for (; ahead < p.num_stages && pf.k < src.count; ++ahead) cursor_next(pf);  // the ring covers these
-  }
+  Feeder f;
+  feeder_init(f, src);
+  Segment sg;
+  int k = 0, t = 0, t_end = 0, tiles_issued = 0;
   int stage = 0;
   uint32_t phase = 0;
   [[maybe_unused]] bool first_tile = true;
-  while (cur.k < src.count) {
-    if (do_pf) {
-      while (ahead < p.num_stages + kPrefetchTiles && pf.k < src.count) {
-        int nvb, page, row0;
-        tile_geom(pf, nvb, page, row0);
-        if (j < nvb) {
-          for (int i = lane; i < nbox; i += 32) {
-            const int pn = (i / bpt) % G::NP;
-            const int kv = i / (bpt * G::NP);
-            tma_prefetch_4d(kv ? vmap : kmap, pn * (128 / G::ES), p.tma_h_first ? pf.sg.kv_head : row0,
-                            p.tma_h_first ? row0 : pf.sg.kv_head, page);
-          }
-        }
-        cursor_next(pf);
-        ++ahead;
+  for (;;) {
+    feeder_step(f, src, k, tiles_issued, lane);
+    if (t >= t_end) {  // next segment that has tiles
+      bool more;
+      for (;;) {
+        more = feeder_await(f, src, k, tiles_issued, lane);
+        if (!more) break;
+        sg = seg_read(src, k);
+        if (sg.tile_end > sg.tile_begin) break;
+        ++k;
       }
+      if (!more) break;
+      t = sg.tile_begin;
+      t_end = sg.tile_end;
     }
-    int nvb, page, row0;
-    tile_geom(cur, nvb, page, row0);
+    // boxes of tile t: page index + first row for this lane's token block j
+    const int tok0 = t * G::TT;
+    const int rem = sg.tok_hi - tok0;  // > 0 by construction
+    const int nvb = rem >= G::TT ? bpt : (rem + rpb - 1) / rpb;
+    const int tok = tok0 + j * rpb;
+    int page = 0;
+    if (j < nvb) {
+      const int pit = tok >> p.page_shift;
+      page = p.kv_indices ? __ldg(p.kv_indices + sg.page_base + pit) : sg.page_base + pit;
+    }
+    const int row0 = tok & p.page_mask;
     FI_TRACE_IF(lane == 0 && first_tile && page >= 0, 3);
     mbar_wait(empty_bar + 8 * stage, phase ^ 1);
     if (lane == 0) mbar_arrive_expect_tx(full_bar + 8 * stage, 2u * G::NP * nvb * box_bytes);
@@ -255,24 +381,24 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
         const int pn = (i / bpt) % G::NP;
         const int kv = i / (bpt * G::NP);
         tma_load_4d(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
-                    full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? cur.sg.kv_head : row0,
-                    p.tma_h_first ? row0 : cur.sg.kv_head, page);
+                    full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? sg.kv_head : row0,
+                    p.tma_h_first ? row0 : sg.kv_head, page);
       }
     }
     __syncwarp();
     FI_TRACE_IF(lane == 0 && first_tile, 4);
     first_tile = false;
     if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
-    cursor_next(cur);
-    --ahead;
+    ++tiles_issued;
+    if (++t >= t_end) ++k;
   }
 }
 
 // ---- producer: 16-byte cp.async gathers (any page size / stride) -------------
-// Runs in kCpAsyncProducerThreads threads (ptid = 0 ..).  Rows past tok_hi are zero-filled.
+// Runs in kCpAsyncProducerThreads threads (ptid = 0 ..): warp 0 is also the feeder, warp 1 reads
+// the ring like a consumer.  Rows past tok_hi are zero-filled.
 template <int KVF, int HD>
-__device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const SegSource& src,
-                                                const Segment* seg_cache, int ptid,
+__device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const SegSource& src, int ptid,
                                                 uint32_t ring, uint32_t full_bar,
                                                 uint32_t empty_bar) {
   using G = TileGeom<KVF, HD>;
@@ -282,15 +408,30 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
   static_assert(kCpAsyncProducerThreads % CPR == 0 && G::TT % RPP == 0, "bad cp.async geometry");
   const int c = ptid % CPR;
   const int r0 = ptid / CPR;
+  const int lane = ptid & 31;
+  const bool feeds = ptid < 32;
   const char* kb = static_cast<const char*>(p.k);
   const char* vb = static_cast<const char*>(p.v);
+  Feeder f;
+  feeder_init(f, src);
+  int tiles_issued = 0;
   int stage = 0;
   uint32_t phase = 0;
-  for (int k = 0; k < src.count; ++k) {
-    const Segment sg = seg_get(src, seg_cache, k);
+  for (int k = 0;; ++k) {
+    Segment sg;
+    if (feeds) {
+      feeder_step(f, src, k, tiles_issued, lane);
+      if (!feeder_await(f, src, k, tiles_issued, lane)) break;
+      sg = seg_read(src, k);
+    } else {
+      if (!seg_fetch(src, k, sg)) break;
+      __syncwarp();
+      if (lane == 0) src.ctl[kQDone1] = k + 1;
+    }
     const int page_base = sg.page_base;
     const int64_t head_off = (int64_t)sg.kv_head * p.kv_stride_h + c * (16 / G::ES);
     for (int t = sg.tile_begin; t < sg.tile_end; ++t) {
+      if (feeds) feeder_step(f, src, k, tiles_issued, lane);
       mbar_wait(empty_bar + 8 * stage, phase ^ 1);
       const uint32_t sk = ring + stage * G::STAGE_BYTES;
 #pragma unroll 4
@@ -313,6 +454,7 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
       }
       cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
       if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+      ++tiles_issued;
     }
   }
 }
@@ -547,6 +689,41 @@ __device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int reques
   }
 }
 
+// Deferred arrival check.  A partial's arrival is an acq_rel atomic on the unit's counter whose
+// RESULT is not looked at until the CTA's next segment epilogue (or the end of its sequence), so
+// the L2 round trip hides behind the next segment.  The CTA whose arrival turns out to have been
+// the last one re-arms the counter and merges the unit; all 128 consumer threads take part, so
+// thread 0 posts the decision in shared memory ahead of a CTA barrier.
+struct PendingMerge {
+  int mu, old, cnt, slot, req, head;  // meaningful in thread 0 only
+};
+__device__ __forceinline__ void merge_arrive(const DecodeParams& p, PendingMerge& pm, const Segment& sg) {
+  pm.old = atom_add_acq_rel_gpu(p.merge_counters + sg.merge_unit, 1);
+  pm.mu = sg.merge_unit; pm.cnt = sg.merge_count; pm.slot = sg.merge_slot;
+  pm.req = sg.request; pm.head = sg.kv_head;
+}
+// thread 0, before a barrier of the consumer threads
+__device__ __forceinline__ void merge_post(const DecodeParams& p, PendingMerge& pm, float* scratch) {
+  volatile int* d = reinterpret_cast<volatile int*>(scratch + kMergeDescFloat);
+  const bool go = pm.mu >= 0 && pm.old == pm.cnt - 1;
+  if (go) {
+    p.merge_counters[pm.mu] = 0;
+    d[1] = pm.req; d[2] = pm.head; d[3] = pm.slot; d[4] = pm.cnt;
+  }
+  d[0] = go ? 1 : 0;
+  pm.mu = -1;
+}
+// all consumer threads, after that barrier (and before the next one)
+template <int QT, int HD>
+__device__ __forceinline__ void merge_run_posted(const DecodeParams& p, const float* scratch, int ctid) {
+  const volatile int* d = reinterpret_cast<const volatile int*>(scratch + kMergeDescFloat);
+  if (d[0]) {
+    __threadfence();
+    merge_unit_cta<QT, HD>(p, d[1], d[2], d[3], d[4], ctid);
+    FI_TRACE_IF(ctid == 0, 9);
+  }
+}
+
 // ---- consumer: 4 warps, online softmax + MMA ---------------------------------
 // Per-warp running state per query head j (two heads per lane: 2t, 2t+1):
 //   m[j]  reference exponent of o / l (16-bit KV: the running max; fp8 KV: max(block max,
@@ -554,8 +731,7 @@ __device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int reques
 //         32-token block's maximum and nothing within 2^-18 of it is flushed),
 //   l[j]  sum of exp2(x - m[j]),  o[..] = sum of exp2(x - m[j]) v  (x 256 for fp8 KV).
 template <int QT, int KVF, int HD, int LOADER>
-__device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& src,
-                                        const Segment* seg_cache, uint32_t ring,
+__device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& src, uint32_t ring,
                                         uint32_t full_bar, uint32_t empty_bar, float* scratch_o,
                                         float* scratch_ml) {
   using G = TileGeom<KVF, HD>;
@@ -573,8 +749,15 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 
   int stage = 0;
   uint32_t phase = 0;
-  for (int k = 0; k < src.count; ++k) {
-    const Segment sg = seg_get(src, seg_cache, k);
+  PendingMerge pm;
+  pm.mu = -1; pm.old = pm.cnt = pm.slot = pm.req = pm.head = 0;
+  // 16-bit KV: the query fragments of segment k + 1 are requested at the start of segment k when
+  // that segment is already published (warp-uniform decision), so a boundary costs no round trip
+  [[maybe_unused]] uint32_t qn[NQ][2];
+  [[maybe_unused]] bool have_qn = false;
+  for (int k = 0;; ++k) {
+    Segment sg;
+    if (!seg_fetch(src, k, sg)) break;
     uint32_t qf[NQ][2];
     uint32_t ql[KVF == 0 ? 1 : NQ][2], ql2[KVF == 0 ? 1 : NQ][2];  // fp8: residual query terms
     float mul[2], pre[2];               // logit scale per head column (2t, 2t+1)
@@ -583,7 +766,20 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
                          ((int64_t)sg.request * p.q_stride_n +
                           (int64_t)(sg.kv_head * GS + g) * p.q_stride_h) * 2;
       if constexpr (KVF == 0) {
-        load_q_frags16<HD>(qf, qrow, g < GS, t);
+        if (have_qn) {
+#pragma unroll
+          for (int i = 0; i < NQ; ++i) { qf[i][0] = qn[i][0]; qf[i][1] = qn[i][1]; }
+        } else {
+          load_q_frags16<HD>(qf, qrow, g < GS, t);
+        }
+        have_qn = __shfl_sync(0xffffffffu, seg_peek(src, k + 1) ? 1 : 0, 0) != 0;
+        if (have_qn) {
+          const Segment sn = seg_read(src, k + 1);
+          const char* nrow = static_cast<const char*>(p.q) +
+                             ((int64_t)sn.request * p.q_stride_n +
+                              (int64_t)(sn.kv_head * GS + g) * p.q_stride_h) * 2;
+          load_q_frags16<HD>(qn, nrow, g < GS, t);
+        }
         ql[0][0] = ql[0][1] = ql2[0][0] = ql2[0][1] = 0u;
         mul[0] = mul[1] = p.sm_scale_log2;
         pre[0] = pre[1] = cap_pre;
@@ -725,7 +921,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
       if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
     }
 
-    FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 6);
+    FI_TRACE_IF(threadIdx.x == 0, 6);
     // ---- segment epilogue: merge the 4 warp states, write o/lse or a partial ----
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -740,7 +936,11 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
         scratch_ml[(warp * kMaxGroup + 2 * t + j) * 2 + 1] = l[j];
       }
     }
+    if (threadIdx.x == 0) merge_post(p, pm, scratch_ml);  // arrival of the previous partial
     named_bar_sync(1, kConsumerWarps * 32);
+    if (threadIdx.x == 0) src.ctl[kQDone0] = k + 1;  // every warp holds its copy of segment k
+    FI_TRACE_IF(threadIdx.x == 0, 10);
+    merge_run_posted<QT, HD>(p, scratch_ml, threadIdx.x);
     float M[2], L[2], f[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -767,6 +967,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
         for (int r = 0; r < 4; ++r) dst[(i * 4 + r) * 32] = o[i][r];
     }
     named_bar_sync(2, kConsumerWarps * 32);
+    FI_TRACE_IF(threadIdx.x == 0, 11);
     if (warp == 0) {
 #pragma unroll
       for (int w = 0; w < kConsumerWarps - 1; ++w) {
@@ -822,32 +1023,19 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
             if (g == 0) p.tmp_lse[(int64_t)sg.slot * GS + h0 + j] = lse2[j];
           }
         }
-        if (sg.merge_unit >= 0) {
-          // publish the partial, then count arrivals; the CTA whose partial arrives last
-          // merges the unit and returns the counter to zero for the next run()
-          __threadfence();
+        if (sg.merge_unit >= 0) {  // publish the partial: count the arrival, look at it later
           __syncwarp();
-          if (lane == 0) {
-            const int cnt = __ldg(&p.merge_units[sg.merge_unit].count);
-            const int last = atomicAdd(p.merge_counters + sg.merge_unit, 1) == cnt - 1;
-            if (last) p.merge_counters[sg.merge_unit] = 0;
-            reinterpret_cast<volatile int*>(scratch_ml)[kConsumerWarps * kMaxGroup * 2] = last;
-          }
+          if (lane == 0) merge_arrive(p, pm, sg);
         }
       }
     }
-    FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 7);
-    if (sg.merge_unit >= 0) {  // CTA-uniform
-      named_bar_sync(3, kConsumerWarps * 32);
-      if (reinterpret_cast<volatile int*>(scratch_ml)[kConsumerWarps * kMaxGroup * 2]) {
-        __threadfence();
-        const int4 mu = __ldg(reinterpret_cast<const int4*>(p.merge_units + sg.merge_unit));
-        merge_unit_cta<QT, HD>(p, mu.x, mu.y, mu.z, mu.w, threadIdx.x);
-        FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 9);
-      }
-    }
-    FI_TRACE_IF(threadIdx.x == 0 && k == src.count - 1, 8);
+    FI_TRACE_IF(threadIdx.x == 0, 7);
   }
+  // end of this CTA's sequence: the last arrival is still unchecked
+  if (threadIdx.x == 0) merge_post(p, pm, scratch_ml);
+  named_bar_sync(1, kConsumerWarps * 32);
+  merge_run_posted<QT, HD>(p, scratch_ml, threadIdx.x);
+  FI_TRACE_IF(threadIdx.x == 0, 8);
 }
 
 // threads per CTA: 4 consumer warps + 1 (TMA) or 4 (cp.async) producer warps
@@ -881,6 +1069,9 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
 
   const int tid = threadIdx.x;
   FI_TRACE_IF(tid == 0, 0);
+#ifdef FI_B200_TRACE
+  if (tid == 0) fi_trace_smid();
+#endif
   if (tid == 0) {
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(full_bar + 8 * s, LOADER == 0 ? 1 : BlockDim<LOADER>::kProducerWarps * 32);
@@ -894,22 +1085,19 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   }
   // the work list was written by plan() (a memcpy), not by the preceding kernel, so it
   // may be read before the PDL dependency resolves
-  const SegSource src = seg_source_init(p, G::TT);
-  for (int i = tid; i < min(src.count, kSegCache); i += blockDim.x) seg_cache[i] = seg_make(src, i);
+  const SegSource src = seg_source_init(p, G::TT, seg_cache, scratch_ml, LOADER != 0);
   __syncthreads();
   FI_TRACE_IF(tid == 0, 1);
-  if (src.count == 0) return;
+  if (src.implicit ? src.count == 0 : src.head_count == 0) return;
   if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
   FI_TRACE_IF(tid == 0, 2);
 
   if (tid < kConsumerWarps * 32) {
-    consume<QT, KVF, HD, LOADER>(p, src, seg_cache, ring, full_bar, empty_bar, scratch_o,
-                                 scratch_ml);
+    consume<QT, KVF, HD, LOADER>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
   } else if (LOADER == 0) {
-    produce_tma<KVF, HD>(p, src, seg_cache, &kmap, &vmap, ring, full_bar, empty_bar);
+    produce_tma<KVF, HD>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
   } else {
-    produce_cpasync<KVF, HD>(p, src, seg_cache, tid - kConsumerWarps * 32, ring, full_bar,
-                             empty_bar);
+    produce_cpasync<KVF, HD>(p, src, tid - kConsumerWarps * 32, ring, full_bar, empty_bar);
   }
   if (p.enable_pdl) pdl_launch_dependents();
 }

@@ -109,7 +109,7 @@ __device__ __forceinline__ void tc5_prepare_q(const DecodeParams& p, const Segme
 // ---- MMA issuer (warp 5; one elected lane issues, the warp stays converged) ---------------------
 template <int KVF>
 __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource& src,
-                                          const Segment* seg_cache, uint32_t ring, uint32_t qbufs,
+                                          uint32_t ring, uint32_t qbufs,
                                           uint32_t pbufs, uint32_t full_bar, uint32_t empty_bar,
                                           const Tc5Bars& bars, uint32_t tmem) {
   using G = TileGeom<KVF, 128>;
@@ -145,8 +145,11 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
     pend = false;
   };
 
-  for (int k = 0; k < src.count; ++k) {
-    const Segment sg = seg_get(src, seg_cache, k);
+  for (int k = 0;; ++k) {
+    Segment sg;
+    if (!seg_fetch(src, k, sg)) break;
+    __syncwarp();
+    if (leader) src.ctl[kQDone1] = k + 1;  // this warp holds its copy of segment k
     mbar_wait(bars.q_ready[k & 1], (k >> 1) & 1u);  // every segment: never lag a phase behind
     const uint32_t qb = qbufs + (k & 1) * 4096u;
     for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
@@ -194,7 +197,7 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
 // ---- softmax warps (0-3): thread tid <-> token tid of each tile, TMEM lane tid ------------------
 template <int QT, int KVF>
 __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSource& src,
-                                            const Segment* seg_cache, uint8_t* smem_ring,
+                                            uint8_t* smem_ring,
                                             uint8_t* qbufs, uint8_t* pbufs, float* scratch,
                                             const Tc5Bars& bars, uint32_t tmem, int num_stages) {
   using G = TileGeom<KVF, 128>;
@@ -214,15 +217,25 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
 
   int stage = 0;
   uint32_t n = 0;  // tiles consumed so far: S / P buffer = n & 1
-  if (src.count > 0) {
-    const Segment s0 = seg_get(src, seg_cache, 0);
-    tc5_prepare_q<QT>(p, s0, qbufs, dqs, tid);
-    fence_proxy_async_smem();
-    __syncwarp();
-    if (lane == 0) mbar_arrive(bars.q_ready[0]);
-  }
-  for (int k = 0; k < src.count; ++k) {
-    const Segment sg = seg_get(src, seg_cache, k);
+  PendingMerge pm;
+  pm.mu = -1; pm.old = pm.cnt = pm.slot = pm.req = pm.head = 0;
+  // The query of segment k + 1 is prepared during segment k when that segment is already
+  // published (so the MMA warp can run ahead), else at the top of segment k + 1.  The decision
+  // must be the same in all 128 threads: thread 0 peeks, the barrier broadcasts.
+  bool have_q = false;
+  for (int k = 0;; ++k) {
+    Segment sg;
+    if (!seg_fetch(src, k, sg)) break;
+    if (!have_q) {
+      tc5_prepare_q<QT>(p, sg, qbufs + (k & 1) * 4096, dqs + (k & 1) * 8, tid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.q_ready[k & 1]);
+    }
+    if (tid == 0) {
+      src.ctl[kQPeek] = seg_peek(src, k + 1) ? 1 : 0;
+      src.ctl[kQDone0] = k;  // every thread is past segment k - 1 (barrier 3 of its epilogue)
+    }
     named_bar_sync(1, 128);  // dq of segment k visible; scratch of segment k-1 no longer read
     float mul[8], pre[8];
 #pragma unroll
@@ -231,8 +244,9 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
       mul[j] = d * p.sm_scale_log2;
       pre[j] = d * cap_pre;
     }
-    if (k + 1 < src.count) {  // query of the next segment, so the MMA warp can run ahead
-      const Segment sn = seg_get(src, seg_cache, k + 1);
+    have_q = src.ctl[kQPeek] != 0;
+    if (have_q) {
+      const Segment sn = seg_read(src, k + 1);
       tc5_prepare_q<QT>(p, sn, qbufs + ((k + 1) & 1) * 4096, dqs + ((k + 1) & 1) * 8, tid);
       fence_proxy_async_smem();
       __syncwarp();
@@ -348,7 +362,7 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
       if (++stage == num_stages) stage = 0;
     }
 
-    FI_TRACE_IF(tid == 0 && k == src.count - 1, 6);
+    FI_TRACE_IF(tid == 0, 6);
     // ---- segment epilogue: thread tid <-> head-dim index d = tid (TMEM lane of O) ---------------
     float o8[8];
     if (sg.tile_end > sg.tile_begin) {
@@ -378,7 +392,9 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
       for (int j = 1; j < 8; ++j) mine = lane == j ? L[j] : mine;
       lsum[warp * 8 + lane] = mine;
     }
+    if (tid == 0) merge_post(p, pm, scratch);  // arrival of the previous partial
     named_bar_sync(3, 128);
+    merge_run_posted<QT, HD>(p, scratch, tid);
 #pragma unroll
     for (int j = 0; j < 8; ++j) L[j] = (lsum[j] + lsum[8 + j]) + (lsum[16 + j] + lsum[24 + j]);
 
@@ -401,26 +417,17 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
         }
       }
     }
-    FI_TRACE_IF(tid == 0 && k == src.count - 1, 7);
-    if (sg.merge_unit >= 0) {  // CTA-uniform: fused split-KV merge, last arriver merges
-      __threadfence();
-      named_bar_sync(2, 128);
-      if (tid == 0) {
-        const int cnt = __ldg(&p.merge_units[sg.merge_unit].count);
-        const int last = atomicAdd(p.merge_counters + sg.merge_unit, 1) == cnt - 1;
-        if (last) p.merge_counters[sg.merge_unit] = 0;
-        *flag = last;
-      }
-      named_bar_sync(3, 128);
-      if (*flag) {
-        __threadfence();
-        const int4 mu = __ldg(reinterpret_cast<const int4*>(p.merge_units + sg.merge_unit));
-        merge_unit_cta<QT, HD>(p, mu.x, mu.y, mu.z, mu.w, tid);
-        FI_TRACE_IF(tid == 0 && k == src.count - 1, 9);
-      }
+    FI_TRACE_IF(tid == 0, 7);
+    if (sg.merge_unit >= 0) {  // CTA-uniform: count the arrival, look at the result later
+      named_bar_sync(2, 128);  // all 128 threads wrote their part of the partial
+      if (tid == 0) merge_arrive(p, pm, sg);
     }
-    FI_TRACE_IF(tid == 0 && k == src.count - 1, 8);
   }
+  // end of this CTA's sequence: the last arrival is still unchecked
+  if (tid == 0) merge_post(p, pm, scratch);
+  named_bar_sync(3, 128);
+  merge_run_posted<QT, HD>(p, scratch, tid);
+  FI_TRACE_IF(tid == 0, 8);
 }
 
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 1 = e4m3, 2 = e5m2 KV.  head_dim 128, TMA-eligible pages.
@@ -468,14 +475,13 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
     tma_prefetch_desc(&kmap);
     tma_prefetch_desc(&vmap);
   }
-  const SegSource src = seg_source_init(p, G::TT);
-  for (int i = tid; i < min(src.count, kSegCache); i += blockDim.x) seg_cache[i] = seg_make(src, i);
+  const SegSource src = seg_source_init(p, G::TT, seg_cache, scratch, /*has_reader1=*/true);
   tc5::fence_before_sync();
   __syncthreads();
   tc5::fence_after_sync();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   FI_TRACE_IF(tid == 0, 1);
-  if (src.count == 0) {
+  if (src.implicit ? src.count == 0 : src.head_count == 0) {
     if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);
     return;
   }
@@ -483,12 +489,11 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   FI_TRACE_IF(tid == 0, 2);
 
   if (warp < 4) {
-    tc5_softmax<QT, KVF>(p, src, seg_cache, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
+    tc5_softmax<QT, KVF>(p, src, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
   } else if (warp == 4) {
-    produce_tma<KVF, 128>(p, src, seg_cache, &kmap, &vmap, ring, full_bar, empty_bar);
+    produce_tma<KVF, 128>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
   } else {
-    tc5_issue<KVF>(p, src, seg_cache, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar,
-                   bars, tmem);
+    tc5_issue<KVF>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
   }
   if (p.enable_pdl) pdl_launch_dependents();
   tc5::fence_before_sync();

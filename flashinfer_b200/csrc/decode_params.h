@@ -5,7 +5,9 @@
 // Params (csrc/batch_decode_customize_config.jinja:28-60), paged_kv_t
 // (include/flashinfer/page.cuh:37-210).  The design differs on purpose: instead of a
 // (request, uniform-chunk) grid the planner cuts the flattened (request, kv-head, tile)
-// stream into one contiguous range per persistent CTA ("stream-K" over KV tiles).
+// stream into contiguous work items ("stream-K" over KV tiles) of decreasing size; each
+// persistent CTA starts on item blockIdx.x and draws further items from an atomic counter,
+// so SMs that stream faster take more of the tail (guided self-scheduling).
 #pragma once
 #include <stdint.h>
 
@@ -17,7 +19,8 @@ constexpr int kConsumerWarps = 4;
 // D = 128 either way.  kvf: 0 = 16-bit KV, 1 = e4m3, 2 = e5m2.
 __host__ __device__ constexpr int tile_tokens(int kvf) { return kvf == 0 ? 64 : 128; }
 constexpr int kMaxStages = 12;
-constexpr int kSegCache = 32;         // segment records cached in smem per CTA
+constexpr int kSegCache = 32;         // segment queue (ring) in smem per CTA; a power of two
+constexpr int kSegRefill = 8;         // segments the feeder loads from the list at a time
 constexpr float kNegInf = -5e4f;      // finite "-inf", reference math.cuh:32
 constexpr int kMaxGroup = 8;          // GQA group size handled by one MMA N tile
 
@@ -36,21 +39,25 @@ struct alignas(16) Segment {
   int32_t tok_hi;
   int32_t merge_unit;  // index of the MergeUnit this partial belongs to (-1 when slot < 0)
   int32_t page_base;   // kv_indptr[request]: first entry of the request in the page table
-  int32_t pad[3];
+  int32_t merge_count; // copy of MergeUnit::count / slot_begin of `merge_unit`, so that the
+  int32_t merge_slot;  //   fused merge never has to load the MergeUnit record
+  int32_t pad;
 };
 static_assert(sizeof(Segment) == 48, "Segment must be 48 bytes");
 
-// Per-CTA head of the work list: the CTA's segment range plus its first kCtaInlineSegs segments
-// inline, so that the kernel prologue needs ONE global round trip before the producer can look
-// up page indices (segments beyond the inline ones are read from the list).
-constexpr int kCtaInlineSegs = 3;
-struct alignas(16) CtaHead {
-  int32_t first;  // index of the CTA's first segment in the list
-  int32_t count;
-  int32_t pad[2];
-  Segment seg[kCtaInlineSegs];
+// Head of one work item: the item's segment range plus its first kItemInlineSegs segments
+// inline, so that one 160-byte read (the kernel prologue for item blockIdx.x, the feeder for
+// drawn items) is all that stands between a CTA and its first page-table lookup.  Segments
+// beyond the inline ones are read from the list, which starts right after the last head.
+constexpr int kItemInlineSegs = 3;
+struct alignas(16) ItemHead {
+  int32_t first;      // index of the item's first segment in the list
+  int32_t count;      // segments in the item
+  int32_t num_items;  // items in the plan (same in every head)
+  int32_t pad;
+  Segment seg[kItemInlineSegs];
 };
-static_assert(sizeof(CtaHead) == 160, "CtaHead must be 160 bytes");
+static_assert(sizeof(ItemHead) == 160, "ItemHead must be 160 bytes");
 
 // A (request, kv_head) unit whose KV range was split over several CTAs: partial
 // slots [slot_begin, slot_begin + count) are merged into o[request, kv_head*G ..].
@@ -64,7 +71,7 @@ struct alignas(16) MergeUnit {
 // Device-resident header (first bytes of the int workspace), rewritten by every plan()
 // so that CUDA-graph replays pick up new counts without new launch geometry.
 struct PlanHeader {
-  int32_t num_ctas_used;
+  int32_t num_items;
   int32_t num_segments;
   int32_t num_merge_units;
   int32_t num_slots;
@@ -80,7 +87,7 @@ enum PlanInfoSlot {
   kPiNumMergeUnits,
   kPiNumSlots,
   kPiOffHeader,
-  kPiOffCtaIndptr,
+  kPiNumItems,
   kPiOffSegments,
   kPiOffMerge,
   kPiOffTmpO,
@@ -99,7 +106,8 @@ enum PlanInfoSlot {
   kPiStages,
   kPiIntBytesUsed,
   kPiOffCounters,   // int32 arrival counters, one per merge unit (fused split-KV merge)
-  kPiOffCtaHeads,
+  kPiOffItemHeads,
+  kPiOffWorkCounter,  // int32 ticket counter of the item scheduler (zero between launches)
   kPiLen
 };
 constexpr int64_t kPlanMagic = 0xF1B2000001LL;
@@ -122,10 +130,10 @@ struct DecodeParams {
   int32_t rows_per_box;  // TMA: min(page_size, 64)
   int32_t tma_h_first;   // TMA map dim order: 1 = (D, h, n, page), 0 = (D, n, h, page)
   // work list (explicit) ...
-  const PlanHeader* header;
-  const int32_t* cta_seg_indptr;   // host-side / test view; the kernels read cta_heads
-  const CtaHead* cta_heads;
-  const Segment* segments;
+  const PlanHeader* header;        // non-null selects this mode (the decode kernel never reads it)
+  const ItemHead* item_heads;      // the segment list follows head num_items - 1
+  int32_t* work_counter;           // tickets: item = ticket + gridDim.x; returns to zero
+  int32_t sched_lookahead;         // draw the next item when <= this many published tiles are left
   // ... or implicit uniform mode (single request, contiguous KV): segments are
   // derived in closed form from these (header == nullptr).
   int32_t imp_units;      // number of kv heads
@@ -146,7 +154,6 @@ struct DecodeParams {
   float soft_cap;          // <= 0 disabled
   float sm_scale;          // plain sm_scale (soft-cap path)
   int32_t enable_pdl;
-  int32_t l2_prefetch;     // TMA producer also prefetches tiles beyond the ring into L2
 };
 
 struct MergeParams {

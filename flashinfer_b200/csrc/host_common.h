@@ -60,4 +60,14 @@ struct Tuning {
 };
 Tuning& tuning();
 
+// Item scheduler knobs (environment, read once): FI_B200_SCHED_F0 / _G (percent),
+// FI_B200_SCHED_TAIL / _LOOKAHEAD (tiles).  See plan.cu.
+struct SchedTuning {
+  int f0_pct;           // share of a CTA's fair share handed out statically (100: static split)
+  int g_pct;            // share of the remainder cut per later round
+  int tail_tiles;       // smallest item of the later rounds
+  int lookahead_tiles;  // kernel: draw the next item when this many published tiles are left
+};
+const SchedTuning& sched_tuning();
+
 }  // namespace fib200

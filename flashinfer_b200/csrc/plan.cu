@@ -78,6 +78,28 @@ int device_sm_count(int device, int* out) {
 
 static inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
+static int env_int(const char* name, int dflt, int lo, int hi) {
+  const char* e = getenv(name);
+  if (e == nullptr || e[0] == 0) return dflt;
+  const int v = atoi(e);
+  return std::min(hi, std::max(lo, v));
+}
+
+const SchedTuning& sched_tuning() {
+  static const SchedTuning t = [] {
+    SchedTuning s;
+    // default: the static equal split.  Guided self-scheduling (e.g. F0=90 G=50 TAIL=4) was
+    // measured on B200 within +-2 % of it on 1 GB shapes and slower on small ones — every extra
+    // segment boundary costs more than the tail imbalance it removes.
+    s.f0_pct = env_int("FI_B200_SCHED_F0", 100, 1, 100);
+    s.g_pct = env_int("FI_B200_SCHED_G", 50, 5, 100);
+    s.tail_tiles = env_int("FI_B200_SCHED_TAIL", 4, 1, 1 << 20);
+    s.lookahead_tiles = env_int("FI_B200_SCHED_LOOKAHEAD", 4, 0, 1 << 20);
+    return s;
+  }();
+  return t;
+}
+
 }  // namespace fib200
 
 using namespace fib200;
@@ -160,61 +182,83 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   }
   if (total_tiles > 0x7fffffffLL) return fail(FI_ERR_INVALID_ARGUMENT, "too many KV tiles");
 
-  // ---- fixed (worst-case) layout: offsets depend only on (bs, heads, num_ctas) -------
+  // ---- work items: guided self-scheduling over the tile stream ------------------------
+  // Round 0 hands every CTA one item of f0 of its fair share (the kernel starts CTA i on
+  // item i without a ticket); every later round cuts g of what is left into num_ctas equal
+  // items, down to `tail` tiles per item.  CTAs draw those in stream order, so an SM that
+  // streams faster (HBM / L2 arbitration is not uniform across the two dies) ends up with
+  // more of the tail instead of idling.  f0 = 100 reproduces the static equal split.
+  const SchedTuning st = sched_tuning();
+  const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
+  std::vector<int64_t> item_end;  // exclusive end (stream position) of every item
+  {
+    int64_t pos = 0;
+    bool first = true;
+    while (pos < total_tiles) {
+      const int64_t rem = total_tiles - pos;
+      int64_t chunk = first ? (total_tiles * st.f0_pct + 100LL * num_ctas - 1) / (100LL * num_ctas)
+                            : (rem * st.g_pct + 100LL * num_ctas - 1) / (100LL * num_ctas);
+      if (first && st.f0_pct >= 100) chunk = (total_tiles + num_ctas - 1) / num_ctas;
+      chunk = std::max<int64_t>(chunk, first ? min_tiles : st.tail_tiles);
+      for (int i = 0; i < num_ctas && pos < total_tiles; ++i) {
+        pos = std::min(total_tiles, pos + chunk);
+        item_end.push_back(pos);
+      }
+      first = false;
+    }
+    if (item_end.empty()) item_end.push_back(0);  // only zero-tile segments (or none at all)
+  }
+  const int64_t num_items = (int64_t)item_end.size();
+
+  // ---- layout: offsets of everything the kernels get as launch parameters depend only on
+  // (bs, heads) — CUDA-graph replays of an earlier run() stay valid after a re-plan; the two
+  // variable-length arrays (item heads, segment list) come last -----------------------------
   const int64_t units = (int64_t)batch_size * num_kv_heads;
-  const int64_t max_segs = units + num_ctas;
-  const int64_t max_merge = num_ctas;
-  const int64_t max_slots = 2 * (int64_t)num_ctas;
+  const int64_t max_segs = units + num_items;   // every item boundary adds at most one segment
+  const int64_t max_merge = std::max<int64_t>(units, 1);
   size_t off = 0;
-  const size_t off_header = off; off = align16(off + sizeof(PlanHeader));
-  const size_t off_indptr = off; off = align16(off + (size_t)(num_ctas + 1) * 4);
+  const size_t off_header = off;   off = align16(off + sizeof(PlanHeader));
+  const size_t off_work = off;     off = align16(off + 16);
   const size_t off_counters = off; off = align16(off + (size_t)max_merge * 4);
-  const size_t off_heads = off;  off = align16(off + (size_t)num_ctas * sizeof(CtaHead));
-  const size_t off_segs = off;   off = align16(off + (size_t)max_segs * sizeof(Segment));
-  const size_t off_merge = off;  off = align16(off + (size_t)max_merge * sizeof(MergeUnit));
+  const size_t off_merge = off;    off = align16(off + (size_t)max_merge * sizeof(MergeUnit));
+  // every launched CTA reads head blockIdx.x: heads past the last item are empty
+  const int64_t head_cap = std::max<int64_t>(num_items, num_ctas);
+  const size_t off_heads = off;    off = align16(off + (size_t)head_cap * sizeof(ItemHead));
+  const size_t off_segs = off;     off = align16(off + (size_t)max_segs * sizeof(Segment));
   const size_t int_need = off;
   if (int_need > int_ws_bytes)
     return fail(FI_ERR_WORKSPACE,
                 "Buffer overflow when allocating the decode work list: need %zu bytes of int "
                 "workspace, have %zu. Increase the workspace buffer size.", int_need, int_ws_bytes);
-  const size_t off_tmp_o = 0;
-  const size_t tmp_o_bytes = align16((size_t)max_slots * group * head_dim * 4);
-  const size_t off_tmp_lse = off_tmp_o + tmp_o_bytes;
-  const size_t float_need = off_tmp_lse + align16((size_t)max_slots * group * 4);
-  if (float_need > float_ws_bytes)
-    return fail(FI_ERR_WORKSPACE,
-                "Buffer overflow when allocating split-KV partials: need %zu bytes of float "
-                "workspace, have %zu. Increase the workspace buffer size.", float_need, float_ws_bytes);
+  // float workspace: [lse of every slot | o of every slot]; the split point depends only on
+  // the workspace size and (group, head_dim), never on the plan
+  const size_t slot_cap = float_ws_bytes / ((size_t)group * (head_dim + 1) * 4 + 1);
+  const size_t off_tmp_lse = 0;
+  const size_t off_tmp_o = align16(slot_cap * group * 4);
 
   char* host = static_cast<char*>(pinned_int_ws);
   PlanHeader* hdr = reinterpret_cast<PlanHeader*>(host + off_header);
-  int32_t* cta_indptr = reinterpret_cast<int32_t*>(host + off_indptr);
   Segment* segs = reinterpret_cast<Segment*>(host + off_segs);
-  // arrival counters of the fused merge: zeroed by every plan (the workspace is not
-  // guaranteed to be zero-initialised) and returned to zero by the kernel itself
-  memset(host + off_counters, 0, (size_t)max_merge * 4);
   MergeUnit* merges = reinterpret_cast<MergeUnit*>(host + off_merge);
+  ItemHead* heads = reinterpret_cast<ItemHead*>(host + off_heads);
+  memset(host + off_work, 0, 16);
 
   // split-KV merge: fused into the decode kernel (default) or a second launch
   // (FI_B200_FUSED_MERGE=0, kept for A/B measurements)
   const char* fm = getenv("FI_B200_FUSED_MERGE");
   const bool fused_merge = !(fm != nullptr && fm[0] == '0');
-  // ---- cut the tile stream into per-CTA ranges ---------------------------------
-  const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
-  int64_t ctas_used = std::min<int64_t>(num_ctas, std::max<int64_t>(1, total_tiles / min_tiles));
-  auto bound = [&](int64_t i) { return (i * total_tiles) / ctas_used; };  // start of CTA i
 
+  // ---- walk the units in stream order and cut them at the item boundaries -----------------
   int64_t nseg = 0, nmerge = 0, nslot = 0;
-  int64_t cta = 0;       // CTA currently being filled
-  int64_t cta_end = bound(1);
-  cta_indptr[0] = 0;
-  int64_t pos = 0;       // stream position (tiles)
+  int64_t item = 0;  // item currently being filled
+  heads[0].first = 0;
+  int64_t pos = 0;   // stream position (tiles)
   for (int b = 0; b < batch_size; ++b) {
     for (int h = 0; h < num_kv_heads; ++h) {
       const int64_t nt = ntile[b];
       Segment s;
       s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b]; s.merge_unit = -1;
-      s.page_base = indptr_host[b]; s.pad[0] = s.pad[1] = s.pad[2] = 0;
+      s.page_base = indptr_host[b]; s.merge_count = 0; s.merge_slot = 0; s.pad = 0;
       if (nt == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
         s.tile_begin = s.tile_end = 0; s.slot = -1;
         segs[nseg++] = s;
@@ -224,12 +268,11 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
       const int64_t end = pos + nt;
       bool split_open = false;
       while (cur < end) {
-        while (cta_end <= cur) {  // advance to the CTA that owns `cur`
-          ++cta;
-          cta_indptr[cta] = (int32_t)nseg;
-          cta_end = bound(cta + 1);
+        while (item_end[item] <= cur) {  // advance to the item that owns `cur`
+          ++item;
+          heads[item].first = (int32_t)nseg;
         }
-        const int64_t e = std::min(end, cta_end);
+        const int64_t e = std::min(end, item_end[item]);
         const bool whole = (cur == pos && e == end);
         s.tile_begin = tile_b[b] + (int32_t)(cur - pos);
         s.tile_end = tile_b[b] + (int32_t)(e - pos);
@@ -249,38 +292,65 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
         segs[nseg++] = s;
         cur = e;
       }
+      if (split_open) {  // the unit's partials are its last `count` segments
+        const MergeUnit& mu = merges[nmerge - 1];
+        for (int64_t i = nseg - mu.count; i < nseg; ++i) {
+          segs[i].merge_count = mu.count;
+          segs[i].merge_slot = mu.slot_begin;
+        }
+      }
       pos = end;
     }
   }
-  for (int64_t i = cta + 1; i <= num_ctas; ++i) cta_indptr[i] = (int32_t)nseg;
-  if (nseg > max_segs || nmerge > max_merge || nslot > max_slots)
-    return fail(FI_ERR_WORKSPACE, "internal planner overflow (%lld segs, %lld merges, %lld slots)",
-                (long long)nseg, (long long)nmerge, (long long)nslot);
-  // per-CTA heads: segment range + the first segments inline (one round trip in the prologue)
-  CtaHead* heads = reinterpret_cast<CtaHead*>(host + off_heads);
-  for (int64_t i = 0; i < num_ctas; ++i) {
-    CtaHead& hd = heads[i];
-    hd.first = cta_indptr[i];
-    hd.count = cta_indptr[i + 1] - cta_indptr[i];
-    hd.pad[0] = hd.pad[1] = 0;
-    for (int j = 0; j < kCtaInlineSegs; ++j) {
+  if (item + 1 != num_items || nseg > max_segs || nmerge > max_merge)
+    return fail(FI_ERR_WORKSPACE, "internal planner overflow (%lld items, %lld segs, %lld merges)",
+                (long long)item + 1, (long long)nseg, (long long)nmerge);
+  if ((size_t)nslot > slot_cap)
+    return fail(FI_ERR_WORKSPACE,
+                "Buffer overflow when allocating split-KV partials: need %zu bytes of float "
+                "workspace, have %zu. Increase the workspace buffer size.",
+                (size_t)nslot * group * (head_dim + 1) * 4 + 64, float_ws_bytes);
+  // item heads: segment range + the first segments inline
+  for (int64_t i = num_items; i < head_cap; ++i) heads[i].first = (int32_t)nseg;
+  for (int64_t i = 0; i < head_cap; ++i) {
+    ItemHead& hd = heads[i];
+    hd.count = (int32_t)((i + 1 < num_items ? heads[i + 1].first : nseg) - hd.first);
+    hd.num_items = (int32_t)num_items;
+    hd.pad = 0;
+    for (int j = 0; j < kItemInlineSegs; ++j) {
       if (j < hd.count) hd.seg[j] = segs[hd.first + j];
       else memset(&hd.seg[j], 0, sizeof(Segment));
     }
   }
-  hdr->num_ctas_used = (int32_t)num_ctas;  // every CTA has a (possibly empty) indptr entry
+  // arrival counters of the fused merge: zeroed by every plan (the workspace is not guaranteed
+  // to be zero-initialised) and returned to zero by the kernel itself
+  memset(host + off_counters, 0, (size_t)std::max<int64_t>(nmerge, 1) * 4);
+  hdr->num_items = (int32_t)num_items;
   hdr->num_segments = (int32_t)nseg;
   hdr->num_merge_units = (int32_t)nmerge;
   hdr->num_slots = (int32_t)nslot;
   hdr->total_tiles = (int32_t)total_tiles;
   hdr->pad[0] = hdr->pad[1] = hdr->pad[2] = 0;
 
-  // ---- one H2D copy of the used prefix (header .. merge list) -------------------
-  const size_t used = off_merge + (size_t)std::max<int64_t>(nmerge, 1) * sizeof(MergeUnit);
+  // ---- H2D: [header, work counter, counters(nmerge)] [merges(nmerge)] [heads, segs(nseg)] —
+  // as one copy when the unused capacity in between is small ------------------------------
+  const size_t used = off_segs + (size_t)std::max<int64_t>(nseg, 1) * sizeof(Segment);
   if (device >= 0) {
     FI_CUDA_TRY(cudaSetDevice(device));
-    FI_CUDA_TRY(cudaMemcpyAsync(int_ws, pinned_int_ws, used, cudaMemcpyHostToDevice,
-                                static_cast<cudaStream_t>(stream)));
+    cudaStream_t cs = static_cast<cudaStream_t>(stream);
+    char* dev = static_cast<char*>(int_ws);
+    const size_t gap = (size_t)(max_merge - nmerge) * (4 + sizeof(MergeUnit));
+    if (gap <= (64u << 10)) {
+      FI_CUDA_TRY(cudaMemcpyAsync(dev, host, used, cudaMemcpyHostToDevice, cs));
+    } else {
+      const size_t n0 = off_counters + (size_t)nmerge * 4;
+      FI_CUDA_TRY(cudaMemcpyAsync(dev, host, n0, cudaMemcpyHostToDevice, cs));
+      if (nmerge > 0)
+        FI_CUDA_TRY(cudaMemcpyAsync(dev + off_merge, host + off_merge, (size_t)nmerge * sizeof(MergeUnit),
+                                    cudaMemcpyHostToDevice, cs));
+      FI_CUDA_TRY(cudaMemcpyAsync(dev + off_heads, host + off_heads, used - off_heads,
+                                  cudaMemcpyHostToDevice, cs));
+    }
   } else {
     if (int_ws != pinned_int_ws) memcpy(int_ws, pinned_int_ws, used);  // CPU-only test mode
   }
@@ -293,7 +363,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   pi[kPiNumMergeUnits] = nmerge;
   pi[kPiNumSlots] = nslot;
   pi[kPiOffHeader] = (int64_t)off_header;
-  pi[kPiOffCtaIndptr] = (int64_t)off_indptr;
+  pi[kPiNumItems] = num_items;
   pi[kPiOffSegments] = (int64_t)off_segs;
   pi[kPiOffMerge] = (int64_t)off_merge;
   pi[kPiOffTmpO] = (int64_t)off_tmp_o;
@@ -310,7 +380,8 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   // second launch (graph mode: fixed upper-bound grid so that replays stay valid)
   pi[kPiMergeGrid] = fused_merge ? 0 : (cuda_graph ? max_merge : nmerge);
   pi[kPiOffCounters] = (int64_t)off_counters;
-  pi[kPiOffCtaHeads] = (int64_t)off_heads;
+  pi[kPiOffItemHeads] = (int64_t)off_heads;
+  pi[kPiOffWorkCounter] = (int64_t)off_work;
   pi[kPiTotalTiles] = total_tiles;
   pi[kPiWindowLeft] = window_left;
   pi[kPiStages] = cfg.stages;

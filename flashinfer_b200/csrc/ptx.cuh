@@ -77,6 +77,14 @@ __device__ __forceinline__ void tma_prefetch_4d(const void* map, int c0, int c1,
 }
 
 // ---- cp.async (16 B, zero-fill when src_bytes == 0) -------------------------
+// arrival at a split-KV unit: release so that the partial written before it (by this thread and,
+// through a preceding barrier, by its warp / CTA) is visible to whoever reads the count after us
+__device__ __forceinline__ int atom_add_acq_rel_gpu(int* addr, int v) {
+  int old;
+  asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(addr), "r"(v) : "memory");
+  return old;
+}
+
 __device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src),
                "r"(src_bytes)

@@ -22,7 +22,7 @@ from flashinfer_b200 import _lib  # noqa: E402
 
 DEV = "cuda:0"
 NAMES = ["entry", "seg cached", "pdl passed", "page idx", "tile issued", "tile landed",
-         "last tile done", "o written", "loop done", "merge done"]
+         "last tile done", "o written", "loop done", "merge done", "bar1 passed", "bar2 passed"]
 
 
 def main():
@@ -75,7 +75,7 @@ def main():
             continue
         print(f"{i} {n:14s} {len(c):4d} {c.min():7.2f} {np.median(c):7.2f} {np.percentile(c, 90):7.2f} {c.max():7.2f}")
     print("per-CTA deltas (median / max, us):")
-    for a, b in [(0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6), (6, 7), (7, 8), (7, 9)]:
+    for a, b in [(0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6), (6, 10), (10, 11), (11, 7), (6, 7), (7, 8), (7, 9)]:
         dlt = rel[:, b] - rel[:, a]
         dlt = dlt[~np.isnan(dlt)]
         if len(dlt):

@@ -92,13 +92,13 @@ class MergeUnit(C.Structure):
 
 # plan-info slots (flashinfer_b200/csrc/decode_params.h PlanInfoSlot)
 PI = dict(magic=0, num_ctas=1, num_segments=2, num_merge=3, num_slots=4, off_header=5,
-          off_cta_indptr=6, off_segments=7, off_merge=8, off_tmp_o=9, off_tmp_lse=10,
+          num_items=6, off_segments=7, off_merge=8, off_tmp_o=9, off_tmp_lse=10,
           batch_size=11, hq=12, hkv=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
           cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23,
-          off_counters=24, off_cta_heads=25)
+          off_counters=24, off_item_heads=25, off_work_counter=26)
 SEG_BYTES = 48    # sizeof(Segment)
-HEAD_BYTES = 160  # sizeof(CtaHead)
-INLINE_SEGS = 3   # kCtaInlineSegs
+HEAD_BYTES = 160  # sizeof(ItemHead)
+INLINE_SEGS = 3   # kItemInlineSegs
 TILE = 64        # tokens per tile for 16-bit KV (csrc/decode_params.h tile_tokens)
 TILE_FP8 = 128   # ... and for fp8 KV
 
@@ -124,32 +124,47 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
         return rc, _lib.last_error(), None
     hdr = ws[info[PI["off_header"]]:info[PI["off_header"]] + 32].view(np.int32)
     ncta = int(info[PI["num_ctas"]])
-    cta_indptr = ws[info[PI["off_cta_indptr"]]:info[PI["off_cta_indptr"]] + 4 * (ncta + 1)].view(np.int32).copy()
+    nitems = int(info[PI["num_items"]])
     nseg = int(hdr[1])
+    assert hdr[0] == nitems and nseg == info[PI["num_segments"]]
     # Segment records are 48 bytes (12 int32): 8 work fields, page_base, 3 pad
     seg_full = ws[info[PI["off_segments"]]:info[PI["off_segments"]] + SEG_BYTES * nseg].view(np.int32)
     seg_full = seg_full.reshape(nseg, SEG_BYTES // 4).copy()
     segs = seg_full[:, :8].copy()
     nm = int(hdr[2])
     merges = ws[info[PI["off_merge"]]:info[PI["off_merge"]] + 16 * nm].view(np.int32).reshape(nm, 4).copy()
-    # per-CTA heads (160 bytes): first, count, 2 pad, then kCtaInlineSegs inline Segment records
-    heads = ws[info[PI["off_cta_heads"]]:info[PI["off_cta_heads"]] + HEAD_BYTES * ncta].view(np.int32)
-    heads = heads.reshape(ncta, HEAD_BYTES // 4).copy()
+    # item heads (160 bytes): first, count, num_items, pad, then kItemInlineSegs inline Segment
+    # records; one head per item, padded with empty heads up to the launch grid
+    nheads = max(nitems, ncta)
+    heads = ws[info[PI["off_item_heads"]]:info[PI["off_item_heads"]] + HEAD_BYTES * nheads].view(np.int32)
+    heads = heads.reshape(nheads, HEAD_BYTES // 4).copy()
+    # the segment list starts right after the last head (the kernel relies on it)
+    assert info[PI["off_segments"]] == info[PI["off_item_heads"]] + HEAD_BYTES * nheads
+    item_indptr = np.concatenate([heads[:nitems, 0], [nseg]]).astype(np.int32)
     # structural checks that need the raw records
     assert np.array_equal(seg_full[:, 8], ip[segs[:, 0]]), "page_base != kv_indptr[request]"
-    assert np.array_equal(heads[:, 0], cta_indptr[:-1]) and np.array_equal(heads[:, 1], np.diff(cta_indptr))
-    for c in range(ncta):
+    for r in seg_full:  # partial segments carry their unit's (count, slot_begin)
+        if r[7] >= 0:
+            assert (r[9], r[10]) == (merges[r[7], 3], merges[r[7], 2]), "merge_count / merge_slot"
+            assert merges[r[7], 2] <= r[4] < merges[r[7], 2] + merges[r[7], 3]
+    assert np.array_equal(heads[:nitems, 1], np.diff(item_indptr))
+    assert np.all(heads[:, 2] == nitems)
+    assert np.all(heads[nitems:, 1] == 0), "heads past the last item must be empty"
+    for c in range(nitems):
         for k in range(min(int(heads[c, 1]), INLINE_SEGS)):
             inl = heads[c, 4 + 12 * k:4 + 12 * (k + 1)]
             assert np.array_equal(inl, seg_full[heads[c, 0] + k]), "inline segment != list segment"
-    return 0, "", dict(info=info, header=hdr.copy(), cta_indptr=cta_indptr, segments=segs, merges=merges,
-                       cta_heads=heads)
+    wc = ws[info[PI["off_work_counter"]]:info[PI["off_work_counter"]] + 4].view(np.int32)
+    cnt = ws[info[PI["off_counters"]]:info[PI["off_counters"]] + 4 * max(nm, 1)].view(np.int32)
+    assert wc[0] == 0 and np.all(cnt == 0), "scheduler / merge counters must start at zero"
+    return 0, "", dict(info=info, header=hdr.copy(), item_indptr=item_indptr, segments=segs,
+                       merges=merges, item_heads=heads)
 
 
 def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1, tile=TILE):
     """Pure-Python replay of the work list: returns per-(request, head) token visit counts
     and checks the structural invariants.  Raises AssertionError on any inconsistency."""
-    segs, merges, cta_indptr, hdr = plan["segments"], plan["merges"], plan["cta_indptr"], plan["header"]
+    segs, merges, cta_indptr, hdr = plan["segments"], plan["merges"], plan["item_indptr"], plan["header"]
     bs = len(kv_lens)
     visits = [np.zeros(max(l, 0), dtype=np.int32) for l in kv_lens for _ in range(num_kv_heads)]
     direct = np.zeros((bs, num_kv_heads), dtype=np.int32)

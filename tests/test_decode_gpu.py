@@ -261,3 +261,39 @@ def test_batch_equals_single():
         k, v = orc.gather_paged_kv(cache[:, 0], cache[:, 1], indptr, indices, last, i, "NHD")
         oi = fi.single_decode_with_kv_cache(q[i].to(DEV), k.contiguous().to(DEV), v.contiguous().to(DEV))
         torch.testing.assert_close(o[i], oi, rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn])
+@pytest.mark.parametrize("loader", [1, 2])
+def test_many_short_requests_refill_the_segment_queue(kv_dtype, loader):
+    """Hundreds of one-tile (and empty) requests: work items hold far more segments than the three
+    inline ones and than the 32-entry shared-memory queue, so the feeder streams them from the list."""
+    rng = np.random.default_rng(7)
+    kv_lens = rng.integers(0, 131, 700).tolist()
+    kv_lens[5:45] = [0] * 40  # a run of empty requests longer than the queue
+    run_batch(kv_lens, 8, 2, 128, 16, "NHD", torch.bfloat16, kv_dtype=kv_dtype, loader=loader,
+              check_requests=list(range(0, 700, 9)))
+
+
+@pytest.mark.parametrize("knobs", ["70,50,2,2", "90,50,4,4", "50,25,1,0"])
+def test_dynamic_item_scheduler(knobs):
+    """The guided self-scheduling mode (items drawn from the ticket counter, segment queue, deferred
+    merge arrivals) is off by default and its knobs are read once per process: run the batch
+    parity tests again in a child process with the scheduler switched on."""
+    import os
+    import subprocess
+    import sys
+
+    if os.environ.get("FI_B200_TEST_CHILD") == "1":
+        pytest.skip("already inside the child run")
+    f0, g, tail, look = knobs.split(",")
+    env = dict(os.environ, FI_B200_TEST_CHILD="1", FI_B200_SCHED_F0=f0, FI_B200_SCHED_G=g,
+               FI_B200_SCHED_TAIL=tail, FI_B200_SCHED_LOOKAHEAD=look)
+    sel = ("test_batch_decode_minimum_slice or test_batch_decode_reference_matrix or "
+           "test_empty_request_regression or test_batch_decode_fp8_kv or "
+           "test_split_kv_long_single_request_and_determinism or test_cuda_graph_replay_with_replan "
+           "or test_batch_decode_page_sizes_and_groups or test_many_short_requests")
+    r = subprocess.run([sys.executable, "-m", "pytest", __file__, "-x", "-q", "-m", "gpu", "-k", sel],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
