@@ -41,9 +41,49 @@ static EncodeTiledFn get_encode_fn() {
 
 // 4-D map over one of K / V: dims (D, n, h, page) — or (D, h, n, page) when the head
 // stride is the smaller one (NHD), so that strides grow with the dimension index.
+// A descriptor is a pure function of these arguments; a serving loop calls run() with the same
+// few caches (one per layer), so the last encodings are kept per thread.
+struct KvMapKey {
+  const void* base;
+  int64_t dim_n, dim_h, dim_page, stride_n, stride_h, stride_page;
+  int kv_dtype, head_dim, rows_per_box;
+  bool operator==(const KvMapKey& o) const {
+    return base == o.base && dim_n == o.dim_n && dim_h == o.dim_h && dim_page == o.dim_page &&
+           stride_n == o.stride_n && stride_h == o.stride_h && stride_page == o.stride_page &&
+           kv_dtype == o.kv_dtype && head_dim == o.head_dim && rows_per_box == o.rows_per_box;
+  }
+};
+constexpr int kMapCacheSize = 256;  // K and V of 128 layers
+struct KvMapCache {
+  KvMapKey key[kMapCacheSize];
+  CUtensorMap map[kMapCacheSize];
+  int used = 0, next = 0;
+};
+
+static int encode_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int head_dim,
+                         int64_t dim_n, int64_t dim_h, int64_t dim_page, int64_t stride_n,
+                         int64_t stride_h, int64_t stride_page, int rows_per_box);
+
 static int make_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int head_dim,
                        int64_t dim_n, int64_t dim_h, int64_t dim_page, int64_t stride_n,
                        int64_t stride_h, int64_t stride_page, int rows_per_box) {
+  static thread_local KvMapCache cache;
+  const KvMapKey key = {base, dim_n, dim_h, dim_page, stride_n, stride_h, stride_page,
+                        kv_dtype, head_dim, rows_per_box};
+  for (int i = 0; i < cache.used; ++i)
+    if (cache.key[i] == key) { *map = cache.map[i]; return FI_OK; }
+  const int rc = encode_kv_map(map, base, kv_dtype, head_dim, dim_n, dim_h, dim_page, stride_n,
+                               stride_h, stride_page, rows_per_box);
+  if (rc != FI_OK) return rc;
+  const int slot = cache.used < kMapCacheSize ? cache.used++ : (cache.next++ % kMapCacheSize);
+  cache.key[slot] = key;
+  cache.map[slot] = *map;
+  return FI_OK;
+}
+
+static int encode_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int head_dim,
+                         int64_t dim_n, int64_t dim_h, int64_t dim_page, int64_t stride_n,
+                         int64_t stride_h, int64_t stride_page, int rows_per_box) {
   EncodeTiledFn enc = get_encode_fn();
   if (enc == nullptr) return fail(FI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
   const int es = dtype_size(kv_dtype);

@@ -182,6 +182,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 raise ValueError("The size of paged_kv_indptr_buffer should be batch_size + 1")
         else:
             self._fixed_batch_size = 0
+        self._indptr_dev = self._indptr_src = None
+        self._last_page_len_dev = self._last_page_len_src = None
         self._paged_kv_indptr_buf = paged_kv_indptr_buffer
         self._paged_kv_indices_buf = paged_kv_indices_buffer
         self._paged_kv_last_page_len_buf = paged_kv_last_page_len_buffer
@@ -194,6 +196,29 @@ class BatchDecodeWithPagedKVCacheWrapper:
     @property
     def use_tensor_cores(self) -> bool:
         return self._use_tensor_cores
+
+    # The kernels take every request's page base and length from the planned work list, so outside
+    # CUDA-graph mode the device copies of indptr / last_page_len (attributes the reference keeps,
+    # decode.py:1009-1017) are made on first access instead of on every plan().
+    @property
+    def _paged_kv_indptr_buf(self):
+        if self._indptr_dev is None and self._indptr_src is not None:
+            self._indptr_dev = self._indptr_src.to(self.device, non_blocking=True)
+        return self._indptr_dev
+
+    @_paged_kv_indptr_buf.setter
+    def _paged_kv_indptr_buf(self, value):
+        self._indptr_dev, self._indptr_src = value, None
+
+    @property
+    def _paged_kv_last_page_len_buf(self):
+        if self._last_page_len_dev is None and self._last_page_len_src is not None:
+            self._last_page_len_dev = self._last_page_len_src.to(self.device, non_blocking=True)
+        return self._last_page_len_dev
+
+    @_paged_kv_last_page_len_buf.setter
+    def _paged_kv_last_page_len_buf(self, value):
+        self._last_page_len_dev, self._last_page_len_src = value, None
 
     @property
     def is_cuda_graph_enabled(self) -> bool:
@@ -269,9 +294,15 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 indices, non_blocking=(indices.device == self.device) and non_blocking
             )
         else:
-            self._paged_kv_indptr_buf = indptr.to(self.device, non_blocking=non_blocking)
             self._paged_kv_indices_buf = indices.to(self.device, non_blocking=non_blocking)
-            self._paged_kv_last_page_len_buf = last_page_len.to(self.device, non_blocking=non_blocking)
+            if indptr.device == self.device:
+                self._paged_kv_indptr_buf = indptr
+            else:
+                self._indptr_dev, self._indptr_src = None, indptr
+            if last_page_len.device == self.device:
+                self._paged_kv_last_page_len_buf = last_page_len
+            else:
+                self._last_page_len_dev, self._last_page_len_src = None, last_page_len
 
         indptr_host, indptr_ptr = _host_i32_ptr(indptr)
         last_page_len_host, lpl_ptr = _host_i32_ptr(last_page_len)
@@ -463,7 +494,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 q.data_ptr(), q.stride(0), q.stride(1),
                 k_cache.data_ptr(), v_cache.data_ptr(), k_cache.shape[0],
                 k_cache.stride(0), stride_n, stride_h,
-                self._paged_kv_indices_buf.data_ptr(), self._paged_kv_indptr_buf.data_ptr(),
+                self._paged_kv_indices_buf.data_ptr(),
+                self._indptr_dev.data_ptr() if self._indptr_dev is not None else None,
                 out.data_ptr(), lse.data_ptr() if return_lse else None,
                 float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
                 float(logits_soft_cap), int(bool(enable_pdl)), device_index(dev),

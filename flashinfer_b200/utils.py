@@ -144,6 +144,7 @@ def check_shape_dtype_device(
 
 
 @functools.cache
+@functools.lru_cache(maxsize=None)
 def device_support_pdl(device: torch.device) -> bool:
     if device.type != "cuda":
         return False

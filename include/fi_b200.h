@@ -108,8 +108,8 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
                          int64_t* plan_info_out);
 
 /*
- * fi_batch_decode_run — launches the decode kernel (+ merge kernel if any
- * request was split).
+ * fi_batch_decode_run — launches the decode kernel; split requests are merged
+ * inside it (FI_B200_FUSED_MERGE=0 at plan time: by a second merge launch).
  * Replaces: BatchDecodeWithPagedKVCacheRun (csrc/batch_decode.cu:81-191) ->
  *           BatchDecodeWithPagedKVCacheDispatched
  *           (include/flashinfer/attention/decode.cuh:739-825).
@@ -119,7 +119,9 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
  *                   (page, n, h), unit on D (reference constraint
  *                   csrc/batch_decode.cu:123-128)
  *  kv_indices   device int32 page table; NULL = identity (page id == position)
- *  kv_indptr    device int32 [bs+1]
+ *  kv_indptr    device int32 [bs+1], or NULL: the kernels take every request's page
+ *               base from the planned work list (plan() read indptr on the host), the
+ *               argument is kept for signature parity with the reference run()
  *  o            [bs, Hq, D] contiguous, q dtype
  *  lse          [bs, Hq] f32 base-2 or NULL
  *  sm_scale     already multiplied by q_scale*k_scale (decode.py:1250-1256)

@@ -92,15 +92,18 @@ struct BatchArgs {
   float sm_scale;
   cudaStream_t stream;
   int64_t* info_out;  // 10 x int64 DecodePlanInfo + [10] = launches (1 or 2)
+  int mode;           // 0 plan + run, 1 plan only (kept for later runs), 2 run with the kept plan
 };
+
+thread_local DecodePlanInfo g_plan;  // the reference keeps this in its Python wrapper between run()s
 
 template <typename Q, typename KV, uint32_t HD>
 int batch_impl(const BatchArgs& a) {
   using P = BatchParams<Q, KV>;
-  DecodePlanInfo info;
+  DecodePlanInfo& info = g_plan;
   cudaError_t st = cudaSuccess;
-  bool ok = false;
-  DISPATCH_GQA_GROUP_SIZE(a.hq / a.hkv, GROUP_SIZE, {
+  bool ok = a.mode == 2;
+  if (a.mode != 2) DISPATCH_GQA_GROUP_SIZE(a.hq / a.hkv, GROUP_SIZE, {
     auto est = BatchDecodeWithPagedKVCacheWorkEstimationDispatched<GROUP_SIZE, HD, PosEncodingMode::kNone,
                                                                    Variant, P>;
     st = DecodePlan<HD, PosEncodingMode::kNone, Variant, P>(a.float_ws, a.float_bytes, a.int_ws,
@@ -111,6 +114,7 @@ int batch_impl(const BatchArgs& a) {
   });
   if (!ok) { g_err = "unsupported group size"; return 4; }
   if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
+  if (a.mode == 1) return 0;
   paged_kv_t<KV, int32_t> kv(a.hkv, a.page_size, HD, a.bs, static_cast<QKVLayout>(a.layout),
                              static_cast<KV*>(a.k), static_cast<KV*>(a.v), a.kv_strides, a.indices,
                              a.indptr, a.last_page_len);
@@ -210,7 +214,28 @@ __attribute__((visibility("default"))) int ref_batch_decode(
   if (head_dim != 128) { g_err = "ref shim is built for head_dim 128"; return 4; }
   BatchArgs a{float_ws, int_ws, pinned_ws, float_bytes, int_bytes, indptr_h, bs, hq, hkv, page_size,
               layout, cuda_graph, q, k, v, o, lse, q_stride_n, q_stride_h, {s0, s1, s2}, indices,
-              indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), info_out};
+              indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), info_out, 0};
+  try {
+    REF_DISPATCH(q_dtype, kv_dtype, return (batch_impl<Q, KV, 128>(a)));
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return 2;
+  }
+}
+
+// same, with plan and run separable as in the reference's Python wrapper (plan once, run per layer):
+// mode 1 = plan only, 2 = run with the plan of the last mode-1 call on this thread, 0 = both
+__attribute__((visibility("default"))) int ref_batch_decode_mode(
+    void* float_ws, size_t float_bytes, void* int_ws, void* pinned_ws, size_t int_bytes,
+    int32_t* indptr_h, int bs, int hq, int hkv, int head_dim, int page_size, int q_dtype,
+    int kv_dtype, int layout, int cuda_graph, void* q, int64_t q_stride_n, int64_t q_stride_h,
+    void* k, void* v, int64_t s0, int64_t s1, int64_t s2, int32_t* indices, int32_t* indptr,
+    int32_t* last_page_len, void* o, float* lse, float sm_scale, void* stream, int64_t* info_out,
+    int mode) {
+  if (head_dim != 128) { g_err = "ref shim is built for head_dim 128"; return 4; }
+  BatchArgs a{float_ws, int_ws, pinned_ws, float_bytes, int_bytes, indptr_h, bs, hq, hkv, page_size,
+              layout, cuda_graph, q, k, v, o, lse, q_stride_n, q_stride_h, {s0, s1, s2}, indices,
+              indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), info_out, mode};
   try {
     REF_DISPATCH(q_dtype, kv_dtype, return (batch_impl<Q, KV, 128>(a)));
   } catch (const std::exception& e) {
