@@ -434,15 +434,16 @@ def hbm_peak_gbs():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic_per_launch():
-    """dram bytes (read+write) of the decode kernel from the committed ncu --set full summary."""
+def ncu_traffic_per_launch(workload_name, world):
+    """dram bytes (read+write) per launch of the decode kernel from the committed `ncu --set full`
+    summary of THIS workload on one GPU; null for any other configuration."""
     p = ROOT / "profiles" / "decode_kernel_traffic.json"
-    if p.exists():
-        try:
-            return json.loads(p.read_text()).get("dram_bytes_per_launch")
-        except Exception:  # noqa: BLE001
-            return None
-    return None
+    if world != 1 or not p.exists():
+        return None
+    try:
+        return json.loads(p.read_text()).get(workload_name, {}).get("dram_bytes_per_launch")
+    except Exception:  # noqa: BLE001
+        return None
 
 
 def emit(args, wl, world, ms_total, kern_ms, e2e_us, ag_us, h2d, d2h, launches, clocks, hq, hkv,
@@ -467,7 +468,7 @@ def emit(args, wl, world, ms_total, kern_ms, e2e_us, ag_us, h2d, d2h, launches, 
                          f"cop{'y' if n_copies == 1 else 'ies'} rotated"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "frac_of_8tbps": achieved / 8000.0,
-                     "traffic": ncu_traffic_per_launch(), "peak_source": peak_src,
+                     "traffic": ncu_traffic_per_launch(args.workload, world), "peak_source": peak_src,
                      "kernel": "paged_decode_kernel / paged_decode_tc5_kernel (split-KV merge fused), "
                                "one launch per run()",
                      "kernel_us": us_step, "kernel_us_isolated": kern_ms * 1e3,

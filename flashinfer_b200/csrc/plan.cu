@@ -155,7 +155,13 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
 
   // ---- per-request token / tile ranges --------------------------------------
   const int TT = tile_tokens(kvf);
-  std::vector<int32_t> tok_lo(batch_size), tok_hi(batch_size), tile_b(batch_size), ntile(batch_size);
+  // one scratch allocation per thread, reused across plans (plan() runs once per decode step)
+  static thread_local std::vector<int32_t> scratch;
+  scratch.resize((size_t)4 * batch_size);
+  int32_t* tok_lo = scratch.data();
+  int32_t* tok_hi = tok_lo + batch_size;
+  int32_t* tile_b = tok_hi + batch_size;
+  int32_t* ntile = tile_b + batch_size;
   int64_t total_tiles = 0;
   for (int b = 0; b < batch_size; ++b) {
     const int64_t npages = (int64_t)indptr_host[b + 1] - indptr_host[b];
@@ -190,7 +196,8 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   // more of the tail instead of idling.  f0 = 100 reproduces the static equal split.
   const SchedTuning st = sched_tuning();
   const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
-  std::vector<int64_t> item_end;  // exclusive end (stream position) of every item
+  static thread_local std::vector<int64_t> item_end;  // exclusive end (stream position) of every item
+  item_end.clear();
   {
     int64_t pos = 0;
     bool first = true;
@@ -245,8 +252,10 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
 
   // split-KV merge: fused into the decode kernel (default) or a second launch
   // (FI_B200_FUSED_MERGE=0, kept for A/B measurements)
-  const char* fm = getenv("FI_B200_FUSED_MERGE");
-  const bool fused_merge = !(fm != nullptr && fm[0] == '0');
+  static const bool fused_merge = [] {
+    const char* fm = getenv("FI_B200_FUSED_MERGE");
+    return !(fm != nullptr && fm[0] == '0');
+  }();
 
   // ---- walk the units in stream order and cut them at the item boundaries -----------------
   int64_t nseg = 0, nmerge = 0, nslot = 0;
@@ -317,10 +326,8 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     hd.count = (int32_t)((i + 1 < num_items ? heads[i + 1].first : nseg) - hd.first);
     hd.num_items = (int32_t)num_items;
     hd.pad = 0;
-    for (int j = 0; j < kItemInlineSegs; ++j) {
-      if (j < hd.count) hd.seg[j] = segs[hd.first + j];
-      else memset(&hd.seg[j], 0, sizeof(Segment));
-    }
+    // inline copies of the first segments; the kernel never reads past `count`
+    for (int j = 0; j < kItemInlineSegs && j < hd.count; ++j) hd.seg[j] = segs[hd.first + j];
   }
   // arrival counters of the fused merge: zeroed by every plan (the workspace is not guaranteed
   // to be zero-initialised) and returned to zero by the kernel itself

@@ -1,6 +1,8 @@
-"""Summarise an `ncu --set full` report into profiles/: python scripts/ncu_summary.py <rep> <tag>
-Writes profiles/<tag>_summary.md (+ decode_kernel_traffic.json when the kernel is the decode
-kernel of the default bench workload)."""
+"""Summarise an `ncu --set full` report into profiles/:
+python scripts/ncu_summary.py <rep> <tag> [--traffic <workload>]
+Writes profiles/<tag>_summary.md and, with --traffic, the measured DRAM bytes per launch of the
+decode kernel on bench workload <workload> (1 GPU) into profiles/decode_kernel_traffic.json, from
+where bench.py reads `roofline.traffic`."""
 import csv
 import io
 import json
@@ -52,10 +54,13 @@ def main():
     out.write_text("\n".join(lines) + "\n")
     print(f"wrote {out}")
     if "--traffic" in sys.argv and traffic:
+        wl = sys.argv[sys.argv.index("--traffic") + 1]
         t = sum(traffic) / len(traffic)
-        (root / "profiles" / "decode_kernel_traffic.json").write_text(json.dumps(
-            {"dram_bytes_per_launch": t, "from": out.name, "launches_averaged": len(traffic)}) + "\n")
-        print(f"traffic per launch {t:.0f} B")
+        path = root / "profiles" / "decode_kernel_traffic.json"
+        table = json.loads(path.read_text()) if path.exists() else {}
+        table[wl] = {"dram_bytes_per_launch": t, "from": out.name, "launches_averaged": len(traffic)}
+        path.write_text(json.dumps(table, indent=1, sort_keys=True) + "\n")
+        print(f"{wl}: traffic per launch {t:.0f} B")
 
 
 if __name__ == "__main__":
