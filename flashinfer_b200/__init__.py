@@ -12,7 +12,7 @@ from .decode import (
     fast_decode_plan,
     single_decode_with_kv_cache,
 )
-from .page import get_seq_lens
+from .page import append_paged_kv_cache, get_batch_indices_positions, get_seq_lens
 
 __version__ = "0.1.0"
 
@@ -26,4 +26,6 @@ __all__ = [
     "merge_states",
     "variable_length_merge_states",
     "get_seq_lens",
+    "get_batch_indices_positions",
+    "append_paged_kv_cache",
 ]

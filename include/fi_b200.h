@@ -189,6 +189,38 @@ FI_API int fi_variable_length_merge_states(const void* v, const float* s,
                                     int skip_empty, float out_scale, int device,
                                     void* stream);
 
+/* ---- page table maintenance: the step before decode in every iteration -------------------- */
+/*
+ * fi_get_batch_indices_positions — ragged append indptr -> per-token (batch index, position).
+ * Replaces the Triton get_batch_indices_positions_kernel launched by
+ * flashinfer.get_batch_indices_positions (flashinfer/page.py:169-221,
+ * flashinfer/triton/page.py:21-42):
+ *   batch_indices[j] = i,  positions[j] = j + seq_lens[i] - append_indptr[i+1]
+ *   for append_indptr[i] <= j < append_indptr[i+1].
+ * All pointers device int32; batch_indices / positions have nnz entries.
+ */
+FI_API int fi_get_batch_indices_positions(const int32_t* append_indptr, const int32_t* seq_lens,
+                                   int32_t* batch_indices, int32_t* positions, int batch_size,
+                                   int nnz, int device, void* stream);
+/*
+ * fi_append_paged_kv_cache — scatter nnz new (token, head) rows of K and V into the paged cache.
+ * Replaces append_paged_kv_cache (csrc/page.cu:24-110) -> AppendPagedKVCache /
+ * AppendPagedKVCacheKernel (include/flashinfer/page.cuh:254-287,370-420).
+ *  append_key/value  [nnz, Hkv, D], element strides (n, h), unit stride on D (may be views)
+ *  k_cache/v_cache   page pools with element strides (page, n, h) as in fi_batch_decode_run
+ *  row j goes to page kv_indices[kv_indptr[b] + pos / page_size], entry pos % page_size,
+ *  b = batch_indices[j], pos = positions[j] (the pages must already be allocated)
+ *  dtype: element type of BOTH the appended rows and the cache (any FI_DTYPE_*: rows are copied
+ *  as bytes, the reference requires the two dtypes to be equal as well, csrc/page.cu:45-52)
+ */
+FI_API int fi_append_paged_kv_cache(const void* append_key, const void* append_value,
+                             int64_t ak_stride_n, int64_t ak_stride_h, int64_t av_stride_n,
+                             int64_t av_stride_h, const int32_t* batch_indices,
+                             const int32_t* positions, int64_t nnz, void* k_cache, void* v_cache,
+                             int64_t kv_stride_page, int64_t kv_stride_n, int64_t kv_stride_h,
+                             const int32_t* kv_indices, const int32_t* kv_indptr, int num_kv_heads,
+                             int head_dim, int page_size, int dtype, int device, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
