@@ -299,7 +299,9 @@ def run_ours(args):
     from flashinfer_b200 import sharding
 
     try:
-        shard = sharding.head_shard(hq_all, hkv_all, rank, world)  # this rank's KV-head slice
+        # --shard-of N (development aid): time rank 0's slice of an N-way sharding on this one GPU
+        shard = sharding.head_shard(hq_all, hkv_all, rank, world) if args.shard_of <= 1 else \
+            sharding.head_shard(hq_all, hkv_all, 0, args.shard_of)
     except ValueError as e:
         raise SystemExit(str(e))
     hq, hkv = shard.num_qo_heads, shard.num_kv_heads
@@ -462,7 +464,9 @@ def emit(args, wl, world, ms_total, kern_ms, e2e_us, ag_us, h2d, d2h, launches, 
         "dtype": "bf16" if kv_es == 2 else "bf16 q/o, e4m3 kv", "data": "synthetic",
         "tokens_per_s": bs / (us_step * 1e-6),
         "hbm_tbps_whole_job": bytes_rank * world / (us_step * 1e-6) / 1e12,
-        "config": {"workload": f"{args.workload}: {wl['desc']}", "sharding": f"kv-head x{world}",
+        "config": {"workload": f"{args.workload}: {wl['desc']}",
+                   "sharding": f"kv-head x{world}" if args.shard_of <= 1 else
+                               f"ONE rank of a kv-head x{args.shard_of} sharding (not the whole job)",
                    "heads_per_rank": [hq, hkv], "page_table": "shuffled",
                    "l2": f"KV per rank {cache_bytes / 2**20:.0f} MiB > L2; {n_copies} cache "
                          f"cop{'y' if n_copies == 1 else 'ies'} rotated"},
@@ -494,6 +498,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--shard-of", type=int, default=1,
+                    help="development aid: run only rank 0's slice of an N-way KV-head sharding on one GPU")
     ap.add_argument("--cpu-reference", action="store_true",
                     help="--impl reference: time the CPU oracle port even when oracle/_ref and a GPU exist")
     args = ap.parse_args()
