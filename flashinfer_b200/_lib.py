@@ -38,7 +38,7 @@ PROTOTYPES = {
     "fi_last_loader": (_i, []),
     "fi_launch_count": (C.c_longlong, []),
     "fi_batch_decode_plan": (_i, [_vp, _sz, _vp, _vp, _sz, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
-                                  _i, _i, _i, _i, _i, _vp, _vp]),
+                                  _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "fi_batch_decode_run": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _i64,
                                  _vp, _vp, _vp, _vp, _f, _f, _f, _i, _i, _vp]),
     "fi_single_decode_run": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,

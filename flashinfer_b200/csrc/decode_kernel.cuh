@@ -232,6 +232,13 @@ struct Feeder {
   int4 v;
 };
 
+// is there nothing at all for this CTA to do?  (static plans: an empty head; plans with more items
+// than CTAs: every CTA draws tickets, an empty first item does not excuse it)
+__device__ __forceinline__ bool seg_source_idle(const SegSource& s) {
+  if (s.implicit) return s.count == 0;
+  return s.head_count == 0 && s.num_items <= (int)gridDim.x;
+}
+
 __device__ __forceinline__ void feeder_init(Feeder& f, const SegSource& s) {
   f.fin = s.implicit ? 1 : 0;
   f.pub = s.implicit ? s.count : min(s.head_count, kItemInlineSegs);
@@ -307,6 +314,9 @@ __device__ __forceinline__ void feeder_step(Feeder& f, const SegSource& s, int c
       f.nload = n;
       f.phase = 3;
     }
+  } else if (f.num_items <= (int)gridDim.x) {  // static plan: item blockIdx.x was all there is
+    f.fin = 1;
+    if (lane == 0) s.ctl[kQPub] = f.pub | kQFinal;
   } else if (space && f.tiles_pub - tiles_issued <= p.sched_lookahead) {
     if (lane == 0) f.ticket = atomicAdd(p.work_counter, 1);
     f.phase = 1;
@@ -1088,7 +1098,7 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   const SegSource src = seg_source_init(p, G::TT, seg_cache, scratch_ml, LOADER != 0);
   __syncthreads();
   FI_TRACE_IF(tid == 0, 1);
-  if (src.implicit ? src.count == 0 : src.head_count == 0) return;
+  if (seg_source_idle(src)) return;
   if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
   FI_TRACE_IF(tid == 0, 2);
 

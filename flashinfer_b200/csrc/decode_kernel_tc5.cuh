@@ -481,7 +481,7 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   tc5::fence_after_sync();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   FI_TRACE_IF(tid == 0, 1);
-  if (src.implicit ? src.count == 0 : src.head_count == 0) {
+  if (seg_source_idle(src)) {
     if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);
     return;
   }

@@ -123,8 +123,8 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
                          const int32_t* last_page_len_host, const int32_t* kv_len_host,
                          int batch_size, int num_qo_heads, int num_kv_heads, int head_dim,
                          int page_size, int q_dtype, int kv_dtype, int window_left,
-                         int cuda_graph, int device, int num_ctas_override, void* stream,
-                         int64_t* plan_info_out) {
+                         int cuda_graph, int fixed_split_pages, int disable_split_kv, int device,
+                         int num_ctas_override, void* stream, int64_t* plan_info_out) {
   static_assert(kPiLen <= FI_PLAN_INFO_LEN, "plan info vector too short");
   (void)float_ws;
   if (batch_size < 0 || num_qo_heads <= 0 || num_kv_heads <= 0 || page_size <= 0)
@@ -184,7 +184,34 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     tok_hi[b] = (int32_t)len;
     tile_b[b] = (int32_t)(lo / TT);
     ntile[b] = len == 0 ? 0 : (int32_t)((len + TT - 1) / TT - tile_b[b]);
-    total_tiles += (int64_t)ntile[b] * num_kv_heads;
+  }
+  // Batch-invariant modes (reference decode.py:880-887): with fixed_split_size every request is
+  // cut at multiples of S tokens from its start, each chunk is ONE indivisible segment whose
+  // arithmetic does not depend on what else is in the batch, and a request with more than one
+  // chunk is always merged from its chunk partials in chunk order; with disable_split_kv a unit
+  // is never cut at all.  Item boundaries then fall only between chunks (coarser balance).
+  const int64_t S = fixed_split_pages > 0 ? (int64_t)fixed_split_pages * page_size : 0;
+  const bool indivisible = S > 0 || disable_split_kv != 0;
+  auto chunk_count = [&](int b) -> int64_t {
+    if (ntile[b] == 0) return 0;
+    if (S <= 0) return 1;
+    return ((int64_t)tok_hi[b] + S - 1) / S - tok_lo[b] / S;
+  };
+  auto chunk_bounds = [&](int b, int64_t c, int32_t& lo, int32_t& hi) {
+    if (S <= 0) { lo = tok_lo[b]; hi = tok_hi[b]; return; }
+    const int64_t c0 = tok_lo[b] / S + c;
+    lo = (int32_t)std::max<int64_t>(tok_lo[b], c0 * S);
+    hi = (int32_t)std::min<int64_t>(tok_hi[b], (c0 + 1) * S);
+  };
+  for (int b = 0; b < batch_size; ++b) {
+    const int64_t nc = chunk_count(b);
+    int64_t t = 0;
+    for (int64_t c = 0; c < nc; ++c) {  // a tile shared by two chunks is streamed by both
+      int32_t lo, hi;
+      chunk_bounds(b, c, lo, hi);
+      t += (hi + TT - 1) / TT - lo / TT;
+    }
+    total_tiles += t * num_kv_heads;
   }
   if (total_tiles > 0x7fffffffLL) return fail(FI_ERR_INVALID_ARGUMENT, "too many KV tiles");
 
@@ -205,7 +232,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
       const int64_t rem = total_tiles - pos;
       int64_t chunk = first ? (total_tiles * st.f0_pct + 100LL * num_ctas - 1) / (100LL * num_ctas)
                             : (rem * st.g_pct + 100LL * num_ctas - 1) / (100LL * num_ctas);
-      if (first && st.f0_pct >= 100) chunk = (total_tiles + num_ctas - 1) / num_ctas;
+      if (first && (st.f0_pct >= 100 || indivisible)) chunk = (total_tiles + num_ctas - 1) / num_ctas;
       chunk = std::max<int64_t>(chunk, first ? min_tiles : st.tail_tiles);
       for (int i = 0; i < num_ctas && pos < total_tiles; ++i) {
         pos = std::min(total_tiles, pos + chunk);
@@ -221,7 +248,12 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   // (bs, heads) — CUDA-graph replays of an earlier run() stay valid after a re-plan; the two
   // variable-length arrays (item heads, segment list) come last -----------------------------
   const int64_t units = (int64_t)batch_size * num_kv_heads;
-  const int64_t max_segs = units + num_items;   // every item boundary adds at most one segment
+  // every item boundary adds at most one segment; fixed-split chunks are one segment each
+  int64_t max_segs = units + num_items;
+  if (S > 0) {
+    max_segs = 0;
+    for (int b = 0; b < batch_size; ++b) max_segs += std::max<int64_t>(chunk_count(b), 1) * num_kv_heads;
+  }
   const int64_t max_merge = std::max<int64_t>(units, 1);
   size_t off = 0;
   const size_t off_header = off;   off = align16(off + sizeof(PlanHeader));
@@ -263,28 +295,20 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   heads[0].first = 0;
   int64_t pos = 0;   // stream position (tiles)
   for (int b = 0; b < batch_size; ++b) {
+    const int64_t nc = chunk_count(b);
     for (int h = 0; h < num_kv_heads; ++h) {
-      const int64_t nt = ntile[b];
       Segment s;
       s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b]; s.merge_unit = -1;
       s.page_base = indptr_host[b]; s.merge_count = 0; s.merge_slot = 0; s.pad = 0;
-      if (nt == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
+      if (nc == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
         s.tile_begin = s.tile_end = 0; s.slot = -1;
         segs[nseg++] = s;
         continue;
       }
-      int64_t cur = pos;
-      const int64_t end = pos + nt;
       bool split_open = false;
-      while (cur < end) {
-        while (item_end[item] <= cur) {  // advance to the item that owns `cur`
-          ++item;
-          heads[item].first = (int32_t)nseg;
-        }
-        const int64_t e = std::min(end, item_end[item]);
-        const bool whole = (cur == pos && e == end);
-        s.tile_begin = tile_b[b] + (int32_t)(cur - pos);
-        s.tile_end = tile_b[b] + (int32_t)(e - pos);
+      auto emit = [&](int32_t tb, int32_t te, bool whole) {
+        s.tile_begin = tb;
+        s.tile_end = te;
         if (whole) {
           s.slot = -1;
           s.merge_unit = -1;
@@ -299,7 +323,32 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
           s.merge_unit = fused_merge ? (int32_t)(nmerge - 1) : -1;
         }
         segs[nseg++] = s;
-        cur = e;
+      };
+      for (int64_t c = 0; c < nc; ++c) {
+        int32_t lo, hi;
+        chunk_bounds(b, c, lo, hi);
+        const int32_t tb = lo / TT, te = (hi + TT - 1) / TT;
+        const int64_t end = pos + (te - tb);
+        while (item_end[item] <= pos) {  // advance to the item that owns `pos`
+          ++item;
+          heads[item].first = (int32_t)nseg;
+        }
+        if (indivisible) {  // the chunk is one segment of the item it starts in
+          s.tok_lo = lo; s.tok_hi = hi;
+          emit(tb, te, nc == 1);
+        } else {  // cut the unit at the item boundaries
+          int64_t cur = pos;
+          while (cur < end) {
+            while (item_end[item] <= cur) {
+              ++item;
+              heads[item].first = (int32_t)nseg;
+            }
+            const int64_t e = std::min(end, item_end[item]);
+            emit(tb + (int32_t)(cur - pos), tb + (int32_t)(e - pos), cur == pos && e == end);
+            cur = e;
+          }
+        }
+        pos = end;
       }
       if (split_open) {  // the unit's partials are its last `count` segments
         const MergeUnit& mu = merges[nmerge - 1];
@@ -308,10 +357,10 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
           segs[i].merge_slot = mu.slot_begin;
         }
       }
-      pos = end;
     }
   }
-  if (item + 1 != num_items || nseg > max_segs || nmerge > max_merge)
+  for (int64_t i = item + 1; i < num_items; ++i) heads[i].first = (int32_t)nseg;  // never reached
+  if (item + 1 > num_items || nseg > max_segs || nmerge > max_merge)
     return fail(FI_ERR_WORKSPACE, "internal planner overflow (%lld items, %lld segs, %lld merges)",
                 (long long)item + 1, (long long)nseg, (long long)nmerge);
   if ((size_t)nslot > slot_cap)

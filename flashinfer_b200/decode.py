@@ -338,6 +338,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._run_plan(
             indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads, head_dim,
             page_size, q_data_type, kv_data_type, window_left,
+            fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv,
         )
         del indptr_host, last_page_len_host, kv_len_host  # only needed during the call
 
@@ -351,7 +352,10 @@ class BatchDecodeWithPagedKVCacheWrapper:
     begin_forward = plan
 
     def _run_plan(self, indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
-                  head_dim, page_size, q_data_type, kv_data_type, window_left) -> None:
+                  head_dim, page_size, q_data_type, kv_data_type, window_left,
+                  fixed_split_size=None, disable_split_kv=False) -> None:
+        # fixed_split_size (pages) / disable_split_kv: batch-invariant planning, reference
+        # decode.py:880-887; None / -1 mean "off" there as here
         lib = _lib.load()
         info = torch.zeros(lib.fi_plan_info_len(), dtype=torch.int64)
         dev_idx = device_index(self.device)
@@ -367,7 +371,9 @@ class BatchDecodeWithPagedKVCacheWrapper:
                         * self._pin_memory_int_workspace_buffer.element_size()),
                     indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
                     head_dim, page_size, dtype_code(q_data_type), dtype_code(kv_data_type),
-                    int(window_left), int(self.is_cuda_graph_enabled), dev_idx, 0,
+                    int(window_left), int(self.is_cuda_graph_enabled),
+                    int(fixed_split_size) if fixed_split_size is not None and fixed_split_size > 0 else 0,
+                    int(bool(disable_split_kv)), dev_idx, 0,
                     current_stream_ptr(self.device), info.data_ptr(),
                 )
             )
@@ -633,7 +639,8 @@ def fast_decode_plan(
     self._num_kv_heads = num_kv_heads
     try:
         self._run_plan(indptr_ptr, last_page_len_host.data_ptr(), None, batch_size, num_qo_heads,
-                       num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left)
+                       num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left,
+                       fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv)
     except Exception as e:
         raise RuntimeError(f"Error in standard plan: {e}") from e
     self._pos_encoding_mode = pos_encoding_mode

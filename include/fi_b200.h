@@ -77,9 +77,9 @@ FI_API long long fi_launch_count(void);
  * Replaces: BatchDecodeWithPagedKVCachePlan (csrc/batch_decode.cu:39-79) ->
  *           DecodePlan (include/flashinfer/attention/scheduler.cuh:424-493).
  *
- * Cuts the flattened (request, kv-head, 64-token tile) stream into `num_ctas` equal
- * contiguous ranges (one per persistent CTA), emits per-CTA segments and the
- * split-KV merge metadata into `pinned_int_ws` (host) and issues ONE async H2D
+ * Cuts the flattened (request, kv-head, tile) stream into contiguous work items (by
+ * default `num_ctas` equal ranges, one per persistent CTA), emits item heads, segments
+ * and the split-KV merge metadata into `pinned_int_ws` (host) and issues an async H2D
  * copy into `int_ws` (device) on `stream`.
  *
  *  float_ws/float_ws_bytes   device scratch for split-KV partials (caller-owned)
@@ -88,8 +88,15 @@ FI_API long long fi_launch_count(void);
  *  last_page_len_host[bs]    host; may be NULL iff kv_len_host != NULL
  *  kv_len_host[bs]           optional explicit token lengths (host) or NULL
  *  window_left               <0: none; else only the last window_left+1 tokens
- *  cuda_graph                1: grid and all array extents are fixed by
- *                            (bs, num_ctas) only, so re-plans are graph-safe
+ *  cuda_graph                1: the grid and every offset run() passes to the kernels are
+ *                            fixed by (bs, heads, num_ctas) only, so re-plans are graph-safe
+ *  fixed_split_pages         >0: batch-invariant split (reference `fixed_split_size`,
+ *                            decode.py:880-885): every request is cut at multiples of
+ *                            this many pages from its start, chunks are never subdivided
+ *                            or fused, requests with more than one chunk are merged in
+ *                            chunk order; <=0: off
+ *  disable_split_kv          !=0: a (request, kv head) unit is never split (reference
+ *                            decode.py:886-887)
  *  num_ctas_override         >0: use this many CTAs along x instead of querying
  *                            the device (used by CPU-only tests; then `device`
  *                            may be -1 and no CUDA call is made: the H2D copy
@@ -103,9 +110,9 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
                          const int32_t* kv_len_host, int batch_size,
                          int num_qo_heads, int num_kv_heads, int head_dim,
                          int page_size, int q_dtype, int kv_dtype,
-                         int window_left, int cuda_graph, int device,
-                         int num_ctas_override, void* stream,
-                         int64_t* plan_info_out);
+                         int window_left, int cuda_graph, int fixed_split_pages,
+                         int disable_split_kv, int device, int num_ctas_override,
+                         void* stream, int64_t* plan_info_out);
 
 /*
  * fi_batch_decode_run — launches the decode kernel; split requests are merged

@@ -105,7 +105,8 @@ TILE_FP8 = 128   # ... and for fp8 KV
 
 def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size,
               num_ctas, q_dtype=1, kv_dtype=1, window_left=-1, cuda_graph=0,
-              kv_len=None, int_bytes=8 << 20, float_bytes=128 << 20):
+              kv_len=None, int_bytes=8 << 20, float_bytes=128 << 20, fixed_split_pages=0,
+              disable_split_kv=0):
     """Run fi_batch_decode_plan in host-only mode (device = -1) and decode the work list."""
     from flashinfer_b200 import _lib
 
@@ -118,8 +119,8 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
     rc = lib.fi_batch_decode_plan(
         None, float_bytes, ws.ctypes.data, ws.ctypes.data, int_bytes, ip.ctypes.data,
         lp.ctypes.data, None if kl is None else kl.ctypes.data, len(lp), num_qo_heads,
-        num_kv_heads, head_dim, page_size, q_dtype, kv_dtype, window_left, cuda_graph, -1,
-        num_ctas, None, info.ctypes.data)
+        num_kv_heads, head_dim, page_size, q_dtype, kv_dtype, window_left, cuda_graph,
+        fixed_split_pages, disable_split_kv, -1, num_ctas, None, info.ctypes.data)
     if rc != 0:
         return rc, _lib.last_error(), None
     hdr = ws[info[PI["off_header"]]:info[PI["off_header"]] + 32].view(np.int32)
@@ -161,7 +162,7 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
                        merges=merges, item_heads=heads)
 
 
-def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1, tile=TILE):
+def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1, tile=TILE, chunked=False):
     """Pure-Python replay of the work list: returns per-(request, head) token visit counts
     and checks the structural invariants.  Raises AssertionError on any inconsistency."""
     segs, merges, cta_indptr, hdr = plan["segments"], plan["merges"], plan["item_indptr"], plan["header"]
@@ -175,7 +176,10 @@ def replay_plan(plan, kv_lens, num_kv_heads, window_left=-1, tile=TILE):
         assert 0 <= r < bs and 0 <= h < num_kv_heads
         L = kv_lens[r]
         exp_lo = max(0, L - 1 - window_left) if window_left >= 0 else 0
-        assert lo == exp_lo and hi == L, (lo, hi, exp_lo, L)
+        if chunked:  # fixed_split_size: a segment attends its own chunk of the request
+            assert (exp_lo <= lo < hi <= L) or (lo == exp_lo and hi == L == 0) or L == 0, (lo, hi, exp_lo, L)
+        else:
+            assert lo == exp_lo and hi == L, (lo, hi, exp_lo, L)
         assert tb <= te
         a, b = max(tb * tile, lo), min(te * tile, hi)
         if b > a:

@@ -144,3 +144,43 @@ def test_plan_errors():
     assert rc == 2 and "workspace" in err.lower()
     rc, err, _ = host_plan(*lens_to_table([64] * 4096, 16), 8, 8, 128, 16, 148, int_bytes=4096)
     assert rc == 2 and "Increase the workspace buffer size" in err
+
+
+def _unit_segments(plan, r, h):
+    return [tuple(int(x) for x in s[2:7:1])[0:2] + (int(s[5]), int(s[6]))
+            for s in plan["segments"] if s[0] == r and s[1] == h]
+
+
+def test_plan_fixed_split_size_is_batch_invariant():
+    """fixed_split_size (reference decode.py:880-885): a request's chunks — hence the arithmetic
+    of its partials and the order they are merged in — do not depend on the rest of the batch."""
+    page, split_pages = 16, 24                      # 384 tokens: not a multiple of the 64-token tile
+    S = page * split_pages
+    target = 5000
+    alone = host_plan(*lens_to_table([target], page), 32, 8, 128, page, 296, fixed_split_pages=split_pages)[2]
+    batch_lens = [77, 30000, target, 1, 0, 2048, 385, 384]
+    batch = host_plan(*lens_to_table(batch_lens, page), 32, 8, 128, page, 296,
+                      fixed_split_pages=split_pages)[2]
+    replay_plan(alone, [target], 8, chunked=True)
+    replay_plan(batch, batch_lens, 8, chunked=True)
+    for h in range(8):
+        a, b = _unit_segments(alone, 0, h), _unit_segments(batch, 2, h)
+        assert a == b and len(a) == -(-target // S)
+        for c, (tb, te, lo, hi) in enumerate(a):    # chunk c covers tokens [c S, (c+1) S)
+            assert (lo, hi) == (c * S, min((c + 1) * S, target))
+            assert (tb, te) == (lo // TILE, -(-hi // TILE))
+    # one-chunk requests are written directly, multi-chunk requests always go through a merge
+    merged = {(int(m[0]), int(m[1])): int(m[3]) for m in batch["merges"]}
+    for r, L in enumerate(batch_lens):
+        for h in range(8):
+            chunks = -(-L // S) if L else 0
+            assert merged.get((r, h), 1 if chunks else 0) == (chunks if chunks > 1 else (1 if chunks else 0))
+
+
+def test_plan_disable_split_kv():
+    kv_lens = [40000, 3, 0, 900, 64]
+    plan = host_plan(*lens_to_table(kv_lens, 16), 16, 4, 128, 16, 296, disable_split_kv=1)[2]
+    replay_plan(plan, kv_lens, 4)
+    assert len(plan["merges"]) == 0 and plan["info"][PI["num_slots"]] == 0
+    assert len(plan["segments"]) == len(kv_lens) * 4            # one whole-unit segment each
+    assert all(int(s[4]) == -1 for s in plan["segments"])

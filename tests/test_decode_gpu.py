@@ -297,3 +297,51 @@ def test_dynamic_item_scheduler(knobs):
                        env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
+
+
+@pytest.mark.parametrize("kv_dtype", [torch.bfloat16, torch.float8_e4m3fn])
+def test_fixed_split_size_outputs_are_batch_invariant(kv_dtype):
+    """fixed_split_size (reference decode.py:880-885): the same request gives bit-identical o / lse
+    whether it is decoded alone or inside a batch of other requests, and matches the oracle."""
+    fi = _fi()
+    hq, hkv, d, page, split_pages = 32, 8, 128, 16, 24   # 384-token chunks (not tile-aligned)
+    lens = [77, 9000, 5000, 1, 0, 2048, 385, 384]
+    target = 2
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=21)
+    cache = cache.to(kv_dtype)
+    q = make_q(len(lens), hq, d, torch.bfloat16, seed=22)
+    cache_d, q_d = cache.to(DEV), q.to(DEV)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD", use_tensor_cores=True)
+    kw = dict(q_data_type=torch.bfloat16, kv_data_type=kv_dtype, fixed_split_size=split_pages)
+    w.plan(indptr, indices, last, hq, hkv, d, page, **kw)
+    o_b, lse_b = w.run(q_d, cache_d, return_lse=True)
+    # the target request alone: same pages, a one-request page table
+    lo, hi = int(indptr[target]), int(indptr[target + 1])
+    w.plan(torch.tensor([0, hi - lo], dtype=torch.int32), indices[lo:hi].contiguous(),
+           last[target:target + 1].contiguous(), hq, hkv, d, page, **kw)
+    o_a, lse_a = w.run(q_d[target:target + 1], cache_d, return_lse=True)
+    torch.cuda.synchronize()
+    assert torch.equal(o_a[0], o_b[target]) and torch.equal(lse_a[0], lse_b[target])
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, "NHD")
+    tol = O_TOL_FP8 if kv_dtype != torch.bfloat16 else O_TOL
+    assert (o_b.float().cpu() - o_ref).abs().max().item() <= tol
+    assert (lse_b.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+    # not a tensor-core wrapper: same error as the reference (decode.py:966-969)
+    w2 = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    with pytest.raises(ValueError):
+        w2.plan(indptr, indices, last, hq, hkv, d, page, **kw)
+
+
+def test_disable_split_kv_matches_oracle_and_never_merges():
+    fi = _fi()
+    hq, hkv, d, page = 16, 4, 128, 16
+    lens = [20000, 3, 0, 900, 64]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "HND", torch.float16, seed=31)
+    q = make_q(len(lens), hq, d, torch.float16, seed=32)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "HND")
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, disable_split_kv=True)
+    assert int(w._plan_info[3]) == 0 and int(w._plan_info[4]) == 0   # no merge units, no partial slots
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True)
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, "HND")
+    assert (o.float().cpu() - o_ref).abs().max().item() <= O_TOL
+    assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
