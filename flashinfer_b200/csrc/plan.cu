@@ -243,6 +243,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     if (item_end.empty()) item_end.push_back(0);  // only zero-tile segments (or none at all)
   }
   const int64_t num_items = (int64_t)item_end.size();
+  const int64_t* const item_end_p = item_end.data();  // not through the TLS wrapper in the hot loop
 
   // ---- layout: offsets of everything the kernels get as launch parameters depend only on
   // (bs, heads) — CUDA-graph replays of an earlier run() stay valid after a re-plan; the two
@@ -294,68 +295,74 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   int64_t item = 0;  // item currently being filled
   heads[0].first = 0;
   int64_t pos = 0;   // stream position (tiles)
+  // A segment is appended to the list and, when it is one of the first kItemInlineSegs of its
+  // item, also copied into the item head while it is still in registers.
+  auto push = [&](const Segment& sg) {
+    const int64_t k = nseg - heads[item].first;
+    if (k < kItemInlineSegs) heads[item].seg[k] = sg;
+    segs[nseg++] = sg;
+  };
+  auto own = [&](int64_t at) {  // advance to the item that owns stream position `at`
+    while (item_end_p[item] <= at) {
+      ++item;
+      heads[item].first = (int32_t)nseg;
+    }
+  };
   for (int b = 0; b < batch_size; ++b) {
     const int64_t nc = chunk_count(b);
     for (int h = 0; h < num_kv_heads; ++h) {
       Segment s;
-      s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b]; s.merge_unit = -1;
-      s.page_base = indptr_host[b]; s.merge_count = 0; s.merge_slot = 0; s.pad = 0;
+      s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b];
+      s.page_base = indptr_host[b]; s.pad = 0;
+      s.slot = -1; s.merge_unit = -1; s.merge_count = 0; s.merge_slot = 0;
       if (nc == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
-        s.tile_begin = s.tile_end = 0; s.slot = -1;
-        segs[nseg++] = s;
+        s.tile_begin = s.tile_end = 0;
+        push(s);
         continue;
       }
-      bool split_open = false;
-      auto emit = [&](int32_t tb, int32_t te, bool whole) {
-        s.tile_begin = tb;
-        s.tile_end = te;
-        if (whole) {
-          s.slot = -1;
-          s.merge_unit = -1;
-        } else {
-          s.slot = (int32_t)nslot++;
-          if (!split_open) {
-            MergeUnit mu = {b, h, s.slot, 0};
-            merges[nmerge++] = mu;
-            split_open = true;
-          }
-          merges[nmerge - 1].count++;
-          s.merge_unit = fused_merge ? (int32_t)(nmerge - 1) : -1;
-        }
-        segs[nseg++] = s;
-      };
+      // how many segments will this unit become?  (known up front, so that every partial can
+      // carry its unit's count / first slot and nothing has to be patched afterwards)
+      int64_t pieces = nc;
+      if (!indivisible) {
+        own(pos);
+        const int64_t end = pos + ntile[b];
+        int64_t k = item;
+        while (item_end_p[k] < end) ++k;
+        pieces = k - item + 1;
+      }
+      const bool split = pieces > 1;
+      if (split) {
+        MergeUnit mu = {b, h, (int32_t)nslot, (int32_t)pieces};
+        merges[nmerge] = mu;
+        s.merge_unit = fused_merge ? (int32_t)nmerge : -1;
+        s.merge_count = (int32_t)pieces;
+        s.merge_slot = (int32_t)nslot;
+        ++nmerge;
+      }
       for (int64_t c = 0; c < nc; ++c) {
         int32_t lo, hi;
         chunk_bounds(b, c, lo, hi);
         const int32_t tb = lo / TT, te = (hi + TT - 1) / TT;
         const int64_t end = pos + (te - tb);
-        while (item_end[item] <= pos) {  // advance to the item that owns `pos`
-          ++item;
-          heads[item].first = (int32_t)nseg;
-        }
+        own(pos);
         if (indivisible) {  // the chunk is one segment of the item it starts in
           s.tok_lo = lo; s.tok_hi = hi;
-          emit(tb, te, nc == 1);
+          s.tile_begin = tb; s.tile_end = te;
+          if (split) s.slot = (int32_t)nslot++;
+          push(s);
         } else {  // cut the unit at the item boundaries
           int64_t cur = pos;
           while (cur < end) {
-            while (item_end[item] <= cur) {
-              ++item;
-              heads[item].first = (int32_t)nseg;
-            }
-            const int64_t e = std::min(end, item_end[item]);
-            emit(tb + (int32_t)(cur - pos), tb + (int32_t)(e - pos), cur == pos && e == end);
+            own(cur);
+            const int64_t e = std::min(end, item_end_p[item]);
+            s.tile_begin = tb + (int32_t)(cur - pos);
+            s.tile_end = tb + (int32_t)(e - pos);
+            if (split) s.slot = (int32_t)nslot++;
+            push(s);
             cur = e;
           }
         }
         pos = end;
-      }
-      if (split_open) {  // the unit's partials are its last `count` segments
-        const MergeUnit& mu = merges[nmerge - 1];
-        for (int64_t i = nseg - mu.count; i < nseg; ++i) {
-          segs[i].merge_count = mu.count;
-          segs[i].merge_slot = mu.slot_begin;
-        }
       }
     }
   }
@@ -375,8 +382,6 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     hd.count = (int32_t)((i + 1 < num_items ? heads[i + 1].first : nseg) - hd.first);
     hd.num_items = (int32_t)num_items;
     hd.pad = 0;
-    // inline copies of the first segments; the kernel never reads past `count`
-    for (int j = 0; j < kItemInlineSegs && j < hd.count; ++j) hd.seg[j] = segs[hd.first + j];
   }
   // arrival counters of the fused merge: zeroed by every plan (the workspace is not guaranteed
   // to be zero-initialised) and returned to zero by the kernel itself
