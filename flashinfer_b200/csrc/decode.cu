@@ -280,8 +280,8 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
                         const void* v_cache, int64_t num_pages, int64_t kv_stride_page,
                         int64_t kv_stride_n, int64_t kv_stride_h, const int32_t* kv_indices,
                         const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
-                        float v_scale, float logits_soft_cap, int enable_pdl, int device,
-                        void* stream_) {
+                        float v_scale, float logits_soft_cap, const float* alibi_slopes,
+                        int enable_pdl, int device, void* stream_) {
   if (plan_info == nullptr || plan_info[kPiMagic] != kPlanMagic)
     return fail(FI_ERR_INVALID_ARGUMENT, "plan info is not initialized");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -330,6 +330,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
   p.v_scale = v_scale;
   p.soft_cap = logits_soft_cap;
+  p.alibi_slopes = alibi_slopes;
   p.enable_pdl = enable_pdl;
 
   const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
@@ -382,8 +383,8 @@ size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int head_d
 int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp, size_t tmp_bytes,
                          void* o, float* lse, int num_qo_heads, int num_kv_heads, int head_dim,
                          int kv_len, int q_dtype, int kv_dtype, int kv_layout, int window_left,
-                         float sm_scale, float v_scale, float logits_soft_cap, int device,
-                         void* stream_) {
+                         float sm_scale, float v_scale, float logits_soft_cap,
+                         const float* alibi_slopes, int device, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (num_kv_heads <= 0 || num_qo_heads % num_kv_heads)
     return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads must be a multiple of num_kv_heads");
@@ -433,7 +434,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.num_qo_heads = num_qo_heads; p.group_size = group;
   p.num_stages = cfg.stages;
   p.sm_scale = sm_scale; p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
-  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0;
+  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.alibi_slopes = alibi_slopes; p.enable_pdl = 0;
 
   const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
   CUtensorMap km, vm;

@@ -802,6 +802,20 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
         pre[0] = d0 * cap_pre; pre[1] = d1 * cap_pre;
       }
     }
+    // ALiBi (reference variants.cuh:68-71, qo_idx = 0 as decode.cuh:95 passes it):
+    // logit = q.k * sm_scale + slope[head] * kv position; alc is the slope in the units of the
+    // expression it is added to (base-2 logits, or the tanh argument when soft-capped, where the
+    // reference multiplies the biased logit by sm_scale / cap once more)
+    float alc[2] = {0.f, 0.f};
+    if (p.alibi_slopes != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int h = 2 * t + j;
+        const float a = h < GS ? __ldg(p.alibi_slopes + sg.kv_head * GS + h) : 0.f;
+        alc[j] = a * (use_cap ? cap_pre : 1.4426950408889634f);
+        pre[j] *= p.sm_scale;
+      }
+    }
     float o[MT][4];
 #pragma unroll
     for (int i = 0; i < MT; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
@@ -833,10 +847,12 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
           const int ta = tok0 + g, tb = ta + 8;
           const bool va = ta >= sg.tok_lo && ta < sg.tok_hi;
           const bool vb = tb >= sg.tok_lo && tb < sg.tok_hi;
+          const float pf[2] = {(float)ta, (float)tb};
           float x[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i)
-            x[i] = use_cap ? cap_post * tanhf_approx(s[i] * pre[i & 1]) : s[i] * mul[i & 1];
+            x[i] = use_cap ? cap_post * tanhf_approx(s[i] * pre[i & 1] + alc[i & 1] * pf[i >> 1])
+                           : s[i] * mul[i & 1] + alc[i & 1] * pf[i >> 1];
           x[0] = va ? x[0] : kNegInf; x[1] = va ? x[1] : kNegInf;
           x[2] = vb ? x[2] : kNegInf; x[3] = vb ? x[3] : kNegInf;
           float mx[2] = {fmaxf(x[0], x[2]), fmaxf(x[1], x[3])};
@@ -882,7 +898,8 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 #pragma unroll
               for (int j = 0; j < 2; ++j) {
                 float& x = s[mb][2 * h + j];
-                x = use_cap ? cap_post * tanhf_approx(x * pre[j]) : x * mul[j];
+                x = use_cap ? cap_post * tanhf_approx(x * pre[j] + alc[j] * (float)tk)
+                            : x * mul[j] + alc[j] * (float)tk;
                 x = valid[mb][h] ? x : kNegInf;
                 mx[j] = fmaxf(mx[j], x);
               }

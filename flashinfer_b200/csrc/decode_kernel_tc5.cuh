@@ -244,6 +244,17 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
       mul[j] = d * p.sm_scale_log2;
       pre[j] = d * cap_pre;
     }
+    float alc[8];  // ALiBi slope per head, in the units of the expression it is added to
+#pragma unroll
+    for (int j = 0; j < 8; ++j) alc[j] = 0.f;
+    if (p.alibi_slopes != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float a = j < GS ? __ldg(p.alibi_slopes + sg.kv_head * GS + j) : 0.f;
+        alc[j] = a * (use_cap ? cap_pre : 1.4426950408889634f);
+        pre[j] *= p.sm_scale;
+      }
+    }
     have_q = src.ctl[kQPeek] != 0;
     if (have_q) {
       const Segment sn = seg_read(src, k + 1);
@@ -274,7 +285,8 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float sdot = c[j] + c[8 + j] + c[16 + j];
-          const float v = use_cap ? cap_post * tanhf_approx(sdot * pre[j]) : sdot * mul[j];
+          const float v = use_cap ? cap_post * tanhf_approx(sdot * pre[j] + alc[j] * (float)tok)
+                                  : sdot * mul[j] + alc[j] * (float)tok;
           x[j] = valid ? v : kNegInf;
         }
       }

@@ -152,6 +152,7 @@ struct DecodeParams {
   float sm_scale_log2;     // sm_scale * log2(e)
   float v_scale;
   float soft_cap;          // <= 0 disabled
+  const float* alibi_slopes;  // [num_qo_heads] or null: logit += slope[head] * kv position (ALiBi)
   float sm_scale;          // plain sm_scale (soft-cap path)
   int32_t enable_pdl;
 };

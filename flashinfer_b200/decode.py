@@ -22,6 +22,7 @@ from .utils import (
     _check_cached_qkv_data_type,
     _check_kv_layout,
     _check_pos_encoding_mode,
+    _get_cache_alibi_slopes_buf,
     _get_cache_buf,
     _get_range_buf,
     _unpack_paged_kv_cache,
@@ -46,12 +47,21 @@ def _host_i32_ptr(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
 
 def _unsupported_variant(pos_encoding_mode: str) -> None:
     _check_pos_encoding_mode(pos_encoding_mode)
-    if pos_encoding_mode != "NONE":
-        # in-kernel RoPE / ALiBi are "next" rows, not built yet.
+    if pos_encoding_mode not in ("NONE", "ALIBI"):
+        # in-kernel RoPE is a "next" row, not built (serving engines rotate q / k
+        # before the cache write; the reference's own callers pass "NONE").
         raise NotImplementedError(
             f"pos_encoding_mode={pos_encoding_mode!r} is not implemented by flashinfer_b200 "
             "(apply RoPE to q/k before the call)"
         )
+
+
+def _alibi_slopes_ptr(pos_encoding_mode: str, num_qo_heads: int, device: torch.device):
+    """Device pointer of the cached ALiBi slopes (reference decode.py:530,1306:
+    `_get_cache_alibi_slopes_buf`) when the mode is "ALIBI", else None."""
+    if pos_encoding_mode != "ALIBI":
+        return None
+    return _get_cache_alibi_slopes_buf(num_qo_heads, device).data_ptr()
 
 
 def single_decode_with_kv_cache(
@@ -122,7 +132,8 @@ def single_decode_with_kv_cache(
             num_qo_heads, num_kv_heads, head_dim, kv_len,
             dtype_code(q.dtype), dtype_code(k.dtype), TensorLayout[kv_layout].value,
             window_left, float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
-            float(logits_soft_cap), dev_idx, current_stream_ptr(dev),
+            float(logits_soft_cap), _alibi_slopes_ptr(pos_encoding_mode, num_qo_heads, dev),
+            dev_idx, current_stream_ptr(dev),
         )
     )
     return (o, lse) if return_lse else o
@@ -192,6 +203,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._use_cuda_graph = use_cuda_graph
         self._backend = backend
         self._plan_info: Optional[torch.Tensor] = None
+        self._pos_encoding_mode = "NONE"
 
     @property
     def use_tensor_cores(self) -> bool:
@@ -397,6 +409,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         rope_theta: Optional[float] = None,
     ) -> torch.Tensor:
         r"""Deprecated alias of :meth:`run` (reference decode.py:1106-1133)."""
+        _unsupported_variant(pos_encoding_mode)
         self._pos_encoding_mode = pos_encoding_mode
         self._window_left = window_left
         self._logits_soft_cap = logits_soft_cap
@@ -504,7 +517,9 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 self._indptr_dev.data_ptr() if self._indptr_dev is not None else None,
                 out.data_ptr(), lse.data_ptr() if return_lse else None,
                 float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
-                float(logits_soft_cap), int(bool(enable_pdl)), device_index(dev),
+                float(logits_soft_cap),
+                _alibi_slopes_ptr(self._pos_encoding_mode, q.shape[1], dev),
+                int(bool(enable_pdl)), device_index(dev),
                 current_stream_ptr(dev),
             )
         )
@@ -527,6 +542,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         rope_theta: Optional[float] = None,
     ) -> Tuple[torch.Tensor, torch.Tensor]:
         r"""Deprecated alias of :meth:`run_return_lse` (reference decode.py:1376-1403)."""
+        _unsupported_variant(pos_encoding_mode)
         self._pos_encoding_mode = pos_encoding_mode
         self._window_left = window_left
         self._logits_soft_cap = logits_soft_cap

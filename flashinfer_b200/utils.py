@@ -93,6 +93,28 @@ def _get_cache_buf(name: str, bytes: int, device: torch.device) -> torch.Tensor:
     return buf
 
 
+def get_alibi_slopes(n_heads: int) -> torch.Tensor:
+    """ALiBi head slopes (reference flashinfer/utils.py:172-180): 2^(-8 i / n) for the largest
+    power of two n <= n_heads, interleaved 2^(-4 (2j - 1) / n) for the remaining heads."""
+    n = 2 ** math.floor(math.log2(n_heads))
+    m_0 = 2.0 ** (-8.0 / n)
+    m = torch.pow(m_0, torch.arange(1, 1 + n))
+    if n < n_heads:
+        m_hat_0 = 2.0 ** (-4.0 / n)
+        m_hat = torch.pow(m_hat_0, torch.arange(1, 1 + 2 * (n_heads - n), 2))
+        m = torch.cat([m, m_hat])
+    return m.float()
+
+
+def _get_cache_alibi_slopes_buf(num_qo_heads: int, device: torch.device) -> torch.Tensor:
+    key = (f"alibi_slopes_{num_qo_heads}", device)
+    buf = _cache_buf.get(key)
+    if buf is None:
+        buf = get_alibi_slopes(num_qo_heads).to(device)
+        _cache_buf[key] = buf
+    return buf
+
+
 def _ceil_pow2(x: int) -> int:
     return 1 << (x - 1).bit_length()
 

@@ -134,6 +134,9 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
  *  sm_scale     already multiplied by q_scale*k_scale (decode.py:1250-1256)
  *  v_scale      multiplies the output (fused; reference: decode.py:1367-1372)
  *  logits_soft_cap  <=0: disabled
+ *  alibi_slopes     device f32 [Hq] or NULL.  Non-NULL selects the reference's ALiBi variant
+ *                   (variants.cuh:68-71 with qo_idx = 0 as passed by decode.cuh:95-96):
+ *                   logit = q.k * sm_scale + alibi_slopes[head] * kv_position
  */
 FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info,
                         const void* q, int64_t q_stride_n, int64_t q_stride_h,
@@ -142,7 +145,7 @@ FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan
                         int64_t kv_stride_h, const int32_t* kv_indices,
                         const int32_t* kv_indptr, void* o, float* lse,
                         float sm_scale, float v_scale, float logits_soft_cap,
-                        int enable_pdl, int device, void* stream);
+                        const float* alibi_slopes, int enable_pdl, int device, void* stream);
 
 /*
  * fi_single_decode_run — one request, contiguous K/V.
@@ -158,7 +161,8 @@ FI_API int fi_single_decode_run(const void* q, const void* k, const void* v, voi
                          int num_kv_heads, int head_dim, int kv_len,
                          int q_dtype, int kv_dtype, int kv_layout,
                          int window_left, float sm_scale, float v_scale,
-                         float logits_soft_cap, int device, void* stream);
+                         float logits_soft_cap, const float* alibi_slopes, int device,
+                         void* stream);
 FI_API size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int head_dim,
                                   int device);
 

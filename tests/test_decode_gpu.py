@@ -345,3 +345,89 @@ def test_disable_split_kv_matches_oracle_and_never_merges():
     o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, "HND")
     assert (o.float().cpu() - o_ref).abs().max().item() <= O_TOL
     assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+
+
+# ---------------------------------------------------------------- ALiBi
+def _alibi_golden():
+    from pathlib import Path
+
+    z = np.load(Path(__file__).resolve().parent / "golden" / "alibi_golden.npz")
+    return z, [str(n) for n in z["names"]]
+
+
+def _alibi_lse_ok(lse, lse_ref):
+    # ALiBi logits grow with the position (slope * 4098 * log2 e ~ 5000 in base 2), where one f32
+    # ulp is already 5e-4: the 1e-3 gate gets a 4-ulp relative term
+    return bool(((lse - lse_ref).abs() <= LSE_TOL + lse_ref.abs() * 2.0 ** -21).all())
+
+
+@pytest.mark.parametrize("name", _alibi_golden()[1])
+def test_single_decode_alibi_against_reference_golden(name):
+    """reference tests/attention/test_alibi.py:55-70 with its oracle's outputs as fixtures"""
+    fi = _fi()
+    z, _ = _alibi_golden()
+    H, D, L, is_bf16 = [int(x) for x in z[f"{name}/meta"]]
+    dt = torch.bfloat16 if is_bf16 else torch.float16
+    q, k, v, o_gold = (torch.from_numpy(z[f"{name}/{key}"].copy()).view(dt) for key in ("q", "k", "v", "o"))
+    o = fi.single_decode_with_kv_cache(q.to(DEV), k.to(DEV), v.to(DEV), pos_encoding_mode="ALIBI")
+    torch.testing.assert_close(o.cpu().float(), o_gold.float(), rtol=1e-3 if not is_bf16 else 1e-2,
+                               atol=1e-3 if not is_bf16 else 1e-2)
+    o2, lse = fi.single_decode_with_kv_cache(q.to(DEV), k.to(DEV), v.to(DEV), pos_encoding_mode="ALIBI",
+                                             return_lse=True)
+    slopes = torch.from_numpy(z[f"{name}/slopes"].copy())
+    o_ref, lse_ref = orc.decode_attention_ref(q, k, v, alibi_slopes=slopes)
+    assert (o2.float().cpu() - o_ref).abs().max().item() <= O_TOL
+    assert _alibi_lse_ok(lse.cpu(), lse_ref)
+
+
+@pytest.mark.parametrize("kv_dtype,loader", [(None, 1), (None, 2), (torch.float8_e4m3fn, 1),
+                                             (torch.float8_e4m3fn, 2)])
+@pytest.mark.parametrize("soft_cap,window_left", [(None, -1), (30.0, -1), (None, 300)])
+def test_batch_decode_alibi(kv_dtype, loader, soft_cap, window_left):
+    fi = _fi()
+    from flashinfer_b200 import _lib
+    from flashinfer_b200.utils import get_alibi_slopes
+
+    hq, hkv, d, page = 32, 8, 128, 16
+    lens = [1, 54, 97, 512, 2048, 0, 4099, 777]
+    q_dtype = torch.bfloat16
+    kvd = kv_dtype or q_dtype
+    is8 = kv_dtype is not None
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=41)
+    k_scale = v_scale = None
+    if is8:
+        k_scale = float(cache[:, 0].abs().amax() / 256)
+        v_scale = float(cache[:, 1].abs().amax() / 256)
+        cache[:, 0] /= k_scale
+        cache[:, 1] /= v_scale
+    cache = cache.to(kvd)
+    q = make_q(len(lens), hq, d, q_dtype, seed=42)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    _lib.load().fi_set_tuning(0, 0, loader, 0)
+    try:
+        w.plan(indptr, indices, last, hq, hkv, d, page, pos_encoding_mode="ALIBI", q_data_type=q_dtype,
+               kv_data_type=kvd, logits_soft_cap=soft_cap, window_left=window_left)
+        o, lse = w.run(q.to(DEV), cache.to(DEV), k_scale=k_scale, v_scale=v_scale, return_lse=True)
+        torch.cuda.synchronize()
+    finally:
+        _lib.load().fi_set_tuning(0, 0, 0, 0)
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, "NHD", k_scale=k_scale or 1.0,
+                                          v_scale=v_scale or 1.0, logits_soft_cap=soft_cap or 0.0,
+                                          window_left=window_left, alibi_slopes=get_alibi_slopes(hq))
+    assert (o.float().cpu() - o_ref).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+    assert _alibi_lse_ok(lse.cpu(), lse_ref), (lse.cpu() - lse_ref).abs().max().item()
+    # the mode given to plan() sticks; NONE afterwards gives a different answer again
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=q_dtype, kv_data_type=kvd,
+           logits_soft_cap=soft_cap, window_left=window_left)
+    o_none = w.run(q.to(DEV), cache.to(DEV), k_scale=k_scale, v_scale=v_scale)
+    assert (o_none.float().cpu() - o_ref).abs().max().item() > 1e-2
+
+
+def test_rope_modes_are_rejected():
+    fi = _fi()
+    q = torch.zeros(8, 128, dtype=torch.float16, device=DEV)
+    k = torch.zeros(16, 2, 128, dtype=torch.float16, device=DEV)
+    with pytest.raises(NotImplementedError):
+        fi.single_decode_with_kv_cache(q, k, k, pos_encoding_mode="ROPE_LLAMA")
+    with pytest.raises(KeyError):
+        fi.single_decode_with_kv_cache(q, k, k, pos_encoding_mode="SOMETHING")

@@ -1,6 +1,7 @@
 """CPU: the oracle restatement (oracle/attention_ref.py) against the golden vectors produced
 by the reference's own test oracle, plus internal consistency of the merge restatements."""
 import math
+from pathlib import Path
 
 import numpy as np
 import pytest
@@ -93,3 +94,30 @@ def test_reference_uniform_chunking_covers_everything():
     assert split and chunk == 1024 and len(req) == 256  # SURVEY.md §8(a3) C2 figure
     split, chunk, req, tile = orc.reference_uniform_chunking([4] * 512, 8, 2368, 16)
     assert not split and len(req) == 512
+
+
+# ---------------------------------------------------------------- ALiBi
+def _alibi_cases():
+    z = np.load(Path(__file__).resolve().parent / "golden" / "alibi_golden.npz")
+    return z, [str(n) for n in z["names"]]
+
+
+def _alibi_inputs(z, name):
+    H, D, L, is_bf16 = [int(x) for x in z[f"{name}/meta"]]
+    dt = torch.bfloat16 if is_bf16 else torch.float16
+    q, k, v, o = (torch.from_numpy(z[f"{name}/{key}"].copy()).view(dt) for key in ("q", "k", "v", "o"))
+    return q, k, v, o, torch.from_numpy(z[f"{name}/slopes"].copy())
+
+
+@pytest.mark.parametrize("name", _alibi_cases()[1])
+def test_oracle_alibi_matches_reference_alibi_attention(name):
+    """oracle ALiBi == the reference's own alibi_attention (tests/test_helpers/alibi_reference.py),
+    executed in the build container by tests/golden/make_golden_alibi.py; slopes == its get_slopes."""
+    from flashinfer_b200.utils import get_alibi_slopes
+
+    z, _ = _alibi_cases()
+    q, k, v, o_gold, slopes = _alibi_inputs(z, name)
+    assert torch.equal(get_alibi_slopes(q.shape[0]), slopes)
+    o, _ = orc.decode_attention_ref(q, k, v, alibi_slopes=slopes)
+    # the golden output was rounded to q's dtype by the reference function
+    assert torch.equal(o.to(q.dtype), o_gold) or (o - o_gold.float()).abs().max().item() <= 2e-3
