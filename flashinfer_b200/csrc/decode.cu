@@ -14,6 +14,7 @@
 
 #include "decode_kernel.cuh"
 #include "decode_kernel_tc5.cuh"
+#include "decode_rope_kernel.cuh"
 #include "host_common.h"
 #include "merge_kernels.cuh"
 
@@ -214,10 +215,39 @@ static bool use_tc5() {
   return on;
 }
 
+// pos_encoding_mode = ROPE_LLAMA: the CUDA-core variant kernel (decode_rope_kernel.cuh)
+template <int QT, int KVF>
+static int launch_rope(const DecodeParams& p, int head_dim, int grid, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kRopeThreads);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.enable_pdl ? 1 : 0;
+  switch (head_dim) {
+    case 64: FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 64>, p)); break;
+    case 128: FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 128>, p)); break;
+    case 256: FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 256>, p)); break;
+    default: return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
+  }
+  return FI_OK;
+}
+
 static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                          int q_dtype, int kvf, int head_dim, int grid, bool tma,
                          cudaStream_t stream) {
   const bool bf = q_dtype == FI_DTYPE_BF16;
+  if (p.rope) {
+    switch (kvf) {
+      case 0: return bf ? launch_rope<1, 0>(p, head_dim, grid, stream) : launch_rope<0, 0>(p, head_dim, grid, stream);
+      case 1: return bf ? launch_rope<1, 1>(p, head_dim, grid, stream) : launch_rope<0, 1>(p, head_dim, grid, stream);
+      case 2: return bf ? launch_rope<1, 2>(p, head_dim, grid, stream) : launch_rope<0, 2>(p, head_dim, grid, stream);
+      default: return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
+    }
+  }
   if (kvf != 0 && head_dim == 128 && tma && use_tc5()) {
     if (kvf == 1) return bf ? launch_tc5<1, 1>(p, km, vm, grid, stream) : launch_tc5<0, 1>(p, km, vm, grid, stream);
     return bf ? launch_tc5<1, 2>(p, km, vm, grid, stream) : launch_tc5<0, 2>(p, km, vm, grid, stream);
@@ -247,6 +277,16 @@ static int launch_merge(const MergeParams& mp, int grid, cudaStream_t stream) {
   cfg.numAttrs = mp.enable_pdl ? 1 : 0;
   if (mp.out_dtype == FI_DTYPE_BF16) FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, decode_merge_kernel<1>, mp));
   else FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, decode_merge_kernel<0>, mp));
+  return FI_OK;
+}
+
+static int check_pos_mode(int mode, const float* alibi_slopes, float rope_scale, float rope_theta) {
+  if (mode != FI_POS_NONE && mode != FI_POS_ROPE_LLAMA && mode != FI_POS_ALIBI)
+    return fail(FI_ERR_INVALID_ARGUMENT, "invalid pos_encoding_mode %d", mode);
+  if (mode == FI_POS_ALIBI && alibi_slopes == nullptr)
+    return fail(FI_ERR_INVALID_ARGUMENT, "ALIBI needs alibi_slopes");
+  if (mode == FI_POS_ROPE_LLAMA && !(rope_scale > 0.f && rope_theta > 0.f))
+    return fail(FI_ERR_INVALID_ARGUMENT, "ROPE_LLAMA needs rope_scale > 0 and rope_theta > 0");
   return FI_OK;
 }
 
@@ -280,8 +320,10 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
                         const void* v_cache, int64_t num_pages, int64_t kv_stride_page,
                         int64_t kv_stride_n, int64_t kv_stride_h, const int32_t* kv_indices,
                         const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
-                        float v_scale, float logits_soft_cap, const float* alibi_slopes,
+                        float v_scale, float logits_soft_cap, int pos_encoding_mode,
+                        const float* alibi_slopes, float rope_scale, float rope_theta,
                         int enable_pdl, int device, void* stream_) {
+  if (int rc = check_pos_mode(pos_encoding_mode, alibi_slopes, rope_scale, rope_theta)) return rc;
   if (plan_info == nullptr || plan_info[kPiMagic] != kPlanMagic)
     return fail(FI_ERR_INVALID_ARGUMENT, "plan info is not initialized");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -330,7 +372,11 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
   p.v_scale = v_scale;
   p.soft_cap = logits_soft_cap;
-  p.alibi_slopes = alibi_slopes;
+  p.alibi_slopes = pos_encoding_mode == FI_POS_ALIBI ? alibi_slopes : nullptr;
+  p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
+  p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
+  if (p.rope && plan_info[kPiNumItems] > plan_info[kPiNumCtas])
+    return fail(FI_ERR_UNSUPPORTED, "ROPE_LLAMA decode needs a static plan (unset FI_B200_SCHED_F0)");
   p.enable_pdl = enable_pdl;
 
   const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
@@ -384,7 +430,9 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
                          void* o, float* lse, int num_qo_heads, int num_kv_heads, int head_dim,
                          int kv_len, int q_dtype, int kv_dtype, int kv_layout, int window_left,
                          float sm_scale, float v_scale, float logits_soft_cap,
-                         const float* alibi_slopes, int device, void* stream_) {
+                         int pos_encoding_mode, const float* alibi_slopes, float rope_scale,
+                         float rope_theta, int device, void* stream_) {
+  if (int rc = check_pos_mode(pos_encoding_mode, alibi_slopes, rope_scale, rope_theta)) return rc;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (num_kv_heads <= 0 || num_qo_heads % num_kv_heads)
     return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads must be a multiple of num_kv_heads");
@@ -434,7 +482,10 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.num_qo_heads = num_qo_heads; p.group_size = group;
   p.num_stages = cfg.stages;
   p.sm_scale = sm_scale; p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
-  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.alibi_slopes = alibi_slopes; p.enable_pdl = 0;
+  p.v_scale = v_scale; p.soft_cap = logits_soft_cap; p.enable_pdl = 0;
+  p.alibi_slopes = pos_encoding_mode == FI_POS_ALIBI ? alibi_slopes : nullptr;
+  p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
+  p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
 
   const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
   CUtensorMap km, vm;

@@ -125,7 +125,8 @@ __device__ __forceinline__ Segment seg_make(const SegSource& s, int k) {
   const DecodeParams& p = *s.p;
   Segment g;
   g.request = 0; g.merge_unit = -1; g.page_base = 0;
-  g.tok_lo = p.imp_tok_lo; g.tok_hi = p.imp_tok_hi;
+  g.merge_count = 0; g.merge_slot = 0;
+  g.tok_lo = p.imp_tok_lo; g.tok_hi = p.imp_tok_hi; g.kv_len = p.imp_tok_hi;
   const int nt = p.imp_tiles;
   if (nt == 0) {
     g.kv_head = k; g.tile_begin = g.tile_end = 0; g.slot = -1;
@@ -142,6 +143,23 @@ __device__ __forceinline__ Segment seg_make(const SegSource& s, int k) {
     g.slot = whole ? -1 : (int)(blockIdx.x + u);
   }
   return g;
+}
+
+// implicit mode: this CTA's share of the closed-form uniform split
+__device__ __forceinline__ void seg_source_implicit_range(SegSource& s) {
+  const DecodeParams& p = *s.p;
+  const long long T = (long long)p.imp_units * p.imp_tiles;
+  const long long C = gridDim.x;
+  s.count = 0;
+  s.imp_begin = s.imp_end = 0;
+  if (T == 0) {
+    s.count = (blockIdx.x == 0) ? p.imp_units : 0;  // empty KV: zero-tile segments
+  } else {
+    s.imp_begin = ((long long)blockIdx.x * T) / C;
+    s.imp_end = ((long long)(blockIdx.x + 1) * T) / C;
+    if (s.imp_end > s.imp_begin)
+      s.count = (int)((s.imp_end - 1) / p.imp_tiles - s.imp_begin / p.imp_tiles) + 1;
+  }
 }
 
 // Called by every thread of the CTA before the first __syncthreads(): reads the head of item
@@ -169,16 +187,7 @@ __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int 
     if (tid < 3 * pub0)
       reinterpret_cast<int4*>(cache)[tid] = __ldg(reinterpret_cast<const int4*>(head->seg) + tid);
   } else {
-    const long long T = (long long)p.imp_units * p.imp_tiles;
-    const long long C = gridDim.x;
-    if (T == 0) {
-      s.count = (blockIdx.x == 0) ? p.imp_units : 0;  // empty KV: zero-tile segments
-    } else {
-      s.imp_begin = ((long long)blockIdx.x * T) / C;
-      s.imp_end = ((long long)(blockIdx.x + 1) * T) / C;
-      if (s.imp_end > s.imp_begin)
-        s.count = (int)((s.imp_end - 1) / p.imp_tiles - s.imp_begin / p.imp_tiles) + 1;
-    }
+    seg_source_implicit_range(s);
     for (int i = tid; i < min(s.count, kSegCache); i += blockDim.x) cache[i] = seg_make(s, i);
     pub0 = s.count | kQFinal;
   }

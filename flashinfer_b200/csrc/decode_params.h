@@ -41,7 +41,7 @@ struct alignas(16) Segment {
   int32_t page_base;   // kv_indptr[request]: first entry of the request in the page table
   int32_t merge_count; // copy of MergeUnit::count / slot_begin of `merge_unit`, so that the
   int32_t merge_slot;  //   fused merge never has to load the MergeUnit record
-  int32_t pad;
+  int32_t kv_len;      // the request's full KV length (tok_hi may be a chunk end): RoPE q position
 };
 static_assert(sizeof(Segment) == 48, "Segment must be 48 bytes");
 
@@ -153,6 +153,8 @@ struct DecodeParams {
   float v_scale;
   float soft_cap;          // <= 0 disabled
   const float* alibi_slopes;  // [num_qo_heads] or null: logit += slope[head] * kv position (ALiBi)
+  int32_t rope;               // 1: rotate q (at kv_len - 1) and every K row (at its position), LLaMA style
+  float rope_rcp_scale, rope_rcp_theta;
   float sm_scale;          // plain sm_scale (soft-cap path)
   int32_t enable_pdl;
 };

@@ -313,7 +313,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     for (int h = 0; h < num_kv_heads; ++h) {
       Segment s;
       s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b];
-      s.page_base = indptr_host[b]; s.pad = 0;
+      s.page_base = indptr_host[b]; s.kv_len = tok_hi[b];
       s.slot = -1; s.merge_unit = -1; s.merge_count = 0; s.merge_slot = 0;
       if (nc == 0) {  // empty request: zero-tile segment, writes o = 0, lse = -5e4
         s.tile_begin = s.tile_end = 0;

@@ -22,6 +22,7 @@ from .utils import (
     _check_cached_qkv_data_type,
     _check_kv_layout,
     _check_pos_encoding_mode,
+    PosEncodingMode,
     _get_cache_alibi_slopes_buf,
     _get_cache_buf,
     _get_range_buf,
@@ -47,13 +48,20 @@ def _host_i32_ptr(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
 
 def _unsupported_variant(pos_encoding_mode: str) -> None:
     _check_pos_encoding_mode(pos_encoding_mode)
-    if pos_encoding_mode not in ("NONE", "ALIBI"):
-        # in-kernel RoPE is a "next" row, not built (serving engines rotate q / k
-        # before the cache write; the reference's own callers pass "NONE").
-        raise NotImplementedError(
-            f"pos_encoding_mode={pos_encoding_mode!r} is not implemented by flashinfer_b200 "
-            "(apply RoPE to q/k before the call)"
-        )
+    # all three reference modes are built: "NONE" and "ALIBI" on the tuned kernels, "ROPE_LLAMA"
+    # on the CUDA-core variant kernel (csrc/decode_rope_kernel.cuh)
+
+
+def _pos_mode_args(pos_encoding_mode: str, num_qo_heads: int, device: torch.device,
+                   rope_scale: Optional[float], rope_theta: Optional[float]):
+    """(mode code, alibi slopes pointer, rope_scale, rope_theta) for the C-ABI run functions;
+    defaults as the reference (decode.py:1257-1260: rope_scale 1.0, rope_theta 1e4)."""
+    return (
+        PosEncodingMode[pos_encoding_mode].value,
+        _alibi_slopes_ptr(pos_encoding_mode, num_qo_heads, device),
+        float(rope_scale) if rope_scale is not None else 1.0,
+        float(rope_theta) if rope_theta is not None else 1e4,
+    )
 
 
 def _alibi_slopes_ptr(pos_encoding_mode: str, num_qo_heads: int, device: torch.device):
@@ -132,7 +140,8 @@ def single_decode_with_kv_cache(
             num_qo_heads, num_kv_heads, head_dim, kv_len,
             dtype_code(q.dtype), dtype_code(k.dtype), TensorLayout[kv_layout].value,
             window_left, float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
-            float(logits_soft_cap), _alibi_slopes_ptr(pos_encoding_mode, num_qo_heads, dev),
+            float(logits_soft_cap),
+            *_pos_mode_args(pos_encoding_mode, num_qo_heads, dev, rope_scale, rope_theta),
             dev_idx, current_stream_ptr(dev),
         )
     )
@@ -204,6 +213,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._backend = backend
         self._plan_info: Optional[torch.Tensor] = None
         self._pos_encoding_mode = "NONE"
+        self._rope_scale = self._rope_theta = None
 
     @property
     def use_tensor_cores(self) -> bool:
@@ -518,7 +528,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 out.data_ptr(), lse.data_ptr() if return_lse else None,
                 float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
                 float(logits_soft_cap),
-                _alibi_slopes_ptr(self._pos_encoding_mode, q.shape[1], dev),
+                *_pos_mode_args(self._pos_encoding_mode, q.shape[1], dev, self._rope_scale,
+                                self._rope_theta),
                 int(bool(enable_pdl)), device_index(dev),
                 current_stream_ptr(dev),
             )

@@ -43,6 +43,12 @@ extern "C" {
 #define FI_DTYPE_F32 4 /* merge operators only */
 
 /* ---- kv layout codes (reference: flashinfer/utils.py:35-38 TensorLayout) - */
+/* position encoding applied inside the kernel: the reference's PosEncodingMode
+ * (include/flashinfer/pos_enc.cuh:34-41, flashinfer/utils.py:35-38) */
+#define FI_POS_NONE 0
+#define FI_POS_ROPE_LLAMA 1
+#define FI_POS_ALIBI 2
+
 #define FI_LAYOUT_NHD 0
 #define FI_LAYOUT_HND 1
 
@@ -134,9 +140,14 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
  *  sm_scale     already multiplied by q_scale*k_scale (decode.py:1250-1256)
  *  v_scale      multiplies the output (fused; reference: decode.py:1367-1372)
  *  logits_soft_cap  <=0: disabled
- *  alibi_slopes     device f32 [Hq] or NULL.  Non-NULL selects the reference's ALiBi variant
- *                   (variants.cuh:68-71 with qo_idx = 0 as passed by decode.cuh:95-96):
+ *  pos_encoding_mode  FI_POS_NONE / FI_POS_ROPE_LLAMA / FI_POS_ALIBI
+ *  alibi_slopes     device f32 [Hq], read in FI_POS_ALIBI mode (variants.cuh:68-71 with
+ *                   qo_idx = 0 as passed by decode.cuh:95-96):
  *                   logit = q.k * sm_scale + alibi_slopes[head] * kv_position
+ *  rope_scale, rope_theta  FI_POS_ROPE_LLAMA: q is rotated at position kv_len - 1 and every K
+ *                   row at its own position, frequencies (1 / rope_scale) * rope_theta^(-2i/D)
+ *                   (decode.cuh:445-466, pos_enc.cuh:79-100; Python defaults 1.0 and 1e4,
+ *                   decode.py:1257-1260).  Served by a CUDA-core variant kernel.
  */
 FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info,
                         const void* q, int64_t q_stride_n, int64_t q_stride_h,
@@ -145,7 +156,8 @@ FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan
                         int64_t kv_stride_h, const int32_t* kv_indices,
                         const int32_t* kv_indptr, void* o, float* lse,
                         float sm_scale, float v_scale, float logits_soft_cap,
-                        const float* alibi_slopes, int enable_pdl, int device, void* stream);
+                        int pos_encoding_mode, const float* alibi_slopes, float rope_scale,
+                        float rope_theta, int enable_pdl, int device, void* stream);
 
 /*
  * fi_single_decode_run — one request, contiguous K/V.
@@ -161,8 +173,9 @@ FI_API int fi_single_decode_run(const void* q, const void* k, const void* v, voi
                          int num_kv_heads, int head_dim, int kv_len,
                          int q_dtype, int kv_dtype, int kv_layout,
                          int window_left, float sm_scale, float v_scale,
-                         float logits_soft_cap, const float* alibi_slopes, int device,
-                         void* stream);
+                         float logits_soft_cap, int pos_encoding_mode,
+                         const float* alibi_slopes, float rope_scale, float rope_theta,
+                         int device, void* stream);
 FI_API size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int head_dim,
                                   int device);
 

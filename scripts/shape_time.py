@@ -17,6 +17,7 @@ DEV = "cuda:0"
 def main():
     kind, kv_len, hkv = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
     bs = int(sys.argv[4]) if len(sys.argv) > 4 else 64
+    pos_mode = sys.argv[5] if len(sys.argv) > 5 else "NONE"
     page, d = 16, 128
     hq = hkv * (4 if kind == "bf16" else 8)
     kv_dtype = torch.bfloat16 if kind == "bf16" else torch.float8_e4m3fn
@@ -32,7 +33,8 @@ def main():
     indptr = torch.tensor([0] + list(np.cumsum(pages)), dtype=torch.int32)
     last = torch.tensor([(kv_len - 1) % page + 1] * bs, dtype=torch.int32)
     q = torch.randn(bs, hq, d, device=DEV, dtype=torch.bfloat16)
-    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.bfloat16, kv_data_type=kv_dtype)
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.bfloat16, kv_data_type=kv_dtype,
+           pos_encoding_mode=pos_mode)
     for _ in range(3):
         w.run(q, cache)
     torch.cuda.synchronize()
@@ -47,7 +49,7 @@ def main():
         ts.append(e0.elapsed_time(e1) * 1e3)
     nbytes = bs * kv_len * hkv * d * 2 * es
     knobs = " ".join(f"{k[14:]}={v}" for k, v in sorted(os.environ.items()) if k.startswith("FI_B200_SCHED_"))
-    print(f"{kind} kv={kv_len} hkv={hkv} bs={bs} [{knobs}]: min {min(ts):7.1f} median {np.median(ts):7.1f} us "
+    print(f"{kind} kv={kv_len} hkv={hkv} bs={bs} {pos_mode} [{knobs}]: min {min(ts):7.1f} median {np.median(ts):7.1f} us "
           f"-> {nbytes / np.median(ts) / 1e6:.2f} TB/s (items {int(w._plan_info[6])}, segs {int(w._plan_info[2])}, "
           f"merges {int(w._plan_info[3])})")
 

@@ -423,11 +423,78 @@ def test_batch_decode_alibi(kv_dtype, loader, soft_cap, window_left):
     assert (o_none.float().cpu() - o_ref).abs().max().item() > 1e-2
 
 
-def test_rope_modes_are_rejected():
+# ---------------------------------------------------------------- RoPE on the fly
+def _rope_golden():
+    from pathlib import Path
+
+    z = np.load(Path(__file__).resolve().parent / "golden" / "rope_golden.npz")
+    return z, [str(n) for n in z["names"]]
+
+
+@pytest.mark.parametrize("name", _rope_golden()[1])
+def test_single_decode_rope_against_reference_golden(name):
+    fi = _fi()
+    z, _ = _rope_golden()
+    Hq, Hkv, D, L, is_bf16 = [int(x) for x in z[f"{name}/meta"]]
+    dt = torch.bfloat16 if is_bf16 else torch.float16
+    q, k, v = (torch.from_numpy(z[f"{name}/{key}"].copy()).view(dt) for key in ("q", "k", "v"))
+    theta = float(z[f"{name}/theta"][0])
+    o, lse = fi.single_decode_with_kv_cache(q.to(DEV), k.to(DEV), v.to(DEV), pos_encoding_mode="ROPE_LLAMA",
+                                            rope_theta=theta, return_lse=True)
+    assert (o.float().cpu() - torch.from_numpy(z[f"{name}/o"].copy())).abs().max().item() <= O_TOL
+    assert (lse.cpu() - torch.from_numpy(z[f"{name}/lse2"].copy())).abs().max().item() <= LSE_TOL
+    # HND layout gives the same answer
+    o2 = fi.single_decode_with_kv_cache(q.to(DEV), k.transpose(0, 1).contiguous().to(DEV),
+                                        v.transpose(0, 1).contiguous().to(DEV), kv_layout="HND",
+                                        pos_encoding_mode="ROPE_LLAMA", rope_theta=theta)
+    assert torch.equal(o2, o)
+
+
+@pytest.mark.parametrize("layout,kv_dtype,page,d", [("NHD", None, 16, 128), ("HND", None, 8, 128),
+                                                     ("NHD", torch.float8_e4m3fn, 16, 128),
+                                                     ("NHD", None, 5, 64), ("HND", None, 16, 256)])
+@pytest.mark.parametrize("soft_cap,window_left", [(None, -1), (30.0, 300)])
+def test_batch_decode_rope(layout, kv_dtype, page, d, soft_cap, window_left):
+    """reference tests/attention/test_batch_decode_kernels.py:58-185 (pos_encoding_mode="ROPE_LLAMA"):
+    long requests are split over CTAs and merged, short and empty ones are not"""
+    fi = _fi()
+    hq, hkv = 16, 4
+    lens = [1, 54, 97, 512, 2048, 0, 9000, 777]
+    q_dtype = torch.float16
+    kvd = kv_dtype or q_dtype
+    is8 = kv_dtype is not None
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, layout, torch.float32, seed=51)
+    k_scale = v_scale = None
+    if is8:
+        k_scale = float(cache[:, 0].abs().amax() / 256)
+        v_scale = float(cache[:, 1].abs().amax() / 256)
+        cache[:, 0] /= k_scale
+        cache[:, 1] /= v_scale
+    cache = cache.to(kvd)
+    q = make_q(len(lens), hq, d, q_dtype, seed=52)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, pos_encoding_mode="ROPE_LLAMA", q_data_type=q_dtype,
+           kv_data_type=kvd, logits_soft_cap=soft_cap, window_left=window_left, rope_theta=1e4)
+    assert int(w._plan_info[3]) > 0   # some unit is split: the fused merge runs
+    o, lse = w.run(q.to(DEV), cache.to(DEV), k_scale=k_scale, v_scale=v_scale, return_lse=True)
+    torch.cuda.synchronize()
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, layout, k_scale=k_scale or 1.0,
+                                          v_scale=v_scale or 1.0, logits_soft_cap=soft_cap or 0.0,
+                                          window_left=window_left, rope=(1.0, 1e4))
+    assert (o.float().cpu() - o_ref).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+    assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+    # batch == single (the reference test's own check, test_batch_decode_kernels.py:176-183)
+    if not is8 and soft_cap is None and window_left < 0:
+        for i in (2, 4):
+            k_i, v_i = orc.gather_paged_kv(*orc.unpack_cache(cache, layout), indptr, indices, last, i, layout)
+            o_i = fi.single_decode_with_kv_cache(q[i].to(DEV), k_i.to(DEV), v_i.to(DEV),
+                                                 pos_encoding_mode="ROPE_LLAMA")
+            torch.testing.assert_close(o[i], o_i, rtol=1e-3, atol=1e-3)
+
+
+def test_invalid_pos_encoding_mode():
     fi = _fi()
     q = torch.zeros(8, 128, dtype=torch.float16, device=DEV)
     k = torch.zeros(16, 2, 128, dtype=torch.float16, device=DEV)
-    with pytest.raises(NotImplementedError):
-        fi.single_decode_with_kv_cache(q, k, k, pos_encoding_mode="ROPE_LLAMA")
     with pytest.raises(KeyError):
         fi.single_decode_with_kv_cache(q, k, k, pos_encoding_mode="SOMETHING")

@@ -121,3 +121,28 @@ def test_oracle_alibi_matches_reference_alibi_attention(name):
     o, _ = orc.decode_attention_ref(q, k, v, alibi_slopes=slopes)
     # the golden output was rounded to q's dtype by the reference function
     assert torch.equal(o.to(q.dtype), o_gold) or (o - o_gold.float()).abs().max().item() <= 2e-3
+
+
+# ---------------------------------------------------------------- RoPE on the fly
+def _rope_cases():
+    z = np.load(Path(__file__).resolve().parent / "golden" / "rope_golden.npz")
+    return z, [str(n) for n in z["names"]]
+
+
+def rope_inputs(z, name):
+    Hq, Hkv, D, L, is_bf16 = [int(x) for x in z[f"{name}/meta"]]
+    dt = torch.bfloat16 if is_bf16 else torch.float16
+    q, k, v = (torch.from_numpy(z[f"{name}/{key}"].copy()).view(dt) for key in ("q", "k", "v"))
+    return q, k, v, float(z[f"{name}/theta"][0]), torch.from_numpy(z[f"{name}/o"].copy()), \
+        torch.from_numpy(z[f"{name}/lse2"].copy())
+
+
+@pytest.mark.parametrize("name", _rope_cases()[1])
+def test_oracle_rope_matches_reference_helpers(name):
+    """oracle ROPE_LLAMA == the reference's rope_reference.py rotation + its attention_ref, executed
+    in the build container by tests/golden/make_golden_rope.py"""
+    z, _ = _rope_cases()
+    q, k, v, theta, o_gold, lse_gold = rope_inputs(z, name)
+    o, lse = orc.decode_attention_ref(q, k, v, rope=(1.0, theta))
+    assert (o - o_gold).abs().max().item() <= 2e-5
+    assert (lse - lse_gold).abs().max().item() <= 2e-4
