@@ -220,19 +220,25 @@ template <int QT, int KVF>
 static int launch_rope(const DecodeParams& p, int head_dim, int grid, cudaStream_t stream) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kRopeThreads);
+  cfg.blockDim = dim3(rope_warps(head_dim) * 32);
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = p.enable_pdl ? 1 : 0;
+#define FI_ROPE_CASE(HD_)                                                                          \
+  case HD_:                                                                                        \
+    if (p.group_size <= 4) FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, HD_, 4>, p)); \
+    else FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, HD_, 8>, p));      \
+    break;
   switch (head_dim) {
-    case 64: FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 64>, p)); break;
-    case 128: FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 128>, p)); break;
-    case 256: FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 256>, p)); break;
+    FI_ROPE_CASE(64)
+    FI_ROPE_CASE(128)
+    FI_ROPE_CASE(256)
     default: return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
   }
+#undef FI_ROPE_CASE
   return FI_OK;
 }
 
