@@ -2,10 +2,18 @@
 FlashInfer's own Python API (reference flashinfer/__init__.py exports the same names).
 
 Only the decode hot path is provided: the batch / single decode entry
-points and the attention-state merge operators.  Everything runs in hand-written CUDA
+points, the attention-state merge operators, the cascade wrappers built on both and the
+page-table maintenance ops.  Everything runs in hand-written CUDA
 behind the C-ABI library `libfi_b200.so` (include/fi_b200.h); there is no CPU fallback.
 """
-from .cascade import merge_state, merge_state_in_place, merge_states, variable_length_merge_states
+from .cascade import (
+    BatchDecodeWithSharedPrefixPagedKVCacheWrapper,
+    MultiLevelCascadeAttentionWrapper,
+    merge_state,
+    merge_state_in_place,
+    merge_states,
+    variable_length_merge_states,
+)
 from .decode import (
     BatchDecodeWithPagedKVCacheWrapper,
     CUDAGraphBatchDecodeWithPagedKVCacheWrapper,
@@ -25,6 +33,8 @@ __all__ = [
     "merge_state_in_place",
     "merge_states",
     "variable_length_merge_states",
+    "MultiLevelCascadeAttentionWrapper",
+    "BatchDecodeWithSharedPrefixPagedKVCacheWrapper",
     "get_seq_lens",
     "get_batch_indices_positions",
     "append_paged_kv_cache",

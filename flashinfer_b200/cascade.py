@@ -155,3 +155,253 @@ def variable_length_merge_states(
         )
     )
     return v_merged, s_merged
+
+
+# --------------------------------------------------------------------------- cascade wrappers
+# the direct callers of decode + merge_state_in_place.  The reference
+# builds them on its prefill kernels (cascade.py:228-556 on BatchPrefillWithPagedKVCacheWrapper,
+# :558-796 on single_prefill_with_kv_cache).  This repo has no prefill path; a query row that
+# attends a page list, with or without the causal mask, IS a decode request over a (possibly
+# truncated) copy of that page list, so every level runs on the decode kernels: row t of an
+# n-row group sees the group's first kv_len - (n - 1 - t) tokens under the causal mask
+# (reference prefill.cuh mask: kv_idx <= kv_len - qo_len + qo_idx) and all kv_len otherwise.
+# Rows of one group read the same pages: the duplicate reads are served by the 126 MB L2.
+
+
+def rows_as_decode_requests(qo_indptr, kv_indptr, kv_indices, kv_last_page_len, page_size: int,
+                            causal: bool):
+    """Expand a (qo_indptr, page table) level into one decode request per query row.
+
+    Returns ``(indptr, indices, last_page_len)`` of the per-row page table: int32 CPU tensors
+    for indptr / last_page_len, ``indices`` gathered on ``kv_indices``' device.
+    """
+    import numpy as np
+
+    qo = qo_indptr.detach().cpu().numpy().astype(np.int64)
+    kvp = kv_indptr.detach().cpu().numpy().astype(np.int64)
+    lpl = kv_last_page_len.detach().cpu().numpy().astype(np.int64)
+    groups = len(qo) - 1
+    if len(kvp) != groups + 1 or len(lpl) != groups:
+        raise ValueError("qo_indptr, paged_kv_indptr and paged_kv_last_page_len disagree on the batch size")
+    if groups < 0 or (groups >= 0 and qo[0] != 0) or np.any(np.diff(qo) < 0) or np.any(np.diff(kvp) < 0):
+        raise ValueError("indptr arrays must start at 0 and be non-decreasing")
+    rows = np.diff(qo)
+    pages = np.diff(kvp)
+    kv_len = np.where(pages > 0, (pages - 1) * page_size + lpl, 0)
+    total = int(qo[-1]) if groups > 0 else 0
+    grp = np.repeat(np.arange(groups), rows)
+    t = np.arange(total) - qo[grp]
+    row_len = kv_len[grp] - (rows[grp] - 1 - t) if causal else kv_len[grp]
+    row_len = np.maximum(row_len, 0)
+    row_pages = -(-row_len // page_size)
+    row_indptr = np.zeros(total + 1, dtype=np.int64)
+    np.cumsum(row_pages, out=row_indptr[1:])
+    row_last = np.where(row_len > 0, (row_len - 1) % page_size + 1, 0)
+    src = (np.arange(int(row_indptr[-1])) - np.repeat(row_indptr[:-1], row_pages) +
+           np.repeat(kvp[grp], row_pages))
+    gather = torch.from_numpy(src).to(kv_indices.device)
+    row_indices = kv_indices.index_select(0, gather) if len(src) else kv_indices[:0]
+    return (torch.from_numpy(row_indptr.astype(np.int32)), row_indices.to(torch.int32).contiguous(),
+            torch.from_numpy(row_last.astype(np.int32)))
+
+
+class MultiLevelCascadeAttentionWrapper:
+    r"""Multi-level cascade attention over one unified page table (reference cascade.py:228-556).
+
+    Same constructor, ``plan`` / ``run`` contract as the reference; every level is executed by a
+    :class:`BatchDecodeWithPagedKVCacheWrapper` with one decode request per query row (see the
+    note above), and the levels are combined with :func:`merge_state_in_place` in the
+    reference's order (last level first, cascade.py:534-543).
+    """
+
+    def __init__(
+        self,
+        num_levels,
+        float_workspace_buffer: torch.Tensor,
+        kv_layout: str = "NHD",
+        use_cuda_graph: bool = False,
+        qo_indptr_buf_arr=None,
+        paged_kv_indptr_buf_arr=None,
+        paged_kv_indices_buf_arr=None,
+        paged_kv_last_page_len_buf_arr=None,
+    ) -> None:
+        from .decode import BatchDecodeWithPagedKVCacheWrapper
+
+        if use_cuda_graph:
+            # the per-row page tables are rebuilt by plan(); the reference's fixed user buffers
+            # describe per-group tables and cannot hold them
+            raise NotImplementedError("use_cuda_graph is not supported by the cascade wrappers")
+        self._use_cuda_graph = False
+        self._batch_decode_wrappers = [
+            BatchDecodeWithPagedKVCacheWrapper(float_workspace_buffer, kv_layout)
+            for _ in range(num_levels)
+        ]
+        self._num_levels = num_levels
+        self._kv_layout = kv_layout
+        self._num_rows = None
+
+    @property
+    def is_cuda_graph_enabled(self) -> bool:
+        return self._use_cuda_graph
+
+    def reset_workspace_buffer(self, float_workspace_buffer: torch.Tensor,
+                               int_workspace_buffers) -> None:
+        for wrapper, int_ws in zip(self._batch_decode_wrappers, int_workspace_buffers):
+            wrapper.reset_workspace_buffer(float_workspace_buffer, int_ws)
+
+    def plan(
+        self,
+        qo_indptr_arr,
+        paged_kv_indptr_arr,
+        paged_kv_indices_arr,
+        paged_kv_last_page_len,
+        num_qo_heads: int,
+        num_kv_heads: int,
+        head_dim: int,
+        page_size: int,
+        causal: bool = False,
+        pos_encoding_mode: str = "NONE",
+        use_fp16_qk_reduction: bool = False,
+        sm_scale: Optional[float] = None,
+        window_left: int = -1,
+        logits_soft_cap: Optional[float] = None,
+        rope_scale: Optional[float] = None,
+        rope_theta: Optional[float] = None,
+        q_data_type="float16",
+        kv_data_type=None,
+    ) -> None:
+        if pos_encoding_mode != "NONE":
+            # positions inside a level are level-local: the reference's own result for RoPE /
+            # ALiBi across levels is not the un-cascaded attention either
+            raise NotImplementedError("cascade attention supports pos_encoding_mode='NONE' only")
+        if not (len(qo_indptr_arr) == len(paged_kv_indptr_arr) == len(paged_kv_indices_arr) ==
+                len(paged_kv_last_page_len) == self._num_levels):
+            raise ValueError("every per-level array must have num_levels entries")
+        num_rows = None
+        for i, (wrapper, qo, kvp, kvi, lpl) in enumerate(zip(
+                self._batch_decode_wrappers, qo_indptr_arr, paged_kv_indptr_arr,
+                paged_kv_indices_arr, paged_kv_last_page_len)):
+            level_causal = causal if i == self._num_levels - 1 else False
+            indptr, indices, last = rows_as_decode_requests(qo, kvp, kvi, lpl, page_size, level_causal)
+            if num_rows is None:
+                num_rows = indptr.numel() - 1
+            elif num_rows != indptr.numel() - 1:
+                raise ValueError("the last element of every qo_indptr must be the total number of queries")
+            wrapper.plan(
+                indptr, indices, last, num_qo_heads, num_kv_heads, head_dim, page_size,
+                pos_encoding_mode="NONE", window_left=window_left, logits_soft_cap=logits_soft_cap,
+                q_data_type=q_data_type, kv_data_type=kv_data_type, sm_scale=sm_scale,
+                rope_scale=rope_scale, rope_theta=rope_theta,
+            )
+        self._num_rows = num_rows
+
+    begin_forward = plan
+
+    def run(self, q: torch.Tensor, paged_kv_cache):
+        if self._num_rows is None:
+            raise RuntimeError("plan() must be called before run()")
+        out, lse = self._batch_decode_wrappers[-1].run(q, paged_kv_cache, return_lse=True)
+        for wrapper in self._batch_decode_wrappers[:-1]:
+            out_i, lse_i = wrapper.run(q, paged_kv_cache, return_lse=True)
+            merge_state_in_place(out, lse, out_i, lse_i)
+        return out
+
+    forward = run
+
+
+def _shared_prefix_pages(k_shared: torch.Tensor, v_shared: torch.Tensor, kv_layout: str):
+    """View a contiguous shared-prefix K / V (``[L, Hkv, D]`` NHD or ``[Hkv, L, D]`` HND) as a
+    ``(k_pages, v_pages)`` paged cache without copying: pages of the largest power of two <= 64
+    that divides L (the TMA loader's case) or single-token pages for any other L."""
+    if k_shared.dim() != 3 or k_shared.shape != v_shared.shape:
+        raise ValueError("k_shared / v_shared must be 3-D tensors of the same shape")
+    k_shared, v_shared = k_shared.contiguous(), v_shared.contiguous()
+    length = k_shared.shape[0] if kv_layout == "NHD" else k_shared.shape[1]
+    page = 64
+    while page >= 8 and length % page:
+        page //= 2
+    if page < 8:
+        page = 1
+    pages = length // page
+
+    def view(x):
+        if kv_layout == "NHD":
+            return x.view(pages, page, x.shape[1], x.shape[2])
+        return x.view(x.shape[0], pages, page, x.shape[2]).permute(1, 0, 2, 3)
+
+    return view(k_shared), view(v_shared), pages, page
+
+
+class BatchDecodeWithSharedPrefixPagedKVCacheWrapper:
+    r"""Batch decode over a shared-prefix KV held in standalone tensors plus a per-request
+    paged KV-cache (reference cascade.py:558-796; deprecated there in favour of
+    :class:`MultiLevelCascadeAttentionWrapper`).
+
+    The reference computes the shared level with ``single_prefill_with_kv_cache(causal=False)``;
+    here it is a batch decode in which every request's page table is the same list of pages
+    viewed over ``k_shared`` / ``v_shared`` in place (planned on first use per
+    (prefix length, batch size) and cached).
+    """
+
+    def __init__(self, float_workspace_buffer: torch.Tensor, kv_layout: str = "NHD") -> None:
+        from .decode import BatchDecodeWithPagedKVCacheWrapper
+
+        self._batch_decode_wrapper = BatchDecodeWithPagedKVCacheWrapper(float_workspace_buffer, kv_layout)
+        self._shared_wrapper = BatchDecodeWithPagedKVCacheWrapper(float_workspace_buffer, kv_layout)
+        self._shared_key = None
+        self._kv_layout = kv_layout
+
+    def reset_workspace_buffer(self, float_workspace_buffer: torch.Tensor, int_workspace_buffer) -> None:
+        self._batch_decode_wrapper.reset_workspace_buffer(float_workspace_buffer, int_workspace_buffer)
+        self._shared_wrapper.reset_workspace_buffer(
+            float_workspace_buffer, torch.empty_like(int_workspace_buffer))
+        self._shared_key = None
+
+    def begin_forward(
+        self,
+        unique_kv_indptr: torch.Tensor,
+        unique_kv_indices: torch.Tensor,
+        unique_kv_last_page_len: torch.Tensor,
+        num_qo_heads: int,
+        num_kv_heads: int,
+        head_dim: int,
+        page_size: int,
+        data_type="float16",
+    ) -> None:
+        self._batch_decode_wrapper.begin_forward(
+            unique_kv_indptr, unique_kv_indices, unique_kv_last_page_len, num_qo_heads,
+            num_kv_heads, head_dim, page_size, pos_encoding_mode="NONE",
+            q_data_type=data_type, kv_data_type=data_type,  # the reference passes data_type= only,
+            # which leaves q at plan()'s float16 default: harmless there (fp16-only tests)
+        )
+        self._shape = (num_qo_heads, num_kv_heads, head_dim)
+        self._shared_key = None
+
+    def _plan_shared(self, batch_size: int, pages: int, page: int, q_dtype, kv_dtype) -> None:
+        key = (batch_size, pages, page, q_dtype, kv_dtype)
+        if key == self._shared_key:
+            return
+        num_qo_heads, num_kv_heads, head_dim = self._shape
+        indptr = torch.arange(batch_size + 1, dtype=torch.int32) * pages
+        indices = torch.arange(pages, dtype=torch.int32).repeat(batch_size)
+        last = torch.full((batch_size,), page if pages else 0, dtype=torch.int32)
+        self._shared_wrapper.plan(
+            indptr, indices, last, num_qo_heads, num_kv_heads, head_dim, page,
+            pos_encoding_mode="NONE", q_data_type=q_dtype, kv_data_type=kv_dtype,
+            sm_scale=self._batch_decode_wrapper._sm_scale,
+        )
+        self._shared_key = key
+
+    def forward(self, q: torch.Tensor, k_shared: torch.Tensor, v_shared: torch.Tensor,
+                unique_kv_cache) -> torch.Tensor:
+        k_pages, v_pages, pages, page = _shared_prefix_pages(k_shared, v_shared, self._kv_layout)
+        self._plan_shared(q.shape[0], pages, page, q.dtype, k_shared.dtype)
+        V_shared, S_shared = self._shared_wrapper.run(q, (k_pages, v_pages), return_lse=True)
+        V_unique, S_unique = self._batch_decode_wrapper.forward_return_lse(
+            q, unique_kv_cache, pos_encoding_mode="NONE")
+        merge_state_in_place(V_shared, S_shared, V_unique, S_unique)
+        return V_shared
+
+    def end_forward(self) -> None:
+        r"""Deprecated in the reference; no effect."""
+        pass
