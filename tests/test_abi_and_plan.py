@@ -47,8 +47,10 @@ CASES = [
 ]
 
 
+@pytest.mark.parametrize("head_group", ["1", "0"])
 @pytest.mark.parametrize("kv_lens,hq,hkv,page,nctas", CASES)
-def test_plan_visits_every_token_once(kv_lens, hq, hkv, page, nctas):
+def test_plan_visits_every_token_once(kv_lens, hq, hkv, page, nctas, head_group, monkeypatch):
+    monkeypatch.setenv("FI_B200_HEAD_GROUP", head_group)
     indptr, last = lens_to_table(kv_lens, page)
     rc, err, plan = host_plan(indptr, last, hq, hkv, 128, page, nctas)
     assert rc == 0, err
@@ -71,6 +73,35 @@ def test_plan_visits_every_token_once(kv_lens, hq, hkv, page, nctas):
             free[np.argmin(free)] += ld
         ideal = -(-total // nctas)
         assert free.max() <= max(ideal + max(int(loads[-2:].max()), 2), int(loads[0]))
+
+
+def test_plan_head_groups_walk_the_same_request_ranges(monkeypatch):
+    """Default stream order when Hkv divides the grid: the Hkv CTAs of a group hold the same
+    (request, tile range) list, one KV head each — in an NHD cache they sweep whole pages together."""
+    monkeypatch.setenv("FI_B200_HEAD_GROUP", "1")
+    rng = np.random.default_rng(1)
+    kv_lens = rng.integers(0, 9000, 40).tolist() + [0, 1, 64]
+    hkv = 8
+    indptr, last = lens_to_table(kv_lens, 16)
+    rc, err, plan = host_plan(indptr, last, 32, hkv, 128, 16, 296)
+    assert rc == 0, err
+    replay_plan(plan, kv_lens, hkv)
+    segs, iip = plan["segments"], plan["item_indptr"]
+    nitems = len(iip) - 1
+    assert nitems % hkv == 0
+    loads = []
+    for g in range(nitems // hkv):
+        ref = [(int(s[0]), int(s[2]), int(s[3])) for s in segs[iip[g * hkv]:iip[g * hkv + 1]]]
+        loads.append(sum(te - tb for _, tb, te in ref))
+        for h in range(hkv):
+            mine = segs[iip[g * hkv + h]:iip[g * hkv + h + 1]]
+            assert all(int(s[1]) == h for s in mine)
+            assert [(int(s[0]), int(s[2]), int(s[3])) for s in mine] == ref
+    assert max(loads[:-1]) == min(loads[:-1]) and 0 < loads[-1] <= loads[0]
+    # partials of a unit sit in consecutive slots in group (= chunk) order
+    for r, h, sb, cnt in plan["merges"]:
+        mine = sorted((int(s[2]), int(s[4])) for s in segs if int(s[0]) == r and int(s[1]) == h)
+        assert [sl for _, sl in mine] == list(range(sb, sb + cnt))
 
 
 def test_plan_fp8_tiles_are_128_tokens():
