@@ -146,10 +146,10 @@ static cudaError_t ensure_smem_attr(K kern, int smem) {
   return e;
 }
 
-template <int QT, int KVF, int HD, int LOADER>
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false>
 static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                       int grid, cudaStream_t stream) {
-  auto kern = paged_decode_kernel<QT, KVF, HD, LOADER>;
+  auto kern = paged_decode_kernel<QT, KVF, HD, LOADER, ROPE>;
   const int smem = SmemLayout<KVF, HD>::total(p.num_stages);
   FI_CUDA_TRY(ensure_smem_attr(kern, smem));
   cudaLaunchConfig_t cfg = {};
@@ -169,6 +169,11 @@ static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtens
 template <int QT, int KVF, int HD>
 static int launch_loader(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                          int grid, bool tma, cudaStream_t stream) {
+  if constexpr (KVF == 0) {  // ROPE_LLAMA on 16-bit KV: K rotated in registers (decode_kernel.cuh)
+    if (p.rope)
+      return tma ? launch_one<QT, KVF, HD, 0, true>(p, km, vm, grid, stream)
+                 : launch_one<QT, KVF, HD, 1, true>(p, km, vm, grid, stream);
+  }
   return tma ? launch_one<QT, KVF, HD, 0>(p, km, vm, grid, stream)
              : launch_one<QT, KVF, HD, 1>(p, km, vm, grid, stream);
 }
@@ -246,7 +251,8 @@ static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUt
                          int q_dtype, int kvf, int head_dim, int grid, bool tma,
                          cudaStream_t stream) {
   const bool bf = q_dtype == FI_DTYPE_BF16;
-  if (p.rope) {
+  static const bool rope_cuda_core = [] { const char* e = getenv("FI_B200_ROPE_CUDA_CORE"); return e && e[0] == '1'; }();
+  if (p.rope && (kvf != 0 || rope_cuda_core)) {  // fp8 KV (or A/B runs): the CUDA-core variant kernel
     switch (kvf) {
       case 0: return bf ? launch_rope<1, 0>(p, head_dim, grid, stream) : launch_rope<0, 0>(p, head_dim, grid, stream);
       case 1: return bf ? launch_rope<1, 1>(p, head_dim, grid, stream) : launch_rope<0, 1>(p, head_dim, grid, stream);
@@ -381,9 +387,12 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.alibi_slopes = pos_encoding_mode == FI_POS_ALIBI ? alibi_slopes : nullptr;
   p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
   p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
-  if (p.rope && plan_info[kPiNumItems] > plan_info[kPiNumCtas])
+  if (p.rope && kvf != 0 && plan_info[kPiNumItems] > plan_info[kPiNumCtas])
     return fail(FI_ERR_UNSUPPORTED, "ROPE_LLAMA decode needs a static plan (unset FI_B200_SCHED_F0)");
-  p.enable_pdl = enable_pdl;
+  // 1: griddepcontrol.launch_dependents right after the kernel's own dependency wait (default);
+  // 2: at the very end (FI_B200_PDL_LATE=1, kept for A/B runs)
+  static const bool pdl_late = [] { const char* e = getenv("FI_B200_PDL_LATE"); return e && e[0] == '1'; }();
+  p.enable_pdl = enable_pdl ? (pdl_late ? 2 : 1) : 0;
 
   const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
                                 page_size, false, 0, TT);

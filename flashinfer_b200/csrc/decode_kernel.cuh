@@ -519,6 +519,91 @@ __device__ __forceinline__ void qk_tile16(float (&s)[4], uint32_t kbase, int row
   for (int i = 0; i < 4; ++i) s[i] += s1[i];
 }
 
+// ---- RoPE on the fly (pos_encoding_mode = ROPE_LLAMA, 16-bit KV) -------------------------------
+// The reference rotates q at position kv_len - 1 and every K row at its own position inside the
+// decode kernel (include/flashinfer/attention/decode.cuh:445-466,72-76; vec_apply_llama_rope,
+// include/flashinfer/pos_enc.cuh:79-100): x'[d] = x[d] cos - x[d + D/2] sin, x'[d + D/2] =
+// x[d + D/2] cos + x[d] sin with angle = position * rcp_scale * rcp_theta^(2 d / D), d < D/2.
+// In the m16n8k16 fragments both members of a rotation pair sit in the SAME lane and register
+// slot, k-steps ks and ks + KS/2 apart (A operand: the K rows; B operand: the query), so K is
+// rotated in registers between ldmatrix and the MMA and the operand path stays TMA -> smem ->
+// ldmatrix -> mma.  Per (token, frequency) one fast sincos (the reference's own __sincosf under
+// -use_fast_math) and four FMAs; freq[4 ks + c] belongs to d = 16 ks + 2 t + (c & 1) + 8 (c >> 1).
+// The rotated K rows and query are handed to the MMA as f16 whatever the storage type: rounding
+// them back to bf16 (8 significant bits) would move the base-2 lse by more than the 1e-3 gate;
+// f16 keeps 11 bits and saturates instead of overflowing.
+__device__ __forceinline__ uint32_t pack2_f16_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+template <bool BF>
+__device__ __forceinline__ float2 unpack2(uint32_t w) {
+  if constexpr (BF) return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+  else return __half22float2(*reinterpret_cast<const __half2*>(&w));
+}
+
+template <int HD>
+__device__ __forceinline__ void rope_freqs(float (&freq)[HD / 8], const DecodeParams& p, int t) {
+#pragma unroll
+  for (int ks = 0; ks < HD / 32; ++ks)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int d = 16 * ks + 2 * t + (c & 1) + 8 * (c >> 1);
+      freq[4 * ks + c] = p.rope_rcp_scale * powf(p.rope_rcp_theta, (float)(2 * d) / (float)HD);
+    }
+}
+
+// rotate the query fragments of one head at position `pos` (exact sincosf: once per segment)
+template <bool BF, int HD>
+__device__ __forceinline__ void rope_rotate_q(uint32_t (&qf)[HD / 16][2], const float (&freq)[HD / 8],
+                                              int pos) {
+  constexpr int H = HD / 32;
+#pragma unroll
+  for (int ks = 0; ks < H; ++ks)
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const float2 x = unpack2<BF>(qf[ks][c]), y = unpack2<BF>(qf[ks + H][c]);
+      float s0, c0, s1, c1;
+      sincosf((float)pos * freq[4 * ks + 2 * c], &s0, &c0);
+      sincosf((float)pos * freq[4 * ks + 2 * c + 1], &s1, &c1);
+      qf[ks][c] = pack2_f16_sat(x.x * c0 - y.x * s0, x.y * c1 - y.y * s1);
+      qf[ks + H][c] = pack2_f16_sat(y.x * c0 + x.x * s0, y.y * c1 + x.y * s1);
+    }
+}
+
+// S^T(16 tokens x 8 heads) with the K rows rotated at their positions; tok_g = token of row g
+template <int QT, int HD>
+__device__ __forceinline__ void qk_tile16_rope(float (&s)[4], uint32_t kbase, int row0, int lane,
+                                               const uint32_t (&qf)[HD / 16][2],
+                                               const float (&freq)[HD / 8], int tok_g) {
+  constexpr bool BF = (QT == 1);
+  constexpr int H = HD / 32;
+  const int krow = row0 + (lane & 7) + 8 * ((lane >> 3) & 1), kch = lane >> 4;
+  const float pos[2] = {(float)tok_g, (float)(tok_g + 8)};
+  float s1[4] = {0.f, 0.f, 0.f, 0.f};
+  s[0] = s[1] = s[2] = s[3] = 0.f;
+#pragma unroll
+  for (int ks = 0; ks < H; ++ks) {
+    uint32_t a[4], b[4];
+    ldmatrix_x4(a, kbase + swz<64>(krow, 2 * ks + kch));
+    ldmatrix_x4(b, kbase + swz<64>(krow, 2 * (ks + H) + kch));
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {  // r & 1: row g / g + 8; r >> 1: columns 2t.. / 2t + 8..
+      float s0, c0, sn1, c1;
+      __sincosf(pos[r & 1] * freq[4 * ks + 2 * (r >> 1)], &s0, &c0);
+      __sincosf(pos[r & 1] * freq[4 * ks + 2 * (r >> 1) + 1], &sn1, &c1);
+      const float2 x = unpack2<BF>(a[r]), y = unpack2<BF>(b[r]);
+      a[r] = pack2_f16_sat(x.x * c0 - y.x * s0, x.y * c1 - y.y * sn1);
+      b[r] = pack2_f16_sat(y.x * c0 + x.x * s0, y.y * c1 + x.y * sn1);
+    }
+    mma_16816<false>(s, a, qf[ks][0], qf[ks][1]);
+    mma_16816<false>(s1, b, qf[ks + H][0], qf[ks + H][1]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) s[i] += s1[i];
+}
+
 // O^T(HD x 8 heads) += V^T . P^T for this warp's 16 tokens; (pb0, pb1) = B fragments of P^T
 template <int QT, int HD>
 __device__ __forceinline__ void pv_tile16(float (&o)[HD / 16][4], uint32_t vbase, int row0,
@@ -749,7 +834,7 @@ __device__ __forceinline__ void merge_run_posted(const DecodeParams& p, const fl
 //         running max - 20), so that probabilities quantised to e4m3 are scaled by their own
 //         32-token block's maximum and nothing within 2^-18 of it is flushed),
 //   l[j]  sum of exp2(x - m[j]),  o[..] = sum of exp2(x - m[j]) v  (x 256 for fp8 KV).
-template <int QT, int KVF, int HD, int LOADER>
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false>
 __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& src, uint32_t ring,
                                         uint32_t full_bar, uint32_t empty_bar, float* scratch_o,
                                         float* scratch_ml) {
@@ -765,6 +850,9 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
   const float cap_pre = use_cap ? p.sm_scale / p.soft_cap : 0.f;
   const float cap_post = use_cap ? p.soft_cap * 1.4426950408889634f : 0.f;
   const int row0 = warp * TPW;
+  static_assert(!ROPE || KVF == 0, "in-register RoPE is built for 16-bit KV");
+  [[maybe_unused]] float freq[ROPE ? HD / 8 : 1];
+  if constexpr (ROPE) rope_freqs<HD>(freq, p, t);
 
   int stage = 0;
   uint32_t phase = 0;
@@ -790,6 +878,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
           for (int i = 0; i < NQ; ++i) { qf[i][0] = qn[i][0]; qf[i][1] = qn[i][1]; }
         } else {
           load_q_frags16<HD>(qf, qrow, g < GS, t);
+          if constexpr (ROPE) rope_rotate_q<BF, HD>(qf, freq, sg.kv_len - 1);
         }
         have_qn = __shfl_sync(0xffffffffu, seg_peek(src, k + 1) ? 1 : 0, 0) != 0;
         if (have_qn) {
@@ -798,6 +887,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
                              ((int64_t)sn.request * p.q_stride_n +
                               (int64_t)(sn.kv_head * GS + g) * p.q_stride_h) * 2;
           load_q_frags16<HD>(qn, nrow, g < GS, t);
+          if constexpr (ROPE) rope_rotate_q<BF, HD>(qn, freq, sn.kv_len - 1);
         }
         ql[0][0] = ql[0][1] = ql2[0][0] = ql2[0][1] = 0u;
         mul[0] = mul[1] = p.sm_scale_log2;
@@ -851,7 +941,8 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
         }
         if constexpr (KVF == 0) {
           float s[4];
-          qk_tile16<QT, HD>(s, kbase, row0, lane, qf);
+          if constexpr (ROPE) qk_tile16_rope<QT, HD>(s, kbase, row0, lane, qf, freq, tok0 + g);
+          else qk_tile16<QT, HD>(s, kbase, row0, lane, qf);
           // s[0],s[1]: token g, heads 2t,2t+1;  s[2],s[3]: token g+8
           const int ta = tok0 + g, tb = ta + 8;
           const bool va = ta >= sg.tok_lo && ta < sg.tok_hi;
@@ -1083,7 +1174,7 @@ struct BlockDim {
 
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 0 = KV has q's dtype, 1 = e4m3, 2 = e5m2.
 // LOADER: 0 = TMA boxes, 1 = cp.async gathers.
-template <int QT, int KVF, int HD, int LOADER>
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false>
 __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
     paged_decode_kernel(const __grid_constant__ DecodeParams p,
                         const __grid_constant__ CUtensorMap kmap,
@@ -1126,16 +1217,21 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   FI_TRACE_IF(tid == 0, 1);
   if (seg_source_idle(src)) return;
   if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
+  // Early trigger: the next kernel in the stream becomes launchable now, so its CTAs move into
+  // SM slots as ours retire (they run their prologue and then block in their own
+  // griddepcontrol.wait until this grid has completed and flushed) — the launch latency and
+  // the tail imbalance of this grid overlap the ramp of the next one.
+  if (p.enable_pdl == 1) pdl_launch_dependents();
   FI_TRACE_IF(tid == 0, 2);
 
   if (tid < kConsumerWarps * 32) {
-    consume<QT, KVF, HD, LOADER>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
+    consume<QT, KVF, HD, LOADER, ROPE>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
   } else if (LOADER == 0) {
     produce_tma<KVF, HD>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
   } else {
     produce_cpasync<KVF, HD>(p, src, tid - kConsumerWarps * 32, ring, full_bar, empty_bar);
   }
-  if (p.enable_pdl) pdl_launch_dependents();
+  if (p.enable_pdl == 2) pdl_launch_dependents();  // FI_B200_PDL_LATE=1 (A/B runs)
 }
 
 }  // namespace fib200

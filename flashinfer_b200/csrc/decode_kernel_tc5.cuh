@@ -498,6 +498,7 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
     return;
   }
   if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
+  if (p.enable_pdl == 1) pdl_launch_dependents();  // early trigger, see paged_decode_kernel
   FI_TRACE_IF(tid == 0, 2);
 
   if (warp < 4) {
@@ -507,7 +508,7 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   } else {
     tc5_issue<KVF>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
   }
-  if (p.enable_pdl) pdl_launch_dependents();
+  if (p.enable_pdl == 2) pdl_launch_dependents();
   tc5::fence_before_sync();
   __syncthreads();
   if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);

@@ -106,6 +106,7 @@ __global__ void __launch_bounds__(rope_warps(HD) * 32)
   }
   if (nseg == 0) return;
   if (p.enable_pdl) pdl_wait();
+  if (p.enable_pdl == 1) pdl_launch_dependents();  // early trigger, see paged_decode_kernel
 
   // dims (C sub + c) and (HD / 2 + C sub + c) are a rotation pair and share one frequency
   float freq[C], cstep[C], sstep[C];
@@ -342,7 +343,7 @@ __global__ void __launch_bounds__(rope_warps(HD) * 32)
       }
     }
   }
-  if (p.enable_pdl) pdl_launch_dependents();
+  if (p.enable_pdl == 2) pdl_launch_dependents();
 }
 
 }  // namespace fib200

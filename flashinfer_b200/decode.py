@@ -379,26 +379,25 @@ class BatchDecodeWithPagedKVCacheWrapper:
         # fixed_split_size (pages) / disable_split_kv: batch-invariant planning, reference
         # decode.py:880-887; None / -1 mean "off" there as here
         lib = _lib.load()
-        info = torch.zeros(lib.fi_plan_info_len(), dtype=torch.int64)
+        # a fresh vector per plan: a CUDA graph captured around an earlier run() read its own
+        # (the C function selects the device itself, like the reference's plan, batch_decode.cu:56)
+        info = torch.empty(lib.fi_plan_info_len(), dtype=torch.int64)
         dev_idx = device_index(self.device)
         fws = self._float_workspace_buffer
-        with torch.cuda.device(self.device):
-            _lib.check(
-                lib.fi_batch_decode_plan(
-                    fws.data_ptr(), fws.numel() * fws.element_size(),
-                    self._int_workspace_buffer.data_ptr(),
-                    self._pin_memory_int_workspace_buffer.data_ptr(),
-                    min(self._int_workspace_buffer.numel() * self._int_workspace_buffer.element_size(),
-                        self._pin_memory_int_workspace_buffer.numel()
-                        * self._pin_memory_int_workspace_buffer.element_size()),
-                    indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
-                    head_dim, page_size, dtype_code(q_data_type), dtype_code(kv_data_type),
-                    int(window_left), int(self.is_cuda_graph_enabled),
-                    int(fixed_split_size) if fixed_split_size is not None and fixed_split_size > 0 else 0,
-                    int(bool(disable_split_kv)), dev_idx, 0,
-                    current_stream_ptr(self.device), info.data_ptr(),
-                )
+        iws, pws = self._int_workspace_buffer, self._pin_memory_int_workspace_buffer
+        _lib.check(
+            lib.fi_batch_decode_plan(
+                fws.data_ptr(), fws.numel() * fws.element_size(),
+                iws.data_ptr(), pws.data_ptr(),
+                min(iws.numel() * iws.element_size(), pws.numel() * pws.element_size()),
+                indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
+                head_dim, page_size, dtype_code(q_data_type), dtype_code(kv_data_type),
+                int(window_left), int(self.is_cuda_graph_enabled),
+                int(fixed_split_size) if fixed_split_size is not None and fixed_split_size > 0 else 0,
+                int(bool(disable_split_kv)), dev_idx, 0,
+                current_stream_ptr(self.device), info.data_ptr(),
             )
+        )
         self._plan_info = info
         self._head_dim = head_dim
         self._page_size = page_size

@@ -93,20 +93,20 @@ struct BatchArgs {
   cudaStream_t stream;
   int64_t* info_out;  // 10 x int64 DecodePlanInfo + [10] = launches (1 or 2)
   int mode;           // 0 plan + run, 1 plan only (kept for later runs), 2 run with the kept plan
+  float rope_rcp_scale = 1.f, rope_rcp_theta = 1e-4f;  // read by the ROPE_LLAMA instantiation only
 };
 
 thread_local DecodePlanInfo g_plan;  // the reference keeps this in its Python wrapper between run()s
 
-template <typename Q, typename KV, uint32_t HD>
+template <typename Q, typename KV, uint32_t HD, PosEncodingMode POS = PosEncodingMode::kNone>
 int batch_impl(const BatchArgs& a) {
   using P = BatchParams<Q, KV>;
   DecodePlanInfo& info = g_plan;
   cudaError_t st = cudaSuccess;
   bool ok = a.mode == 2;
   if (a.mode != 2) DISPATCH_GQA_GROUP_SIZE(a.hq / a.hkv, GROUP_SIZE, {
-    auto est = BatchDecodeWithPagedKVCacheWorkEstimationDispatched<GROUP_SIZE, HD, PosEncodingMode::kNone,
-                                                                   Variant, P>;
-    st = DecodePlan<HD, PosEncodingMode::kNone, Variant, P>(a.float_ws, a.float_bytes, a.int_ws,
+    auto est = BatchDecodeWithPagedKVCacheWorkEstimationDispatched<GROUP_SIZE, HD, POS, Variant, P>;
+    st = DecodePlan<HD, POS, Variant, P>(a.float_ws, a.float_bytes, a.int_ws,
                                                             a.pinned_ws, a.int_bytes, info, a.indptr_h,
                                                             a.bs, a.hq, a.page_size, a.cuda_graph != 0,
                                                             a.stream, est);
@@ -126,8 +126,8 @@ int batch_impl(const BatchArgs& a) {
   p.maybe_alibi_slopes = nullptr;
   p.logits_soft_cap = 0.f;
   p.sm_scale = a.sm_scale;
-  p.rope_rcp_scale = 1.f;
-  p.rope_rcp_theta = 1e-4f;
+  p.rope_rcp_scale = a.rope_rcp_scale;
+  p.rope_rcp_theta = a.rope_rcp_theta;
   p.padded_batch_size = info.padded_batch_size;
   p.num_qo_heads = a.hq;
   p.q_stride_n = a.q_stride_n;
@@ -149,8 +149,7 @@ int batch_impl(const BatchArgs& a) {
     if (info.enable_cuda_graph)
       p.block_valid_mask = reinterpret_cast<bool*>(ib + info.block_valid_mask_offset);
   }
-  st = BatchDecodeWithPagedKVCacheDispatched<HD, PosEncodingMode::kNone, Variant>(p, tmp_v, tmp_s,
-                                                                                 false, a.stream);
+  st = BatchDecodeWithPagedKVCacheDispatched<HD, POS, Variant>(p, tmp_v, tmp_s, false, a.stream);
   if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
   if (a.info_out) {
     auto v = info.ToVector();
@@ -238,6 +237,34 @@ __attribute__((visibility("default"))) int ref_batch_decode_mode(
               indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), info_out, mode};
   try {
     REF_DISPATCH(q_dtype, kv_dtype, return (batch_impl<Q, KV, 128>(a)));
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return 2;
+  }
+}
+
+// pos_encoding_mode = ROPE_LLAMA (reference decode.cuh:445-466: q rotated at kv_len - 1, every K
+// row at its position), 16-bit KV only; same plan / run modes as ref_batch_decode_mode
+__attribute__((visibility("default"))) int ref_batch_decode_rope(
+    void* float_ws, size_t float_bytes, void* int_ws, void* pinned_ws, size_t int_bytes,
+    int32_t* indptr_h, int bs, int hq, int hkv, int head_dim, int page_size, int q_dtype,
+    int kv_dtype, int layout, int cuda_graph, void* q, int64_t q_stride_n, int64_t q_stride_h,
+    void* k, void* v, int64_t s0, int64_t s1, int64_t s2, int32_t* indices, int32_t* indptr,
+    int32_t* last_page_len, void* o, float* lse, float sm_scale, float rope_scale, float rope_theta,
+    void* stream, int64_t* info_out, int mode) {
+  if (head_dim != 128) { g_err = "ref shim is built for head_dim 128"; return 4; }
+  BatchArgs a{float_ws, int_ws, pinned_ws, float_bytes, int_bytes, indptr_h, bs, hq, hkv, page_size,
+              layout, cuda_graph, q, k, v, o, lse, q_stride_n, q_stride_h, {s0, s1, s2}, indices,
+              indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), info_out, mode};
+  a.rope_rcp_scale = 1.f / rope_scale;
+  a.rope_rcp_theta = 1.f / rope_theta;
+  try {
+    if (q_dtype == 0 && kv_dtype == 0)
+      return batch_impl<half, half, 128, PosEncodingMode::kRoPELlama>(a);
+    if (q_dtype == 1 && kv_dtype == 1)
+      return batch_impl<nv_bfloat16, nv_bfloat16, 128, PosEncodingMode::kRoPELlama>(a);
+    g_err = "ROPE_LLAMA shim: 16-bit KV only";
+    return 4;
   } catch (const std::exception& e) {
     g_err = e.what();
     return 2;

@@ -86,6 +86,66 @@ def test_batch_decode_matches_reference_kernel(ref, layout, q_dtype, kv_dtype, k
     assert (lse - lse_ref).abs().max().item() <= 1e-3
 
 
+def ref_batch_decode_rope(ref, q, cache, indptr, indices, last, hq, hkv, page, layout, sm_scale,
+                          rope_scale, rope_theta):
+    bs, d = q.shape[0], q.shape[2]
+    k, v = cache[:, 0], cache[:, 1]
+    fws = torch.zeros(128 << 20, dtype=torch.uint8, device=DEV)
+    iws = torch.zeros(8 << 20, dtype=torch.uint8, device=DEV)
+    pws = torch.zeros(8 << 20, dtype=torch.uint8).pin_memory()
+    o = torch.empty_like(q)
+    lse = torch.empty(bs, hq, dtype=torch.float32, device=DEV)
+    ip_h = indptr.contiguous()
+    ip_d, ix_d, lp_d = indptr.to(DEV), indices.to(DEV), last.to(DEV)
+    info = torch.zeros(16, dtype=torch.int64)
+    vp = C.c_void_p
+    rc = ref.ref_batch_decode_rope(
+        vp(fws.data_ptr()), C.c_size_t(fws.numel()), vp(iws.data_ptr()), vp(pws.data_ptr()),
+        C.c_size_t(iws.numel()), vp(ip_h.data_ptr()), bs, hq, hkv, d, page, DT[q.dtype],
+        DT[cache.dtype], 0 if layout == "NHD" else 1, 0, vp(q.data_ptr()),
+        C.c_int64(q.stride(0)), C.c_int64(q.stride(1)), vp(k.data_ptr()), vp(v.data_ptr()),
+        C.c_int64(k.stride(0)), C.c_int64(k.stride(1)), C.c_int64(k.stride(2)),
+        vp(ix_d.data_ptr()), vp(ip_d.data_ptr()), vp(lp_d.data_ptr()), vp(o.data_ptr()),
+        vp(lse.data_ptr()), C.c_float(sm_scale), C.c_float(rope_scale), C.c_float(rope_theta),
+        vp(torch.cuda.current_stream().cuda_stream), vp(info.data_ptr()), 0)
+    assert rc == 0, ref.ref_last_error()
+    torch.cuda.synchronize()
+    return o, lse
+
+
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("kv_lens,hq,hkv,rope_scale,rope_theta", [
+    ([1, 54, 97, 512, 2048, 33, 64, 65, 128, 1000, 17, 3], 32, 8, 1.0, 1e4),
+    ([4096] * 16, 32, 8, 1.0, 5e5),    # C2 shape, Llama-3 theta
+    ([40000, 7], 8, 2, 2.0, 1e4),      # split-KV in both implementations, long positions
+])
+def test_rope_llama_decode_matches_reference_kernel(ref, layout, dtype, kv_lens, hq, hkv, rope_scale,
+                                                    rope_theta):
+    """pos_encoding_mode="ROPE_LLAMA": our in-register K rotation against the reference's own
+    kernel instantiated with PosEncodingMode::kRoPELlama (decode.cuh:445-466)."""
+    import flashinfer_b200 as fi
+
+    if not hasattr(ref, "ref_batch_decode_rope"):
+        pytest.skip("prebuilt checker predates the ROPE_LLAMA instantiation")
+    d, page = 128, 16
+    cache, indptr, indices, last = make_paged_case(kv_lens, hkv, d, page, layout, torch.float32, seed=17)
+    cache = cache.to(dtype).to(DEV)
+    q = make_q(len(kv_lens), hq, d, dtype, seed=18).to(DEV)
+    sm_scale = 1.0 / d ** 0.5
+    o_ref, lse_ref = ref_batch_decode_rope(ref, q, cache, indptr, indices, last, hq, hkv, page, layout,
+                                           sm_scale, rope_scale, rope_theta)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(torch.zeros(128 << 20, dtype=torch.uint8, device=DEV), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, pos_encoding_mode="ROPE_LLAMA", q_data_type=dtype,
+           rope_scale=rope_scale, rope_theta=rope_theta)
+    o, lse = w.run(q, cache, return_lse=True)
+    ulp = 2.0 ** -7 if dtype == torch.bfloat16 else 2.0 ** -10
+    torch.testing.assert_close(o.float(), o_ref.float(), atol=1e-2, rtol=ulp)
+    # both sides round the rotated K (and q) to 16 bits and take fast sincos of fp32 angles: the
+    # logits of a 40000-token request agree to ~1e-3, so does the base-2 lse
+    assert (lse - lse_ref).abs().max().item() <= (1e-3 if max(kv_lens) <= 4096 else 5e-3)
+
+
 @pytest.mark.parametrize("kv_len", [1, 255, 2048, 33001])
 @pytest.mark.parametrize("layout", ["NHD", "HND"])
 def test_single_decode_matches_reference_kernel(ref, kv_len, layout):
