@@ -37,8 +37,12 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
+static int env_int(const char* name, int dflt, int lo, int hi);
+
+// process-wide overrides: fi_set_tuning(), initialised from FI_B200_STAGES / FI_B200_CTAS_PER_SM
+// (A/B runs of bench.py without touching its code)
 Tuning& tuning() {
-  static Tuning t = {0, 0, 0, 0};
+  static Tuning t = {env_int("FI_B200_STAGES", 0, 0, kMaxStages), env_int("FI_B200_CTAS_PER_SM", 0, 0, 2), 0, 0};
   return t;
 }
 

@@ -42,7 +42,8 @@ def main():
     total = sum(pages)
     cache = torch.randn(total, 2, page, hkv, d, device=DEV, dtype=torch.bfloat16)
     cache = cache.to(kv_dtype) if kind != "bf16" else cache
-    indices = torch.randperm(total, device=DEV).to(torch.int32)
+    order = os.environ.get("PAGE_ORDER", "random")
+    indices = (torch.randperm(total, device=DEV) if order == "random" else torch.arange(total, device=DEV)).to(torch.int32)
     indptr = torch.tensor([0] + list(np.cumsum(pages)), dtype=torch.int32)
     last = torch.tensor([(kv_len - 1) % page + 1] * bs, dtype=torch.int32)
     q = torch.randn(bs, hq, d, device=DEV, dtype=torch.bfloat16)
@@ -74,6 +75,25 @@ def main():
         if len(c) == 0:
             continue
         print(f"{i} {n:14s} {len(c):4d} {c.min():7.2f} {np.median(c):7.2f} {np.percentile(c, 90):7.2f} {c.max():7.2f}")
+    # where does the spread of the streaming phase come from?  (Hkv = 1, static equal split:
+    # CTA i owns pages [i n, (i + 1) n) of the flattened page list)
+    dur = rel[:, 6] - rel[:, 5]
+    ok = ~np.isnan(dur)
+    if hkv == 1 and ok.sum() > 8:
+        idx = indices.cpu().numpy().astype(np.float64)
+        n = total // ncta
+        per = idx[: n * ncta].reshape(ncta, n)
+        upper = (per >= total / 2).mean(axis=1)
+        smid = buf[:, 15].astype(np.float64) - 1
+        print(f"page order {order}: streaming phase {np.nanmin(dur):.1f} .. {np.nanmax(dur):.1f} us, std {np.nanstd(dur):.2f}")
+        print(f"  corr(duration, share of pages in the upper half of the cache) = {np.corrcoef(dur[ok], upper[ok])[0, 1]:+.2f}")
+        print(f"  corr(duration, mean page index)                              = {np.corrcoef(dur[ok], per.mean(axis=1)[ok])[0, 1]:+.2f}")
+        print(f"  corr(duration, sm id)                                        = {np.corrcoef(dur[ok], smid[ok])[0, 1]:+.2f}")
+        print(f"  corr(duration, sm id parity / cta slot)                      = {np.corrcoef(dur[ok], (np.arange(ncta) >= ncta // 2)[ok])[0, 1]:+.2f}")
+        for lo in range(0, 160, 20):
+            m = ok & (smid >= lo) & (smid < lo + 20)
+            if m.sum():
+                print(f"    SMs {lo:3d}-{lo + 19:3d}: mean duration {dur[m].mean():6.2f} us  (n={m.sum()})")
     print("per-CTA deltas (median / max, us):")
     for a, b in [(0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6), (6, 10), (10, 11), (11, 7), (6, 7), (7, 8), (7, 9)]:
         dlt = rel[:, b] - rel[:, a]
