@@ -365,13 +365,13 @@ def run_ours(args):
     launches = lib.fi_launch_count() - n0
     ms_total = e0.elapsed_time(e1)
 
-    # ---- the same kernel timed one launch at a time (L2 flushed by a 256 MB memset the host
+    # ---- the same kernel timed one launch at a time (L2 flushed by reading a 256 MB buffer the host
     # enqueues ahead, so the launch is already queued when the first event fires): reported as
     # roofline.kernel_us_isolated; the roofline itself uses the average over the timed region
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush = torch.zeros(64 << 20, dtype=torch.float32, device=dev)  # 256 MB, twice the L2
     per = []
     for i in range(min(args.steps, 50)):
-        flush.zero_()
+        flush.sum()  # READ 256 MB: the L2 now holds someone else's clean lines, as between a model's GEMMs
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         step(i)

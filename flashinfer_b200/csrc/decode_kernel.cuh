@@ -179,13 +179,17 @@ __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int 
   int pub0;
   if (!s.implicit) {
     const ItemHead* head = p.item_heads + blockIdx.x;  // heads exist for every launched CTA
-    const int4 h = __ldg(reinterpret_cast<const int4*>(head));
+    const uint64_t keep = l2_policy_evict_last();
+    const int4 h = (p.l2_hints & 2) ? ldg_int4_hint(reinterpret_cast<const int4*>(head), keep)
+                              : __ldg(reinterpret_cast<const int4*>(head));
     s.first = h.x;
     s.head_count = h.y;
     s.num_items = h.z;
     pub0 = min(s.head_count, kItemInlineSegs);
     if (tid < 3 * pub0)
-      reinterpret_cast<int4*>(cache)[tid] = __ldg(reinterpret_cast<const int4*>(head->seg) + tid);
+      reinterpret_cast<int4*>(cache)[tid] =
+          (p.l2_hints & 2) ? ldg_int4_hint(reinterpret_cast<const int4*>(head->seg) + tid, keep)
+                     : __ldg(reinterpret_cast<const int4*>(head->seg) + tid);
   } else {
     seg_source_implicit_range(s);
     for (int i = tid; i < min(s.count, kSegCache); i += blockDim.x) cache[i] = seg_make(s, i);
@@ -357,6 +361,9 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   const int j = lane % bpt;  // same j for every i = lane + 32 k since bpt | 32
   const uint32_t box_bytes = (uint32_t)rpb * 128u;
 
+  const bool hints = (p.l2_hints & 1) != 0, keep_meta = (p.l2_hints & 2) != 0;
+  const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
+
   Feeder f;
   feeder_init(f, src);
   Segment sg;
@@ -387,7 +394,9 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
     int page = 0;
     if (j < nvb) {
       const int pit = tok >> p.page_shift;
-      page = p.kv_indices ? __ldg(p.kv_indices + sg.page_base + pit) : sg.page_base + pit;
+      if (p.kv_indices == nullptr) page = sg.page_base + pit;
+      else page = keep_meta ? ldg_s32_hint(p.kv_indices + sg.page_base + pit, pol_keep)
+                        : __ldg(p.kv_indices + sg.page_base + pit);
     }
     const int row0 = tok & p.page_mask;
     FI_TRACE_IF(lane == 0 && first_tile && page >= 0, 3);
@@ -399,9 +408,14 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
       for (int i = lane; i < nbox; i += 32) {
         const int pn = (i / bpt) % G::NP;
         const int kv = i / (bpt * G::NP);
-        tma_load_4d(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
-                    full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? sg.kv_head : row0,
-                    p.tma_h_first ? row0 : sg.kv_head, page);
+        if (hints)
+          tma_load_4d_hint(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
+                           full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? sg.kv_head : row0,
+                           p.tma_h_first ? row0 : sg.kv_head, page, pol_stream);
+        else
+          tma_load_4d(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
+                      full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? sg.kv_head : row0,
+                      p.tma_h_first ? row0 : sg.kv_head, page);
       }
     }
     __syncwarp();

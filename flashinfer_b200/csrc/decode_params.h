@@ -157,6 +157,7 @@ struct DecodeParams {
   float rope_rcp_scale, rope_rcp_theta;
   float sm_scale;          // plain sm_scale (soft-cap path)
   int32_t enable_pdl;
+  int32_t l2_hints;  // bit 0: KV boxes L2 evict_first; bit 1: page table / work list L2 evict_last
 };
 
 struct MergeParams {
