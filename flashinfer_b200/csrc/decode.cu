@@ -383,7 +383,8 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.merge_units = reinterpret_cast<const MergeUnit*>(iw + plan_info[kPiOffMerge]);
   p.merge_counters = reinterpret_cast<int32_t*>(iw + plan_info[kPiOffCounters]);
   p.num_qo_heads = Hq;
-  p.group_size = Hq / Hkv;
+  p.group_size = Hq / Hkv;  // Hkv counts virtual heads: <= kMaxGroup query heads each
+  p.kv_head_div = std::max<int>((int)plan_info[kPiKvHeadDiv], 1);
   p.num_stages = (int)plan_info[kPiStages];
   p.sm_scale = sm_scale;
   p.sm_scale_log2 = sm_scale * 1.4426950408889634f;
@@ -414,10 +415,11 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   memset(&km, 0, sizeof(km));
   memset(&vm, 0, sizeof(vm));
   if (tma) {
-    int rc = make_kv_map(&km, k_cache, kv_dtype, head_dim, page_size, Hkv, num_pages, kv_stride_n,
+    const int Hkv_mem = Hkv / p.kv_head_div;  // heads the cache really has
+    int rc = make_kv_map(&km, k_cache, kv_dtype, head_dim, page_size, Hkv_mem, num_pages, kv_stride_n,
                          kv_stride_h, kv_stride_page, p.rows_per_box);
     if (rc != FI_OK) return rc;
-    rc = make_kv_map(&vm, v_cache, kv_dtype, head_dim, page_size, Hkv, num_pages, kv_stride_n,
+    rc = make_kv_map(&vm, v_cache, kv_dtype, head_dim, page_size, Hkv_mem, num_pages, kv_stride_n,
                      kv_stride_h, kv_stride_page, p.rows_per_box);
     if (rc != FI_OK) return rc;
   }
@@ -463,8 +465,10 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (num_kv_heads <= 0 || num_qo_heads % num_kv_heads)
     return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads must be a multiple of num_kv_heads");
+  const int kv_div = group_split(num_qo_heads / num_kv_heads);
+  const int num_kv_heads_mem = num_kv_heads;  // heads k / v really have
+  num_kv_heads *= kv_div;                     // virtual heads: one unit each (see DecodeParams)
   const int group = num_qo_heads / num_kv_heads;
-  if (group > kMaxGroup) return fail(FI_ERR_UNSUPPORTED, "Unsupported group_size: %d", group);
   const int kvf = kv_format(q_dtype, kv_dtype);
   if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair");
   if (!(head_dim == 64 || head_dim == 128 || head_dim == 256) || (kvf != 0 && head_dim == 64))
@@ -495,7 +499,8 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   memset(&p, 0, sizeof(p));
   p.q = q; p.q_stride_n = 0; p.q_stride_h = head_dim;
   p.o = o; p.lse = lse; p.k = k; p.v = v;
-  if (kv_layout == FI_LAYOUT_NHD) { p.kv_stride_n = (int64_t)num_kv_heads * head_dim; p.kv_stride_h = head_dim; }
+  p.kv_head_div = kv_div;
+  if (kv_layout == FI_LAYOUT_NHD) { p.kv_stride_n = (int64_t)num_kv_heads_mem * head_dim; p.kv_stride_h = head_dim; }
   else { p.kv_stride_n = head_dim; p.kv_stride_h = (int64_t)kv_len * head_dim; }
   p.kv_stride_page = 0;
   p.page_size = kv_len > 0 ? kv_len : 1;
@@ -519,10 +524,10 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   memset(&km, 0, sizeof(km));
   memset(&vm, 0, sizeof(vm));
   if (tma) {
-    const int64_t sp = (int64_t)kv_len * num_kv_heads * head_dim;  // single "page"
-    rc = make_kv_map(&km, k, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, TT);
+    const int64_t sp = (int64_t)kv_len * num_kv_heads_mem * head_dim;  // single "page"
+    rc = make_kv_map(&km, k, kv_dtype, head_dim, kv_len, num_kv_heads_mem, 1, p.kv_stride_n, p.kv_stride_h, sp, TT);
     if (rc != FI_OK) return rc;
-    rc = make_kv_map(&vm, v, kv_dtype, head_dim, kv_len, num_kv_heads, 1, p.kv_stride_n, p.kv_stride_h, sp, TT);
+    rc = make_kv_map(&vm, v, kv_dtype, head_dim, kv_len, num_kv_heads_mem, 1, p.kv_stride_n, p.kv_stride_h, sp, TT);
     if (rc != FI_OK) return rc;
   }
   rc = launch_decode(p, km, vm, q_dtype, kvf, head_dim, (int)grid, tma, stream);

@@ -367,7 +367,7 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   Feeder f;
   feeder_init(f, src);
   Segment sg;
-  int k = 0, t = 0, t_end = 0, tiles_issued = 0;
+  int k = 0, t = 0, t_end = 0, tiles_issued = 0, mem_head = 0;
   int stage = 0;
   uint32_t phase = 0;
   [[maybe_unused]] bool first_tile = true;
@@ -385,6 +385,7 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
       if (!more) break;
       t = sg.tile_begin;
       t_end = sg.tile_end;
+      mem_head = sg.kv_head / p.kv_head_div;
     }
     // boxes of tile t: page index + first row for this lane's token block j
     const int tok0 = t * G::TT;
@@ -410,12 +411,12 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
         const int kv = i / (bpt * G::NP);
         if (hints)
           tma_load_4d_hint(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
-                           full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? sg.kv_head : row0,
-                           p.tma_h_first ? row0 : sg.kv_head, page, pol_stream);
+                           full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? mem_head : row0,
+                           p.tma_h_first ? row0 : mem_head, page, pol_stream);
         else
           tma_load_4d(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
-                      full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? sg.kv_head : row0,
-                      p.tma_h_first ? row0 : sg.kv_head, page);
+                      full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? mem_head : row0,
+                      p.tma_h_first ? row0 : mem_head, page);
       }
     }
     __syncwarp();
@@ -462,7 +463,7 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
       if (lane == 0) src.ctl[kQDone1] = k + 1;
     }
     const int page_base = sg.page_base;
-    const int64_t head_off = (int64_t)sg.kv_head * p.kv_stride_h + c * (16 / G::ES);
+    const int64_t head_off = (int64_t)(sg.kv_head / p.kv_head_div) * p.kv_stride_h + c * (16 / G::ES);
     for (int t = sg.tile_begin; t < sg.tile_end; ++t) {
       if (feeds) feeder_step(f, src, k, tiles_issued, lane);
       mbar_wait(empty_bar + 8 * stage, phase ^ 1);

@@ -23,6 +23,12 @@ constexpr int kSegCache = 32;         // segment queue (ring) in smem per CTA; a
 constexpr int kSegRefill = 8;         // segments the feeder loads from the list at a time
 constexpr float kNegInf = -5e4f;      // finite "-inf", reference math.cuh:32
 constexpr int kMaxGroup = 8;          // GQA group size handled by one MMA N tile
+// smallest d with group % d == 0 and group / d <= kMaxGroup (1 for group <= kMaxGroup)
+__host__ __device__ constexpr int group_split(int group) {
+  for (int d = 1; d <= group; ++d)
+    if (group % d == 0 && group / d <= kMaxGroup) return d;
+  return group;
+}
 
 // One unit of work for a CTA: tiles [tile_begin, tile_end) (absolute tile index on the
 // request's token axis, tile t covers tokens [TT t, TT t + TT), TT = tile_tokens(kvf)) of KV head `kv_head`
@@ -108,6 +114,7 @@ enum PlanInfoSlot {
   kPiOffCounters,   // int32 arrival counters, one per merge unit (fused split-KV merge)
   kPiOffItemHeads,
   kPiOffWorkCounter,  // int32 ticket counter of the item scheduler (zero between launches)
+  kPiKvHeadDiv,       // virtual KV heads per real one (kPiNumKvHeads counts virtual heads)
   kPiLen
 };
 constexpr int64_t kPlanMagic = 0xF1B2000001LL;
@@ -158,6 +165,10 @@ struct DecodeParams {
   float sm_scale;          // plain sm_scale (soft-cap path)
   int32_t enable_pdl;
   int32_t l2_hints;  // bit 0: KV boxes L2 evict_first; bit 1: page table / work list L2 evict_last
+  // GQA groups larger than kMaxGroup are run as `kv_head_div` virtual KV heads per real one, each
+  // with group / kv_head_div (<= kMaxGroup) query heads: Segment::kv_head counts virtual heads
+  // (query / output addressing), the cache is addressed with kv_head / kv_head_div
+  int32_t kv_head_div;
 };
 
 struct MergeParams {

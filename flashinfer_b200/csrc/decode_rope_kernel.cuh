@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(rope_warps(HD) * 32)
 
     const int t_begin = max(sg.tile_begin * TT, sg.tok_lo);
     const int t_end = min(sg.tile_end * TT, sg.tok_hi);
-    const int64_t head_off = (int64_t)sg.kv_head * p.kv_stride_h + sub * C;
+    const int64_t head_off = (int64_t)(sg.kv_head / p.kv_head_div) * p.kv_stride_h + sub * C;
 
     // rows of U tokens: [u][0] = the low-half fragment, [u][1] = its rotation partners
     auto load_rows = [&](int first, Raw (&kr)[U][2], Raw (&vr)[U][2]) {

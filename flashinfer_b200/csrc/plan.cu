@@ -144,9 +144,11 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   if (num_qo_heads % num_kv_heads != 0)
     return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads %d is not a multiple of num_kv_heads %d",
                 num_qo_heads, num_kv_heads);
+  // a GQA group larger than one MMA N tile becomes kv_div virtual KV heads per real one (the
+  // reference's CUDA-core decode stops at group 8; its tensor-core decode takes any group)
+  const int kv_div = group_split(num_qo_heads / num_kv_heads);
+  num_kv_heads *= kv_div;
   const int group = num_qo_heads / num_kv_heads;
-  if (group > kMaxGroup)
-    return fail(FI_ERR_UNSUPPORTED, "Unsupported group_size: %d (max %d)", group, kMaxGroup);
   const int kvf = kv_format(q_dtype, kv_dtype);
   if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair (%d, %d)", q_dtype, kv_dtype);
   if (!(head_dim == 64 || head_dim == 128 || head_dim == 256) || (kvf != 0 && head_dim == 64))
@@ -525,6 +527,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   pi[kPiOffCounters] = (int64_t)off_counters;
   pi[kPiOffItemHeads] = (int64_t)off_heads;
   pi[kPiOffWorkCounter] = (int64_t)off_work;
+  pi[kPiKvHeadDiv] = kv_div;
   pi[kPiTotalTiles] = total_tiles;
   pi[kPiWindowLeft] = window_left;
   pi[kPiStages] = cfg.stages;

@@ -93,9 +93,9 @@ class MergeUnit(C.Structure):
 # plan-info slots (flashinfer_b200/csrc/decode_params.h PlanInfoSlot)
 PI = dict(magic=0, num_ctas=1, num_segments=2, num_merge=3, num_slots=4, off_header=5,
           num_items=6, off_segments=7, off_merge=8, off_tmp_o=9, off_tmp_lse=10,
-          batch_size=11, hq=12, hkv=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
+          batch_size=11, hq=12, hkv=13, num_kv_heads=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
           cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23,
-          off_counters=24, off_item_heads=25, off_work_counter=26)
+          off_counters=24, off_item_heads=25, off_work_counter=26, kv_head_div=27)
 SEG_BYTES = 48    # sizeof(Segment)
 HEAD_BYTES = 160  # sizeof(ItemHead)
 INLINE_SEGS = 3   # kItemInlineSegs

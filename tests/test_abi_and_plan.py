@@ -164,8 +164,10 @@ def test_plan_errors():
     indptr, last = lens_to_table([100], 16)
     rc, err, _ = host_plan(indptr, last, 30, 8, 128, 16, 148)
     assert rc == 1 and "multiple" in err
-    rc, err, _ = host_plan(indptr, last, 32, 2, 128, 16, 148)
-    assert rc == 4 and "group_size" in err
+    # a GQA group of 16 is planned as two virtual KV heads of 8 query heads per real KV head
+    rc, err, plan = host_plan(indptr, last, 32, 2, 128, 16, 148)
+    assert rc == 0 and plan["info"][PI["num_kv_heads"]] == 4 and plan["info"][PI["kv_head_div"]] == 2
+    replay_plan(plan, [100], 4)
     rc, err, _ = host_plan(indptr, last, 8, 2, 96, 16, 148)
     assert rc == 4 and "head_dim" in err
     rc, err, _ = host_plan(indptr, [17], 8, 2, 128, 16, 148)

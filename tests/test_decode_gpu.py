@@ -90,6 +90,32 @@ def test_batch_decode_page_sizes_and_groups(page, group):
               seed=page * 10 + group)
 
 
+@pytest.mark.parametrize("hq,hkv", [(16, 1), (32, 2), (24, 2), (64, 2), (9, 1), (40, 4)])
+@pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn])
+def test_batch_decode_large_gqa_groups(hq, hkv, kv_dtype):
+    """GQA groups above one MMA N tile (16, 12, 32, 9, 10) run as virtual KV heads of <= 8 query
+    heads that address the same cache head (the reference's CUDA-core decode stops at group 8,
+    utils.cuh:123-143; its tensor-core decode, which engines pick for large groups, takes any)."""
+    fi = _fi()
+    lens = [1, 97, 512, 3000, 0, 64]
+    d, page = 128, 16
+    is8 = kv_dtype is not None
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=61)
+    cache = (cache * 0.5 if is8 else cache).to(kv_dtype or torch.float16)
+    q = make_q(len(lens), hq, d, torch.float16, seed=62)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD", use_tensor_cores=True)
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, kv_data_type=cache.dtype)
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True)
+    torch.cuda.synchronize()
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, "NHD")
+    assert (o.float().cpu() - o_ref).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+    assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+    # single decode takes the same route
+    k_i, v_i = orc.gather_paged_kv(*orc.unpack_cache(cache, "NHD"), indptr, indices, last, 3, "NHD")
+    o_i = fi.single_decode_with_kv_cache(q[3].to(DEV), k_i.to(DEV), v_i.to(DEV))
+    assert (o_i.float().cpu() - o_ref[3]).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+
+
 @pytest.mark.parametrize("d", [64, 128, 256])
 @pytest.mark.parametrize("layout", ["NHD", "HND"])
 def test_batch_decode_head_dims(d, layout):
