@@ -364,6 +364,14 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   const bool hints = (p.l2_hints & 1) != 0, keep_meta = (p.l2_hints & 2) != 0;
   const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
 
+  // Programmatic dependent launch: the work list and the page table were fixed at plan() time (host
+  // memcpys ordered before every later kernel), so the first tile's page indices are requested
+  // BEFORE the dependency wait and are in flight while the upstream kernel drains; the KV cache
+  // itself (append_paged_kv_cache may be that upstream kernel) is only touched after the wait.
+  // Plans with drawn items touch the ticket counter, which the previous launch re-arms: wait first.
+  bool waited = p.enable_pdl == 0;
+  if (!waited && src.num_items > (int)gridDim.x) { pdl_wait(); waited = true; }
+
   Feeder f;
   feeder_init(f, src);
   Segment sg;
@@ -400,6 +408,7 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
                         : __ldg(p.kv_indices + sg.page_base + pit);
     }
     const int row0 = tok & p.page_mask;
+    if (!waited) { pdl_wait(); waited = true; }
     FI_TRACE_IF(lane == 0 && first_tile && page >= 0, 3);
     mbar_wait(empty_bar + 8 * stage, phase ^ 1);
     if (lane == 0) mbar_arrive_expect_tx(full_bar + 8 * stage, 2u * G::NP * nvb * box_bytes);
@@ -1231,7 +1240,6 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   __syncthreads();
   FI_TRACE_IF(tid == 0, 1);
   if (seg_source_idle(src)) return;
-  if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
   // Early trigger: the next kernel in the stream becomes launchable now, so its CTAs move into
   // SM slots as ours retire (they run their prologue and then block in their own
   // griddepcontrol.wait until this grid has completed and flushed) — the launch latency and
@@ -1239,11 +1247,15 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   if (p.enable_pdl == 1) pdl_launch_dependents();
   FI_TRACE_IF(tid == 0, 2);
 
+  // every role waits for the upstream kernel itself, right before its first access to data an
+  // upstream kernel may have produced (q, the KV cache, counters)
   if (tid < kConsumerWarps * 32) {
+    if (p.enable_pdl) pdl_wait();
     consume<QT, KVF, HD, LOADER, ROPE>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
   } else if (LOADER == 0) {
-    produce_tma<KVF, HD>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
+    produce_tma<KVF, HD>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);  // waits inside
   } else {
+    if (p.enable_pdl) pdl_wait();
     produce_cpasync<KVF, HD>(p, src, tid - kConsumerWarps * 32, ring, full_bar, empty_bar);
   }
   if (p.enable_pdl == 2) pdl_launch_dependents();  // FI_B200_PDL_LATE=1 (A/B runs)

@@ -497,11 +497,13 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
     if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);
     return;
   }
-  if (p.enable_pdl) pdl_wait();  // q (and the KV cache) come from upstream kernels
   if (p.enable_pdl == 1) pdl_launch_dependents();  // early trigger, see paged_decode_kernel
   FI_TRACE_IF(tid == 0, 2);
 
+  // dependency wait per role (see paged_decode_kernel): the softmax warps read q, the producer
+  // requests its first page indices and then waits, the MMA issuer touches no global memory
   if (warp < 4) {
+    if (p.enable_pdl) pdl_wait();
     tc5_softmax<QT, KVF>(p, src, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
   } else if (warp == 4) {
     produce_tma<KVF, 128>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
