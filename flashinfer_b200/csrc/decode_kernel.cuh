@@ -775,20 +775,16 @@ __device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int reques
                                                int slot_begin, int count, int ctid) {
   const int GS = p.group_size;
   constexpr int CPH = HD / 4;  // float4 chunks per head row
+  // One pass with a running maximum (rescaled on the fly) over batches of four partials: the lse
+  // and o loads of a batch are issued together, so a unit of <= 4 partials costs ONE L2 round trip.
+#pragma unroll 1
   for (int item = ctid; item < GS * CPH; item += kConsumerWarps * 32) {
     const int h = item / CPH, c = item - h * CPH;
     const float* lse = p.tmp_lse + (int64_t)slot_begin * GS + h;
     const float* row = p.tmp_o + ((int64_t)slot_begin * GS + h) * HD + 4 * c;
-    float mx = kNegInf;
-    for (int k0 = 0; k0 < count; k0 += 4) {
-      float s4[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) s4[j] = k0 + j < count ? __ldcg(lse + (int64_t)(k0 + j) * GS) : kNegInf;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) mx = fmaxf(mx, s4[j]);
-    }
-    float d = 0.f;
+    float mx = kNegInf, d = 0.f;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
     for (int k0 = 0; k0 < count; k0 += 4) {
       float s4[4];
       float4 x4[4];
@@ -799,9 +795,16 @@ __device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int reques
         x4[j] = ok ? __ldcg(reinterpret_cast<const float4*>(row + (int64_t)(k0 + j) * GS * HD))
                    : make_float4(0.f, 0.f, 0.f, 0.f);
       }
+      float mn = mx;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) mn = fmaxf(mn, s4[j]);
+      const float sc = ex2f(mx - mn);  // 1 when the maximum did not move, 0 out of the sentinel
+      mx = mn;
+      d *= sc;
+      acc.x *= sc; acc.y *= sc; acc.z *= sc; acc.w *= sc;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float w = k0 + j < count ? ex2f(s4[j] - mx) : 0.f;
+        const float w = k0 + j < count ? ex2f(s4[j] - mn) : 0.f;
         d += w;
         acc.x += w * x4[j].x; acc.y += w * x4[j].y; acc.z += w * x4[j].z; acc.w += w * x4[j].w;
       }
