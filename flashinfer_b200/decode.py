@@ -212,6 +212,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._use_cuda_graph = use_cuda_graph
         self._backend = backend
         self._plan_info: Optional[torch.Tensor] = None
+        self._mtp_children = {}
+        self._mtp_src = None
         self._pos_encoding_mode = "NONE"
         self._rope_scale = self._rope_theta = None
 
@@ -370,8 +372,46 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._sm_scale = sm_scale
         self._rope_scale = rope_scale
         self._rope_theta = rope_theta
+        # what run(q_len_per_req > 1) needs to plan the per-row requests on first use
+        self._mtp_children = {}
+        self._mtp_src = (indptr, indices, last_page_len, head_dim, page_size, q_data_type, kv_data_type,
+                         fixed_split_size, disable_split_kv)
 
     begin_forward = plan
+
+    def _run_multi_token(self, q, paged_kv_cache, q_len_per_req, **run_kw):
+        r"""``q_len_per_req`` > 1 (speculative / multi-token decode, reference decode.py:1177,1278;
+        SURVEY.md §8(f) rank 4): ``q`` holds ``q_len_per_req`` consecutive query tokens per request
+        and the cache already holds their K / V; token ``t`` of a request attends the request's
+        first ``kv_len - (q_len_per_req - 1 - t)`` tokens (causal among the new tokens).  A query
+        row that attends a prefix of a page list is a decode request over that prefix, so the
+        rows run as ``batch_size * q_len_per_req`` planned decode requests on the same kernels;
+        the plan of the expanded table is made on the first call (host work, not graph-capturable)
+        and kept until the next ``plan()``."""
+        from .cascade import rows_as_decode_requests
+
+        if self._mtp_src is None:
+            raise RuntimeError("q_len_per_req > 1 needs a regular plan() (not fast_decode_plan)")
+        if q.shape[0] != self._batch_size * q_len_per_req:
+            raise ValueError(
+                f"q must hold batch_size * q_len_per_req = {self._batch_size * q_len_per_req} rows, "
+                f"got {q.shape[0]}"
+            )
+        child = self._mtp_children.get(q_len_per_req)
+        if child is None:
+            (indptr, indices, last_page_len, head_dim, page_size, q_dt, kv_dt, fss, dskv) = self._mtp_src
+            qo_indptr = torch.arange(self._batch_size + 1, dtype=torch.int32) * q_len_per_req
+            r_indptr, r_indices, r_last = rows_as_decode_requests(
+                qo_indptr, indptr, indices, last_page_len, page_size, causal=True)
+            child = BatchDecodeWithPagedKVCacheWrapper(
+                self._float_workspace_buffer, self._kv_layout, use_tensor_cores=self.use_tensor_cores)
+            child.plan(r_indptr, r_indices, r_last, self._num_qo_heads, self._num_kv_heads, head_dim,
+                       page_size, pos_encoding_mode=self._pos_encoding_mode, window_left=self._window_left,
+                       logits_soft_cap=self._logits_soft_cap, q_data_type=q_dt, kv_data_type=kv_dt,
+                       sm_scale=self._sm_scale, rope_scale=self._rope_scale, rope_theta=self._rope_theta,
+                       fixed_split_size=fss, disable_split_kv=dskv)
+            self._mtp_children[q_len_per_req] = child
+        return child.run(q, paged_kv_cache, **run_kw)
 
     def _run_plan(self, indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
                   head_dim, page_size, q_data_type, kv_data_type, window_left,
@@ -456,7 +496,11 @@ class BatchDecodeWithPagedKVCacheWrapper:
         if sinks is not None:
             raise NotImplementedError("attention sinks are not supported")
         if q_len_per_req not in (None, 1):
-            raise NotImplementedError("q_len_per_req > 1 is not supported")
+            if self.is_cuda_graph_enabled:
+                raise NotImplementedError("q_len_per_req > 1 is not supported in CUDA-graph mode")
+            return self._run_multi_token(
+                q, paged_kv_cache, int(q_len_per_req), q_scale=q_scale, k_scale=k_scale, v_scale=v_scale,
+                out=out, lse=lse, return_lse=return_lse, enable_pdl=enable_pdl, window_left=window_left)
         if enable_pdl is None:
             enable_pdl = device_support_pdl(q.device)
         k_cache, v_cache = _unpack_paged_kv_cache(paged_kv_cache, self._kv_layout)
@@ -675,3 +719,6 @@ def fast_decode_plan(
     self._sm_scale = sm_scale
     self._rope_scale = rope_scale
     self._rope_theta = rope_theta
+    self._mtp_children = {}
+    self._mtp_src = (indptr_src, indices, last_page_len, head_dim, page_size, q_data_type, kv_data_type,
+                     fixed_split_size, disable_split_kv)

@@ -524,3 +524,38 @@ def test_invalid_pos_encoding_mode():
     k = torch.zeros(16, 2, 128, dtype=torch.float16, device=DEV)
     with pytest.raises(KeyError):
         fi.single_decode_with_kv_cache(q, k, k, pos_encoding_mode="SOMETHING")
+
+
+@pytest.mark.parametrize("q_len_per_req", [2, 4])
+@pytest.mark.parametrize("kv_dtype,pos_mode", [(None, "NONE"), (torch.float8_e4m3fn, "NONE"), (None, "ROPE_LLAMA")])
+def test_multi_token_decode_q_len_per_req(q_len_per_req, kv_dtype, pos_mode):
+    """run(q_len_per_req = n) (reference decode.py:1177,1278): n query tokens per
+    request whose K / V are already in the cache; token t attends the first kv_len - (n - 1 - t) tokens."""
+    fi = _fi()
+    hq, hkv, d, page = 16, 4, 128, 16
+    lens = [5, 97, 512, 3000, 64, 4]
+    n = q_len_per_req
+    is8 = kv_dtype is not None
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=71)
+    cache = (cache * 0.5 if is8 else cache).to(kv_dtype or torch.float16)
+    q = make_q(len(lens) * n, hq, d, torch.float16, seed=72)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, hq, hkv, d, page, pos_encoding_mode=pos_mode, q_data_type=torch.float16,
+           kv_data_type=cache.dtype)
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True, q_len_per_req=n)
+    assert o.shape == q.shape and lse.shape == (len(lens) * n, hq)
+    torch.cuda.synchronize()
+    k4, v4 = orc.unpack_cache(cache, "NHD")
+    rope = (1.0, 1e4) if pos_mode == "ROPE_LLAMA" else None
+    for b, L in enumerate(lens):
+        k, v = orc.gather_paged_kv(k4, v4, indptr, indices, last, b, "NHD")
+        for t in range(n):
+            Lt = max(L - (n - 1 - t), 0)
+            o_ref, lse_ref = orc.decode_attention_ref(q[b * n + t], k[:Lt].float(), v[:Lt].float(), rope=rope)
+            assert (o[b * n + t].float().cpu() - o_ref).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+            assert (lse[b * n + t].cpu() - lse_ref).abs().max().item() <= LSE_TOL
+    # second call reuses the plan of the expanded table; a wrong row count is refused
+    o2 = w.run(q.to(DEV), cache.to(DEV), q_len_per_req=n)
+    assert torch.equal(o2, o)
+    with pytest.raises(ValueError):
+        w.run(q[:-1].to(DEV), cache.to(DEV), q_len_per_req=n)
