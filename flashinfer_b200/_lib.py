@@ -40,7 +40,7 @@ PROTOTYPES = {
     "fi_batch_decode_plan": (_i, [_vp, _sz, _vp, _vp, _sz, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
                                   _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "fi_batch_decode_run": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _i64,
-                                 _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _f, _f, _i, _i, _vp]),
+                                 _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _f, _f, _vp, _i, _i, _vp]),
     "fi_single_decode_run": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,
                                   _i, _f, _f, _f, _i, _vp, _f, _f, _i, _vp]),
     "fi_single_decode_tmp_bytes": (_sz, [_i, _i, _i, _i]),

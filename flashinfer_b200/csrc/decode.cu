@@ -339,7 +339,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
                         const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
                         float v_scale, float logits_soft_cap, int pos_encoding_mode,
                         const float* alibi_slopes, float rope_scale, float rope_theta,
-                        int enable_pdl, int device, void* stream_) {
+                        const float* sinks, int enable_pdl, int device, void* stream_) {
   if (int rc = check_pos_mode(pos_encoding_mode, alibi_slopes, rope_scale, rope_theta)) return rc;
   if (plan_info == nullptr || plan_info[kPiMagic] != kPlanMagic)
     return fail(FI_ERR_INVALID_ARGUMENT, "plan info is not initialized");
@@ -406,6 +406,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   // (scripts/l2_context_probe.py) C3 385 -> 362 us, C2 167.9 -> 165.9 us.  Only a launch that finds
   // the L2 full of DIRTY lines (a 256 MB memset right before it) is slower (C2 +4 %, C4 +10 %).
   p.l2_hints = default_l2_hints();
+  p.sinks = sinks;
 
   const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
                                 page_size, false, 0, TT);
@@ -437,6 +438,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
     mp.tmp_o = p.tmp_o; mp.tmp_lse = p.tmp_lse;
     mp.o = o; mp.lse = lse;
     mp.num_qo_heads = Hq; mp.group_size = p.group_size; mp.head_dim = head_dim;
+    mp.sinks = sinks;
     mp.out_scale = v_scale;
     mp.out_dtype = q_dtype;
     mp.enable_pdl = enable_pdl;

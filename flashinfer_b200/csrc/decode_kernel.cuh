@@ -810,6 +810,7 @@ __device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int reques
       }
     }
     const int64_t hq = (int64_t)request * p.num_qo_heads + kv_head * GS + h;
+    if (p.sinks != nullptr && mx > kNegInf) d += ex2f(__ldg(p.sinks + kv_head * GS + h) * 1.4426950408889634f - mx);
     const float inv = p.v_scale / d;
     uint2 u;
     u.x = pack2<QT == 1>(acc.x * inv, acc.y * inv);
@@ -1136,6 +1137,8 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         const bool any = L[j] > 0.f;
+        if (direct && any && p.sinks != nullptr && 2 * t + j < GS)
+          L[j] += ex2f(__ldg(p.sinks + sg.kv_head * GS + 2 * t + j) * 1.4426950408889634f - M[j]);
         // fp8 KV: the accumulator carries the x256 scale of the quantised probabilities
         inv[j] = any ? (direct ? p.v_scale : 1.f) * (KVF == 0 ? 1.f : 1.f / 256.f) / L[j] : 0.f;
         lse2[j] = any ? M[j] + lg2f(L[j]) : kNegInf;

@@ -416,6 +416,8 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
     for (int j = 0; j < 8; ++j) {
       if (j < GS) {
         const bool any = L[j] > 0.f;
+        if (direct && any && p.sinks != nullptr)  // L is relative to rho and carries 2^kTc5PShift
+          L[j] += ex2f(__ldg(p.sinks + sg.kv_head * GS + j) * 1.4426950408889634f - rho[j] + kTc5PShift);
         // numerator and denominator both carry the 2^kTc5PShift scale of p
         const float val = any ? o8[j] * ((direct ? p.v_scale : 1.f) / L[j]) : 0.f;
         const float lse2 = any ? rho[j] + lg2f(L[j]) - kTc5PShift : kNegInf;

@@ -169,6 +169,11 @@ struct DecodeParams {
   // with group / kv_head_div (<= kMaxGroup) query heads: Segment::kv_head counts virtual heads
   // (query / output addressing), the cache is addressed with kv_head / kv_head_div
   int32_t kv_head_div;
+  // attention sinks (reference decode.py:1176, tests/test_helpers/sink_attention_reference.py:23-36):
+  // one extra logit per query head that takes part in the softmax denominator only —
+  // p_i = exp(s_i) / (sum_j exp(s_j) + exp(sink[head])); natural-log units, not scaled by sm_scale.
+  // Added once per (request, head): where the final o / lse are written, never to a partial.
+  const float* sinks;
 };
 
 struct MergeParams {
@@ -183,6 +188,7 @@ struct MergeParams {
   float out_scale;
   int32_t out_dtype;
   int32_t enable_pdl;
+  const float* sinks;  // see DecodeParams::sinks
 };
 
 }  // namespace fib200

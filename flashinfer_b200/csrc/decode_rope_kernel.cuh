@@ -318,6 +318,8 @@ __global__ void __launch_bounds__(rope_warps(HD) * 32)
         acc += sm_o[w][j][d] * f;
       }
       const bool any = L > 0.f;
+      if (direct && any && p.sinks != nullptr)
+        L += ex2f(__ldg(p.sinks + sg.kv_head * GS + j) * 1.4426950408889634f - M);
       const float val = any ? acc * ((direct ? p.v_scale : 1.f) / L) : 0.f;
       const float lse2 = any ? M + lg2f(L) : kNegInf;
       if (direct) {

@@ -200,6 +200,7 @@ __global__ void decode_merge_kernel(const __grid_constant__ MergeParams p) {
     // partials of empty pieces carry lse = -5e4 and o = 0; if every piece is empty the
     // weights are all 1 and o stays 0, lse = -5e4 + log2(count): clamp to the sentinel
     const bool any = m > kNegInf;
+    if (any && p.sinks != nullptr) d += ex2f(__ldg(p.sinks + kv_head * G + head) * 1.4426950408889634f - m);
     const float inv = p.out_scale / d;
     const int64_t orow = ((int64_t)request * p.num_qo_heads + kv_head * G + head) * D + c * 4;
     if constexpr (DT_OUT == 1) {

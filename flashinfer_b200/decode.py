@@ -494,13 +494,17 @@ class BatchDecodeWithPagedKVCacheWrapper:
         if self._plan_info is None:
             raise RuntimeError("plan() must be called before run()")
         if sinks is not None:
-            raise NotImplementedError("attention sinks are not supported")
+            # one extra logit per query head in the softmax denominator (reference decode.py:1176)
+            if sinks.dim() != 1 or sinks.shape[0] != self._num_qo_heads or sinks.device != q.device:
+                raise ValueError("sinks must be a [num_qo_heads] tensor on q's device")
+            sinks = sinks.to(torch.float32).contiguous()
         if q_len_per_req not in (None, 1):
             if self.is_cuda_graph_enabled:
                 raise NotImplementedError("q_len_per_req > 1 is not supported in CUDA-graph mode")
             return self._run_multi_token(
                 q, paged_kv_cache, int(q_len_per_req), q_scale=q_scale, k_scale=k_scale, v_scale=v_scale,
-                out=out, lse=lse, return_lse=return_lse, enable_pdl=enable_pdl, window_left=window_left)
+                out=out, lse=lse, return_lse=return_lse, enable_pdl=enable_pdl, window_left=window_left,
+                sinks=sinks)
         if enable_pdl is None:
             enable_pdl = device_support_pdl(q.device)
         k_cache, v_cache = _unpack_paged_kv_cache(paged_kv_cache, self._kv_layout)
@@ -573,6 +577,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 float(logits_soft_cap),
                 *_pos_mode_args(self._pos_encoding_mode, q.shape[1], dev, self._rope_scale,
                                 self._rope_theta),
+                sinks.data_ptr() if sinks is not None else None,
                 int(bool(enable_pdl)), device_index(dev),
                 current_stream_ptr(dev),
             )

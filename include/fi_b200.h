@@ -147,7 +147,11 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
  *  rope_scale, rope_theta  FI_POS_ROPE_LLAMA: q is rotated at position kv_len - 1 and every K
  *                   row at its own position, frequencies (1 / rope_scale) * rope_theta^(-2i/D)
  *                   (decode.cuh:445-466, pos_enc.cuh:79-100; Python defaults 1.0 and 1e4,
- *                   decode.py:1257-1260).  Served by a CUDA-core variant kernel.
+ *                   decode.py:1257-1260).  16-bit KV: K rotated in registers inside the MMA kernel;
+ *                   fp8 KV: a CUDA-core variant kernel.
+ *  sinks            device f32 [Hq] or NULL (reference run(..., sinks), decode.py:1176): one extra
+ *                   logit per query head in the softmax denominator only,
+ *                   p_i = exp(s_i) / (sum_j exp(s_j) + exp(sinks[head])); lse includes it
  */
 FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info,
                         const void* q, int64_t q_stride_n, int64_t q_stride_h,
@@ -157,7 +161,8 @@ FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan
                         const int32_t* kv_indptr, void* o, float* lse,
                         float sm_scale, float v_scale, float logits_soft_cap,
                         int pos_encoding_mode, const float* alibi_slopes, float rope_scale,
-                        float rope_theta, int enable_pdl, int device, void* stream);
+                        float rope_theta, const float* sinks, int enable_pdl, int device,
+                        void* stream);
 
 /*
  * fi_single_decode_run — one request, contiguous K/V.

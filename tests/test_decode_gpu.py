@@ -559,3 +559,39 @@ def test_multi_token_decode_q_len_per_req(q_len_per_req, kv_dtype, pos_mode):
     assert torch.equal(o2, o)
     with pytest.raises(ValueError):
         w.run(q[:-1].to(DEV), cache.to(DEV), q_len_per_req=n)
+
+
+@pytest.mark.parametrize("kv_dtype,pos_mode,hq", [(None, "NONE", 16), (torch.float8_e4m3fn, "NONE", 32),
+                                                  (None, "ROPE_LLAMA", 16), (torch.float8_e4m3fn, "ROPE_LLAMA", 16),
+                                                  (None, "NONE", 64)])
+def test_attention_sinks(kv_dtype, pos_mode, hq):
+    """run(sinks=[Hq]) (reference decode.py:1176; oracle = the reference's sink_softmax,
+    tests/test_helpers/sink_attention_reference.py:23-36): one extra logit per query head in the
+    softmax denominator; split requests add it once, in the merge."""
+    fi = _fi()
+    hkv, d, page = 4, 128, 16
+    lens = [1, 97, 512, 9000, 0, 64, 2048]
+    is8 = kv_dtype is not None
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=81)
+    cache = (cache * 0.5 if is8 else cache).to(kv_dtype or torch.float16)
+    q = make_q(len(lens), hq, d, torch.float16, seed=82)
+    g = torch.Generator().manual_seed(83)
+    sinks = torch.randn(hq, generator=g) * 2 + 1
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, hq, hkv, d, page, pos_encoding_mode=pos_mode, q_data_type=torch.float16,
+           kv_data_type=cache.dtype)
+    assert int(w._plan_info[3]) > 0  # some unit is split: its sink is added in the merge
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True, sinks=sinks.to(DEV))
+    torch.cuda.synchronize()
+    k4, v4 = orc.unpack_cache(cache, "NHD")
+    rope = (1.0, 1e4) if pos_mode == "ROPE_LLAMA" else None
+    for b in range(len(lens)):
+        k, v = orc.gather_paged_kv(k4, v4, indptr, indices, last, b, "NHD")
+        o_ref, lse_ref = orc.decode_attention_ref(q[b], k.float(), v.float(), rope=rope, sinks=sinks)
+        assert (o[b].float().cpu() - o_ref).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL), b
+        if lens[b] > 0:
+            assert (lse[b].cpu() - lse_ref).abs().max().item() <= LSE_TOL, b
+    # without sinks the same wrapper gives the plain result again (the pointer is per call)
+    o0 = w.run(q.to(DEV), cache.to(DEV))
+    o_ref0, _ = orc.batch_decode_ref(q, cache, indptr, indices, last, "NHD", rope=rope)
+    assert (o0.float().cpu() - o_ref0).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
