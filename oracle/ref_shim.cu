@@ -210,11 +210,20 @@ __attribute__((visibility("default"))) int ref_batch_decode(
     int kv_dtype, int layout, int cuda_graph, void* q, int64_t q_stride_n, int64_t q_stride_h,
     void* k, void* v, int64_t s0, int64_t s1, int64_t s2, int32_t* indices, int32_t* indptr,
     int32_t* last_page_len, void* o, float* lse, float sm_scale, void* stream, int64_t* info_out) {
-  if (head_dim != 128) { g_err = "ref shim is built for head_dim 128"; return 4; }
   BatchArgs a{float_ws, int_ws, pinned_ws, float_bytes, int_bytes, indptr_h, bs, hq, hkv, page_size,
               layout, cuda_graph, q, k, v, o, lse, q_stride_n, q_stride_h, {s0, s1, s2}, indices,
               indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), info_out, 0};
   try {
+    if (head_dim == 64 || head_dim == 256) {  // 16-bit KV only (keeps the build short)
+      if (q_dtype == 0 && kv_dtype == 0)
+        return head_dim == 64 ? batch_impl<half, half, 64>(a) : batch_impl<half, half, 256>(a);
+      if (q_dtype == 1 && kv_dtype == 1)
+        return head_dim == 64 ? batch_impl<nv_bfloat16, nv_bfloat16, 64>(a)
+                              : batch_impl<nv_bfloat16, nv_bfloat16, 256>(a);
+      g_err = "ref shim: head_dim 64 / 256 are built for 16-bit KV";
+      return 4;
+    }
+    if (head_dim != 128) { g_err = "ref shim is built for head_dim 64 / 128 / 256"; return 4; }
     REF_DISPATCH(q_dtype, kv_dtype, return (batch_impl<Q, KV, 128>(a)));
   } catch (const std::exception& e) {
     g_err = e.what();

@@ -86,6 +86,34 @@ def test_batch_decode_matches_reference_kernel(ref, layout, q_dtype, kv_dtype, k
     assert (lse - lse_ref).abs().max().item() <= 1e-3
 
 
+@pytest.mark.parametrize("head_dim", [64, 256])
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("page", [8, 16])
+def test_batch_decode_head_dims_match_reference_kernel(ref, head_dim, layout, dtype, page):
+    """head_dim 64 / 256 (reference utils.cuh:175-202 DISPATCH_HEAD_DIM) against the reference's own
+    kernel instantiated at that head_dim."""
+    import flashinfer_b200 as fi
+
+    kv_lens, hq, hkv = [1, 54, 97, 512, 2048, 33, 6000, 17], 16, 4
+    cache, indptr, indices, last = make_paged_case(kv_lens, hkv, head_dim, page, layout, torch.float32, seed=27)
+    cache = cache.to(dtype).to(DEV)
+    q = make_q(len(kv_lens), hq, head_dim, dtype, seed=28).to(DEV)
+    sm_scale = 1.0 / head_dim ** 0.5
+    try:
+        o_ref, lse_ref, _ = ref_batch_decode(ref, q, cache, indptr, indices, last, hq, hkv, page, layout, sm_scale)
+    except AssertionError as e:
+        if "head_dim" in str(e):
+            pytest.skip("prebuilt checker predates the head_dim 64 / 256 instantiations")
+        raise
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(torch.zeros(128 << 20, dtype=torch.uint8, device=DEV), layout)
+    w.plan(indptr, indices, last, hq, hkv, head_dim, page, q_data_type=dtype, kv_data_type=dtype)
+    o, lse = w.run(q, cache, return_lse=True)
+    ulp = 2.0 ** -7 if dtype == torch.bfloat16 else 2.0 ** -10
+    torch.testing.assert_close(o.float(), o_ref.float(), atol=1e-2, rtol=ulp)
+    assert (lse - lse_ref).abs().max().item() <= 1e-3
+
+
 def ref_batch_decode_rope(ref, q, cache, indptr, indices, last, hq, hkv, page, layout, sm_scale,
                           rope_scale, rope_theta):
     bs, d = q.shape[0], q.shape[2]
