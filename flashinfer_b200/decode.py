@@ -42,6 +42,8 @@ _INT_WORKSPACE_BYTES = 8 * 1024 * 1024
 
 def _host_i32_ptr(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
     """Contiguous CPU int32 copy of `t` and its address (kept alive by the caller)."""
+    if t.device.type == "cpu" and t.dtype == torch.int32 and t.is_contiguous():
+        return t, t.data_ptr()
     h = t.detach().to("cpu", torch.int32).contiguous()
     return h, h.data_ptr()
 
@@ -507,23 +509,45 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 sinks=sinks)
         if enable_pdl is None:
             enable_pdl = device_support_pdl(q.device)
-        k_cache, v_cache = _unpack_paged_kv_cache(paged_kv_cache, self._kv_layout)
-        _check_cached_qkv_data_type(q, k_cache, self._cached_q_data_type, self._cached_kv_data_type)
-        if v_cache.dtype != k_cache.dtype:
-            raise ValueError("k_cache and v_cache must have the same dtype")
-        if self._kv_layout == "NHD":
-            page_size, num_kv_heads = k_cache.shape[1], k_cache.shape[2]
-            stride_n, stride_h = k_cache.stride(1), k_cache.stride(2)
+        if torch.is_tensor(paged_kv_cache) and paged_kv_cache.dim() == 5:
+            # the common 5-D cache: K and V are the two halves of dim 1 (flashinfer/utils.py:160-162
+            # unbinds them) — same strides by construction, no view objects on the hot path
+            c = paged_kv_cache
+            cs = c.stride()
+            kv_dtype = c.dtype
+            kv_dev = c.device
+            k_ptr = c.data_ptr()
+            v_ptr = k_ptr + cs[1] * c.element_size()
+            num_pages, stride_page, last_stride = c.shape[0], cs[0], cs[4]
+            d2, d3, s2, s3 = c.shape[2], c.shape[3], cs[2], cs[3]
         else:
-            num_kv_heads, page_size = k_cache.shape[1], k_cache.shape[2]
-            stride_h, stride_n = k_cache.stride(1), k_cache.stride(2)
+            k_cache, v_cache = _unpack_paged_kv_cache(paged_kv_cache, self._kv_layout)
+            if v_cache.dtype != k_cache.dtype:
+                raise ValueError("k_cache and v_cache must have the same dtype")
+            if k_cache.stride() != v_cache.stride():
+                raise ValueError("k/v strides must be identical")
+            ks = k_cache.stride()
+            kv_dtype, kv_dev = k_cache.dtype, k_cache.device
+            k_ptr, v_ptr = k_cache.data_ptr(), v_cache.data_ptr()
+            num_pages, stride_page, last_stride = k_cache.shape[0], ks[0], ks[3]
+            d2, d3, s2, s3 = k_cache.shape[1], k_cache.shape[2], ks[1], ks[2]
+        if q.dtype != self._cached_q_data_type:
+            raise ValueError(
+                f"The dtype of q {q.dtype} does not match the q_data_type {self._cached_q_data_type} "
+                "specified in plan function.")
+        if kv_dtype != self._cached_kv_data_type:
+            raise ValueError(
+                f"The dtype of k {kv_dtype} does not match the kv_data_type {self._cached_kv_data_type} "
+                "specified in plan function.")
+        if self._kv_layout == "NHD":
+            page_size, num_kv_heads, stride_n, stride_h = d2, d3, s2, s3
+        else:
+            num_kv_heads, page_size, stride_h, stride_n = d2, d3, s2, s3
         if page_size != self._page_size or num_kv_heads != self._num_kv_heads:
             raise ValueError(
                 "paged_kv_cache shape does not match the (page_size, num_kv_heads) given to plan()"
             )
-        if k_cache.stride() != v_cache.stride():
-            raise ValueError("k/v strides must be identical")
-        if k_cache.stride(-1) != 1 or q.stride(-1) != 1:
+        if last_stride != 1 or q.stride(-1) != 1:
             raise ValueError("the last dimension of q / k / v must be contiguous")
         if q.dim() != 3 or q.shape[0] != self._batch_size or q.shape[1] != self._num_qo_heads \
                 or q.shape[2] != self._head_dim:
@@ -532,7 +556,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 f"got {list(q.shape)}"
             )
         dev = q.device
-        if dev != self.device or k_cache.device != dev:
+        if dev != self.device or kv_dev != dev:
             raise ValueError("q / paged_kv_cache must be on the wrapper's device")
 
         window_left = self._window_left if window_left is None else window_left
@@ -568,8 +592,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 self._float_workspace_buffer.data_ptr(), self._int_workspace_buffer.data_ptr(),
                 self._plan_info.data_ptr(),
                 q.data_ptr(), q.stride(0), q.stride(1),
-                k_cache.data_ptr(), v_cache.data_ptr(), k_cache.shape[0],
-                k_cache.stride(0), stride_n, stride_h,
+                k_ptr, v_ptr, num_pages,
+                stride_page, stride_n, stride_h,
                 self._paged_kv_indices_buf.data_ptr(),
                 self._indptr_dev.data_ptr() if self._indptr_dev is not None else None,
                 out.data_ptr(), lse.data_ptr() if return_lse else None,

@@ -203,7 +203,14 @@ def device_index(device: torch.device) -> int:
     return device.index if device.index is not None else torch.cuda.current_device()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def current_stream_ptr(device: torch.device) -> int:
+    """cudaStream_t of torch's current stream on `device` (the raw getter skips the Stream object:
+    ~0.3 us instead of ~2 us on every plan() / run())."""
+    if _raw_stream is not None and device.index is not None:
+        return _raw_stream(device.index)
     return torch.cuda.current_stream(device).cuda_stream
 
 
