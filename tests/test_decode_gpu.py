@@ -595,3 +595,41 @@ def test_attention_sinks(kv_dtype, pos_mode, hq):
     o0 = w.run(q.to(DEV), cache.to(DEV))
     o_ref0, _ = orc.batch_decode_ref(q, cache, indptr, indices, last, "NHD", rope=rope)
     assert (o0.float().cpu() - o_ref0).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+
+
+def _sink_golden():
+    from pathlib import Path
+
+    z = np.load(Path(__file__).resolve().parent / "golden" / "sink_golden.npz")
+    return z, [str(n) for n in z["names"]]
+
+
+@pytest.mark.parametrize("name", _sink_golden()[1])
+def test_attention_sinks_against_reference_golden(name):
+    """batch decode with sinks (and sliding window) against outputs of the reference's own
+    sink_attention_unified (tests/golden/make_golden_sink.py)."""
+    fi = _fi()
+    z, _ = _sink_golden()
+    B, L, Hq, Hkv, D, win, is_bf16 = [int(x) for x in z[f"{name}/meta"]]
+    dt = torch.bfloat16 if is_bf16 else torch.float16
+    q, k, v, o_gold = (torch.from_numpy(z[f"{name}/{key}"].copy()).view(dt) for key in ("q", "k", "v", "o"))
+    q, o_gold = q.view(B, Hq, D), o_gold.view(B, Hq, D)
+    k, v = k.view(B, L, Hkv, D), v.view(B, L, Hkv, D)
+    sink = torch.from_numpy(z[f"{name}/sink"].copy())
+    page = 16
+    npg = -(-L // page)
+    cache = torch.zeros(B * npg, 2, page, Hkv, D, dtype=dt)
+    for b in range(B):
+        pad = torch.zeros(npg * page, Hkv, D, dtype=dt)
+        pad[:L] = k[b]
+        cache[b * npg:(b + 1) * npg, 0] = pad.view(npg, page, Hkv, D)
+        pad = torch.zeros(npg * page, Hkv, D, dtype=dt)
+        pad[:L] = v[b]
+        cache[b * npg:(b + 1) * npg, 1] = pad.view(npg, page, Hkv, D)
+    indptr = torch.arange(B + 1, dtype=torch.int32) * npg
+    indices = torch.arange(B * npg, dtype=torch.int32)
+    last = torch.full((B,), (L - 1) % page + 1, dtype=torch.int32)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, Hq, Hkv, D, page, q_data_type=dt, window_left=win)
+    o = w.run(q.to(DEV), cache.to(DEV), sinks=sink.to(DEV))
+    assert (o.float().cpu() - o_gold.float()).abs().max().item() <= O_TOL

@@ -146,3 +146,26 @@ def test_oracle_rope_matches_reference_helpers(name):
     o, lse = orc.decode_attention_ref(q, k, v, rope=(1.0, theta))
     assert (o - o_gold).abs().max().item() <= 2e-5
     assert (lse - lse_gold).abs().max().item() <= 2e-4
+
+
+# ---------------------------------------------------------------- attention sinks
+def _sink_cases():
+    z = np.load(Path(__file__).resolve().parent / "golden" / "sink_golden.npz")
+    return z, [str(n) for n in z["names"]]
+
+
+@pytest.mark.parametrize("name", _sink_cases()[1])
+def test_oracle_sinks_match_reference_sink_attention(name):
+    """oracle sinks == the reference's own sink_attention_unified (incremental mode, built on its
+    sink_softmax, tests/test_helpers/sink_attention_reference.py), executed in the build container
+    by tests/golden/make_golden_sink.py."""
+    z, _ = _sink_cases()
+    B, L, Hq, Hkv, D, win, is_bf16 = [int(x) for x in z[f"{name}/meta"]]
+    dt = torch.bfloat16 if is_bf16 else torch.float16
+    q, k, v, o_gold = (torch.from_numpy(z[f"{name}/{key}"].copy()).view(dt) for key in ("q", "k", "v", "o"))
+    q, o_gold = q.view(B, Hq, D), o_gold.view(B, Hq, D)
+    k, v = k.view(B, L, Hkv, D), v.view(B, L, Hkv, D)
+    sink = torch.from_numpy(z[f"{name}/sink"].copy())
+    for b in range(B):
+        o, _ = orc.decode_attention_ref(q[b], k[b], v[b], window_left=win, sinks=sink)
+        assert (o - o_gold[b].float()).abs().max().item() <= 2e-3  # the golden output is rounded to q's dtype
