@@ -38,6 +38,43 @@ for d in ((128, 256) if fp8 else (64, 128, 256)):
     torch.cuda.synchronize()
     us = a.elapsed_time(b) * 10
     nbytes = bs * kv_len * hkv * d * 2 * es
+    ref_txt = ""
+    so = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "liboracle_ref.so"
+    if so.exists() and not fp8:  # the reference's own kernel at this head_dim (16-bit KV instantiations)
+        import ctypes as C
+        ref = C.CDLL(str(so))
+        ref.ref_last_error.restype = C.c_char_p
+        vp = C.c_void_p
+        k, v = cache[:, 0], cache[:, 1]
+        fws = torch.zeros(256 << 20, dtype=torch.uint8, device=DEV)
+        iws = torch.zeros(8 << 20, dtype=torch.uint8, device=DEV)
+        pws = torch.zeros(8 << 20, dtype=torch.uint8).pin_memory()
+        ip_d, ix_d, lp_d = indptr.to(DEV), indices.to(DEV), last.to(DEV)
+        info = torch.zeros(16, dtype=torch.int64)
+
+        def call():
+            rc = ref.ref_batch_decode(
+                vp(fws.data_ptr()), C.c_size_t(fws.numel()), vp(iws.data_ptr()), vp(pws.data_ptr()),
+                C.c_size_t(iws.numel()), vp(indptr.data_ptr()), bs, hq, hkv, d, page, 1, 1, 0, 0,
+                vp(q.data_ptr()), C.c_int64(q.stride(0)), C.c_int64(q.stride(1)), vp(k.data_ptr()),
+                vp(v.data_ptr()), C.c_int64(k.stride(0)), C.c_int64(k.stride(1)), C.c_int64(k.stride(2)),
+                vp(ix_d.data_ptr()), vp(ip_d.data_ptr()), vp(lp_d.data_ptr()), vp(out.data_ptr()), None,
+                C.c_float(1.0 / d ** 0.5), vp(torch.cuda.current_stream().cuda_stream), vp(info.data_ptr()))
+            assert rc == 0, ref.ref_last_error()
+
+        for _ in range(3):
+            call()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()  # plan's H2D + kernels; the host-side planning stays off the timeline
+        with torch.cuda.graph(g):
+            call()
+        a.record()
+        for _ in range(20):
+            g.replay()
+        b.record()
+        torch.cuda.synchronize()
+        ref_us = a.elapsed_time(b) * 50
+        ref_txt = f"   reference's own kernel: {ref_us:7.1f} us  {nbytes / ref_us / 1e6:.2f} TB/s"
     print(f"{'e4m3' if fp8 else 'bf16'} D={d} kv_len={kv_len}: {us:7.1f} us  {nbytes / us / 1e6:.2f} TB/s  "
-          f"(ctas {int(w._plan_info[1])}, stages {int(w._plan_info[22])})")
+          f"(ctas {int(w._plan_info[1])}, stages {int(w._plan_info[22])}){ref_txt}")
     del cache
