@@ -203,7 +203,7 @@ def run_reference_gpu(args, wl, so_path):
             raise RuntimeError(f"reference shim failed: {ref.ref_last_error().decode()}")
 
     call(1)
-    for i in range(max(args.warmup, 3)):
+    for i in range(max(args.warmup, 30)):
         call(2, i)
     torch.cuda.synchronize()
     sampler = ClockSampler(0)
