@@ -488,7 +488,8 @@ def emit(args, wl, world, ms_total, kern_ms, e2e_us, ag_us, h2d, d2h, launches, 
     if ag_us is not None:
         line["allgather_us"] = ag_us
     if world == 1 and not args.no_cpu:
-        us, info = cpu_reference_time(wl, sample_requests=2, reps=3)
+        # a quarter of the C2 batch (~0.2 s per pass on 16 cores); 2 requests of the heavier workloads
+        us, info = cpu_reference_time(wl, sample_requests=16 if args.workload == "c2" else 2, reps=3)
         line["cpu_baseline"] = {"value": us, "unit": "us", **info}
     print(json.dumps(line))
 
