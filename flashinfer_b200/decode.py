@@ -19,7 +19,6 @@ import torch
 from . import _lib
 from .page import get_seq_lens
 from .utils import (
-    _check_cached_qkv_data_type,
     _check_kv_layout,
     _check_pos_encoding_mode,
     PosEncodingMode,
