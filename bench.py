@@ -319,7 +319,9 @@ def run_ours(args):
     torch.manual_seed(1234 + rank)
     caches = []
     for _ in range(n_copies):
-        c = torch.randn(total_pages, 2, PAGE, hkv, HEAD_DIM, device=dev, dtype=torch.bfloat16)
+        shape = (total_pages, 2, PAGE, hkv, HEAD_DIM) if args.kv_layout == "NHD" else \
+            (total_pages, 2, hkv, PAGE, HEAD_DIM)
+        c = torch.randn(*shape, device=dev, dtype=torch.bfloat16)
         caches.append(c.to(kv_dtype) if kv_es == 1 else c)
         del c
     k_scale = v_scale = None
@@ -330,7 +332,7 @@ def run_ours(args):
     q = q_host.to(dev)
     out = torch.empty_like(q)
     ws = torch.zeros(128 << 20, dtype=torch.uint8, device=dev)
-    wrapper = fi.BatchDecodeWithPagedKVCacheWrapper(ws, "NHD")
+    wrapper = fi.BatchDecodeWithPagedKVCacheWrapper(ws, args.kv_layout)
     lib = _lib.load()
 
     def plan():
@@ -467,7 +469,8 @@ def emit(args, wl, world, ms_total, kern_ms, e2e_us, ag_us, h2d, d2h, launches, 
         "dtype": "bf16" if kv_es == 2 else "bf16 q/o, e4m3 kv", "data": "synthetic",
         "tokens_per_s": bs / (us_step * 1e-6),
         "hbm_tbps_whole_job": bytes_rank * world / (us_step * 1e-6) / 1e12,
-        "config": {"workload": f"{args.workload}: {wl['desc']}",
+        "config": {"workload": f"{args.workload}: {wl['desc']}" +
+                               (" [cache laid out HND for this run]" if args.kv_layout != "NHD" else ""),
                    "sharding": f"kv-head x{world}" if args.shard_of <= 1 else
                                f"ONE rank of a kv-head x{args.shard_of} sharding (not the whole job)",
                    "heads_per_rank": [hq, hkv], "page_table": "shuffled",
@@ -502,6 +505,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--kv-layout", default="NHD", choices=["NHD", "HND"],
+                    help="paged cache layout (BASELINE's configs are NHD; HND is the fast one for fp8 KV)")
     ap.add_argument("--shard-of", type=int, default=1,
                     help="development aid: run only rank 0's slice of an N-way KV-head sharding on one GPU")
     ap.add_argument("--cpu-reference", action="store_true",
