@@ -191,12 +191,13 @@ int single_impl(void* q, void* k, void* v, void* tmp, void* o, float* lse, int h
 }  // namespace refshim
 using namespace refshim;
 
-// dtype codes as in include/fi_b200.h: 0 f16, 1 bf16, 2 e4m3
+// dtype codes as in include/fi_b200.h: 0 f16, 1 bf16, 2 e4m3, 3 e5m2 (f16 queries only)
 #define REF_DISPATCH(qd, kvd, ...)                                                                  \
   if (qd == 0 && kvd == 0) { using Q = half; using KV = half; __VA_ARGS__; }                        \
   else if (qd == 1 && kvd == 1) { using Q = nv_bfloat16; using KV = nv_bfloat16; __VA_ARGS__; }     \
   else if (qd == 0 && kvd == 2) { using Q = half; using KV = __nv_fp8_e4m3; __VA_ARGS__; }          \
   else if (qd == 1 && kvd == 2) { using Q = nv_bfloat16; using KV = __nv_fp8_e4m3; __VA_ARGS__; }   \
+  else if (qd == 0 && kvd == 3) { using Q = half; using KV = __nv_fp8_e5m2; __VA_ARGS__; }          \
   else { g_err = "unsupported dtype pair"; return 4; }
 
 extern "C" {

@@ -14,7 +14,7 @@ from helpers import make_paged_case, make_q
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 REF_SO = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "liboracle_ref.so"
-DT = {torch.float16: 0, torch.bfloat16: 1, torch.float8_e4m3fn: 2}
+DT = {torch.float16: 0, torch.bfloat16: 1, torch.float8_e4m3fn: 2, torch.float8_e5m2: 3}
 
 
 @pytest.fixture(scope="module")
@@ -56,7 +56,8 @@ def ref_batch_decode(ref, q, cache, indptr, indices, last, hq, hkv, page, layout
 @pytest.mark.parametrize("q_dtype,kv_dtype", [(torch.float16, torch.float16),
                                               (torch.bfloat16, torch.bfloat16),
                                               (torch.float16, torch.float8_e4m3fn),
-                                              (torch.bfloat16, torch.float8_e4m3fn)])
+                                              (torch.bfloat16, torch.float8_e4m3fn),
+                                              (torch.float16, torch.float8_e5m2)])
 @pytest.mark.parametrize("kv_lens,hq,hkv", [
     ([1, 54, 97, 512, 2048, 33, 64, 65, 128, 1000, 17, 3], 32, 8),
     ([4096] * 16, 32, 8),          # C2 shape, smaller batch
@@ -68,7 +69,8 @@ def test_batch_decode_matches_reference_kernel(ref, layout, q_dtype, kv_dtype, k
 
     d, page = 128, 16
     cache, indptr, indices, last = make_paged_case(kv_lens, hkv, d, page, layout, torch.float32, seed=7)
-    if kv_dtype == torch.float8_e4m3fn:
+    is8 = kv_dtype in (torch.float8_e4m3fn, torch.float8_e5m2)
+    if is8:
         cache = cache * 0.5
     cache = cache.to(kv_dtype).to(DEV)
     q = make_q(len(kv_lens), hq, d, q_dtype, seed=8).to(DEV)
@@ -78,7 +80,7 @@ def test_batch_decode_matches_reference_kernel(ref, layout, q_dtype, kv_dtype, k
     w = fi.BatchDecodeWithPagedKVCacheWrapper(torch.zeros(128 << 20, dtype=torch.uint8, device=DEV), layout)
     w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=q_dtype, kv_data_type=kv_dtype)
     o, lse = w.run(q, cache, return_lse=True)
-    tol = 3e-2 if kv_dtype == torch.float8_e4m3fn else 1e-2
+    tol = 3e-2 if is8 else 1e-2
     # both sides are rounded to q's dtype: two correctly-rounded bf16 values of magnitude >= 2
     # may differ by one ulp (2^-7 relative = 0.0156 at 2..4), so allow one ulp on top of the gate
     ulp = 2.0 ** -7 if q_dtype == torch.bfloat16 else 2.0 ** -10
