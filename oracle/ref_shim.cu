@@ -94,19 +94,24 @@ struct BatchArgs {
   int64_t* info_out;  // 10 x int64 DecodePlanInfo + [10] = launches (1 or 2)
   int mode;           // 0 plan + run, 1 plan only (kept for later runs), 2 run with the kept plan
   float rope_rcp_scale = 1.f, rope_rcp_theta = 1e-4f;  // read by the ROPE_LLAMA instantiation only
+  // read by the logits-transform instantiations only (ref_batch_decode_variant)
+  int32_t window_left = -1;
+  float logits_soft_cap = 0.f;
+  float* alibi_slopes = nullptr;
 };
 
 thread_local DecodePlanInfo g_plan;  // the reference keeps this in its Python wrapper between run()s
 
-template <typename Q, typename KV, uint32_t HD, PosEncodingMode POS = PosEncodingMode::kNone>
+template <typename Q, typename KV, uint32_t HD, PosEncodingMode POS = PosEncodingMode::kNone,
+          typename VAR = Variant>
 int batch_impl(const BatchArgs& a) {
   using P = BatchParams<Q, KV>;
   DecodePlanInfo& info = g_plan;
   cudaError_t st = cudaSuccess;
   bool ok = a.mode == 2;
   if (a.mode != 2) DISPATCH_GQA_GROUP_SIZE(a.hq / a.hkv, GROUP_SIZE, {
-    auto est = BatchDecodeWithPagedKVCacheWorkEstimationDispatched<GROUP_SIZE, HD, POS, Variant, P>;
-    st = DecodePlan<HD, POS, Variant, P>(a.float_ws, a.float_bytes, a.int_ws,
+    auto est = BatchDecodeWithPagedKVCacheWorkEstimationDispatched<GROUP_SIZE, HD, POS, VAR, P>;
+    st = DecodePlan<HD, POS, VAR, P>(a.float_ws, a.float_bytes, a.int_ws,
                                                             a.pinned_ws, a.int_bytes, info, a.indptr_h,
                                                             a.bs, a.hq, a.page_size, a.cuda_graph != 0,
                                                             a.stream, est);
@@ -123,8 +128,8 @@ int batch_impl(const BatchArgs& a) {
   p.paged_kv = kv;
   p.o = static_cast<Q*>(a.o);
   p.lse = a.lse;
-  p.maybe_alibi_slopes = nullptr;
-  p.logits_soft_cap = 0.f;
+  p.maybe_alibi_slopes = a.alibi_slopes;
+  p.logits_soft_cap = a.logits_soft_cap;
   p.sm_scale = a.sm_scale;
   p.rope_rcp_scale = a.rope_rcp_scale;
   p.rope_rcp_theta = a.rope_rcp_theta;
@@ -132,7 +137,7 @@ int batch_impl(const BatchArgs& a) {
   p.num_qo_heads = a.hq;
   p.q_stride_n = a.q_stride_n;
   p.q_stride_h = a.q_stride_h;
-  p.window_left = -1;
+  p.window_left = a.window_left;
   p.enable_pdl = false;
   char* ib = static_cast<char*>(a.int_ws);
   p.request_indices = reinterpret_cast<int32_t*>(ib + info.request_indices_offset);
@@ -149,7 +154,7 @@ int batch_impl(const BatchArgs& a) {
     if (info.enable_cuda_graph)
       p.block_valid_mask = reinterpret_cast<bool*>(ib + info.block_valid_mask_offset);
   }
-  st = BatchDecodeWithPagedKVCacheDispatched<HD, POS, Variant>(p, tmp_v, tmp_s, false, a.stream);
+  st = BatchDecodeWithPagedKVCacheDispatched<HD, POS, VAR>(p, tmp_v, tmp_s, false, a.stream);
   if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
   if (a.info_out) {
     auto v = info.ToVector();
@@ -274,6 +279,35 @@ __attribute__((visibility("default"))) int ref_batch_decode_rope(
     if (q_dtype == 1 && kv_dtype == 1)
       return batch_impl<nv_bfloat16, nv_bfloat16, 128, PosEncodingMode::kRoPELlama>(a);
     g_err = "ROPE_LLAMA shim: 16-bit KV only";
+    return 4;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return 2;
+  }
+}
+
+// logits transforms of DefaultAttention (variants.cuh:31-93), f16 q / kv, head_dim 128:
+// variant 1 = sliding window + logits soft cap, variant 2 = ALiBi
+__attribute__((visibility("default"))) int ref_batch_decode_variant(
+    void* float_ws, size_t float_bytes, void* int_ws, void* pinned_ws, size_t int_bytes,
+    int32_t* indptr_h, int bs, int hq, int hkv, int page_size, int layout, void* q, int64_t q_stride_n,
+    int64_t q_stride_h, void* k, void* v, int64_t s0, int64_t s1, int64_t s2, int32_t* indices,
+    int32_t* indptr, int32_t* last_page_len, void* o, float* lse, float sm_scale, int variant,
+    int window_left, float logits_soft_cap, float* alibi_slopes, void* stream) {
+  BatchArgs a{float_ws, int_ws, pinned_ws, float_bytes, int_bytes, indptr_h, bs, hq, hkv, page_size,
+              layout, 0, q, k, v, o, lse, q_stride_n, q_stride_h, {s0, s1, s2}, indices,
+              indptr, last_page_len, sm_scale, static_cast<cudaStream_t>(stream), nullptr, 0};
+  a.window_left = window_left;
+  a.logits_soft_cap = logits_soft_cap;
+  a.alibi_slopes = alibi_slopes;
+  try {
+    if (variant == 1)
+      return batch_impl<half, half, 128, PosEncodingMode::kNone,
+                        DefaultAttention<false, /*swa=*/true, /*softcap=*/true, false>>(a);
+    if (variant == 2)
+      return batch_impl<half, half, 128, PosEncodingMode::kALiBi,
+                        DefaultAttention<false, false, false, /*alibi=*/true>>(a);
+    g_err = "unknown variant";
     return 4;
   } catch (const std::exception& e) {
     g_err = e.what();

@@ -116,6 +116,54 @@ def test_batch_decode_head_dims_match_reference_kernel(ref, head_dim, layout, dt
     assert (lse - lse_ref).abs().max().item() <= 1e-3
 
 
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("variant", ["window+softcap", "alibi"])
+def test_logits_variants_match_reference_kernel(ref, layout, variant):
+    """sliding window + logits soft cap, and ALiBi, against the reference's own
+    kernel instantiated with the corresponding DefaultAttention variant (variants.cuh:31-93)."""
+    import flashinfer_b200 as fi
+    from flashinfer_b200.utils import get_alibi_slopes
+
+    if not hasattr(ref, "ref_batch_decode_variant"):
+        pytest.skip("prebuilt checker predates the variant instantiations")
+    d, page, hq, hkv = 128, 16, 32, 8
+    kv_lens = [1, 54, 97, 512, 2048, 33, 64, 65, 5000, 1000, 17, 3]
+    dtype = torch.float16
+    cache, indptr, indices, last = make_paged_case(kv_lens, hkv, d, page, layout, torch.float32, seed=37)
+    cache = cache.to(dtype).to(DEV)
+    q = make_q(len(kv_lens), hq, d, dtype, seed=38).to(DEV)
+    sm_scale = 1.0 / d ** 0.5
+    window_left, soft_cap = (300, 30.0) if variant == "window+softcap" else (-1, 0.0)
+    slopes = get_alibi_slopes(hq).to(DEV) if variant == "alibi" else None
+    k, v = cache[:, 0], cache[:, 1]
+    fws = torch.zeros(128 << 20, dtype=torch.uint8, device=DEV)
+    iws = torch.zeros(8 << 20, dtype=torch.uint8, device=DEV)
+    pws = torch.zeros(8 << 20, dtype=torch.uint8).pin_memory()
+    o_ref = torch.empty_like(q)
+    lse_ref = torch.empty(len(kv_lens), hq, dtype=torch.float32, device=DEV)
+    ip_d, ix_d, lp_d = indptr.to(DEV), indices.to(DEV), last.to(DEV)
+    vp = C.c_void_p
+    rc = ref.ref_batch_decode_variant(
+        vp(fws.data_ptr()), C.c_size_t(fws.numel()), vp(iws.data_ptr()), vp(pws.data_ptr()),
+        C.c_size_t(iws.numel()), vp(indptr.contiguous().data_ptr()), len(kv_lens), hq, hkv, page,
+        0 if layout == "NHD" else 1, vp(q.data_ptr()), C.c_int64(q.stride(0)), C.c_int64(q.stride(1)),
+        vp(k.data_ptr()), vp(v.data_ptr()), C.c_int64(k.stride(0)), C.c_int64(k.stride(1)),
+        C.c_int64(k.stride(2)), vp(ix_d.data_ptr()), vp(ip_d.data_ptr()), vp(lp_d.data_ptr()),
+        vp(o_ref.data_ptr()), vp(lse_ref.data_ptr()), C.c_float(sm_scale),
+        1 if variant == "window+softcap" else 2, window_left, C.c_float(soft_cap),
+        vp(slopes.data_ptr()) if slopes is not None else None,
+        vp(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, ref.ref_last_error()
+    torch.cuda.synchronize()
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(torch.zeros(128 << 20, dtype=torch.uint8, device=DEV), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=dtype,
+           pos_encoding_mode="ALIBI" if variant == "alibi" else "NONE",
+           window_left=window_left, logits_soft_cap=soft_cap or None)
+    o, lse = w.run(q, cache, return_lse=True)
+    torch.testing.assert_close(o.float(), o_ref.float(), atol=1e-2, rtol=2.0 ** -10)
+    assert (lse - lse_ref).abs().max().item() <= 1e-3
+
+
 def ref_batch_decode_rope(ref, q, cache, indptr, indices, last, hq, hkv, page, layout, sm_scale,
                           rope_scale, rope_theta):
     bs, d = q.shape[0], q.shape[2]
