@@ -633,3 +633,29 @@ def test_attention_sinks_against_reference_golden(name):
     w.plan(indptr, indices, last, Hq, Hkv, D, page, q_data_type=dt, window_left=win)
     o = w.run(q.to(DEV), cache.to(DEV), sinks=sink.to(DEV))
     assert (o.float().cpu() - o_gold.float()).abs().max().item() <= O_TOL
+
+
+@pytest.mark.parametrize("switches", [
+    {"FI_B200_FUSED_MERGE": "0"},                              # split-KV merge as a second launch
+    {"FI_B200_FP8_TC5": "0", "FI_B200_L2_HINTS": "0"},         # fp8 on the register path, no L2 hints
+    {"FI_B200_HEAD_GROUP": "0", "FI_B200_PDL_LATE": "1"},      # request-major order, late PDL trigger
+    {"FI_B200_ROPE_CUDA_CORE": "1"},                           # RoPE on the CUDA-core variant kernel
+])
+def test_ab_switches_keep_parity(switches):
+    """The A/B switches of DESIGN.md §6b select older / alternative code paths that stay in the library;
+    most are read once per process, so the parity tests run again in a child process with each set."""
+    import os
+    import subprocess
+    import sys
+
+    if os.environ.get("FI_B200_TEST_CHILD") == "1":
+        pytest.skip("already inside the child run")
+    env = dict(os.environ, FI_B200_TEST_CHILD="1", **switches)
+    sel = ("test_batch_decode_minimum_slice or test_empty_request_regression or test_batch_decode_fp8_kv or "
+           "test_split_kv_long_single_request_and_determinism or test_cuda_graph_replay_with_replan or "
+           "test_batch_decode_rope or test_attention_sinks or test_batch_decode_large_gqa_groups or "
+           "test_window_left_and_soft_cap")
+    r = subprocess.run([sys.executable, "-m", "pytest", __file__, "-x", "-q", "-m", "gpu", "-k", sel],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
