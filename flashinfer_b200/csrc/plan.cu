@@ -236,7 +236,30 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   // streams faster (HBM / L2 arbitration is not uniform across the two dies) ends up with
   // more of the tail instead of idling.  f0 = 100 reproduces the static equal split.
   const SchedTuning st = sched_tuning();
-  const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 4;
+  // smallest item: 2 tiles (a bs = 1, kv 2048 decode takes 8.7 us with 2-tile items, 10.2 us with 4)
+  const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 2;
+  // Uniform batches (every non-empty request has the same tile count n_u): a chunk that divides n_u
+  // — or is a multiple of it — keeps every CTA inside one unit, i.e. one segment epilogue per CTA
+  // and no unit cut in odd places; taken when it costs at most 1/8 more tiles per CTA
+  // (bs 4 x kv 4096: 296 items of 7 tiles 18.6 us -> 256 items of 8 tiles 15.9 us).
+  int64_t uniform_tiles = -1;
+  for (int b = 0; b < batch_size; ++b) {
+    if (ntile[b] == 0) continue;
+    if (uniform_tiles < 0) uniform_tiles = ntile[b];
+    else if (uniform_tiles != ntile[b]) { uniform_tiles = 0; break; }
+  }
+  auto align_chunk = [&](int64_t c0) -> int64_t {
+    const int64_t n_u = uniform_tiles;
+    if (n_u <= 0 || indivisible || st.f0_pct < 100 || c0 <= 0) return c0;
+    const int64_t hi = c0 + std::max<int64_t>(1, c0 / 8);
+    if (c0 >= n_u) {
+      const int64_t c = (c0 + n_u - 1) / n_u * n_u;
+      return c <= hi ? c : c0;
+    }
+    for (int64_t c = c0; c <= hi; ++c)
+      if (n_u % c == 0) return c;
+    return c0;
+  };
   static thread_local std::vector<int64_t> item_end;  // exclusive end (stream position) of every item
   item_end.clear();
   {
@@ -248,6 +271,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
                             : (rem * st.g_pct + 100LL * num_ctas - 1) / (100LL * num_ctas);
       if (first && (st.f0_pct >= 100 || indivisible)) chunk = (total_tiles + num_ctas - 1) / num_ctas;
       chunk = std::max<int64_t>(chunk, first ? min_tiles : st.tail_tiles);
+      if (first) chunk = align_chunk(chunk);
       for (int i = 0; i < num_ctas && pos < total_tiles; ++i) {
         pos = std::min(total_tiles, pos + chunk);
         item_end.push_back(pos);
@@ -265,7 +289,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   int64_t hg_chunk = 0, hg_groups = 0;
   if (head_group) {
     const int64_t tr = total_tiles / num_kv_heads, groups = num_ctas / num_kv_heads;
-    hg_chunk = std::max<int64_t>((tr + groups - 1) / groups, min_tiles);
+    hg_chunk = align_chunk(std::max<int64_t>((tr + groups - 1) / groups, min_tiles));
     hg_groups = (tr + hg_chunk - 1) / hg_chunk;
     item_end.assign((size_t)(hg_groups * num_kv_heads), 0);  // only the count is used below
   }

@@ -104,6 +104,27 @@ def test_plan_head_groups_walk_the_same_request_ranges(monkeypatch):
         assert [sl for _, sl in mine] == list(range(sb, sb + cnt))
 
 
+def test_plan_uniform_batch_aligns_items_to_units():
+    """bs 4 x kv 4096, 8 KV heads (64 tiles per unit, 2048 tiles, 296 CTAs): 7-tile items would straddle
+    units; the planner takes 8-tile items instead — 256 items of exactly one segment each."""
+    kv_lens = [4096] * 4
+    indptr, last = lens_to_table(kv_lens, 16)
+    rc, err, plan = host_plan(indptr, last, 32, 8, 128, 16, 296)
+    assert rc == 0, err
+    replay_plan(plan, kv_lens, 8)
+    segs, iip = plan["segments"], plan["item_indptr"]
+    assert len(iip) - 1 == 256
+    assert all(iip[i + 1] - iip[i] == 1 for i in range(256))
+    assert all(int(s[3] - s[2]) == 8 for s in segs)
+    # many short requests: an item holds whole units (5 requests of 2 tiles -> 10-tile items, not 9 or 11)
+    kv_lens = [128] * 1480
+    indptr, last = lens_to_table(kv_lens, 16)
+    rc, err, plan = host_plan(indptr, last, 8, 1, 128, 16, 296)
+    assert rc == 0, err
+    replay_plan(plan, kv_lens, 1)
+    assert len(plan["merges"]) == 0
+
+
 def test_plan_fp8_tiles_are_128_tokens():
     kv_lens = [8192] * 16 + [1, 127, 128, 129, 5000]
     indptr, last = lens_to_table(kv_lens, 16)
