@@ -240,8 +240,9 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   const int min_tiles = tuning().min_tiles_per_cta > 0 ? tuning().min_tiles_per_cta : 2;
   // Uniform batches (every non-empty request has the same tile count n_u): a chunk that divides n_u
   // — or is a multiple of it — keeps every CTA inside one unit, i.e. one segment epilogue per CTA
-  // and no unit cut in odd places; taken when it costs at most 1/8 more tiles per CTA
-  // (bs 4 x kv 4096: 296 items of 7 tiles 18.6 us -> 256 items of 8 tiles 15.9 us).
+  // and no unit cut in odd places; taken when it costs at most 1/6 more tiles per CTA
+  // (bs 4 x kv 4096: 296 items of 7 tiles 18.6 us -> 256 items of 8 tiles 15.9 us; 8-way per-rank
+  // C2: 293 items of 14 tiles 27.3 us -> 256 items of 16 tiles 25.6 us; per-rank C3 53.0 -> 50.8 us).
   int64_t uniform_tiles = -1;
   for (int b = 0; b < batch_size; ++b) {
     if (ntile[b] == 0) continue;
@@ -251,7 +252,8 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   auto align_chunk = [&](int64_t c0) -> int64_t {
     const int64_t n_u = uniform_tiles;
     if (n_u <= 0 || indivisible || st.f0_pct < 100 || c0 <= 0) return c0;
-    const int64_t hi = c0 + std::max<int64_t>(1, c0 / 8);
+    static const int den = env_int("FI_B200_ALIGN_DEN", 6, 1, 1 << 20);  // A/B: 1000 = never align
+    const int64_t hi = c0 + std::max<int64_t>(1, c0 / den);
     if (c0 >= n_u) {
       const int64_t c = (c0 + n_u - 1) / n_u * n_u;
       return c <= hi ? c : c0;
