@@ -172,6 +172,8 @@ def test_full_size_split_consistency_and_plan_independence(name):
 
     # a plan that never cuts a unit (different work list, no partials, no merge)
     o3, l3, w3 = _decode(cache, q, indptr, indices, last, hq, hkv, kv_dtype, scales, disable_split_kv=True)
-    assert int(w3._plan_info[3]) == 0 and int(w._plan_info[3]) > 0
+    assert int(w3._plan_info[3]) == 0
+    if name == "c4":  # the uniform C2 / C3 plans hold whole requests per head group: nothing to merge either
+        assert int(w._plan_info[3]) > 0
     assert (o3.float() - o.float()).abs().max().item() <= tol
     assert (l3 - lse).abs().max().item() <= 1e-3
