@@ -44,6 +44,8 @@ PROTOTYPES = {
     "fi_single_decode_run": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,
                                   _i, _f, _f, _f, _i, _vp, _f, _f, _i, _vp]),
     "fi_single_decode_tmp_bytes": (_sz, [_i, _i, _i, _i]),
+    "fi_single_decode_run_static": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,
+                                         _i, _f, _f, _f, _i, _vp, _f, _f, _i, _vp]),
     "fi_merge_state": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "fi_merge_state_in_place": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "fi_merge_states": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),

@@ -552,3 +552,54 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
 }
 
 }  // extern "C"
+
+// ---- allocation-free single decode (no reference counterpart; see fi_b200.h) -------------------
+// The split-KV partials of fi_single_decode_run_static live in this file-scope array.  In host code
+// `g_fi_static_tmp` is only a stand-in for the symbol, not a device address: the pointer the
+// kernels get comes from cudaGetSymbolAddress, taken once per device with that device current.
+static __device__ __align__(256) unsigned char g_fi_static_tmp[FI_SINGLE_DECODE_STATIC_TMP_BYTES];
+
+namespace fib200 {
+static int static_tmp_address(int device, void** out) {
+  static std::mutex mu;
+  static void* addr[64];
+  if (device < 0 || device >= 64) return fail(FI_ERR_INVALID_ARGUMENT, "bad device %d", device);
+  std::lock_guard<std::mutex> lk(mu);
+  if (addr[device] == nullptr) {
+    FI_CUDA_TRY(cudaSetDevice(device));
+    void* p = nullptr;
+    FI_CUDA_TRY(cudaGetSymbolAddress(&p, g_fi_static_tmp));
+    if (p == nullptr) return fail(FI_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+    addr[device] = p;
+  }
+  *out = addr[device];
+  return FI_OK;
+}
+}  // namespace fib200
+
+extern "C" int fi_single_decode_run_static(const void* q, const void* k, const void* v, void* o,
+                                           float* lse, int num_qo_heads, int num_kv_heads,
+                                           int head_dim, int kv_len, int q_dtype, int kv_dtype,
+                                           int kv_layout, int window_left, float sm_scale,
+                                           float v_scale, float logits_soft_cap,
+                                           int pos_encoding_mode, const float* alibi_slopes,
+                                           float rope_scale, float rope_theta, int device,
+                                           void* stream) {
+  if (num_kv_heads <= 0 || num_qo_heads <= 0 || num_qo_heads % num_kv_heads)
+    return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads must be a multiple of num_kv_heads");
+  const size_t need = fi_single_decode_tmp_bytes(num_qo_heads, num_kv_heads, head_dim, device);
+  if (need > (size_t)FI_SINGLE_DECODE_STATIC_TMP_BYTES)
+    return fail(FI_ERR_WORKSPACE,
+                "fi_single_decode_run_static: %d/%d heads at head_dim %d need %zu bytes of scratch, the "
+                "static array holds %zu (FI_SINGLE_DECODE_STATIC_TMP_BYTES); use fi_single_decode_run "
+                "with a caller-owned tmp buffer",
+                num_qo_heads, num_kv_heads, head_dim, need, (size_t)FI_SINGLE_DECODE_STATIC_TMP_BYTES);
+  void* tmp = nullptr;
+  if (int rc = static_tmp_address(device, &tmp)) return rc;
+  // nothing in the scratch has to start at zero (every partial slot is written by the decode launch
+  // before the merge launch reads it), so the previous call's contents are simply overwritten
+  return fi_single_decode_run(q, k, v, tmp, (size_t)FI_SINGLE_DECODE_STATIC_TMP_BYTES, o, lse,
+                              num_qo_heads, num_kv_heads, head_dim, kv_len, q_dtype, kv_dtype,
+                              kv_layout, window_left, sm_scale, v_scale, logits_soft_cap,
+                              pos_encoding_mode, alibi_slopes, rope_scale, rope_theta, device, stream);
+}

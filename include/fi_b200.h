@@ -185,6 +185,31 @@ FI_API size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int
                                   int device);
 
 /*
+ * fi_single_decode_run_static — fi_single_decode_run without the caller's `tmp`.
+ * No counterpart in the reference: added for callers
+ * that cannot allocate device memory (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  The split-KV partials go to a file-scope `static __device__` array of
+ * FI_SINGLE_DECODE_STATIC_TMP_BYTES inside the library (every GPU that loads the library holds
+ * it until the process exits); its address is taken with cudaGetSymbolAddress once per device.
+ * The call allocates nothing: no cudaMalloc / cudaFree / allocating library routine.
+ *  - shapes whose scratch need (fi_single_decode_tmp_bytes) exceeds the array are rejected with
+ *    FI_ERR_WORKSPACE and a message naming both sizes;
+ *  - every call on a device shares the one array, which keeps the previous call's contents
+ *    (nothing in it has to start at zero: each launch writes every partial slot before its merge
+ *    reads it); calls that overlap on the GPU (two streams, or two host threads) race on it —
+ *    serialise them on one stream.
+ * All other arguments as fi_single_decode_run.
+ */
+#define FI_SINGLE_DECODE_STATIC_TMP_BYTES (4u << 20)
+FI_API int fi_single_decode_run_static(const void* q, const void* k, const void* v, void* o,
+                                float* lse, int num_qo_heads, int num_kv_heads, int head_dim,
+                                int kv_len, int q_dtype, int kv_dtype, int kv_layout,
+                                int window_left, float sm_scale, float v_scale,
+                                float logits_soft_cap, int pos_encoding_mode,
+                                const float* alibi_slopes, float rope_scale, float rope_theta,
+                                int device, void* stream);
+
+/*
  * State-merge operators.  Replaces csrc/cascade.cu:23 / :59 / :102 ->
  * MergeState / MergeStateInPlace / MergeStates
  * (include/flashinfer/attention/cascade.cuh:573 / :605 / :638).
