@@ -101,6 +101,10 @@ struct BatchArgs {
 };
 
 thread_local DecodePlanInfo g_plan;  // the reference keeps this in its Python wrapper between run()s
+// Programmatic dependent launch: the reference's wrapper defaults enable_pdl to
+// device_support_pdl(q.device), i.e. ON for sm_90+ (flashinfer/decode.py:1226-1227); the launch
+// path is decode.cuh:775-821.  ref_set_pdl(0) switches it off for A/B runs.
+int g_enable_pdl = 1;
 
 template <typename Q, typename KV, uint32_t HD, PosEncodingMode POS = PosEncodingMode::kNone,
           typename VAR = Variant>
@@ -138,7 +142,7 @@ int batch_impl(const BatchArgs& a) {
   p.q_stride_n = a.q_stride_n;
   p.q_stride_h = a.q_stride_h;
   p.window_left = a.window_left;
-  p.enable_pdl = false;
+  p.enable_pdl = g_enable_pdl != 0;
   char* ib = static_cast<char*>(a.int_ws);
   p.request_indices = reinterpret_cast<int32_t*>(ib + info.request_indices_offset);
   p.kv_tile_indices = reinterpret_cast<int32_t*>(ib + info.kv_tile_indices_offset);
@@ -154,7 +158,7 @@ int batch_impl(const BatchArgs& a) {
     if (info.enable_cuda_graph)
       p.block_valid_mask = reinterpret_cast<bool*>(ib + info.block_valid_mask_offset);
   }
-  st = BatchDecodeWithPagedKVCacheDispatched<HD, POS, VAR>(p, tmp_v, tmp_s, false, a.stream);
+  st = BatchDecodeWithPagedKVCacheDispatched<HD, POS, VAR>(p, tmp_v, tmp_s, g_enable_pdl != 0, a.stream);
   if (st != cudaSuccess) { g_err = cudaGetErrorString(st); return 3; }
   if (a.info_out) {
     auto v = info.ToVector();
@@ -208,6 +212,8 @@ using namespace refshim;
 extern "C" {
 
 __attribute__((visibility("default"))) const char* ref_last_error() { return g_err.c_str(); }
+__attribute__((visibility("default"))) void ref_set_pdl(int on) { g_enable_pdl = on; }
+__attribute__((visibility("default"))) int ref_get_pdl() { return g_enable_pdl; }
 
 // plan (reference DecodePlan) + run (reference kernel [+ reference merge]); head_dim 128 only
 __attribute__((visibility("default"))) int ref_batch_decode(
