@@ -52,6 +52,7 @@ PROTOTYPES = {
     "fi_variable_length_merge_states": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f,
                                              _i, _vp]),
     "fi_get_batch_indices_positions": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "fi_peer_gather": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i64, _i64, _i64, _i64, C.c_uint32, _i, _i, _vp]),
     "fi_append_paged_kv_cache": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _i64, _vp, _vp,
                                       _i64, _i64, _i64, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
 }

@@ -18,7 +18,7 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 OUT = HERE / "libfi_b200.so"
 OBJ = HERE / "build"
-SOURCES = ["plan.cu", "decode.cu", "merge.cu", "page.cu"]
+SOURCES = ["plan.cu", "decode.cu", "merge.cu", "page.cu", "gather.cu"]
 NVCC = os.environ.get("FI_B200_NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-std=c++17", "-O3", "-lineinfo", "--expt-relaxed-constexpr",

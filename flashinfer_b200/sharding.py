@@ -7,11 +7,16 @@ output heads (what a tensor-parallel layer feeds to its row-parallel o_proj anyw
 stacks usually skip even that).  The reference has no multi-GPU decode path of its own
 (SURVEY.md §8e): frameworks on top of it shard exactly like this.
 
-Everything here is host-side index arithmetic plus one torch.distributed collective; it runs
-unchanged on the gloo backend with CPU tensors, which is how tests/test_sharding.py covers it.
+Everything up to `gather_heads` is host-side index arithmetic plus one torch.distributed collective;
+it runs unchanged on the gloo backend with CPU tensors, which is how tests/test_sharding.py covers it.
+`PeerGather` is the NVLink-native form of that collective: one kernel of libfi_b200.so
+(csrc/gather.cu), chained to the decode launch, that stores the rank's heads straight into every
+rank's [bs, Hq, D] buffer (NVLS multicast or peer-mapped stores) and returns when all ranks' heads
+have arrived — no NCCL call, no transpose copy, no allocation per call.
 """
 from __future__ import annotations
 
+import ctypes as C
 from dataclasses import dataclass
 from typing import Optional, Tuple, Union
 
@@ -99,3 +104,81 @@ def gather_heads(o_local: torch.Tensor, world: int, group: Optional[dist.Process
         out.copy_(res)
         return out
     return res
+
+
+class PeerGather:
+    """Peer-write gather of the output heads: `gather(o_local)` returns this rank's `[bs, Hq, D]`
+    view holding every rank's heads, in rank (= head) order, exactly what `gather_heads` returns.
+
+    Set-up (once): two symmetric `[bs, Hq, D]` buffers (ping-pong by call parity) and a 256-byte
+    control block per rank, allocated with torch's symmetric memory (CUDA VMM handles exchanged over
+    the process group's store) so that every rank has every rank's buffers mapped, plus the NVLS
+    multicast address when the fabric offers one.  Per call: ONE launch of `fi_peer_gather` on the
+    current stream (programmatic dependent launch after the decode kernel), no host synchronisation.
+
+    Why two buffers are enough: a rank starts call t + 2 (which overwrites the buffer of call t) only
+    after its call t + 1 completed, and that needed every rank's flag for t + 1, which a rank raises
+    from a kernel that follows — in its stream — whatever consumed the result of call t.  Callers
+    that read the returned view from ANOTHER stream must order that read before their next-but-one
+    `gather` themselves.  The returned tensor is a view of library-owned memory: copy it if it must
+    outlive the next-but-one call."""
+
+    def __init__(self, full_shape, dtype: torch.dtype, device: torch.device, shard: HeadShard,
+                 group: Optional[dist.ProcessGroup] = None, use_multicast: Optional[bool] = None):
+        import os
+
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from . import _lib
+
+        if not torch.device(device).type == "cuda":
+            raise ValueError("PeerGather needs CUDA tensors (use gather_heads on the CPU)")
+        if shard.world > 16:
+            raise ValueError("PeerGather supports at most 16 ranks")
+        bs, hq, d = full_shape
+        if hq != shard.num_qo_heads * shard.world:
+            raise ValueError("full_shape[1] must be world * heads per rank")
+        self.shard, self.dtype, self.device = shard, dtype, torch.device(device)
+        self.full_shape = (bs, hq, d)
+        self._lib, self._check = _lib.load(), _lib.check
+        grp = group if group is not None else dist.group.WORLD
+        self._buf = symm_mem.empty((2, bs, hq, d), dtype=dtype, device=self.device)
+        self._ctl = symm_mem.empty((64,), dtype=torch.int32, device=self.device)
+        self._ctl.zero_()
+        torch.cuda.synchronize(self.device)
+        self._hbuf = symm_mem.rendezvous(self._buf, grp)
+        self._hctl = symm_mem.rendezvous(self._ctl, grp)
+        self._hctl.barrier()  # every rank's control block is zero before anybody's first flag
+        world = shard.world
+        half = bs * hq * d * self._buf.element_size()
+        self._dst = [(C.c_void_p * world)(*[int(p) + k * half for p in self._hbuf.buffer_ptrs]) for k in (0, 1)]
+        self._ctl_ptrs = (C.c_void_p * world)(*[int(p) for p in self._hctl.buffer_ptrs])
+        if use_multicast is None:
+            use_multicast = os.environ.get("FI_B200_GATHER_MULTICAST", "1") != "0"
+        mc = int(getattr(self._hbuf, "multicast_ptr", 0) or 0) if use_multicast else 0
+        self._mc = [mc + k * half if mc else None for k in (0, 1)]
+        self.transport = "nvls multicast (multimem.st)" if mc else "peer-mapped stores (P2P)"
+        self._row_bytes = shard.num_qo_heads * d * self._buf.element_size()
+        self._stride = hq * d * self._buf.element_size()
+        self._epoch = 0
+        self._dev_idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+
+    def gather(self, o_local: torch.Tensor, enable_pdl: bool = True) -> torch.Tensor:
+        from .utils import current_stream_ptr
+
+        bs, hq, d = self.full_shape
+        if tuple(o_local.shape) != (bs, self.shard.num_qo_heads, d) or o_local.dtype != self.dtype:
+            raise ValueError(f"o_local must be [{bs}, {self.shard.num_qo_heads}, {d}] {self.dtype}")
+        if not o_local.is_contiguous():
+            raise ValueError("o_local must be contiguous")
+        self._epoch += 1
+        k = self._epoch & 1
+        self._check(self._lib.fi_peer_gather(
+            o_local.data_ptr(), self._dst[k], self._mc[k], self._ctl_ptrs, self.shard.world, self.shard.rank,
+            bs, self._row_bytes, self._stride, self.shard.rank * self._row_bytes,
+            self._epoch & 0xFFFFFFFF, int(bool(enable_pdl)), self._dev_idx, current_stream_ptr(self.device)))
+        return self._buf[k]
+
+    def status(self) -> int:
+        """0, or 1 + the rank whose flag a wait gave up on after 2 s (synchronises the device)."""
+        return int(self._ctl[33].item())

@@ -275,6 +275,30 @@ FI_API int fi_append_paged_kv_cache(const void* append_key, const void* append_v
                              const int32_t* kv_indices, const int32_t* kv_indptr, int num_kv_heads,
                              int head_dim, int page_size, int dtype, int device, void* stream);
 
+/* ---- multi-GPU: gather of the per-rank output heads over NVLink -------------------------- */
+/*
+ * fi_peer_gather — store this rank's rows into the gather buffer of EVERY rank and wait until every
+ * rank's rows have arrived in ours.  The reference's decode path has no multi-GPU step (frameworks on
+ * top of it all-gather O with NCCL); this replaces that all-gather + transpose for KV-head sharding
+ * (flashinfer_b200/sharding.py PeerGather; protocol studied in flashinfer/comm/cuda_ipc.py and
+ * flashinfer/comm/vllm_ar.py:105-155).
+ *  src              this rank's rows [rows, row_bytes] (e.g. o_local [bs, Hq/N, D]), device memory
+ *  peer_dst[world]  HOST array: rank p's destination buffer as mapped in this process (peer memory:
+ *                   CUDA IPC / symmetric memory); row r of this rank lands at
+ *                   peer_dst[p] + dst_offset_bytes + r * dst_row_stride_bytes
+ *  mc_dst           NVLS multicast address of the same buffer or NULL: when set (and everything is
+ *                   16-byte aligned) one multimem.st per chunk replaces the `world` unicast stores
+ *  peer_ctl[world]  HOST array: rank p's 256-byte control block as mapped here (zero at creation:
+ *                   uint32 flag[16], CTA counter, status word)
+ *  epoch            must grow by one per call on every rank (same value on all ranks for one gather)
+ * The kernel is chained to the preceding launch of `stream` with programmatic dependent launch when
+ * enable_pdl != 0.  A peer that never arrives makes the wait time out after 2 s (status word != 0).
+ */
+FI_API int fi_peer_gather(const void* src, void* const* peer_dst, void* mc_dst,
+                          void* const* peer_ctl, int world, int rank, int64_t rows,
+                          int64_t row_bytes, int64_t dst_row_stride_bytes, int64_t dst_offset_bytes,
+                          uint32_t epoch, int enable_pdl, int device, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

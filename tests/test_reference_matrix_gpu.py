@@ -7,10 +7,9 @@ caches (the `[:, 1, :, 1, :, 1, :, 1, :]` view of a 16x larger allocation) — a
 every request of the batch equals `single_decode_with_kv_cache` on its gathered K / V
 (rtol = atol = 1e-3 as the reference for 16-bit KV; fp8 KV runs the tcgen05 kernel in the batch and
 may split differently in the single call, so it is held to 1e-2), plus the user-allocated
-output buffer.  A sample of every case is also checked against the CPU oracle.
+output buffer.  Every sampled request is also anchored on the oracle's fp32 attention (independent of
+the kernels), o within 2e-3 + 2e-3 |o| for f16 KV and 1e-2 + 1e-2 |o| for e4m3 KV, lse within 1e-3.
 """
-import zlib
-
 import pytest
 import torch
 
@@ -24,6 +23,15 @@ def _fi():
     import flashinfer_b200 as fi
 
     return fi
+
+
+@pytest.fixture(autouse=True)
+def _release_big_blocks():
+    """The grid mixes 100 KB and 60 GB caches: hand cached blocks back between cases so that one
+    case's allocation pattern (or a failed case's traceback) cannot starve the next."""
+    yield
+    if torch.cuda.memory_reserved() > (8 << 30):
+        torch.cuda.empty_cache()
 
 
 def _make_cache(batch_size, kv_len, page_size, num_kv_heads, head_dim, kv_layout, kv_dtype, contiguous_kv):
@@ -81,14 +89,13 @@ def test_batch_decode_with_paged_kv_cache(batch_size, kv_len, page_size, num_kv_
                                           head_dim, kv_layout, pos_encoding_mode, kv_dtype, contiguous_kv):
     fi = _fi()
     q_dtype = torch.float16
+    # the whole grid (5760 cases) runs except where the reference's own construction — an fp32
+    # master copy, 16x larger still for the strided variant — does not fit next to its kv_dtype copy
+    # in the 180 GB of one B200 (about 4 % of the grid: strided caches of 128 x 16384 tokens, of
+    # 12 / 17 x 16384 tokens at head_dim 256 and of 128 x 2048 tokens at head_dim 256)
     elems = batch_size * kv_len * num_kv_heads * head_dim * 2 * (1 if contiguous_kv else 16)
-    if elems * 4 > (12 << 30):
-        pytest.skip("the fp32 master copy of this case does not fit the test budget")
-    # the whole grid is 5760 cases; keep every axis but thin the cross product deterministically
-    key = zlib.crc32(repr((batch_size, kv_len, page_size, num_qo_heads, head_dim, kv_layout,
-                           pos_encoding_mode, str(kv_dtype), contiguous_kv)).encode()) % 4
-    if key != 0 and not (batch_size == 12 and kv_len in (54, 2048)):
-        pytest.skip("thinned cross product (every axis value is still exercised)")
+    if elems * 4 > (40 << 30):
+        pytest.skip("the fp32 master copy of this strided case does not fit the GPU's memory")
     torch.manual_seed(42)
     q = torch.randn(batch_size, num_qo_heads, head_dim, device=DEV, dtype=q_dtype)
     kv_data, kv_data_fp32, kv_indptr, kv_indices, kv_last_page_len = _make_cache(
@@ -109,10 +116,17 @@ def test_batch_decode_with_paged_kv_cache(batch_size, kv_len, page_size, num_kv_
         o_ref_i = fi.single_decode_with_kv_cache(q[i], ki, vi, pos_encoding_mode=pos_encoding_mode,
                                                  logits_soft_cap=0.0)
         torch.testing.assert_close(o[i], o_ref_i, rtol=tol, atol=tol)
-    # anchor on the CPU oracle (request 0)
+    # anchor EVERY sampled request on the oracle's fp32 attention (evaluated on the GPU, TF32 off;
+    # request 0 also on the CPU): the batch == single check above shares kernels and math
+    rope = (1.0, 1e4) if pos_encoding_mode == "ROPE_LLAMA" else None
+    for i in sorted({0, 1, batch_size // 2, batch_size - 1}):
+        ki, vi = _request_kv(kv_data_fp32, ip, lp, i, kv_layout, num_kv_heads, head_dim, kv_dtype)
+        oi, lsei = orc.decode_attention_ref(q[i].float(), ki.float(), vi.float(), rope=rope)
+        excess = (o[i].float() - oi).abs() - ((1e-2 + 1e-2 * oi.abs()) if is8 else (2e-3 + 2e-3 * oi.abs()))
+        assert excess.max().item() <= 0.0, (i, excess.max().item())
+        assert (lse[i] - lsei).abs().max().item() <= 1e-3
     ki, vi = _request_kv(kv_data_fp32, ip, lp, 0, kv_layout, num_kv_heads, head_dim, kv_dtype)
-    o0, lse0 = orc.decode_attention_ref(q[0].cpu(), ki.float().cpu(), vi.float().cpu(),
-                                        rope=(1.0, 1e4) if pos_encoding_mode == "ROPE_LLAMA" else None)
+    o0, lse0 = orc.decode_attention_ref(q[0].cpu(), ki.float().cpu(), vi.float().cpu(), rope=rope)
     assert (o[0].float().cpu() - o0).abs().max().item() <= (3e-2 if is8 else 1e-2)
     assert (lse[0].cpu() - lse0).abs().max().item() <= 1e-3
 

@@ -1,0 +1,239 @@
+"""GPU: the remaining decode tests of the reference, ported with their full parameter grids.
+
+* CUDA-graph capture with re-plans across DIFFERENT kv lengths between replays
+  (tests/attention/test_batch_decode_kernels.py:492-676);
+* packed-QKV strided q at page sizes 1 / 5 and 1 / 4 / 8 KV heads, head_dim 64 / 128 / 256
+  (tests/attention/test_non_contiguous_decode.py:36-118);
+* fp8 calibration scales, e4m3 and e5m2, NHD and HND, NONE and ROPE_LLAMA, single and batch
+  (tests/attention/test_decode_fp8_calibration_scale.py:23-153).
+
+Where the reference compares two of its own paths (batch vs single, packed vs contiguous, fp8 vs
+fp16), the port keeps that check and adds an independent anchor: the oracle's fp32 PyTorch
+attention (oracle/attention_ref.py, evaluated on the GPU for speed, TF32 off) on the sampled
+requests, at the north-star gates or tighter.
+"""
+import pytest
+import torch
+
+from oracle import attention_ref as orc
+from test_reference_matrix_gpu import _make_cache, _request_kv
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _fi():
+    import flashinfer_b200 as fi
+
+    return fi
+
+
+@pytest.fixture(autouse=True)
+def _release_big_blocks():
+    yield
+    if torch.cuda.memory_reserved() > (8 << 30):
+        torch.cuda.empty_cache()
+
+
+def _close(o, o_orc, atol, rtol):
+    """|o - oracle| <= atol + rtol |oracle| elementwise; returns the worst excess for the message."""
+    d = (o.float() - o_orc).abs() - (atol + rtol * o_orc.abs())
+    return d.max().item() <= 0.0, d.max().item()
+
+
+# gates vs the fp32 oracle (north star: 1e-2 flat for 16-bit KV, 3e-2 for fp8 KV): an f16 output
+# carries half an ulp of its own magnitude plus the f16 rounding of the probabilities
+F16_GATE = dict(atol=2e-3, rtol=2e-3)
+FP8_GATE = dict(atol=1e-2, rtol=1e-2)
+
+
+def _oracle_gpu(q_i, k_i, v_i, rope=False, k_scale=1.0, v_scale=1.0):
+    """fp32 oracle attention of one request on the GPU: (o [Hq, D], lse2 [Hq])."""
+    d = q_i.shape[-1]
+    o, lse = orc.decode_attention_ref(q_i.float(), k_i.float(), v_i.float(), sm_scale=k_scale / d ** 0.5,
+                                      rope=(1.0, 1e4) if rope else None)
+    return o * v_scale, lse
+
+
+@pytest.mark.parametrize("batch_size", [12, 17, 128])
+@pytest.mark.parametrize("kv_len", [54, 2048, 16384])
+@pytest.mark.parametrize("page_size", [1, 8, 16])
+@pytest.mark.parametrize("num_qo_heads", [4, 32])
+@pytest.mark.parametrize("head_dim", [128, 256])
+@pytest.mark.parametrize("pos_encoding_mode", ["NONE", "ROPE_LLAMA"])
+@pytest.mark.parametrize("kv_dtype", [torch.float16, torch.float8_e4m3fn])
+def test_cuda_graph_batch_decode_with_paged_kv_cache(batch_size, kv_len, page_size, num_qo_heads, head_dim,
+                                                     pos_encoding_mode, kv_dtype):
+    fi = _fi()
+    num_kv_heads, kv_layout, q_dtype = 4, "NHD", torch.float16
+    torch.manual_seed(batch_size * 7 + kv_len)
+    q = torch.randn(batch_size, num_qo_heads, head_dim, device=DEV, dtype=q_dtype)
+    num_pages_per_seq = (kv_len + page_size - 1) // page_size
+    total_num_pages = num_pages_per_seq * batch_size
+    kv_data, kv_data_fp32, _, _, _ = _make_cache(batch_size, kv_len, page_size, num_kv_heads, head_dim,
+                                                 kv_layout, kv_dtype, True)
+    # the wrapper owns copies in user buffers that are larger than needed, as in the reference
+    indptr_buf = torch.empty(batch_size + 1, device=DEV, dtype=torch.int32)
+    indices_buf = torch.empty(total_num_pages, device=DEV, dtype=torch.int32)
+    last_buf = torch.empty(batch_size, device=DEV, dtype=torch.int32)
+    workspace_buffer = torch.zeros(128 * 1024 * 1024, dtype=torch.int8, device=DEV)
+    wrapper = fi.CUDAGraphBatchDecodeWithPagedKVCacheWrapper(workspace_buffer, indptr_buf, indices_buf,
+                                                             last_buf, kv_layout)
+    kw = dict(data_type=kv_dtype, pos_encoding_mode=pos_encoding_mode, q_data_type=q_dtype)
+    # warm-up plan: ONE page per request
+    wrapper.plan(torch.arange(0, batch_size + 1, device=DEV, dtype=torch.int32),
+                 torch.arange(0, batch_size, device=DEV, dtype=torch.int32),
+                 torch.full((batch_size,), page_size, dtype=torch.int32),
+                 num_qo_heads, num_kv_heads, head_dim, page_size, **kw)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            o = wrapper.run(q, kv_data)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        o = wrapper.run(q, kv_data)
+
+    def check(kv_indptr_host, kv_last_host):
+        for i in sorted({0, 1, batch_size // 2, batch_size - 1}):
+            ki, vi = _request_kv(kv_data_fp32, kv_indptr_host, kv_last_host, i, kv_layout, num_kv_heads,
+                                 head_dim, kv_dtype)
+            o_ref_i = fi.single_decode_with_kv_cache(q[i], ki, vi, pos_encoding_mode=pos_encoding_mode)
+            tol = 1e-2 if kv_dtype == torch.float8_e4m3fn else 1e-3
+            torch.testing.assert_close(o[i], o_ref_i, rtol=tol, atol=tol)
+            o_orc, _ = _oracle_gpu(q[i], ki, vi, rope=pos_encoding_mode == "ROPE_LLAMA")
+            ok, worst = _close(o[i], o_orc, **(FP8_GATE if kv_dtype == torch.float8_e4m3fn else F16_GATE))
+            assert ok, worst
+
+    # replays with re-plans in between: 1, 2, 3 pages per request, then the full length
+    for i in range(1, min(4, num_pages_per_seq)):
+        ip = torch.arange(0, batch_size + 1).int() * i
+        lp = torch.full((batch_size,), page_size, dtype=torch.int32)
+        # page j of request r is page r * i + j of the pool: different tokens than the full table's
+        wrapper.plan(ip, torch.arange(0, i * batch_size).int(), lp, num_qo_heads, num_kv_heads, head_dim,
+                     page_size, **kw)
+        g.replay()
+        torch.cuda.synchronize()
+        check(ip, lp)
+    ip = torch.arange(0, batch_size + 1).int() * num_pages_per_seq
+    lp = torch.full((batch_size,), (kv_len - 1) % page_size + 1, dtype=torch.int32)
+    wrapper.plan(ip, torch.arange(0, total_num_pages).int(), lp, num_qo_heads, num_kv_heads, head_dim,
+                 page_size, **kw)
+    g.replay()
+    torch.cuda.synchronize()
+    check(ip, lp)
+
+
+@pytest.mark.parametrize("batch_size", [1, 19, 99])
+@pytest.mark.parametrize("page_size", [1, 5])
+@pytest.mark.parametrize("seq_len", [1, 11])
+@pytest.mark.parametrize("num_kv_heads", [1, 4, 8])
+@pytest.mark.parametrize("num_qo_heads", [4, 8])
+@pytest.mark.parametrize("head_dim", [64, 128, 256])
+def test_batch_paged_decode_packed_input(batch_size, page_size, seq_len, num_kv_heads, num_qo_heads, head_dim):
+    """q is a strided view into a packed QKV projection output (the reference runs seq_len = 1;
+    11 adds a case whose last page is partial at page_size 5)."""
+    fi = _fi()
+    if num_qo_heads % num_kv_heads != 0:
+        pytest.skip("num_qo_heads must be a multiple of num_kv_heads")
+    torch.manual_seed(batch_size + seq_len)
+    num_pages_per_req = (seq_len + page_size - 1) // page_size
+    num_pages = batch_size * num_pages_per_req
+    last_page_len = (seq_len - 1) % page_size + 1
+    k_cache = torch.randn(num_pages, page_size, num_kv_heads, head_dim, dtype=torch.float16, device=DEV)
+    v_cache = torch.randn_like(k_cache)
+    workspace_buffer = torch.zeros(64 * 1024 * 1024, dtype=torch.uint8, device=DEV)
+    indptr = torch.tensor([i * num_pages_per_req for i in range(batch_size + 1)], dtype=torch.int32, device=DEV)
+    indices = torch.arange(num_pages, dtype=torch.int32, device=DEV)
+    last = torch.full((batch_size,), last_page_len, dtype=torch.int32, device=DEV)
+    wrapper = fi.BatchDecodeWithPagedKVCacheWrapper(workspace_buffer)
+    wrapper.plan(indptr=indptr, indices=indices, last_page_len=last, num_qo_heads=num_qo_heads,
+                 num_kv_heads=num_kv_heads, head_dim=head_dim, page_size=page_size)
+    qkv_packed = torch.randn(batch_size, (num_qo_heads + 2 * num_kv_heads) * head_dim, dtype=torch.float16,
+                             device=DEV)
+    q, _, _ = qkv_packed.split((num_qo_heads * head_dim, num_kv_heads * head_dim, num_kv_heads * head_dim),
+                               dim=-1)
+    q = q.view(-1, num_qo_heads, head_dim)
+    assert not q.is_contiguous() or batch_size == 1
+    o_packed = wrapper.run(q, (k_cache, v_cache))
+    o_contiguous = wrapper.run(q.contiguous(), (k_cache, v_cache))
+    torch.testing.assert_close(o_packed, o_contiguous, rtol=1e-3, atol=1e-3)
+    for i in sorted({0, batch_size // 2, batch_size - 1}):
+        ki = k_cache[i * num_pages_per_req:(i + 1) * num_pages_per_req].reshape(-1, num_kv_heads, head_dim)[:seq_len]
+        vi = v_cache[i * num_pages_per_req:(i + 1) * num_pages_per_req].reshape(-1, num_kv_heads, head_dim)[:seq_len]
+        o_orc, _ = _oracle_gpu(q[i], ki, vi)
+        ok, worst = _close(o_packed[i], o_orc, **F16_GATE)
+        assert ok, worst
+
+
+@pytest.mark.parametrize("kv_len", [7, 19, 39, 1170, 39275])
+@pytest.mark.parametrize("num_qo_heads", [4, 32])
+@pytest.mark.parametrize("kv_layout", ["NHD", "HND"])
+@pytest.mark.parametrize("fp8_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
+def test_single_decode_fp8_calibration_scale(kv_len, num_qo_heads, kv_layout, fp8_dtype):
+    fi = _fi()
+    num_kv_heads, head_dim = 4, 128
+    torch.manual_seed(42)
+    q = torch.randn(num_qo_heads, head_dim, dtype=torch.float16).to(DEV)
+    shape = (kv_len, num_kv_heads, head_dim) if kv_layout == "NHD" else (num_kv_heads, kv_len, head_dim)
+    k = torch.randn(*shape, dtype=torch.float16).to(DEV)
+    v = (0.1 * torch.randn(*shape, dtype=torch.float16)).to(DEV)
+    o_fp16 = fi.single_decode_with_kv_cache(q, k, v, kv_layout=kv_layout)
+    k_scale = k.amax().item() / 256
+    v_scale = v.amax().item() / 256
+    k_fp8 = (k / k_scale).to(fp8_dtype)
+    v_fp8 = (v / v_scale).to(fp8_dtype)
+    o_fp8 = fi.single_decode_with_kv_cache(q, k_fp8, v_fp8, kv_layout=kv_layout, k_scale=k_scale,
+                                           v_scale=v_scale)
+    # the reference's own check: quantisation error of the cache, fp8 vs fp16 kernels
+    torch.testing.assert_close(o_fp16, o_fp8, atol=1e-2, rtol=2e-2 if fp8_dtype == torch.float8_e4m3fn else 2e-1)
+    # the kernel's own error: the oracle on the SAME quantised cache
+    kn, vn = (k_fp8, v_fp8) if kv_layout == "NHD" else (k_fp8.transpose(0, 1), v_fp8.transpose(0, 1))
+    o_orc, lse_orc = _oracle_gpu(q, kn, vn, k_scale=k_scale, v_scale=v_scale)
+    assert (o_fp8.float() - o_orc).abs().max().item() <= 5e-3   # |v| ~ 0.1: far inside the 3e-2 gate
+
+
+@pytest.mark.parametrize("batch_size", [12, 17])
+@pytest.mark.parametrize("kv_len", [54, 97])
+@pytest.mark.parametrize("page_size", [1, 8, 16])
+@pytest.mark.parametrize("num_qo_heads", [4, 32])
+@pytest.mark.parametrize("head_dim", [128, 256])
+@pytest.mark.parametrize("kv_layout", ["HND", "NHD"])
+@pytest.mark.parametrize("pos_encoding_mode", ["NONE", "ROPE_LLAMA"])
+@pytest.mark.parametrize("dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
+def test_batch_decode_with_paged_kv_cache_fp8_calibration_scale(batch_size, kv_len, page_size, num_qo_heads,
+                                                                head_dim, kv_layout, pos_encoding_mode, dtype):
+    fi = _fi()
+    num_kv_heads = 4
+    torch.manual_seed(42)
+    q = torch.randn(batch_size, num_qo_heads, head_dim, dtype=torch.float16).to(DEV)
+    num_pages_per_seq = (kv_len + page_size - 1) // page_size
+    total_num_pages = num_pages_per_seq * batch_size
+    shape = (total_num_pages, 2, num_kv_heads, page_size, head_dim) if kv_layout == "HND" else \
+        (total_num_pages, 2, page_size, num_kv_heads, head_dim)
+    kv_data = (0.1 * torch.randn(*shape, dtype=torch.float16)).to(DEV)
+    kv_indptr = torch.arange(0, batch_size + 1).to(DEV).int() * num_pages_per_seq
+    kv_indices = torch.arange(0, total_num_pages).to(DEV).int()
+    kv_last_page_len = torch.full((batch_size,), (kv_len - 1) % page_size + 1, dtype=torch.int32).to(DEV)
+    workspace_buffer = torch.zeros(32 * 1024 * 1024, dtype=torch.int8).to(DEV)
+    wrapper = fi.BatchDecodeWithPagedKVCacheWrapper(workspace_buffer, kv_layout)
+    wrapper.plan(kv_indptr, kv_indices, kv_last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size,
+                 pos_encoding_mode=pos_encoding_mode, data_type=torch.float16, q_data_type=torch.float16)
+    o_fp16 = wrapper.run(q, kv_data)
+    k_data, v_data = torch.chunk(kv_data, 2, dim=1)
+    k_scale = k_data.amax().item() / 256
+    v_scale = v_data.amax().item() / 256
+    kv_data_fp8 = torch.cat([(k_data / k_scale).to(dtype), (v_data / v_scale).to(dtype)], dim=1)
+    wrapper.plan(kv_indptr, kv_indices, kv_last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size,
+                 pos_encoding_mode=pos_encoding_mode, data_type=dtype, q_data_type=torch.float16)
+    o_fp8, lse_fp8 = wrapper.run(q, kv_data_fp8, k_scale=k_scale, v_scale=v_scale, return_lse=True)
+    torch.testing.assert_close(o_fp16, o_fp8, atol=1e-2, rtol=2e-1)
+    # the kernel's own error: the oracle on the same quantised cache, every sampled request
+    ip, lp = kv_indptr.cpu(), kv_last_page_len.cpu()
+    for i in sorted({0, 1, batch_size // 2, batch_size - 1}):
+        ki, vi = _request_kv(kv_data_fp8.float(), ip, lp, i, kv_layout, num_kv_heads, head_dim, torch.float32)
+        o_orc, lse_orc = _oracle_gpu(q[i], ki, vi, rope=pos_encoding_mode == "ROPE_LLAMA", k_scale=k_scale,
+                                     v_scale=v_scale)
+        assert (o_fp8[i].float() - o_orc).abs().max().item() <= 5e-3   # |v| ~ 0.1: far inside the 3e-2 gate
+        assert (lse_fp8[i] - lse_orc).abs().max().item() <= 1e-3
