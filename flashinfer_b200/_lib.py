@@ -29,6 +29,32 @@ LAYOUT_NHD, LAYOUT_HND = 0, 1
 
 _vp, _i, _i64, _f, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 
+_i32, _u32 = C.c_int32, C.c_uint32
+
+
+class DecodePlanArgs(C.Structure):
+    """FiDecodePlanArgs (include/fi_b200.h), field for field."""
+    _fields_ = [("float_ws", _vp), ("float_ws_bytes", _sz), ("int_ws", _vp), ("pinned_int_ws", _vp),
+                ("int_ws_bytes", _sz), ("indptr_host", _vp), ("last_page_len_host", _vp),
+                ("kv_len_host", _vp), ("batch_size", _i32), ("num_qo_heads", _i32),
+                ("num_kv_heads", _i32), ("head_dim", _i32), ("page_size", _i32), ("q_dtype", _i32),
+                ("kv_dtype", _i32), ("window_left", _i32), ("cuda_graph", _i32),
+                ("fixed_split_pages", _i32), ("disable_split_kv", _i32), ("device", _i32),
+                ("num_ctas_override", _i32), ("pad_", _i32), ("stream", _vp), ("kv_indices_host", _vp),
+                ("num_indices", _i64), ("plan_info_out", _vp)]
+
+
+class DecodeRunArgs(C.Structure):
+    """FiDecodeRunArgs (include/fi_b200.h), field for field."""
+    _fields_ = [("float_ws", _vp), ("int_ws", _vp), ("plan_info", _vp), ("q", _vp),
+                ("q_stride_n", _i64), ("q_stride_h", _i64), ("k_cache", _vp), ("v_cache", _vp),
+                ("num_pages", _i64), ("kv_stride_page", _i64), ("kv_stride_n", _i64),
+                ("kv_stride_h", _i64), ("kv_indices", _vp), ("kv_indptr", _vp), ("o", _vp), ("lse", _vp),
+                ("sm_scale", _f), ("v_scale", _f), ("logits_soft_cap", _f), ("pos_encoding_mode", _i32),
+                ("alibi_slopes", _vp), ("rope_scale", _f), ("rope_theta", _f), ("sinks", _vp),
+                ("enable_pdl", _i32), ("device", _i32), ("stream", _vp)]
+
+
 # name -> (restype, argtypes); must list every symbol include/fi_b200.h declares
 PROTOTYPES = {
     "fi_last_error": (C.c_char_p, []),
@@ -38,9 +64,11 @@ PROTOTYPES = {
     "fi_last_loader": (_i, []),
     "fi_launch_count": (C.c_longlong, []),
     "fi_batch_decode_plan": (_i, [_vp, _sz, _vp, _vp, _sz, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i,
-                                  _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+                                  _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i64, _vp]),
     "fi_batch_decode_run": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _i64,
                                  _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _f, _f, _vp, _i, _i, _vp]),
+    "fi_batch_decode_plan_args": (_i, [C.POINTER(DecodePlanArgs)]),
+    "fi_batch_decode_run_args": (_i, [C.POINTER(DecodeRunArgs)]),
     "fi_single_decode_run": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,
                                   _i, _f, _f, _f, _i, _vp, _f, _f, _i, _vp]),
     "fi_single_decode_tmp_bytes": (_sz, [_i, _i, _i, _i]),

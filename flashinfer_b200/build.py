@@ -28,13 +28,15 @@ FLAGS = [
 ]
 
 
-def _digest() -> str:
+def _digest(src: str, flags) -> str:
+    """Per translation unit: its own text, every header (any TU may include any of them), the
+    public header, this file and the flags — editing one .cu recompiles only that .cu."""
     h = hashlib.sha256()
-    for p in sorted(list(CSRC.glob("*")) + [HERE.parent / "include" / "fi_b200.h", Path(__file__)]):
-        if p.is_file():
-            h.update(p.name.encode())
-            h.update(p.read_bytes())
-    h.update(" ".join(FLAGS).encode())
+    deps = [CSRC / src] + sorted(list(CSRC.glob("*.h")) + list(CSRC.glob("*.cuh")))
+    for p in deps + [HERE.parent / "include" / "fi_b200.h", Path(__file__)]:
+        h.update(p.name.encode())
+        h.update(p.read_bytes())
+    h.update(" ".join(flags).encode())
     return h.hexdigest()
 
 
@@ -44,9 +46,15 @@ def build(force: bool = False, verbose: bool = False, trace: bool = False) -> Pa
     out = HERE / "libfi_b200_trace.so" if trace else OUT
     obj_dir = HERE / "build_trace" if trace else OBJ
     flags = FLAGS + (["-DFI_B200_TRACE"] if trace else [])
-    stamp = obj_dir / "stamp.txt"
-    dig = _digest()
-    if not force and out.exists() and stamp.exists() and stamp.read_text() == dig:
+    digs = {src: _digest(src, flags) for src in SOURCES}
+    stamps = {src: obj_dir / (src + ".stamp") for src in SOURCES}
+
+    def fresh(src: str) -> bool:
+        return (not force and (obj_dir / (src + ".o")).exists() and stamps[src].exists()
+                and stamps[src].read_text() == digs[src])
+
+    if out.exists() and all(fresh(src) for src in SOURCES) and \
+            out.stat().st_mtime >= max((obj_dir / (src + ".o")).stat().st_mtime for src in SOURCES):
         return out
     if not Path(NVCC).exists():
         raise RuntimeError(f"nvcc not found at {NVCC}; cannot build {out.name}")
@@ -54,6 +62,8 @@ def build(force: bool = False, verbose: bool = False, trace: bool = False) -> Pa
 
     def cc(src: str) -> Path:
         obj = obj_dir / (src + ".o")
+        if fresh(src):
+            return obj
         cmd = [NVCC, *flags, "-c", str(CSRC / src), "-o", str(obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
@@ -62,6 +72,7 @@ def build(force: bool = False, verbose: bool = False, trace: bool = False) -> Pa
             raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
         if verbose:
             print(r.stderr)
+        stamps[src].write_text(digs[src])
         return obj
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
@@ -71,7 +82,6 @@ def build(force: bool = False, verbose: bool = False, trace: bool = False) -> Pa
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    stamp.write_text(dig)
     return out
 
 

@@ -368,6 +368,11 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.k = k_cache; p.v = v_cache;
   p.kv_stride_page = kv_stride_page; p.kv_stride_n = kv_stride_n; p.kv_stride_h = kv_stride_h;
   p.kv_indices = kv_indices; p.kv_indptr = kv_indptr;
+  // no page table passed: plan() put its own device copy behind the work list (it had the table on
+  // the host).  NULL without such a copy keeps its old meaning: identity page table.
+  if (kv_indices == nullptr && plan_info[kPiOffIndices] >= 0)
+    p.kv_indices = reinterpret_cast<const int32_t*>(iw + plan_info[kPiOffIndices]);
+  p.indices_early = plan_info[kPiIndicesStable] != 0 || p.kv_indices == nullptr;
   p.page_size = page_size;
   p.page_shift = is_pow2(page_size) ? ilog2(page_size) : -1;
   p.page_mask = is_pow2(page_size) ? page_size - 1 : 0;
@@ -449,6 +454,15 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   return FI_OK;
 }
 
+int fi_batch_decode_run_args(const FiDecodeRunArgs* a) {
+  if (a == nullptr) return fail(FI_ERR_INVALID_ARGUMENT, "null run argument block");
+  return fi_batch_decode_run(a->float_ws, a->int_ws, a->plan_info, a->q, a->q_stride_n, a->q_stride_h,
+                             a->k_cache, a->v_cache, a->num_pages, a->kv_stride_page, a->kv_stride_n,
+                             a->kv_stride_h, a->kv_indices, a->kv_indptr, a->o, a->lse, a->sm_scale,
+                             a->v_scale, a->logits_soft_cap, a->pos_encoding_mode, a->alibi_slopes,
+                             a->rope_scale, a->rope_theta, a->sinks, a->enable_pdl, a->device, a->stream);
+}
+
 size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int head_dim, int device) {
   int sms = 148;
   if (device >= 0) device_sm_count(device, &sms);
@@ -502,6 +516,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.q = q; p.q_stride_n = 0; p.q_stride_h = head_dim;
   p.o = o; p.lse = lse; p.k = k; p.v = v;
   p.kv_head_div = kv_div;
+  p.indices_early = 1;
   if (kv_layout == FI_LAYOUT_NHD) { p.kv_stride_n = (int64_t)num_kv_heads_mem * head_dim; p.kv_stride_h = head_dim; }
   else { p.kv_stride_n = head_dim; p.kv_stride_h = (int64_t)kv_len * head_dim; }
   p.kv_stride_page = 0;

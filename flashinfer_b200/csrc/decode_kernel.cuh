@@ -106,6 +106,8 @@ constexpr int kQFinal = 1 << 30;
 constexpr int kQNoReader = 0x3fffffff;
 constexpr int kQueueCtlFloat = 160;  // offset of the control words in the warp scratch (floats)
 constexpr int kMergeDescFloat = 168; // {go, request, kv_head, slot_begin, count} of a posted merge
+constexpr int kHeadPagesFloat = 176; // kItemInlinePages page ids of item blockIdx.x's first tiles
+static_assert((kHeadPagesFloat + kItemInlinePages) * 4 <= 768, "inline pages do not fit the scratch");
 
 // In the implicit mode (single request, header == nullptr) the sequence is static and in closed
 // form: nothing is drawn, the ring holds the first kSegCache segments and later ones are recomputed.
@@ -115,6 +117,8 @@ struct SegSource {
   volatile int* ctl;
   bool implicit;
   int first, head_count, num_items;  // explicit: head of item blockIdx.x
+  int num_pages;                     // explicit: page ids of the item's first tiles held in `pages`
+  const int* pages;                  //   (shared memory), 0 when plan() did not have the table
   int count;                         // implicit: segments of this CTA
   long long imp_begin, imp_end;      // implicit: stream range of this CTA
   int tt;                            // tokens per tile
@@ -175,6 +179,8 @@ __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int 
   s.implicit = p.header == nullptr;
   s.first = s.head_count = s.num_items = s.count = 0;
   s.imp_begin = s.imp_end = 0;
+  s.num_pages = 0;
+  s.pages = reinterpret_cast<const int*>(scratch + kHeadPagesFloat);
   const int tid = threadIdx.x;
   int pub0;
   if (!s.implicit) {
@@ -185,11 +191,16 @@ __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int 
     s.first = h.x;
     s.head_count = h.y;
     s.num_items = h.z;
+    s.num_pages = h.w;
     pub0 = min(s.head_count, kItemInlineSegs);
     if (tid < 3 * pub0)
       reinterpret_cast<int4*>(cache)[tid] =
           (p.l2_hints & 2) ? ldg_int4_hint(reinterpret_cast<const int4*>(head->seg) + tid, keep)
                      : __ldg(reinterpret_cast<const int4*>(head->seg) + tid);
+    else if (tid >= 32 && tid < 32 + kItemInlinePages / 4 && h.w > 0)
+      reinterpret_cast<int4*>(scratch + kHeadPagesFloat)[tid - 32] =
+          (p.l2_hints & 2) ? ldg_int4_hint(reinterpret_cast<const int4*>(head->pages) + (tid - 32), keep)
+                     : __ldg(reinterpret_cast<const int4*>(head->pages) + (tid - 32));
   } else {
     seg_source_implicit_range(s);
     for (int i = tid; i < min(s.count, kSegCache); i += blockDim.x) cache[i] = seg_make(s, i);
@@ -369,13 +380,16 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   // BEFORE the dependency wait and are in flight while the upstream kernel drains; the KV cache
   // itself (append_paged_kv_cache may be that upstream kernel) is only touched after the wait.
   // Plans with drawn items touch the ticket counter, which the previous launch re-arms: wait first.
+  // A page table the caller keeps on the device (fast_decode_plan, device tensors given to plan())
+  // may be rewritten by the upstream kernel: then nothing is read from it before the wait.
   bool waited = p.enable_pdl == 0;
-  if (!waited && src.num_items > (int)gridDim.x) { pdl_wait(); waited = true; }
+  if (!waited && (src.num_items > (int)gridDim.x || !p.indices_early)) { pdl_wait(); waited = true; }
 
   Feeder f;
   feeder_init(f, src);
   Segment sg;
   int k = 0, t = 0, t_end = 0, tiles_issued = 0, mem_head = 0;
+  int page0 = 0, npage0 = 0;  // segment 0 only: its first pages are in the item head (shared memory)
   int stage = 0;
   uint32_t phase = 0;
   [[maybe_unused]] bool first_tile = true;
@@ -394,6 +408,8 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
       t = sg.tile_begin;
       t_end = sg.tile_end;
       mem_head = sg.kv_head / p.kv_head_div;
+      npage0 = k == 0 ? src.num_pages : 0;
+      page0 = (sg.tile_begin * G::TT) >> p.page_shift;
     }
     // boxes of tile t: page index + first row for this lane's token block j
     const int tok0 = t * G::TT;
@@ -404,6 +420,7 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
     if (j < nvb) {
       const int pit = tok >> p.page_shift;
       if (p.kv_indices == nullptr) page = sg.page_base + pit;
+      else if ((unsigned)(pit - page0) < (unsigned)npage0) page = src.pages[pit - page0];
       else page = keep_meta ? ldg_s32_hint(p.kv_indices + sg.page_base + pit, pol_keep)
                         : __ldg(p.kv_indices + sg.page_base + pit);
     }

@@ -52,18 +52,24 @@ struct alignas(16) Segment {
 static_assert(sizeof(Segment) == 48, "Segment must be 48 bytes");
 
 // Head of one work item: the item's segment range plus its first kItemInlineSegs segments
-// inline, so that one 160-byte read (the kernel prologue for item blockIdx.x, the feeder for
-// drawn items) is all that stands between a CTA and its first page-table lookup.  Segments
-// beyond the inline ones are read from the list, which starts right after the last head.
+// inline and — when plan() was given the page table on the host — the page ids of the item's
+// first tiles, so that one 224-byte read (the kernel prologue for item blockIdx.x, the feeder for
+// drawn items) is all that stands between a CTA and its first TMA box: no page-table lookup on the
+// critical path of the launch.  Segments beyond the inline ones are read from the list, which
+// starts right after the last head.
 constexpr int kItemInlineSegs = 3;
+constexpr int kItemInlinePages = 16;
 struct alignas(16) ItemHead {
   int32_t first;      // index of the item's first segment in the list
   int32_t count;      // segments in the item
   int32_t num_items;  // items in the plan (same in every head)
-  int32_t pad;
+  int32_t num_pages;  // valid entries of pages[] (0: look the pages up in the table)
   Segment seg[kItemInlineSegs];
+  // kv_indices[seg[0].page_base + first_page + i], first_page = page of token
+  // max(seg[0].tile_begin * tile_tokens, 0): the pages the item's first tiles gather
+  int32_t pages[kItemInlinePages];
 };
-static_assert(sizeof(ItemHead) == 160, "ItemHead must be 160 bytes");
+static_assert(sizeof(ItemHead) == 224, "ItemHead must be 224 bytes");
 
 // A (request, kv_head) unit whose KV range was split over several CTAs: partial
 // slots [slot_begin, slot_begin + count) are merged into o[request, kv_head*G ..].
@@ -115,6 +121,9 @@ enum PlanInfoSlot {
   kPiOffItemHeads,
   kPiOffWorkCounter,  // int32 ticket counter of the item scheduler (zero between launches)
   kPiKvHeadDiv,       // virtual KV heads per real one (kPiNumKvHeads counts virtual heads)
+  kPiOffIndices,      // byte offset in the int workspace of plan()'s device copy of kv_indices, or -1
+  kPiNumIndices,      // entries of that copy
+  kPiIndicesStable,   // 1: kv_indices is written by host copies only (plan() had it on the host)
   kPiLen
 };
 constexpr int64_t kPlanMagic = 0xF1B2000001LL;
@@ -164,6 +173,7 @@ struct DecodeParams {
   float rope_rcp_scale, rope_rcp_theta;
   float sm_scale;          // plain sm_scale (soft-cap path)
   int32_t enable_pdl;
+  int32_t indices_early;  // 1: kv_indices may be read before the PDL dependency wait (plan-owned copy)
   int32_t l2_hints;  // bit 0: KV boxes L2 evict_first; bit 1: page table / work list L2 evict_last
   // GQA groups larger than kMaxGroup are run as `kv_head_div` virtual KV heads per real one, each
   // with group / kv_head_div (<= kMaxGroup) query heads: Segment::kv_head counts virtual heads

@@ -136,7 +136,8 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
                          int batch_size, int num_qo_heads, int num_kv_heads, int head_dim,
                          int page_size, int q_dtype, int kv_dtype, int window_left,
                          int cuda_graph, int fixed_split_pages, int disable_split_kv, int device,
-                         int num_ctas_override, void* stream, int64_t* plan_info_out) {
+                         int num_ctas_override, void* stream, const int32_t* kv_indices_host,
+                         int64_t num_indices, int64_t* plan_info_out) {
   static_assert(kPiLen <= FI_PLAN_INFO_LEN, "plan info vector too short");
   (void)float_ws;
   if (batch_size < 0 || num_qo_heads <= 0 || num_kv_heads <= 0 || page_size <= 0)
@@ -319,6 +320,17 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   const size_t off_heads = off;    off = align16(off + (size_t)head_cap * sizeof(ItemHead));
   const size_t off_segs = off;     off = align16(off + (size_t)max_segs * sizeof(Segment));
   const size_t int_need = off;
+  // The page table, when plan() has it on the host: appended to the work list so that ONE H2D copy
+  // brings everything run() needs (outside CUDA-graph mode, where the caller's fixed buffer is the
+  // kernel parameter), and the page ids of every item's first tiles go into its head.
+  if (kv_indices_host != nullptr) {
+    if (num_indices < 0 || (batch_size > 0 && indptr_host[batch_size] > num_indices))
+      return fail(FI_ERR_INVALID_ARGUMENT, "kv_indices has %lld entries, indptr needs %d",
+                  (long long)num_indices, batch_size > 0 ? indptr_host[batch_size] : 0);
+  }
+  const bool idx_in_ws = kv_indices_host != nullptr && !cuda_graph &&
+                         off + (size_t)num_indices * 4 + 16 <= int_ws_bytes;
+  const size_t off_idx = off;
   if (int_need > int_ws_bytes)
     return fail(FI_ERR_WORKSPACE,
                 "Buffer overflow when allocating the decode work list: need %zu bytes of int "
@@ -391,30 +403,56 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
         nslot += pieces * num_kv_heads;
       }
     }
+    // Every head of a group walks the same request range: the group's segments are built ONCE
+    // (as for head 0) and replicated per head with the head-dependent fields patched — the walk
+    // is the planner's hot loop (C2: 512 segments).
+    static thread_local std::vector<Segment> tmpl;
+    static thread_local std::vector<int32_t> tmpl_pieces;
     int b_lo = 0;
     for (int64_t g = 0; g < hg_groups; ++g) {
       const int64_t gs = g * hg_chunk, ge = gs + hg_chunk;
       while (b_lo < batch_size && g_last[b_lo] < g) ++b_lo;
+      tmpl.clear();
+      tmpl_pieces.clear();
+      for (int b = b_lo; b < batch_size && g_first[b] <= g; ++b) {
+        Segment s;
+        s.request = b; s.kv_head = 0; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b];
+        s.page_base = indptr_host[b]; s.kv_len = tok_hi[b];
+        s.slot = -1; s.merge_unit = -1; s.merge_count = 0; s.merge_slot = 0;
+        const int64_t lo = std::max(gs, pos_b[b]), hi = std::min(ge, pos_b[b] + ntile[b]);
+        s.tile_begin = ntile[b] == 0 ? 0 : tile_b[b] + (int32_t)(lo - pos_b[b]);
+        s.tile_end = ntile[b] == 0 ? 0 : tile_b[b] + (int32_t)(hi - pos_b[b]);
+        int32_t pieces = 0;
+        if (mbase[b] >= 0) {
+          pieces = (int32_t)(g_last[b] - g_first[b] + 1);
+          s.merge_unit = fused_merge ? (int32_t)mbase[b] : -1;
+          s.merge_count = pieces;
+          s.merge_slot = (int32_t)sbase[b];
+          s.slot = s.merge_slot + (int32_t)(g - g_first[b]);
+        }
+        tmpl.push_back(s);
+        tmpl_pieces.push_back(pieces);
+      }
+      const int nt = (int)tmpl.size();
+      const Segment* tp = tmpl.data();
+      const int32_t* pp = tmpl_pieces.data();
       for (int h = 0; h < num_kv_heads; ++h) {
         item = g * num_kv_heads + h;
-        heads[item].first = (int32_t)nseg;
-        for (int b = b_lo; b < batch_size && g_first[b] <= g; ++b) {
-          Segment s;
-          s.request = b; s.kv_head = h; s.tok_lo = tok_lo[b]; s.tok_hi = tok_hi[b];
-          s.page_base = indptr_host[b]; s.kv_len = tok_hi[b];
-          s.slot = -1; s.merge_unit = -1; s.merge_count = 0; s.merge_slot = 0;
-          const int64_t lo = std::max(gs, pos_b[b]), hi = std::min(ge, pos_b[b] + ntile[b]);
-          s.tile_begin = ntile[b] == 0 ? 0 : tile_b[b] + (int32_t)(lo - pos_b[b]);
-          s.tile_end = ntile[b] == 0 ? 0 : tile_b[b] + (int32_t)(hi - pos_b[b]);
-          if (mbase[b] >= 0) {
-            const int64_t pieces = g_last[b] - g_first[b] + 1;
-            s.merge_unit = fused_merge ? (int32_t)(mbase[b] + h) : -1;
-            s.merge_count = (int32_t)pieces;
-            s.merge_slot = (int32_t)(sbase[b] + h * pieces);
-            s.slot = s.merge_slot + (int32_t)(g - g_first[b]);
+        ItemHead& hd = heads[item];
+        hd.first = (int32_t)nseg;
+        Segment* dst = segs + nseg;
+        for (int i = 0; i < nt; ++i) {
+          Segment s = tp[i];
+          s.kv_head = h;
+          if (pp[i] > 0) {  // head h of a split request: its own merge unit and slot range
+            if (fused_merge) s.merge_unit += h;
+            s.merge_slot += h * pp[i];
+            s.slot += h * pp[i];
           }
-          push(s);
+          dst[i] = s;
+          if (i < kItemInlineSegs) hd.seg[i] = s;
         }
+        nseg += nt;
       }
     }
   }
@@ -491,7 +529,15 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
     ItemHead& hd = heads[i];
     hd.count = (int32_t)((i + 1 < num_items ? heads[i + 1].first : nseg) - hd.first);
     hd.num_items = (int32_t)num_items;
-    hd.pad = 0;
+    hd.num_pages = 0;
+    if (kv_indices_host != nullptr && hd.count > 0 && hd.seg[0].tile_end > hd.seg[0].tile_begin) {
+      const Segment& s0 = hd.seg[0];
+      const int64_t first_page = (int64_t)s0.tile_begin * TT / page_size;
+      const int64_t req_pages = (int64_t)indptr_host[s0.request + 1] - indptr_host[s0.request];
+      const int64_t n = std::min<int64_t>(kItemInlinePages, req_pages - first_page);
+      for (int64_t j = 0; j < n; ++j) hd.pages[j] = kv_indices_host[s0.page_base + first_page + j];
+      hd.num_pages = (int32_t)std::max<int64_t>(n, 0);
+    }
   }
   // arrival counters of the fused merge: zeroed by every plan (the workspace is not guaranteed
   // to be zero-initialised) and returned to zero by the kernel itself
@@ -505,12 +551,18 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
 
   // ---- H2D: [header, work counter, counters(nmerge)] [merges(nmerge)] [heads, segs(nseg)] —
   // as one copy when the unused capacity in between is small ------------------------------
-  const size_t used = off_segs + (size_t)std::max<int64_t>(nseg, 1) * sizeof(Segment);
+  const size_t used_segs = off_segs + (size_t)std::max<int64_t>(nseg, 1) * sizeof(Segment);
+  size_t used = used_segs;
+  if (idx_in_ws) {
+    memcpy(host + off_idx, kv_indices_host, (size_t)num_indices * 4);
+    used = off_idx + (size_t)num_indices * 4;
+  }
   if (device >= 0) {
     FI_CUDA_TRY(cudaSetDevice(device));
     cudaStream_t cs = static_cast<cudaStream_t>(stream);
     char* dev = static_cast<char*>(int_ws);
-    const size_t gap = (size_t)(max_merge - nmerge) * (4 + sizeof(MergeUnit));
+    const size_t gap = (size_t)(max_merge - nmerge) * (4 + sizeof(MergeUnit)) +
+                       (idx_in_ws ? off_idx - used_segs : 0);
     if (gap <= (64u << 10)) {
       FI_CUDA_TRY(cudaMemcpyAsync(dev, host, used, cudaMemcpyHostToDevice, cs));
     } else {
@@ -519,8 +571,11 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
       if (nmerge > 0)
         FI_CUDA_TRY(cudaMemcpyAsync(dev + off_merge, host + off_merge, (size_t)nmerge * sizeof(MergeUnit),
                                     cudaMemcpyHostToDevice, cs));
-      FI_CUDA_TRY(cudaMemcpyAsync(dev + off_heads, host + off_heads, used - off_heads,
+      FI_CUDA_TRY(cudaMemcpyAsync(dev + off_heads, host + off_heads, used_segs - off_heads,
                                   cudaMemcpyHostToDevice, cs));
+      if (idx_in_ws && num_indices > 0)
+        FI_CUDA_TRY(cudaMemcpyAsync(dev + off_idx, host + off_idx, (size_t)num_indices * 4,
+                                    cudaMemcpyHostToDevice, cs));
     }
   } else {
     if (int_ws != pinned_int_ws) memcpy(int_ws, pinned_int_ws, used);  // CPU-only test mode
@@ -558,7 +613,24 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   pi[kPiWindowLeft] = window_left;
   pi[kPiStages] = cfg.stages;
   pi[kPiIntBytesUsed] = (int64_t)used;
+  pi[kPiOffIndices] = idx_in_ws ? (int64_t)off_idx : -1;
+  pi[kPiNumIndices] = idx_in_ws ? num_indices : 0;
+  // the page table was fixed by host copies ordered before every later kernel of the stream (ours
+  // above, or the wrapper's copy into the caller's CUDA-graph buffer): the decode kernel may read it
+  // ahead of its programmatic-dependent-launch wait.  Tables the caller keeps on the device
+  // (fast_decode_plan, device tensors handed to plan()) may be rewritten by an upstream kernel.
+  pi[kPiIndicesStable] = kv_indices_host != nullptr ? 1 : 0;
   return FI_OK;
+}
+
+int fi_batch_decode_plan_args(const FiDecodePlanArgs* a) {
+  if (a == nullptr) return fail(FI_ERR_INVALID_ARGUMENT, "null plan argument block");
+  return fi_batch_decode_plan(a->float_ws, a->float_ws_bytes, a->int_ws, a->pinned_int_ws, a->int_ws_bytes,
+                              a->indptr_host, a->last_page_len_host, a->kv_len_host, a->batch_size,
+                              a->num_qo_heads, a->num_kv_heads, a->head_dim, a->page_size, a->q_dtype,
+                              a->kv_dtype, a->window_left, a->cuda_graph, a->fixed_split_pages,
+                              a->disable_split_kv, a->device, a->num_ctas_override, a->stream,
+                              a->kv_indices_host, a->num_indices, a->plan_info_out);
 }
 
 }  // extern "C"

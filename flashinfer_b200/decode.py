@@ -37,6 +37,8 @@ from .utils import (
 )
 
 _INT_WORKSPACE_BYTES = 8 * 1024 * 1024
+_PI_OFF_INDICES = 28  # PlanInfoSlot kPiOffIndices (csrc/decode_params.h)
+_PlanInfo = C.c_int64 * 32  # FI_PLAN_INFO_LEN; a ctypes array: no tensor object on the per-step path
 
 
 def _host_i32_ptr(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
@@ -205,6 +207,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
             self._fixed_batch_size = 0
         self._indptr_dev = self._indptr_src = None
         self._last_page_len_dev = self._last_page_len_src = None
+        self._indices_dev = self._indices_src = None
         self._paged_kv_indptr_buf = paged_kv_indptr_buffer
         self._paged_kv_indices_buf = paged_kv_indices_buffer
         self._paged_kv_last_page_len_buf = paged_kv_last_page_len_buffer
@@ -212,7 +215,20 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._use_tensor_cores = use_tensor_cores or backend == "trtllm-gen"
         self._use_cuda_graph = use_cuda_graph
         self._backend = backend
-        self._plan_info: Optional[torch.Tensor] = None
+        self._plan_info = None  # opaque (FI_PLAN_INFO_LEN x int64), written by the C planner
+        # argument blocks of the C-ABI calls (include/fi_b200.h FiDecodePlanArgs / FiDecodeRunArgs):
+        # filled once, per step only the fields that change are rewritten and the call takes ONE
+        # pointer (the 26 per-call argument conversions were a third of plan()'s / run()'s host time)
+        self._pa, self._ra = _lib.DecodePlanArgs(), _lib.DecodeRunArgs()
+        self._pa_ref, self._ra_ref = C.byref(self._pa), C.byref(self._ra)
+        self._bound_ws = (None, None, None)
+        self._kv_key = None            # (weakref to the last 5-D cache tensor, its data_ptr)
+        self._pos_key = None
+        self._planned_window_left = -1
+        self._kv_sig = None
+        self._dev_idx = device_index(self.device)
+        self._lib = _lib.load()
+        self._pdl_default = int(device_support_pdl(self.device))
         self._mtp_children = {}
         self._mtp_src = None
         self._pos_encoding_mode = "NONE"
@@ -234,6 +250,19 @@ class BatchDecodeWithPagedKVCacheWrapper:
     @_paged_kv_indptr_buf.setter
     def _paged_kv_indptr_buf(self, value):
         self._indptr_dev, self._indptr_src = value, None
+
+    # The page table itself: when plan() gets it on the host, the C planner appends it to the work
+    # list (one H2D copy for everything) and the kernels read that copy; the attribute the reference
+    # keeps (decode.py:1009-1012) is materialised on first access.
+    @property
+    def _paged_kv_indices_buf(self):
+        if self._indices_dev is None and self._indices_src is not None:
+            self._indices_dev = self._indices_src.to(self.device, non_blocking=True)
+        return self._indices_dev
+
+    @_paged_kv_indices_buf.setter
+    def _paged_kv_indices_buf(self, value):
+        self._indices_dev, self._indices_src = value, None
 
     @property
     def _paged_kv_last_page_len_buf(self):
@@ -297,11 +326,11 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._workspace_size = (
             self._float_workspace_buffer.numel() * self._float_workspace_buffer.element_size()
         )
-        batch_size = len(last_page_len)
+        batch_size = last_page_len.shape[0]
         if logits_soft_cap is None:
             logits_soft_cap = 0.0
 
-        if self.is_cuda_graph_enabled:
+        if self._use_cuda_graph:
             if batch_size != self._fixed_batch_size:
                 raise ValueError(
                     "The batch size should be fixed in cudagraph mode, the runtime batch size {} "
@@ -319,7 +348,10 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 indices, non_blocking=(indices.device == self.device) and non_blocking
             )
         else:
-            self._paged_kv_indices_buf = indices.to(self.device, non_blocking=non_blocking)
+            if indices.device.type == "cpu":
+                self._indices_dev, self._indices_src = None, indices  # the planner copies it (below)
+            else:
+                self._paged_kv_indices_buf = indices.to(self.device, non_blocking=non_blocking)
             if indptr.device == self.device:
                 self._paged_kv_indptr_buf = indptr
             else:
@@ -331,7 +363,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
 
         indptr_host, indptr_ptr = _host_i32_ptr(indptr)
         last_page_len_host, lpl_ptr = _host_i32_ptr(last_page_len)
-        if len(indptr_host) != batch_size + 1:
+        if indptr_host.shape[0] != batch_size + 1:
             raise ValueError("indptr must have batch_size + 1 entries")
 
         if data_type is not None:
@@ -360,12 +392,22 @@ class BatchDecodeWithPagedKVCacheWrapper:
             if len(kv_len_host) != batch_size:
                 raise ValueError("seq_lens must have batch_size entries")
 
+        # the page table, when it is on the host: the planner inlines every work item's first page
+        # ids into its head and (outside CUDA-graph mode) ships the table with the work list
+        indices_host = None
+        if indices.device.type == "cpu":
+            indices_host = indices if indices.is_contiguous() else indices.contiguous()
         self._run_plan(
             indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads, head_dim,
             page_size, q_data_type, kv_data_type, window_left,
             fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv,
+            indices_host=indices_host,
         )
-        del indptr_host, last_page_len_host, kv_len_host  # only needed during the call
+        if indices_host is not None and not self._use_cuda_graph \
+                and self._plan_info[_PI_OFF_INDICES] < 0:
+            # the table did not fit behind the work list in the int workspace: our own device copy
+            self._indices_dev = indices_host.to(self.device, non_blocking=non_blocking)
+        del indptr_host, last_page_len_host, kv_len_host, indices_host  # only needed during the call
 
         self._pos_encoding_mode = pos_encoding_mode
         self._window_left = window_left
@@ -414,34 +456,60 @@ class BatchDecodeWithPagedKVCacheWrapper:
             self._mtp_children[q_len_per_req] = child
         return child.run(q, paged_kv_cache, **run_kw)
 
+    def _bind_workspaces(self) -> None:
+        fws, iws, pws = (self._float_workspace_buffer, self._int_workspace_buffer,
+                         self._pin_memory_int_workspace_buffer)
+        pa, ra = self._pa, self._ra
+        pa.float_ws = ra.float_ws = fws.data_ptr()
+        pa.float_ws_bytes = fws.numel() * fws.element_size()
+        pa.int_ws = ra.int_ws = iws.data_ptr()
+        pa.pinned_int_ws = pws.data_ptr()
+        pa.int_ws_bytes = min(iws.numel() * iws.element_size(), pws.numel() * pws.element_size())
+        pa.device = ra.device = self._dev_idx
+        self._bound_ws = (fws, iws, pws)
+
     def _run_plan(self, indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
                   head_dim, page_size, q_data_type, kv_data_type, window_left,
-                  fixed_split_size=None, disable_split_kv=False) -> None:
+                  fixed_split_size=None, disable_split_kv=False, indices_host=None) -> None:
         # fixed_split_size (pages) / disable_split_kv: batch-invariant planning, reference
         # decode.py:880-887; None / -1 mean "off" there as here
         lib = _lib.load()
-        # a fresh vector per plan: a CUDA graph captured around an earlier run() read its own
-        # (the C function selects the device itself, like the reference's plan, batch_decode.cu:56)
-        info = torch.empty(lib.fi_plan_info_len(), dtype=torch.int64)
-        dev_idx = device_index(self.device)
-        fws = self._float_workspace_buffer
-        iws, pws = self._int_workspace_buffer, self._pin_memory_int_workspace_buffer
-        _lib.check(
-            lib.fi_batch_decode_plan(
-                fws.data_ptr(), fws.numel() * fws.element_size(),
-                iws.data_ptr(), pws.data_ptr(),
-                min(iws.numel() * iws.element_size(), pws.numel() * pws.element_size()),
-                indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
-                head_dim, page_size, dtype_code(q_data_type), dtype_code(kv_data_type),
-                int(window_left), int(self.is_cuda_graph_enabled),
-                int(fixed_split_size) if fixed_split_size is not None and fixed_split_size > 0 else 0,
-                int(bool(disable_split_kv)), dev_idx, 0,
-                current_stream_ptr(self.device), info.data_ptr(),
-            )
-        )
+        b = self._bound_ws  # engines swap the workspace attributes (reset_workspace_buffer, pokes)
+        if b[0] is not self._float_workspace_buffer or b[1] is not self._int_workspace_buffer \
+                or b[2] is not self._pin_memory_int_workspace_buffer:
+            self._bind_workspaces()
+        # a fresh vector per plan (the C function selects the device itself, like the reference's
+        # plan, batch_decode.cu:56)
+        info = _PlanInfo()
+        pa = self._pa
+        pa.indptr_host, pa.last_page_len_host, pa.kv_len_host = indptr_ptr, lpl_ptr, kv_len_ptr
+        pa.batch_size, pa.num_qo_heads, pa.num_kv_heads = batch_size, num_qo_heads, num_kv_heads
+        pa.head_dim, pa.page_size = head_dim, page_size
+        pa.q_dtype, pa.kv_dtype = dtype_code(q_data_type), dtype_code(kv_data_type)
+        pa.window_left = int(window_left)
+        pa.cuda_graph = int(self._use_cuda_graph)
+        pa.fixed_split_pages = int(fixed_split_size) if fixed_split_size is not None and fixed_split_size > 0 else 0
+        pa.disable_split_kv = int(bool(disable_split_kv))
+        pa.num_ctas_override = 0
+        pa.stream = current_stream_ptr(self.device)
+        if indices_host is not None:
+            pa.kv_indices_host, pa.num_indices = indices_host.data_ptr(), indices_host.numel()
+        else:
+            pa.kv_indices_host, pa.num_indices = None, 0
+        pa.plan_info_out = C.addressof(info)
+        rc = lib.fi_batch_decode_plan_args(self._pa_ref)
+        if rc:
+            _lib.check(rc)
         self._plan_info = info
+        sig = (page_size, num_kv_heads, kv_data_type)
+        if sig != self._kv_sig:  # what _bind_cache validated the last cache against has changed
+            self._kv_sig, self._kv_key = sig, None
+        self._ra.plan_info = C.addressof(info)
         self._head_dim = head_dim
         self._page_size = page_size
+        self._q_shape = (batch_size, num_qo_heads, head_dim)
+        self._default_sm_scale = 1.0 / math.sqrt(head_dim)
+        self._planned_window_left = int(window_left)
 
     # ------------------------------------------------------------------- run
     def forward(
@@ -506,8 +574,87 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 q, paged_kv_cache, int(q_len_per_req), q_scale=q_scale, k_scale=k_scale, v_scale=v_scale,
                 out=out, lse=lse, return_lse=return_lse, enable_pdl=enable_pdl, window_left=window_left,
                 sinks=sinks)
-        if enable_pdl is None:
-            enable_pdl = device_support_pdl(q.device)
+        ra = self._ra
+        # ---- the cache: geometry validated once per cache tensor (a serving loop passes the same
+        # per-layer tensors every step); tuples and re-allocated caches take the full path
+        kv = self._kv_key
+        if kv is None or kv[0]() is not paged_kv_cache or kv[1] != paged_kv_cache.data_ptr():
+            self._bind_cache(paged_kv_cache)
+        # ---- q / out / lse
+        if q.dtype != self._cached_q_data_type:
+            raise ValueError(
+                f"The dtype of q {q.dtype} does not match the q_data_type {self._cached_q_data_type} "
+                "specified in plan function.")
+        qs = q.stride()
+        if q.shape != self._q_shape:
+            raise ValueError(
+                f"q must have shape [{self._batch_size}, {self._num_qo_heads}, {self._head_dim}], "
+                f"got {list(q.shape)}"
+            )
+        if qs[2] != 1:
+            raise ValueError("the last dimension of q / k / v must be contiguous")
+        dev = q.device
+        if dev != self.device:
+            raise ValueError("q / paged_kv_cache must be on the wrapper's device")
+
+        # window_left is baked into the plan (the segments' token bounds): a different value at run
+        # time cannot be honoured (the reference passes it to its kernel, decode.py:1295)
+        if (self._window_left if window_left is None else window_left) != self._planned_window_left:
+            raise ValueError(
+                f"window_left {self._window_left if window_left is None else window_left} differs from "
+                f"the planned one ({self._planned_window_left}): call plan() again")
+        logits_soft_cap = self._logits_soft_cap
+        sm_scale = self._sm_scale
+        if sm_scale is None:
+            sm_scale = self._default_sm_scale
+        if q_scale is not None:
+            sm_scale *= q_scale
+        if k_scale is not None:
+            sm_scale *= k_scale
+
+        if return_lse:
+            if lse is None:
+                lse = torch.empty((q.shape[0], q.shape[1]), dtype=torch.float32, device=dev)
+            else:
+                check_shape_dtype_device(lse, (q.size(0), q.size(1)), torch.float32, dev, "lse")
+                if not lse.is_contiguous():
+                    raise ValueError("lse must be contiguous")
+            ra.lse = lse.data_ptr()
+        else:
+            ra.lse = None
+        if out is None:
+            out = torch.empty(q.shape, dtype=q.dtype, device=dev)
+        elif out.shape != q.shape or out.dtype != q.dtype or out.device != dev:
+            check_shape_dtype_device(out, q.shape, q.dtype, dev, "out")
+        elif not out.is_contiguous():
+            raise ValueError("out must be contiguous")
+
+        pk = (self._pos_encoding_mode, self._rope_scale, self._rope_theta)
+        if pk != self._pos_key:
+            (ra.pos_encoding_mode, ra.alibi_slopes, ra.rope_scale, ra.rope_theta) = _pos_mode_args(
+                self._pos_encoding_mode, q.shape[1], dev, self._rope_scale, self._rope_theta)
+            self._pos_key = pk
+        ra.q, ra.q_stride_n, ra.q_stride_h = q.data_ptr(), qs[0], qs[1]
+        ra.kv_indices = self._indices_dev.data_ptr() if self._indices_dev is not None else None
+        ra.kv_indptr = self._indptr_dev.data_ptr() if self._indptr_dev is not None else None
+        ra.o = out.data_ptr()
+        ra.sm_scale = sm_scale
+        # v_scale is fused into the kernel epilogue (the reference multiplies afterwards,
+        # decode.py:1367-1372)
+        ra.v_scale = v_scale if v_scale is not None else 1.0
+        ra.logits_soft_cap = logits_soft_cap if logits_soft_cap is not None else 0.0
+        ra.sinks = sinks.data_ptr() if sinks is not None else None
+        ra.enable_pdl = self._pdl_default if enable_pdl is None else int(bool(enable_pdl))
+        ra.stream = current_stream_ptr(dev)
+        rc = self._lib.fi_batch_decode_run_args(self._ra_ref)
+        if rc:
+            _lib.check(rc)
+        return (out, lse) if return_lse else out
+
+    def _bind_cache(self, paged_kv_cache) -> None:
+        """Validate the cache against the plan and write its geometry into the run argument block."""
+        import weakref
+
         if torch.is_tensor(paged_kv_cache) and paged_kv_cache.dim() == 5:
             # the common 5-D cache: K and V are the two halves of dim 1 (flashinfer/utils.py:160-162
             # unbinds them) — same strides by construction, no view objects on the hot path
@@ -519,6 +666,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
             v_ptr = k_ptr + cs[1] * c.element_size()
             num_pages, stride_page, last_stride = c.shape[0], cs[0], cs[4]
             d2, d3, s2, s3 = c.shape[2], c.shape[3], cs[2], cs[3]
+            key = (weakref.ref(c), k_ptr)
         else:
             k_cache, v_cache = _unpack_paged_kv_cache(paged_kv_cache, self._kv_layout)
             if v_cache.dtype != k_cache.dtype:
@@ -530,10 +678,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
             k_ptr, v_ptr = k_cache.data_ptr(), v_cache.data_ptr()
             num_pages, stride_page, last_stride = k_cache.shape[0], ks[0], ks[3]
             d2, d3, s2, s3 = k_cache.shape[1], k_cache.shape[2], ks[1], ks[2]
-        if q.dtype != self._cached_q_data_type:
-            raise ValueError(
-                f"The dtype of q {q.dtype} does not match the q_data_type {self._cached_q_data_type} "
-                "specified in plan function.")
+            key = None  # tuples / views are rebuilt by the caller on every call: nothing to key on
+        self._kv_key = None
         if kv_dtype != self._cached_kv_data_type:
             raise ValueError(
                 f"The dtype of k {kv_dtype} does not match the kv_data_type {self._cached_kv_data_type} "
@@ -546,68 +692,14 @@ class BatchDecodeWithPagedKVCacheWrapper:
             raise ValueError(
                 "paged_kv_cache shape does not match the (page_size, num_kv_heads) given to plan()"
             )
-        if last_stride != 1 or q.stride(-1) != 1:
+        if last_stride != 1:
             raise ValueError("the last dimension of q / k / v must be contiguous")
-        if q.dim() != 3 or q.shape[0] != self._batch_size or q.shape[1] != self._num_qo_heads \
-                or q.shape[2] != self._head_dim:
-            raise ValueError(
-                f"q must have shape [{self._batch_size}, {self._num_qo_heads}, {self._head_dim}], "
-                f"got {list(q.shape)}"
-            )
-        dev = q.device
-        if dev != self.device or kv_dev != dev:
+        if kv_dev != self.device:
             raise ValueError("q / paged_kv_cache must be on the wrapper's device")
-
-        window_left = self._window_left if window_left is None else window_left
-        assert window_left == self._window_left, "window_left must equal the planned one"
-        logits_soft_cap = self._logits_soft_cap
-        sm_scale = self._sm_scale
-        if logits_soft_cap is None:
-            logits_soft_cap = 0.0
-        if sm_scale is None:
-            sm_scale = 1.0 / math.sqrt(q.shape[-1])
-        if q_scale is not None:
-            sm_scale *= q_scale
-        if k_scale is not None:
-            sm_scale *= k_scale
-
-        if return_lse:
-            if lse is None:
-                lse = torch.empty((q.size(0), q.size(1)), dtype=torch.float32, device=dev)
-            else:
-                check_shape_dtype_device(lse, (q.size(0), q.size(1)), torch.float32, dev, "lse")
-                if not lse.is_contiguous():
-                    raise ValueError("lse must be contiguous")
-        if out is None:
-            out = torch.empty(q.shape, dtype=q.dtype, device=dev)
-        else:
-            check_shape_dtype_device(out, q.shape, q.dtype, dev, "out")
-            if not out.is_contiguous():
-                raise ValueError("out must be contiguous")
-
-        lib = _lib.load()
-        _lib.check(
-            lib.fi_batch_decode_run(
-                self._float_workspace_buffer.data_ptr(), self._int_workspace_buffer.data_ptr(),
-                self._plan_info.data_ptr(),
-                q.data_ptr(), q.stride(0), q.stride(1),
-                k_ptr, v_ptr, num_pages,
-                stride_page, stride_n, stride_h,
-                self._paged_kv_indices_buf.data_ptr(),
-                self._indptr_dev.data_ptr() if self._indptr_dev is not None else None,
-                out.data_ptr(), lse.data_ptr() if return_lse else None,
-                float(sm_scale), float(v_scale) if v_scale is not None else 1.0,
-                float(logits_soft_cap),
-                *_pos_mode_args(self._pos_encoding_mode, q.shape[1], dev, self._rope_scale,
-                                self._rope_theta),
-                sinks.data_ptr() if sinks is not None else None,
-                int(bool(enable_pdl)), device_index(dev),
-                current_stream_ptr(dev),
-            )
-        )
-        # v_scale is fused into the kernel epilogue (the reference multiplies afterwards,
-        # decode.py:1367-1372)
-        return (out, lse) if return_lse else out
+        ra = self._ra
+        ra.k_cache, ra.v_cache, ra.num_pages = k_ptr, v_ptr, num_pages
+        ra.kv_stride_page, ra.kv_stride_n, ra.kv_stride_h = stride_page, stride_n, stride_h
+        self._kv_key = key
 
     def forward_return_lse(
         self,
@@ -686,12 +778,16 @@ def fast_decode_plan(
     fixed_split_size: Optional[int] = None,
     disable_split_kv: bool = False,
     global_override_indptr_cpu: Optional[torch.Tensor] = None,
+    last_page_len_cpu: Optional[torch.Tensor] = None,
 ) -> None:
     r"""Lighter ``plan`` that adopts the caller's device index tensors without copying
     (reference decode.py:2416-2579).  ``global_override_indptr_cpu`` avoids the D2H read of
-    ``indptr``; ``last_page_len`` is read on the host unless ``page_size == 1``.
+    ``indptr``; ``last_page_len`` is read on the host unless ``page_size == 1`` or the caller hands
+    over its host copy as ``last_page_len_cpu`` (an addition to the reference's signature: the token-
+    exact planner needs the lengths, and a serving engine has them on the host anyway), which makes
+    the call free of device synchronisation.
     """
-    batch_size = len(last_page_len)
+    batch_size = last_page_len.shape[0]
     if logits_soft_cap is None:
         logits_soft_cap = 0.0
     _unsupported_variant(pos_encoding_mode)
@@ -726,7 +822,11 @@ def fast_decode_plan(
 
     indptr_src = global_override_indptr_cpu if global_override_indptr_cpu is not None else indptr
     indptr_host, indptr_ptr = _host_i32_ptr(indptr_src)
-    if page_size == 1:
+    if last_page_len_cpu is not None:
+        last_page_len_host, _ = _host_i32_ptr(last_page_len_cpu)
+        if last_page_len_host.shape[0] != batch_size:
+            raise ValueError("last_page_len_cpu must have batch_size entries")
+    elif page_size == 1:
         last_page_len_host = torch.ones((batch_size,), dtype=torch.int32)
     else:
         last_page_len_host = last_page_len.detach().to("cpu", torch.int32).contiguous()

@@ -107,6 +107,16 @@ FI_API long long fi_launch_count(void);
  *                            the device (used by CPU-only tests; then `device`
  *                            may be -1 and no CUDA call is made: the H2D copy
  *                            becomes a memcpy into int_ws)
+ *  kv_indices_host[num_indices]  optional: the page table on the host (NULL: unknown to the
+ *                            planner).  When given, (a) the page ids of every work item's first tiles
+ *                            are written into its head, so the kernel issues its first TMA boxes
+ *                            without a page-table lookup, (b) outside CUDA-graph mode the table is
+ *                            appended to the work list and travels in the same H2D copy: run() may
+ *                            then be called with kv_indices = NULL, (c) the kernel may read the table
+ *                            ahead of its programmatic-dependent-launch wait (it is only ever written
+ *                            by host copies).  The reference copies the table to the device in its
+ *                            Python wrapper (flashinfer/decode.py:1009-1012) and never shows it to
+ *                            the planner.
  *  plan_info_out[FI_PLAN_INFO_LEN]
  */
 FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws,
@@ -118,7 +128,8 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
                          int page_size, int q_dtype, int kv_dtype,
                          int window_left, int cuda_graph, int fixed_split_pages,
                          int disable_split_kv, int device, int num_ctas_override,
-                         void* stream, int64_t* plan_info_out);
+                         void* stream, const int32_t* kv_indices_host, int64_t num_indices,
+                         int64_t* plan_info_out);
 
 /*
  * fi_batch_decode_run — launches the decode kernel; split requests are merged
@@ -131,7 +142,8 @@ FI_API int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int
  *  k_cache/v_cache  page pools of num_pages pages sharing element strides
  *                   (page, n, h), unit on D (reference constraint
  *                   csrc/batch_decode.cu:123-128)
- *  kv_indices   device int32 page table; NULL = identity (page id == position)
+ *  kv_indices   device int32 page table; NULL = the copy plan() made from kv_indices_host, or,
+ *               when plan() was not given one, the identity (page id == position)
  *  kv_indptr    device int32 [bs+1], or NULL: the kernels take every request's page
  *               base from the planned work list (plan() read indptr on the host), the
  *               argument is kept for signature parity with the reference run()
@@ -163,6 +175,41 @@ FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan
                         int pos_encoding_mode, const float* alibi_slopes, float rope_scale,
                         float rope_theta, const float* sinks, int enable_pdl, int device,
                         void* stream);
+
+/*
+ * The same two calls with their arguments in a caller-owned block: a serving loop fills the block
+ * once per (wrapper, cache) and rewrites only the pointers that change per step / per layer, so the
+ * per-step cost of the binding (ctypes here, cgo / JNI elsewhere) is one pointer argument instead
+ * of 26.  Field for field the arguments of fi_batch_decode_plan / fi_batch_decode_run above; no
+ * reference counterpart (tvm-ffi packs its arguments per call, csrc/batch_decode_jit_binding.cu:23-40).
+ */
+typedef struct FiDecodePlanArgs {
+  void* float_ws; size_t float_ws_bytes;
+  void* int_ws; void* pinned_int_ws; size_t int_ws_bytes;
+  const int32_t* indptr_host; const int32_t* last_page_len_host; const int32_t* kv_len_host;
+  int32_t batch_size, num_qo_heads, num_kv_heads, head_dim, page_size, q_dtype, kv_dtype;
+  int32_t window_left, cuda_graph, fixed_split_pages, disable_split_kv, device, num_ctas_override;
+  int32_t pad_;
+  void* stream;
+  const int32_t* kv_indices_host; int64_t num_indices;
+  int64_t* plan_info_out;
+} FiDecodePlanArgs;
+FI_API int fi_batch_decode_plan_args(const FiDecodePlanArgs* a);
+
+typedef struct FiDecodeRunArgs {
+  void* float_ws; void* int_ws; const int64_t* plan_info;
+  const void* q; int64_t q_stride_n, q_stride_h;
+  const void* k_cache; const void* v_cache;
+  int64_t num_pages, kv_stride_page, kv_stride_n, kv_stride_h;
+  const int32_t* kv_indices; const int32_t* kv_indptr;
+  void* o; float* lse;
+  float sm_scale, v_scale, logits_soft_cap; int32_t pos_encoding_mode;
+  const float* alibi_slopes; float rope_scale, rope_theta;
+  const float* sinks;
+  int32_t enable_pdl, device;
+  void* stream;
+} FiDecodeRunArgs;
+FI_API int fi_batch_decode_run_args(const FiDecodeRunArgs* a);
 
 /*
  * fi_single_decode_run — one request, contiguous K/V.

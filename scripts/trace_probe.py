@@ -1,6 +1,6 @@
 """Per-CTA phase timestamps of one decode launch (needs the trace build:
 `python flashinfer_b200/build.py --trace`, then FI_B200_LIB=flashinfer_b200/libfi_b200_trace.so).
-python scripts/trace_probe.py [bf16|fp8] [kv_len] [hkv]
+python scripts/trace_probe.py [bf16|fp8] [kv_len] [hkv] [bs]
 
 Slots (ns on %globaltimer, relative to the earliest CTA entry):
  0 entry  1 work list cached  2 PDL wait passed  3 producer: first page index known
@@ -29,7 +29,8 @@ def main():
     kind = sys.argv[1] if len(sys.argv) > 1 else "bf16"
     kv_len = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
     hkv = int(sys.argv[3]) if len(sys.argv) > 3 else 1
-    bs, page, d = 64, 16, 128
+    bs = int(sys.argv[4]) if len(sys.argv) > 4 else 64
+    page, d = 16, 128
     hq = hkv * (4 if kind == "bf16" else 8)
     kv_dtype = torch.bfloat16 if kind == "bf16" else torch.float8_e4m3fn
     lib = _lib.load()

@@ -95,9 +95,11 @@ PI = dict(magic=0, num_ctas=1, num_segments=2, num_merge=3, num_slots=4, off_hea
           num_items=6, off_segments=7, off_merge=8, off_tmp_o=9, off_tmp_lse=10,
           batch_size=11, hq=12, hkv=13, num_kv_heads=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
           cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23,
-          off_counters=24, off_item_heads=25, off_work_counter=26, kv_head_div=27)
+          off_counters=24, off_item_heads=25, off_work_counter=26, kv_head_div=27, off_indices=28,
+          num_indices=29, indices_stable=30)
 SEG_BYTES = 48    # sizeof(Segment)
-HEAD_BYTES = 160  # sizeof(ItemHead)
+HEAD_BYTES = 224  # sizeof(ItemHead)
+INLINE_PAGES = 16  # kItemInlinePages
 INLINE_SEGS = 3   # kItemInlineSegs
 TILE = 64        # tokens per tile for 16-bit KV (csrc/decode_params.h tile_tokens)
 TILE_FP8 = 128   # ... and for fp8 KV
@@ -106,7 +108,7 @@ TILE_FP8 = 128   # ... and for fp8 KV
 def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size,
               num_ctas, q_dtype=1, kv_dtype=1, window_left=-1, cuda_graph=0,
               kv_len=None, int_bytes=8 << 20, float_bytes=128 << 20, fixed_split_pages=0,
-              disable_split_kv=0):
+              disable_split_kv=0, indices=None):
     """Run fi_batch_decode_plan in host-only mode (device = -1) and decode the work list."""
     from flashinfer_b200 import _lib
 
@@ -116,11 +118,13 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
     lp = np.ascontiguousarray(np.asarray(last_page_len, dtype=np.int32))
     kl = None if kv_len is None else np.ascontiguousarray(np.asarray(kv_len, dtype=np.int32))
     info = np.zeros(lib.fi_plan_info_len(), dtype=np.int64)
+    ix = None if indices is None else np.ascontiguousarray(np.asarray(indices, dtype=np.int32))
     rc = lib.fi_batch_decode_plan(
         None, float_bytes, ws.ctypes.data, ws.ctypes.data, int_bytes, ip.ctypes.data,
         lp.ctypes.data, None if kl is None else kl.ctypes.data, len(lp), num_qo_heads,
         num_kv_heads, head_dim, page_size, q_dtype, kv_dtype, window_left, cuda_graph,
-        fixed_split_pages, disable_split_kv, -1, num_ctas, None, info.ctypes.data)
+        fixed_split_pages, disable_split_kv, -1, num_ctas, None,
+        None if indices is None else ix.ctypes.data, 0 if indices is None else len(ix), info.ctypes.data)
     if rc != 0:
         return rc, _lib.last_error(), None
     hdr = ws[info[PI["off_header"]]:info[PI["off_header"]] + 32].view(np.int32)
@@ -134,8 +138,8 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
     segs = seg_full[:, :8].copy()
     nm = int(hdr[2])
     merges = ws[info[PI["off_merge"]]:info[PI["off_merge"]] + 16 * nm].view(np.int32).reshape(nm, 4).copy()
-    # item heads (160 bytes): first, count, num_items, pad, then kItemInlineSegs inline Segment
-    # records; one head per item, padded with empty heads up to the launch grid
+    # item heads (224 bytes): first, count, num_items, num_pages, kItemInlineSegs inline Segment
+    # records, then kItemInlinePages page ids; one head per item, padded with empty heads up to the grid
     nheads = max(nitems, ncta)
     heads = ws[info[PI["off_item_heads"]]:info[PI["off_item_heads"]] + HEAD_BYTES * nheads].view(np.int32)
     heads = heads.reshape(nheads, HEAD_BYTES // 4).copy()
@@ -155,6 +159,29 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
         for k in range(min(int(heads[c, 1]), INLINE_SEGS)):
             inl = heads[c, 4 + 12 * k:4 + 12 * (k + 1)]
             assert np.array_equal(inl, seg_full[heads[c, 0] + k]), "inline segment != list segment"
+    # inline page ids: exactly the table entries the item's first tiles gather (or none at all)
+    tile = TILE if kv_dtype in (0, 1) else TILE_FP8
+    for c in range(nheads):
+        npg = int(heads[c, 3])
+        if ix is None or c >= nitems or heads[c, 1] == 0:
+            assert npg == 0
+            continue
+        s0 = seg_full[heads[c, 0]]
+        if s0[3] <= s0[2]:
+            assert npg == 0
+            continue
+        first_page = int(s0[2]) * tile // page_size
+        req_pages = int(ip[s0[0] + 1] - ip[s0[0]])
+        assert npg == min(INLINE_PAGES, req_pages - first_page) and npg > 0
+        exp = ix[s0[8] + first_page: s0[8] + first_page + npg]
+        assert np.array_equal(heads[c, 4 + 12 * INLINE_SEGS: 4 + 12 * INLINE_SEGS + npg], exp), "inline pages"
+    if ix is not None and not cuda_graph:
+        oi = int(info[PI["off_indices"]])
+        assert oi >= info[PI["off_segments"]] + SEG_BYTES * nseg and info[PI["num_indices"]] == len(ix)
+        assert np.array_equal(ws[oi:oi + 4 * len(ix)].view(np.int32), ix), "workspace copy of kv_indices"
+        assert info[PI["indices_stable"]] == 1
+    else:
+        assert info[PI["off_indices"]] == -1
     wc = ws[info[PI["off_work_counter"]]:info[PI["off_work_counter"]] + 4].view(np.int32)
     cnt = ws[info[PI["off_counters"]]:info[PI["off_counters"]] + 4 * max(nm, 1)].view(np.int32)
     assert wc[0] == 0 and np.all(cnt == 0), "scheduler / merge counters must start at zero"

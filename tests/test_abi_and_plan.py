@@ -48,11 +48,16 @@ CASES = [
 
 
 @pytest.mark.parametrize("head_group", ["1", "0"])
+@pytest.mark.parametrize("with_indices", [False, True])
 @pytest.mark.parametrize("kv_lens,hq,hkv,page,nctas", CASES)
-def test_plan_visits_every_token_once(kv_lens, hq, hkv, page, nctas, head_group, monkeypatch):
+def test_plan_visits_every_token_once(kv_lens, hq, hkv, page, nctas, head_group, with_indices, monkeypatch):
     monkeypatch.setenv("FI_B200_HEAD_GROUP", head_group)
     indptr, last = lens_to_table(kv_lens, page)
-    rc, err, plan = host_plan(indptr, last, hq, hkv, 128, page, nctas)
+    # a shuffled page table handed to the planner: host_plan checks that every item head carries
+    # exactly the page ids its first tiles gather and that the table is appended to the work list
+    indices = np.random.default_rng(len(kv_lens)).permutation(int(indptr[-1]) + 3)[: int(indptr[-1])] \
+        if with_indices else None
+    rc, err, plan = host_plan(indptr, last, hq, hkv, 128, page, nctas, indices=indices)
     assert rc == 0, err
     replay_plan(plan, kv_lens, hkv)
     # work items: contiguous stream ranges of non-increasing size (guided self-scheduling);
@@ -238,3 +243,47 @@ def test_plan_disable_split_kv():
     assert len(plan["merges"]) == 0 and plan["info"][PI["num_slots"]] == 0
     assert len(plan["segments"]) == len(kv_lens) * 4            # one whole-unit segment each
     assert all(int(s[4]) == -1 for s in plan["segments"])
+
+
+def test_argument_block_entry_points_match_the_positional_ones():
+    """fi_batch_decode_plan_args(FiDecodePlanArgs*) == fi_batch_decode_plan(...) bit for bit (host
+    mode), and the ctypes mirrors have the C layout (sizes are checked against a compiled probe)."""
+    import ctypes as C
+    import subprocess
+    import tempfile
+
+    from flashinfer_b200 import _lib
+
+    lib = _lib.load()
+    kv_lens, hq, hkv, page, nctas = [4096] * 8 + [77, 0, 5000], 32, 8, 16, 296
+    indptr, last = lens_to_table(kv_lens, page)
+    idx = np.random.default_rng(1).permutation(int(indptr[-1])).astype(np.int32)
+    rc, err, plan = host_plan(indptr, last, hq, hkv, 128, page, nctas, indices=idx)
+    assert rc == 0, err
+    ws = np.zeros(8 << 20, dtype=np.uint8)
+    info = np.zeros(lib.fi_plan_info_len(), dtype=np.int64)
+    a = _lib.DecodePlanArgs()
+    a.float_ws, a.float_ws_bytes = None, 128 << 20
+    a.int_ws = a.pinned_int_ws = ws.ctypes.data
+    a.int_ws_bytes = ws.size
+    a.indptr_host, a.last_page_len_host, a.kv_len_host = indptr.ctypes.data, last.ctypes.data, None
+    a.batch_size, a.num_qo_heads, a.num_kv_heads, a.head_dim, a.page_size = len(kv_lens), hq, hkv, 128, page
+    a.q_dtype = a.kv_dtype = 1
+    a.window_left, a.cuda_graph, a.fixed_split_pages, a.disable_split_kv = -1, 0, 0, 0
+    a.device, a.num_ctas_override, a.stream = -1, nctas, None
+    a.kv_indices_host, a.num_indices = idx.ctypes.data, len(idx)
+    a.plan_info_out = info.ctypes.data
+    assert lib.fi_batch_decode_plan_args(C.byref(a)) == 0, _lib.last_error()
+    assert np.array_equal(info, plan["info"])
+    used = int(info[PI["int_bytes"]])
+    rc2, _, plan2 = host_plan(indptr, last, hq, hkv, 128, page, nctas, indices=idx)
+    assert used == plan2["info"][PI["int_bytes"]]
+    assert lib.fi_batch_decode_plan_args(None) == _lib.FI_ERR_INVALID_ARGUMENT
+    assert lib.fi_batch_decode_run_args(None) == _lib.FI_ERR_INVALID_ARGUMENT
+    # struct layout: compile a three-line probe against the public header
+    src = '#include <stdio.h>\n#include "fi_b200.h"\nint main(void){printf("%zu %zu\\n", sizeof(FiDecodePlanArgs), sizeof(FiDecodeRunArgs));return 0;}\n'
+    with tempfile.TemporaryDirectory() as d:
+        (Path(d) / "p.c").write_text(src)
+        subprocess.run(["gcc", "-I", str(ROOT / "include"), "-o", f"{d}/p", f"{d}/p.c"], check=True)
+        sizes = subprocess.run([f"{d}/p"], capture_output=True, text=True, check=True).stdout.split()
+    assert [int(x) for x in sizes] == [C.sizeof(_lib.DecodePlanArgs), C.sizeof(_lib.DecodeRunArgs)]
