@@ -156,7 +156,7 @@ class Case:
     Distinct cache copies are rotated when one copy would fit in the 126 MB L2 several times over,
     so every step streams from HBM."""
 
-    def __init__(self, name, wl, hq, hkv, dev, kv_layout="NHD", page=16, seed=1234):
+    def __init__(self, name, wl, hq, hkv, dev, kv_layout="NHD", page=16, seed=1234, shuffle=True):
         import flashinfer_b200 as fi
 
         self.name, self.wl, self.hq, self.hkv, self.dev, self.page = name, wl, hq, hkv, dev, page
@@ -166,7 +166,7 @@ class Case:
         self.kv_dtype = torch.float8_e4m3fn if wl["kv_dtype"] == "e4m3" else torch.bfloat16
         self.kv_es = 1 if wl["kv_dtype"] == "e4m3" else 2
         self.q_dtype = torch.bfloat16
-        indptr, indices, last, self.total_pages = page_table(self.kv_lens, page)
+        indptr, indices, last, self.total_pages = page_table(self.kv_lens, page, shuffle=shuffle)
         self.indptr, self.indices, self.last = indptr.pin_memory(), indices.pin_memory(), last.pin_memory()
         self.cache_bytes = self.total_pages * 2 * page * hkv * HEAD_DIM * self.kv_es
         self.n_copies = max(1, min(8, math.ceil((512 << 20) / self.cache_bytes)))
@@ -350,7 +350,7 @@ def config_block(args, wl, world, hq, hkv, cache_bytes, n_copies):
                         (f" [page_size {args.page_size}]" if args.page_size != 16 else ""),
             "sharding": f"kv-head x{world}" if args.shard_of <= 1 else
                         f"ONE rank of a kv-head x{args.shard_of} sharding (not the whole job)",
-            "heads_per_rank": [hq, hkv], "page_table": "shuffled",
+            "heads_per_rank": [hq, hkv], "page_table": args.page_order,
             "l2": f"KV per rank {cache_bytes / 2**20:.0f} MiB > L2; {n_copies} cache "
                   f"cop{'y' if n_copies == 1 else 'ies'} rotated"}
 
@@ -374,7 +374,7 @@ def run_reference_gpu(args, wl, so_path):
     bs = len(kv_lens)
     kv_dtype = torch.float8_e4m3fn if wl["kv_dtype"] == "e4m3" else torch.bfloat16
     kv_es = 1 if wl["kv_dtype"] == "e4m3" else 2
-    indptr, indices, last, total_pages = page_table(kv_lens, page)
+    indptr, indices, last, total_pages = page_table(kv_lens, page, shuffle=args.page_order == "shuffled")
     cache_bytes = total_pages * 2 * page * hkv * HEAD_DIM * kv_es
     n_copies = max(1, min(8, math.ceil((512 << 20) / cache_bytes)))
     torch.manual_seed(1234)
@@ -717,7 +717,10 @@ def run_ours(args):
 
     sampler = ClockSampler(local_rank)
     sampler.start()  # before the warm-up; mark() tags the timed region
-    case = Case(args.workload, wl, hq, hkv, dev, kv_layout=args.kv_layout, page=args.page_size, seed=1234 + rank)
+    if args.loader != "auto":  # A/B of the two loaders on the same page geometry (development aid)
+        lib.fi_set_tuning(0, 0, 1 if args.loader == "tma" else 2, 0)
+    case = Case(args.workload, wl, hq, hkv, dev, kv_layout=args.kv_layout, page=args.page_size, seed=1234 + rank,
+                shuffle=args.page_order == "shuffled")
     bs = case.bs
     case.plan()
 
@@ -787,7 +790,8 @@ def run_ours(args):
     ms_total, kern_us, e2e, ag_max, pg_max = [float(x) for x in vals.tolist()]
 
     extras = {}
-    if not args.no_extras and args.shard_of <= 1 and args.workload == "c2" and args.page_size == 16:
+    plain = args.page_size == 16 and args.page_order == "shuffled" and args.loader == "auto"
+    if not args.no_extras and args.shard_of <= 1 and args.workload == "c2" and plain:
         steps_x = 30
         for nm in ("c3", "c4", "c5"):
             w2 = workload(nm)
@@ -813,7 +817,7 @@ def run_ours(args):
         line["parity"] = parity
         if extras:
             line["other_workloads"] = extras
-        if world == 1 and not args.no_extras and args.shard_of <= 1:
+        if world == 1 and not args.no_extras and args.shard_of <= 1 and plain:
             line["comparators"] = comparators_block(case)
             if args.workload == "c2":
                 line["sample_config"] = sample_config_block(dev)
@@ -901,6 +905,10 @@ def main():
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--page-size", type=int, default=16,
                     help="page size of the synthetic cache (BASELINE's configs use 16; 1 is SGLang's default)")
+    ap.add_argument("--page-order", default="shuffled", choices=["shuffled", "sequential"],
+                    help="page table of the synthetic cache: a random permutation (default) or the identity")
+    ap.add_argument("--loader", default="auto", choices=["auto", "tma", "cpasync"],
+                    help="development aid: force one of the two KV loaders of the 16-bit kernel")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip other_workloads / comparators / sample_config (development runs, ncu)")

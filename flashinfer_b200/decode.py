@@ -226,6 +226,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._pos_key = None
         self._planned_window_left = -1
         self._kv_sig = None
+        self._plan_sig = None
         self._dev_idx = device_index(self.device)
         self._lib = _lib.load()
         self._pdl_default = int(device_support_pdl(self.device))
@@ -319,10 +320,13 @@ class BatchDecodeWithPagedKVCacheWrapper:
 
         Cannot be captured in a CUDA graph (it reads indptr / last_page_len on the host).
         """
-        for tensor, name in [(indptr, "indptr"), (indices, "indices"), (last_page_len, "last_page_len")]:
-            if tensor.dtype != torch.int32:
-                raise ValueError(f"{name} must have dtype torch.int32, got {tensor.dtype}")
-        _unsupported_variant(pos_encoding_mode)
+        i32 = torch.int32
+        if indptr.dtype != i32 or indices.dtype != i32 or last_page_len.dtype != i32:
+            for tensor, name in [(indptr, "indptr"), (indices, "indices"), (last_page_len, "last_page_len")]:
+                if tensor.dtype != i32:
+                    raise ValueError(f"{name} must have dtype torch.int32, got {tensor.dtype}")
+        if pos_encoding_mode != "NONE":
+            _unsupported_variant(pos_encoding_mode)
         self._workspace_size = (
             self._float_workspace_buffer.numel() * self._float_workspace_buffer.element_size()
         )
@@ -483,14 +487,20 @@ class BatchDecodeWithPagedKVCacheWrapper:
         info = _PlanInfo()
         pa = self._pa
         pa.indptr_host, pa.last_page_len_host, pa.kv_len_host = indptr_ptr, lpl_ptr, kv_len_ptr
-        pa.batch_size, pa.num_qo_heads, pa.num_kv_heads = batch_size, num_qo_heads, num_kv_heads
-        pa.head_dim, pa.page_size = head_dim, page_size
-        pa.q_dtype, pa.kv_dtype = dtype_code(q_data_type), dtype_code(kv_data_type)
-        pa.window_left = int(window_left)
-        pa.cuda_graph = int(self._use_cuda_graph)
-        pa.fixed_split_pages = int(fixed_split_size) if fixed_split_size is not None and fixed_split_size > 0 else 0
-        pa.disable_split_kv = int(bool(disable_split_kv))
-        pa.num_ctas_override = 0
+        pa.batch_size = batch_size
+        # the problem description changes rarely between steps: rewritten only when it does
+        sig = (num_qo_heads, num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left,
+               fixed_split_size, disable_split_kv, self._use_cuda_graph)
+        if sig != self._plan_sig:
+            pa.num_qo_heads, pa.num_kv_heads = num_qo_heads, num_kv_heads
+            pa.head_dim, pa.page_size = head_dim, page_size
+            pa.q_dtype, pa.kv_dtype = dtype_code(q_data_type), dtype_code(kv_data_type)
+            pa.window_left = int(window_left)
+            pa.cuda_graph = int(self._use_cuda_graph)
+            pa.fixed_split_pages = int(fixed_split_size) if fixed_split_size is not None and fixed_split_size > 0 else 0
+            pa.disable_split_kv = int(bool(disable_split_kv))
+            pa.num_ctas_override = 0
+            self._plan_sig = sig
         pa.stream = current_stream_ptr(self.device)
         if indices_host is not None:
             pa.kv_indices_host, pa.num_indices = indices_host.data_ptr(), indices_host.numel()
