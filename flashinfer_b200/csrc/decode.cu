@@ -41,17 +41,20 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 4-D map over one of K / V: dims (D, n, h, page) — or (D, h, n, page) when the head
-// stride is the smaller one (NHD), so that strides grow with the dimension index.
+// stride is the smaller one (NHD), so that strides grow with the dimension index.  With
+// stride_kv > 0 the map is 5-D, (D, n|h, h|n, K|V, page), over K and V together: one box
+// {128 B, rows_per_box, 1, 2, 1} brings the K and the V rows of a token block.
 // A descriptor is a pure function of these arguments; a serving loop calls run() with the same
 // few caches (one per layer), so the last encodings are kept per thread.
 struct KvMapKey {
   const void* base;
-  int64_t dim_n, dim_h, dim_page, stride_n, stride_h, stride_page;
+  int64_t dim_n, dim_h, dim_page, stride_n, stride_h, stride_page, stride_kv;
   int kv_dtype, head_dim, rows_per_box;
   bool operator==(const KvMapKey& o) const {
     return base == o.base && dim_n == o.dim_n && dim_h == o.dim_h && dim_page == o.dim_page &&
            stride_n == o.stride_n && stride_h == o.stride_h && stride_page == o.stride_page &&
-           kv_dtype == o.kv_dtype && head_dim == o.head_dim && rows_per_box == o.rows_per_box;
+           stride_kv == o.stride_kv && kv_dtype == o.kv_dtype && head_dim == o.head_dim &&
+           rows_per_box == o.rows_per_box;
   }
 };
 constexpr int kMapCacheSize = 256;  // K and V of 128 layers
@@ -63,18 +66,18 @@ struct KvMapCache {
 
 static int encode_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int head_dim,
                          int64_t dim_n, int64_t dim_h, int64_t dim_page, int64_t stride_n,
-                         int64_t stride_h, int64_t stride_page, int rows_per_box);
+                         int64_t stride_h, int64_t stride_page, int rows_per_box, int64_t stride_kv);
 
 static int make_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int head_dim,
                        int64_t dim_n, int64_t dim_h, int64_t dim_page, int64_t stride_n,
-                       int64_t stride_h, int64_t stride_page, int rows_per_box) {
+                       int64_t stride_h, int64_t stride_page, int rows_per_box, int64_t stride_kv = 0) {
   static thread_local KvMapCache cache;
-  const KvMapKey key = {base, dim_n, dim_h, dim_page, stride_n, stride_h, stride_page,
+  const KvMapKey key = {base, dim_n, dim_h, dim_page, stride_n, stride_h, stride_page, stride_kv,
                         kv_dtype, head_dim, rows_per_box};
   for (int i = 0; i < cache.used; ++i)
     if (cache.key[i] == key) { *map = cache.map[i]; return FI_OK; }
   const int rc = encode_kv_map(map, base, kv_dtype, head_dim, dim_n, dim_h, dim_page, stride_n,
-                               stride_h, stride_page, rows_per_box);
+                               stride_h, stride_page, rows_per_box, stride_kv);
   if (rc != FI_OK) return rc;
   const int slot = cache.used < kMapCacheSize ? cache.used++ : (cache.next++ % kMapCacheSize);
   cache.key[slot] = key;
@@ -84,24 +87,30 @@ static int make_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int hea
 
 static int encode_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int head_dim,
                          int64_t dim_n, int64_t dim_h, int64_t dim_page, int64_t stride_n,
-                         int64_t stride_h, int64_t stride_page, int rows_per_box) {
+                         int64_t stride_h, int64_t stride_page, int rows_per_box, int64_t stride_kv) {
   EncodeTiledFn enc = get_encode_fn();
   if (enc == nullptr) return fail(FI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
   const int es = dtype_size(kv_dtype);
   CUtensorMapDataType dt = es == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
                                    : (kv_dtype == FI_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                                 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
-  cuuint64_t dims[4] = {(cuuint64_t)head_dim, (cuuint64_t)dim_n, (cuuint64_t)dim_h,
-                        (cuuint64_t)dim_page};
-  cuuint64_t strides[3] = {(cuuint64_t)(stride_n * es), (cuuint64_t)(stride_h * es),
-                           (cuuint64_t)(stride_page * es)};
-  cuuint32_t box[4] = {(cuuint32_t)(128 / es), (cuuint32_t)rows_per_box, 1, 1};
+  const bool five = stride_kv > 0;
+  cuuint64_t dims[5] = {(cuuint64_t)head_dim, (cuuint64_t)dim_n, (cuuint64_t)dim_h,
+                        (cuuint64_t)dim_page, 1};
+  cuuint64_t strides[4] = {(cuuint64_t)(stride_n * es), (cuuint64_t)(stride_h * es),
+                           (cuuint64_t)(stride_page * es), 0};
+  cuuint32_t box[5] = {(cuuint32_t)(128 / es), (cuuint32_t)rows_per_box, 1, 1, 1};
+  if (five) {  // (D, n, h, K|V, page)
+    dims[3] = 2; dims[4] = (cuuint64_t)dim_page;
+    strides[2] = (cuuint64_t)(stride_kv * es); strides[3] = (cuuint64_t)(stride_page * es);
+    box[3] = 2;
+  }
   if (stride_h < stride_n) {
     std::swap(dims[1], dims[2]);
     std::swap(strides[0], strides[1]);
     std::swap(box[1], box[2]);
   }
-  cuuint32_t estr[4] = {1, 1, 1, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   // L2 promotion must not exceed the contiguous run of one (token, head) row: a 128-byte row
   // (fp8 D=128, 16-bit D=64) inside an NHD page has another head's row next to it, and
   // promoting to 256 B would drag that row through DRAM for nothing (measured 1.49x traffic).
@@ -110,7 +119,7 @@ static int encode_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int h
   const CUtensorMapL2promotion promo = (row_bytes >= 256 || rows_adjacent)
                                            ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B
                                            : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
-  CUresult r = enc(map, dt, 4, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(map, dt, five ? 5 : 4, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(FI_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
@@ -422,12 +431,21 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   memset(&vm, 0, sizeof(vm));
   if (tma) {
     const int Hkv_mem = Hkv / p.kv_head_div;  // heads the cache really has
+    // K and V of a page interleaved inside the page stride (the 5-D cache every engine allocates):
+    // one 5-D map over both, one TMA box per (page, token block) instead of two (mma.sync kernel)
+    const int64_t kv_gap = (static_cast<const char*>(v_cache) - static_cast<const char*>(k_cache)) / es;
+    static const bool pair_env = [] { const char* e = getenv("FI_B200_TMA_PAIRED"); return !(e && e[0] == '0'); }();
+    const bool tc5 = kvf != 0 && head_dim == 128 && use_tc5() && !p.rope;
+    p.tma_paired = pair_env && !tc5 && v_cache > k_cache && kv_gap * es % 16 == 0 && kv_gap < kv_stride_page &&
+                   (static_cast<const char*>(v_cache) - static_cast<const char*>(k_cache)) % es == 0;
     int rc = make_kv_map(&km, k_cache, kv_dtype, head_dim, page_size, Hkv_mem, num_pages, kv_stride_n,
-                         kv_stride_h, kv_stride_page, p.rows_per_box);
+                         kv_stride_h, kv_stride_page, p.rows_per_box, p.tma_paired ? kv_gap : 0);
     if (rc != FI_OK) return rc;
-    rc = make_kv_map(&vm, v_cache, kv_dtype, head_dim, page_size, Hkv_mem, num_pages, kv_stride_n,
-                     kv_stride_h, kv_stride_page, p.rows_per_box);
-    if (rc != FI_OK) return rc;
+    if (!p.tma_paired) {
+      rc = make_kv_map(&vm, v_cache, kv_dtype, head_dim, page_size, Hkv_mem, num_pages, kv_stride_n,
+                       kv_stride_h, kv_stride_page, p.rows_per_box);
+      if (rc != FI_OK) return rc;
+    }
   }
   int rc = launch_decode(p, km, vm, q_dtype, kvf, head_dim, (int)plan_info[kPiNumCtas], tma, stream);
   if (rc != FI_OK) return rc;

@@ -85,12 +85,30 @@ struct SmemLayout {
   }
 };
 
-// byte offset of (row, 16B-chunk) inside the K (or V) part of a stage, 128B swizzle
+// byte offset of (row, 16B-chunk) inside the K (or V) part of a stage, 128B swizzle — the layout of
+// the tcgen05 kernel (its MMA descriptors want the 128 K rows of a tile contiguous): K part, V part
 template <int TT>
 __device__ __forceinline__ uint32_t swz(int row, int chunk) {
   return (uint32_t)((chunk >> 3) * (TT * 128) + row * 128 +
                     (((chunk & 7) ^ (row & 7)) << 4));
 }
+
+// Layout of the mma.sync kernel: K and V of the same token block sit next to each other, so that ONE
+// 5-D TMA box {128 B, rows_per_box tokens, 1 head, K|V, 1 page} fills both — half as many TMA
+// instructions per tile as a K box and a V box (the TMA unit's per-box cost, not DRAM, bounds small
+// boxes: C2 at page 8 ran at 227 us vs 162 us at page 16 and 158 us at page 32 with K / V boxes):
+//   stage = [128-byte panel pn][token block j of rpb rows][K rows | V rows][row][128 B, swizzled]
+// rmask = ~(rpb - 1); the V row is vdelta = rpb * 128 bytes after its K row.  With rpb = TT (the
+// cp.async loader) this degenerates to [panel][K | V][row].
+template <int TT>
+struct StageRow {
+  uint32_t base, r7;
+  __device__ __forceinline__ StageRow(int row, int rmask)
+      : base((uint32_t)(row + (row & rmask)) * 128u), r7((uint32_t)row & 7u) {}
+  __device__ __forceinline__ uint32_t at(int chunk) const {  // K; V: + vdelta
+    return (uint32_t)(chunk >> 3) * (2u * TT * 128u) + base + ((((uint32_t)chunk & 7u) ^ r7) << 4);
+  }
+};
 
 // ---- segment queue ---------------------------------------------------------------
 // A CTA works through a run-time sequence of segments: those of item blockIdx.x, then those of
@@ -360,7 +378,9 @@ __device__ __forceinline__ bool feeder_await(Feeder& f, const SegSource& s, int 
 // (A variant that also pulled tiles beyond the ring into L2 with cp.async.bulk.prefetch.tensor
 // was measured 1.5x SLOWER on B200 — the prefetch boxes compete with the demand boxes — and
 // was removed; see DESIGN.md.)
-template <int KVF, int HD>
+// PAIRED (the mma.sync kernel): the StageRow layout; with p.tma_paired the K and V panels of a
+// (page, token block) come in ONE 5-D box through `kmap`, else as a K box and a V box.
+template <int KVF, int HD, bool PAIRED = false>
 __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSource& src,
                                             const CUtensorMap* kmap, const CUtensorMap* vmap,
                                             uint32_t ring, uint32_t full_bar, uint32_t empty_bar) {
@@ -368,7 +388,8 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
   const int lane = threadIdx.x & 31;
   const int rpb = p.rows_per_box;
   const int bpt = G::TT / rpb;  // boxes per tile along tokens: a power of two <= 16
-  const int nbox = 2 * G::NP * bpt;
+  const bool one_box = PAIRED && p.tma_paired != 0;
+  const int nbox = (one_box ? 1 : 2) * G::NP * bpt;
   const int j = lane % bpt;  // same j for every i = lane + 32 k since bpt | 32
   const uint32_t box_bytes = (uint32_t)rpb * 128u;
 
@@ -431,18 +452,28 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
     if (lane == 0) mbar_arrive_expect_tx(full_bar + 8 * stage, 2u * G::NP * nvb * box_bytes);
     __syncwarp();
     if (j < nvb) {
-      const uint32_t sbase = ring + stage * G::STAGE_BYTES + j * box_bytes;
+      const uint32_t sbase = ring + stage * G::STAGE_BYTES + (PAIRED ? 2 : 1) * j * box_bytes;
+      const int c1 = p.tma_h_first ? mem_head : row0, c2 = p.tma_h_first ? row0 : mem_head;
       for (int i = lane; i < nbox; i += 32) {
         const int pn = (i / bpt) % G::NP;
         const int kv = i / (bpt * G::NP);
-        if (hints)
+        if constexpr (PAIRED) {
+          const uint32_t dst = sbase + pn * (2 * G::PANEL_BYTES) + kv * box_bytes;
+          if (one_box) {
+            if (hints) tma_load_5d_hint(dst, kmap, full_bar + 8 * stage, pn * (128 / G::ES), c1, c2, 0, page, pol_stream);
+            else tma_load_5d(dst, kmap, full_bar + 8 * stage, pn * (128 / G::ES), c1, c2, 0, page);
+          } else if (hints) {
+            tma_load_4d_hint(dst, kv ? vmap : kmap, full_bar + 8 * stage, pn * (128 / G::ES), c1, c2, page, pol_stream);
+          } else {
+            tma_load_4d(dst, kv ? vmap : kmap, full_bar + 8 * stage, pn * (128 / G::ES), c1, c2, page);
+          }
+        } else if (hints) {
           tma_load_4d_hint(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
-                           full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? mem_head : row0,
-                           p.tma_h_first ? row0 : mem_head, page, pol_stream);
-        else
+                           full_bar + 8 * stage, pn * (128 / G::ES), c1, c2, page, pol_stream);
+        } else {
           tma_load_4d(sbase + kv * G::KV_BYTES + pn * G::PANEL_BYTES, kv ? vmap : kmap,
-                      full_bar + 8 * stage, pn * (128 / G::ES), p.tma_h_first ? mem_head : row0,
-                      p.tma_h_first ? row0 : mem_head, page);
+                      full_bar + 8 * stage, pn * (128 / G::ES), c1, c2, page);
+        }
       }
     }
     __syncwarp();
@@ -457,26 +488,66 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
 // ---- producer: 16-byte cp.async gathers (any page size / stride) -------------
 // Runs in kCpAsyncProducerThreads threads (ptid = 0 ..): warp 0 is also the feeder, warp 1 reads
 // the ring like a consumer.  Rows past tok_hi are zero-filled.
+// A thread owns one 16-byte chunk column of PASSES rows of every tile.  Two things bounded the first
+// version of this loader at 2.1x .. 4.3x the TMA loader's time (C2: 342 us at page 16, 690 us at page
+// 1, against 162 us): a dependent page-table load in front of every row's address, and ~40 integer
+// instructions per row in two warps.  Now
+//   * the page ids of a tile are fetched ONE TILE AHEAD, one table entry per lane (a tile touches at
+//     most 64 pages), and handed to the rows by warp shuffles;
+//   * everything about a row that does not depend on the tile (destination, offset inside the page)
+//     is folded at compile time or hoisted, so a row costs one 64-bit multiply-add and two cp.async.
+template <int KVF, int HD>
+struct CpAsyncGeom {
+  using G = TileGeom<KVF, HD>;
+  static constexpr int CPR = G::CHUNKS;
+  static constexpr int RPP = kCpAsyncProducerThreads / CPR;  // rows per pass
+  static constexpr int PASSES = G::TT / RPP;
+  static constexpr int SLOTS = (G::TT + 31) / 32;            // page-id registers per lane
+  static_assert(kCpAsyncProducerThreads % CPR == 0 && G::TT % RPP == 0, "bad cp.async geometry");
+};
+
+// page ids of tile t of segment sg: slot i <-> the i-th page the tile touches, lane (i & 31) holds it
+template <int KVF, int HD>
+__device__ __forceinline__ void cpasync_tile_pages(int (&pg)[CpAsyncGeom<KVF, HD>::SLOTS],
+                                                   const DecodeParams& p, const Segment& sg, int t,
+                                                   int lane) {
+  using G = TileGeom<KVF, HD>;
+  const int tok0 = t * G::TT;
+  const int pit0 = p.page_shift >= 0 ? tok0 >> p.page_shift : tok0 / p.page_size;
+  const int last_tok = min(tok0 + G::TT, sg.tok_hi) - 1;  // >= tok0: a listed tile has tokens
+  const int pit1 = p.page_shift >= 0 ? last_tok >> p.page_shift : last_tok / p.page_size;
+#pragma unroll
+  for (int i = 0; i < CpAsyncGeom<KVF, HD>::SLOTS; ++i) {
+    const int pit = pit0 + 32 * i + lane;
+    int page = 0;
+    if (pit <= pit1) page = p.kv_indices ? __ldg(p.kv_indices + sg.page_base + pit) : sg.page_base + pit;
+    pg[i] = page;
+  }
+}
+
 template <int KVF, int HD>
 __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const SegSource& src, int ptid,
                                                 uint32_t ring, uint32_t full_bar,
                                                 uint32_t empty_bar) {
   using G = TileGeom<KVF, HD>;
-  constexpr int CPR = G::CHUNKS;
-  constexpr int RPP = kCpAsyncProducerThreads / CPR;  // rows per pass
-  constexpr int PASSES = G::TT / RPP;
-  static_assert(kCpAsyncProducerThreads % CPR == 0 && G::TT % RPP == 0, "bad cp.async geometry");
-  const int c = ptid % CPR;
-  const int r0 = ptid / CPR;
+  using R = CpAsyncGeom<KVF, HD>;
+  const int c = ptid % R::CPR;
+  const int r0 = ptid / R::CPR;
   const int lane = ptid & 31;
   const bool feeds = ptid < 32;
   const char* kb = static_cast<const char*>(p.k);
   const char* vb = static_cast<const char*>(p.v);
+  // page sizes that are a power of two <= the tile: a row's place inside its page does not depend on
+  // the tile, and its page slot is a shift of the row index
+  const bool pow2_page = p.page_shift >= 0 && p.page_size <= G::TT;
+  const int64_t stride_page_b = p.kv_stride_page * G::ES, stride_n_b = p.kv_stride_n * G::ES;
   Feeder f;
   feeder_init(f, src);
   int tiles_issued = 0;
   int stage = 0;
   uint32_t phase = 0;
+  int cur[R::SLOTS], nxt[R::SLOTS];
+  bool have_nxt = false;  // nxt holds the pages of the tile about to be issued (warp-uniform)
   for (int k = 0;; ++k) {
     Segment sg;
     if (feeds) {
@@ -488,29 +559,61 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
       __syncwarp();
       if (lane == 0) src.ctl[kQDone1] = k + 1;
     }
-    const int page_base = sg.page_base;
-    const int64_t head_off = (int64_t)(sg.kv_head / p.kv_head_div) * p.kv_stride_h + c * (16 / G::ES);
+    const int64_t col_b = ((int64_t)(sg.kv_head / p.kv_head_div) * p.kv_stride_h + c * (16 / G::ES)) * G::ES;
     for (int t = sg.tile_begin; t < sg.tile_end; ++t) {
       if (feeds) feeder_step(f, src, k, tiles_issued, lane);
+      if (have_nxt) {
+#pragma unroll
+        for (int i = 0; i < R::SLOTS; ++i) cur[i] = nxt[i];
+      } else {
+        cpasync_tile_pages<KVF, HD>(cur, p, sg, t, lane);
+      }
+      // the next tile's pages: same segment, or the first tile of the next segment that has tiles
+      // when it is already published (a non-blocking look: the feeder must not wait here)
+      have_nxt = false;
+      if (t + 1 < sg.tile_end) {
+        cpasync_tile_pages<KVF, HD>(nxt, p, sg, t + 1, lane);
+        have_nxt = true;
+      } else {
+        const bool pub = feeds ? (k + 1 < f.pub) : seg_peek(src, k + 1);
+        if (__shfl_sync(0xffffffffu, pub ? 1 : 0, 0) != 0) {
+          const Segment sn = seg_read(src, k + 1);
+          if (sn.tile_end > sn.tile_begin) {
+            cpasync_tile_pages<KVF, HD>(nxt, p, sn, sn.tile_begin, lane);
+            have_nxt = true;
+          }
+        }
+      }
       mbar_wait(empty_bar + 8 * stage, phase ^ 1);
       const uint32_t sk = ring + stage * G::STAGE_BYTES;
-#pragma unroll 4
-      for (int ps = 0; ps < PASSES; ++ps) {
-        const int row = ps * RPP + r0;
-        const int tok = t * G::TT + row;
-        const bool valid = tok < sg.tok_hi;
-        int64_t off = 0;
-        if (valid) {
-          int pit, rip;
-          if (p.page_shift >= 0) { pit = tok >> p.page_shift; rip = tok & p.page_mask; }
-          else { pit = tok / p.page_size; rip = tok - pit * p.page_size; }
-          const int page = p.kv_indices ? __ldg(p.kv_indices + page_base + pit) : page_base + pit;
-          off = ((int64_t)page * p.kv_stride_page + (int64_t)rip * p.kv_stride_n + head_off) *
-                G::ES;
+      const int tok0 = t * G::TT;
+      const int nvalid = sg.tok_hi - tok0;  // rows of this tile that hold tokens (>= TT: all)
+      const int pit0 = p.page_shift >= 0 ? tok0 >> p.page_shift : tok0 / p.page_size;
+#pragma unroll
+      for (int ps = 0; ps < R::PASSES; ++ps) {
+        const int row = ps * R::RPP + r0;
+        int slot, rip;
+        if (pow2_page) { slot = row >> p.page_shift; rip = row & p.page_mask; }
+        else {
+          const int tok = tok0 + row;
+          const int pit = p.page_shift >= 0 ? tok >> p.page_shift : tok / p.page_size;
+          slot = pit - pit0;
+          rip = tok - pit * p.page_size;
         }
-        const uint32_t d = sk + swz<G::TT>(row, c);
+        // every lane takes part in the shuffle; rows past the end read a valid lane's (unused) value
+        int page = __shfl_sync(0xffffffffu, cur[0], slot & 31);
+        if constexpr (R::SLOTS > 1) {
+#pragma unroll
+          for (int i = 1; i < R::SLOTS; ++i) {
+            const int other = __shfl_sync(0xffffffffu, cur[i], slot & 31);
+            page = (slot >> 5) == i ? other : page;
+          }
+        }
+        const bool valid = row < nvalid;
+        const int64_t off = valid ? (int64_t)page * stride_page_b + (int64_t)rip * stride_n_b + col_b : 0;
+        const uint32_t d = sk + StageRow<G::TT>(row, ~(G::TT - 1)).at(c);
         cp_async_16(d, kb + off, valid ? 16u : 0u);
-        cp_async_16(d + G::KV_BYTES, vb + off, valid ? 16u : 0u);
+        cp_async_16(d + G::PANEL_BYTES, vb + off, valid ? 16u : 0u);
       }
       cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
       if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
@@ -542,17 +645,18 @@ __device__ __forceinline__ void load_q_frags16(uint32_t (&qf)[HD / 16][2], const
 // S^T(16 tokens x 8 heads) for this warp's token slice (rows row0 .. row0+15 of the stage)
 template <int QT, int HD>
 __device__ __forceinline__ void qk_tile16(float (&s)[4], uint32_t kbase, int row0, int lane,
-                                          const uint32_t (&qf)[HD / 16][2]) {
+                                          const uint32_t (&qf)[HD / 16][2], int rmask) {
   constexpr bool BF = (QT == 1);
   constexpr int KS = HD / 16;
   // ldmatrix.x4 address pattern: row = (lane&7) + 8*((lane>>3)&1), chunk += lane>>4
-  const int krow = row0 + (lane & 7) + 8 * ((lane >> 3) & 1), kch = lane >> 4;
+  const int kch = lane >> 4;
+  const StageRow<64> kr(row0 + (lane & 7) + 8 * ((lane >> 3) & 1), rmask);
   float s1[4] = {0.f, 0.f, 0.f, 0.f};
   s[0] = s[1] = s[2] = s[3] = 0.f;
 #pragma unroll
   for (int ks = 0; ks < KS; ++ks) {
     uint32_t a[4];
-    ldmatrix_x4(a, kbase + swz<64>(krow, 2 * ks + kch));
+    ldmatrix_x4(a, kbase + kr.at(2 * ks + kch));
     if (ks & 1) mma_16816<BF>(s1, a, qf[ks][0], qf[ks][1]);
     else mma_16816<BF>(s, a, qf[ks][0], qf[ks][1]);
   }
@@ -617,18 +721,19 @@ __device__ __forceinline__ void rope_rotate_q(uint32_t (&qf)[HD / 16][2], const 
 template <int QT, int HD>
 __device__ __forceinline__ void qk_tile16_rope(float (&s)[4], uint32_t kbase, int row0, int lane,
                                                const uint32_t (&qf)[HD / 16][2],
-                                               const float (&freq)[HD / 8], int tok_g) {
+                                               const float (&freq)[HD / 8], int tok_g, int rmask) {
   constexpr bool BF = (QT == 1);
   constexpr int H = HD / 32;
-  const int krow = row0 + (lane & 7) + 8 * ((lane >> 3) & 1), kch = lane >> 4;
+  const int kch = lane >> 4;
+  const StageRow<64> kr(row0 + (lane & 7) + 8 * ((lane >> 3) & 1), rmask);
   const float pos[2] = {(float)tok_g, (float)(tok_g + 8)};
   float s1[4] = {0.f, 0.f, 0.f, 0.f};
   s[0] = s[1] = s[2] = s[3] = 0.f;
 #pragma unroll
   for (int ks = 0; ks < H; ++ks) {
     uint32_t a[4], b[4];
-    ldmatrix_x4(a, kbase + swz<64>(krow, 2 * ks + kch));
-    ldmatrix_x4(b, kbase + swz<64>(krow, 2 * (ks + H) + kch));
+    ldmatrix_x4(a, kbase + kr.at(2 * ks + kch));
+    ldmatrix_x4(b, kbase + kr.at(2 * (ks + H) + kch));
 #pragma unroll
     for (int r = 0; r < 4; ++r) {  // r & 1: row g / g + 8; r >> 1: columns 2t.. / 2t + 8..
       float s0, c0, sn1, c1;
@@ -648,14 +753,15 @@ __device__ __forceinline__ void qk_tile16_rope(float (&s)[4], uint32_t kbase, in
 // O^T(HD x 8 heads) += V^T . P^T for this warp's 16 tokens; (pb0, pb1) = B fragments of P^T
 template <int QT, int HD>
 __device__ __forceinline__ void pv_tile16(float (&o)[HD / 16][4], uint32_t vbase, int row0,
-                                          int lane, uint32_t pb0, uint32_t pb1) {
+                                          int lane, uint32_t pb0, uint32_t pb1, int rmask) {
   constexpr bool BF = (QT == 1);
   // ldmatrix.x4.trans pattern: row = (lane&7) + 8*(lane>>4), chunk += (lane>>3)&1
-  const int vrow = row0 + (lane & 7) + 8 * (lane >> 4), vch = (lane >> 3) & 1;
+  const int vch = (lane >> 3) & 1;
+  const StageRow<64> vr(row0 + (lane & 7) + 8 * (lane >> 4), rmask);
 #pragma unroll
   for (int mt = 0; mt < HD / 16; ++mt) {
     uint32_t a[4];
-    ldmatrix_x4_trans(a, vbase + swz<64>(vrow, 2 * mt + vch));
+    ldmatrix_x4_trans(a, vbase + vr.at(2 * mt + vch));
     mma_16816<BF>(o[mt], a, pb0, pb1);
   }
 }
@@ -717,9 +823,10 @@ template <int KVF, int HD>
 __device__ __forceinline__ void qk_tile8(float (&s)[2][4], uint32_t kbase, int row0, int lane,
                                          const uint32_t (&qhi)[HD / 32][2],
                                          const uint32_t (&qlo)[HD / 32][2],
-                                         const uint32_t (&ql2)[HD / 32][2]) {
+                                         const uint32_t (&ql2)[HD / 32][2], int rmask) {
   constexpr int KB = HD / 32;
   const int krow = row0 + (lane & 7) + 8 * ((lane >> 3) & 1), kch = lane >> 4;
+  const StageRow<128> kr0(krow, rmask), kr1(krow + 16, rmask);
   float s2[2][4];
 #pragma unroll
   for (int mb = 0; mb < 2; ++mb)
@@ -730,7 +837,7 @@ __device__ __forceinline__ void qk_tile8(float (&s)[2][4], uint32_t kbase, int r
 #pragma unroll
     for (int mb = 0; mb < 2; ++mb) {
       uint32_t a[4];
-      ldmatrix_x4(a, kbase + swz<128>(krow + 16 * mb, 2 * c + kch));
+      ldmatrix_x4(a, kbase + (mb ? kr1 : kr0).at(2 * c + kch));
       mma_16832_fp8<KVF == 2>(s[mb], a, qhi[c][0], qhi[c][1]);
       mma_16832_fp8<KVF == 2>(s2[mb], a, qlo[c][0], qlo[c][1]);
       mma_16832_fp8<KVF == 2>(s2[mb], a, ql2[c][0], ql2[c][1]);
@@ -748,12 +855,12 @@ __device__ __forceinline__ void qk_tile8(float (&s)[2][4], uint32_t kbase, int r
 // same token order.
 template <int KVF, int HD>
 __device__ __forceinline__ void pv_tile8(float (&o)[HD / 16][4], uint32_t vbase, int row0, int lane,
-                                         const uint32_t (&bh)[2], const uint32_t (&bl)[2]) {
-  const int vrow = row0 + lane;  // matrix j = lane>>3 covers tokens 8j .. 8j+7
+                                         const uint32_t (&bh)[2], const uint32_t (&bl)[2], int rmask) {
+  const StageRow<128> vr(row0 + lane, rmask);  // matrix j = lane>>3 covers tokens 8j .. 8j+7
 #pragma unroll
   for (int c = 0; c < HD / 16; ++c) {
     uint32_t r[4], a[4];
-    ldmatrix_x4_trans(r, vbase + swz<128>(vrow, c));
+    ldmatrix_x4_trans(r, vbase + vr.at(c));
     a[0] = prmt(r[0], r[1], 0x6420u);
     a[1] = prmt(r[0], r[1], 0x7531u);
     a[2] = prmt(r[2], r[3], 0x6420u);
@@ -895,6 +1002,11 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
   const float cap_pre = use_cap ? p.sm_scale / p.soft_cap : 0.f;
   const float cap_post = use_cap ? p.soft_cap * 1.4426950408889634f : 0.f;
   const int row0 = warp * TPW;
+  // stage layout (StageRow): token blocks of rpb rows, K rows then V rows; the cp.async loader
+  // writes whole-tile blocks
+  const int rpb = LOADER == 0 ? p.rows_per_box : G::TT;
+  const int rmask = ~(rpb - 1);
+  const uint32_t vdelta = (uint32_t)rpb * 128u;
   static_assert(!ROPE || KVF == 0, "in-register RoPE is built for 16-bit KV");
   [[maybe_unused]] float freq[ROPE ? HD / 8 : 1];
   if constexpr (ROPE) rope_freqs<HD>(freq, p, t);
@@ -973,12 +1085,12 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
       const int vcount = min(TPW, sg.tok_hi - tok0);
       if (vcount > 0 && tok0 + TPW > sg.tok_lo) {  // warp-uniform
         const uint32_t kbase = ring + stage * G::STAGE_BYTES;
-        const uint32_t vbase = kbase + G::KV_BYTES;
+        const uint32_t vbase = kbase + vdelta;
         if constexpr (LOADER == 0) {
           if (vcount < TPW) {  // rows the TMA did not (validly) fill: zero V so 0 * junk != NaN
             for (int i = lane; i < (TPW - vcount) * G::CHUNKS; i += 32) {
               const int row = row0 + vcount + i / G::CHUNKS;
-              const uint32_t a = vbase + swz<G::TT>(row, i % G::CHUNKS);
+              const uint32_t a = vbase + StageRow<G::TT>(row, rmask).at(i % G::CHUNKS);
               asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(a), "r"(0u) : "memory");
             }
             __syncwarp();
@@ -986,8 +1098,8 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
         }
         if constexpr (KVF == 0) {
           float s[4];
-          if constexpr (ROPE) qk_tile16_rope<QT, HD>(s, kbase, row0, lane, qf, freq, tok0 + g);
-          else qk_tile16<QT, HD>(s, kbase, row0, lane, qf);
+          if constexpr (ROPE) qk_tile16_rope<QT, HD>(s, kbase, row0, lane, qf, freq, tok0 + g, rmask);
+          else qk_tile16<QT, HD>(s, kbase, row0, lane, qf, rmask);
           // s[0],s[1]: token g, heads 2t,2t+1;  s[2],s[3]: token g+8
           const int ta = tok0 + g, tb = ta + 8;
           const bool va = ta >= sg.tok_lo && ta < sg.tok_hi;
@@ -1027,10 +1139,10 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
           }
           const uint32_t pb0 = movmatrix_trans(pack2<BF>(pr[0], pr[1]));
           const uint32_t pb1 = movmatrix_trans(pack2<BF>(pr[2], pr[3]));
-          pv_tile16<QT, HD>(o, vbase, row0, lane, pb0, pb1);
+          pv_tile16<QT, HD>(o, vbase, row0, lane, pb0, pb1, rmask);
         } else {
           float s[2][4];
-          qk_tile8<KVF, HD>(s, kbase, row0, lane, qf, ql, ql2);
+          qk_tile8<KVF, HD>(s, kbase, row0, lane, qf, ql, ql2, rmask);
           // s[mb][0..1]: token 16mb+g, heads 2t,2t+1;  s[mb][2..3]: token 16mb+g+8
           bool valid[2][2];
           float mx[2] = {kNegInf, kNegInf};
@@ -1082,7 +1194,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
           // after the transpose lane (g, t) holds, for head g, [tok 2t: hi, lo | tok 2t+1: hi, lo]
           const uint32_t bh[2] = {prmt(tq[0], tq[1], 0x6420u), prmt(tq[2], tq[3], 0x6420u)};
           const uint32_t bl[2] = {prmt(tq[0], tq[1], 0x7531u), prmt(tq[2], tq[3], 0x7531u)};
-          pv_tile8<KVF, HD>(o, vbase, row0, lane, bh, bl);
+          pv_tile8<KVF, HD>(o, vbase, row0, lane, bh, bl, rmask);
         }
         if constexpr (LOADER == 0) {
           if (vcount < TPW) fence_proxy_async_smem();  // generic zero-fill before next TMA write
@@ -1276,7 +1388,7 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
     if (p.enable_pdl) pdl_wait();
     consume<QT, KVF, HD, LOADER, ROPE>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
   } else if (LOADER == 0) {
-    produce_tma<KVF, HD>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);  // waits inside
+    produce_tma<KVF, HD, true>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);  // waits inside
   } else {
     if (p.enable_pdl) pdl_wait();
     produce_cpasync<KVF, HD>(p, src, tid - kConsumerWarps * 32, ring, full_bar, empty_bar);

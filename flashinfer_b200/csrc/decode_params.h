@@ -145,6 +145,7 @@ struct DecodeParams {
   int32_t page_mask;   // page_size - 1 when a power of two (0x7fffffff: one giant page)
   int32_t rows_per_box;  // TMA: min(page_size, 64)
   int32_t tma_h_first;   // TMA map dim order: 1 = (D, h, n, page), 0 = (D, n, h, page)
+  int32_t tma_paired;    // 1: kmap is 5-D (D, n|h, h|n, K|V, page): one box brings K and V of a token block
   // work list (explicit) ...
   const PlanHeader* header;        // non-null selects this mode (the decode kernel never reads it)
   const ItemHead* item_heads;      // the segment list follows head num_items - 1
