@@ -426,6 +426,8 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
                                 page_size, false, 0, TT);
   if (!tma && tuning().loader == 1)
     return fail(FI_ERR_UNSUPPORTED, "TMA loader forced but page geometry is not eligible");
+  if (!tma && (kv_stride_page * es >= (int64_t(1) << 32) || kv_stride_n * es >= (int64_t(1) << 32)))
+    return fail(FI_ERR_UNSUPPORTED, "page / token strides of 4 GiB or more are not supported by the gather loader");
   CUtensorMap km, vm;
   memset(&km, 0, sizeof(km));
   memset(&vm, 0, sizeof(vm));

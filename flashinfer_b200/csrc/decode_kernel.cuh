@@ -21,6 +21,8 @@
 #pragma once
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "decode_params.h"
 #include "ptx.cuh"
 
@@ -52,9 +54,12 @@ __device__ __forceinline__ void fi_trace_smid() {
 #define FI_TRACE_IF(cond, slot)
 #endif
 
-// cp.async gather loader: 2 producer warps keep the CTA at 192 threads so that two CTAs per SM
-// fit the register file next to the 4 consumer warps
-constexpr int kCpAsyncProducerThreads = 64;
+// cp.async gather loader: FOUR producer warps = one warpgroup, one warp on each of the SM's four
+// sub-partitions (cp.async goes through each sub-partition's load/store instruction queue; with two
+// producer warps half of the queues stayed idle).  Two 256-thread CTAs per SM fit the register file
+// because the producer warpgroup hands registers to the consumer warpgroup (setmaxnreg).
+constexpr int kCpAsyncProducerThreads = 128;
+constexpr int kCpAsyncConsumerRegs = 176, kCpAsyncProducerRegs = 80;  // 128 * (176 + 80) = 32768
 
 template <int KVF, int HD>
 struct TileGeom {
@@ -120,6 +125,8 @@ constexpr int kQPub = 0;    // segments published so far, | kQFinal once nothing
 constexpr int kQDone0 = 1;  // consumer group: ring entries below this index are no longer read
 constexpr int kQDone1 = 2;  // second reader (cp.async producer warp 1 / tcgen05 issuer)
 constexpr int kQPeek = 3;   // tcgen05 softmax: "segment k + 1 is already published" broadcast
+constexpr int kQDone2 = 4;  // cp.async producer warps 2 and 3
+constexpr int kQDone3 = 5;
 constexpr int kQFinal = 1 << 30;
 constexpr int kQNoReader = 0x3fffffff;
 constexpr int kQueueCtlFloat = 160;  // offset of the control words in the warp scratch (floats)
@@ -188,7 +195,8 @@ __device__ __forceinline__ void seg_source_implicit_range(SegSource& s) {
 // blockIdx.x (one global round trip), publishes its inline segments and sets up the control words.
 // has_reader1: the kernel has a second ring reader that reports progress in kQDone1.
 __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int tt, Segment* cache,
-                                                     float* scratch, bool has_reader1) {
+                                                     float* scratch, bool has_reader1,
+                                                     bool has_reader23 = false) {
   SegSource s;
   s.p = &p;
   s.cache = cache;
@@ -228,6 +236,7 @@ __device__ __forceinline__ SegSource seg_source_init(const DecodeParams& p, int 
     s.ctl[kQPub] = pub0;
     s.ctl[kQDone0] = 0;
     s.ctl[kQDone1] = has_reader1 ? 0 : kQNoReader;
+    s.ctl[kQDone2] = s.ctl[kQDone3] = has_reader23 ? 0 : kQNoReader;
     s.ctl[kQPeek] = 0;
   }
   return s;
@@ -344,7 +353,7 @@ __device__ __forceinline__ void feeder_step(Feeder& f, const SegSource& s, int c
     return;
   }
   // idle: is there room in the ring, and is it time to fetch more?
-  const int done = min(s.ctl[kQDone0], s.ctl[kQDone1]);
+  const int done = min(min(s.ctl[kQDone0], s.ctl[kQDone1]), min(s.ctl[kQDone2], s.ctl[kQDone3]));
   const bool space = f.pub + kSegRefill <= done + kSegCache;
   if (f.item_next < f.item_count) {  // rest of the current item, from the list
     if (space && f.pub - cur_k < kSegRefill) {
@@ -486,8 +495,8 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
 }
 
 // ---- producer: 16-byte cp.async gathers (any page size / stride) -------------
-// Runs in kCpAsyncProducerThreads threads (ptid = 0 ..): warp 0 is also the feeder, warp 1 reads
-// the ring like a consumer.  Rows past tok_hi are zero-filled.
+// Runs in kCpAsyncProducerThreads threads (ptid = 0 ..): warp 0 is also the feeder, warps 1 .. 3 read
+// the ring like consumers.  Rows past tok_hi are zero-filled.
 // A thread owns one 16-byte chunk column of PASSES rows of every tile.  Two things bounded the first
 // version of this loader at 2.1x .. 4.3x the TMA loader's time (C2: 342 us at page 16, 690 us at page
 // 1, against 162 us): a dependent page-table load in front of every row's address, and ~40 integer
@@ -540,7 +549,11 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
   // page sizes that are a power of two <= the tile: a row's place inside its page does not depend on
   // the tile, and its page slot is a shift of the row index
   const bool pow2_page = p.page_shift >= 0 && p.page_size <= G::TT;
-  const int64_t stride_page_b = p.kv_stride_page * G::ES, stride_n_b = p.kv_stride_n * G::ES;
+  // byte strides fit 32 bits (checked by the launcher): one IMAD.WIDE per row instead of 64 x 64
+  const uint32_t spage = (uint32_t)(p.kv_stride_page * G::ES), sn = (uint32_t)(p.kv_stride_n * G::ES);
+  const int64_t v_minus_k = vb - kb;
+  // floor(2^32 / page_size): tok / page_size = umulhi(tok, magic) or that + 1 (any tok < 2^32)
+  const uint32_t magic = p.page_shift >= 0 ? 0u : (uint32_t)(0x100000000ull / (uint32_t)p.page_size);
   Feeder f;
   feeder_init(f, src);
   int tiles_issued = 0;
@@ -557,9 +570,10 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
     } else {
       if (!seg_fetch(src, k, sg)) break;
       __syncwarp();
-      if (lane == 0) src.ctl[kQDone1] = k + 1;
+      if (lane == 0) src.ctl[kQDone1 + (ptid >> 5) - 1 + ((ptid >> 5) > 1 ? 1 : 0)] = k + 1;  // warps 1, 2, 3
     }
-    const int64_t col_b = ((int64_t)(sg.kv_head / p.kv_head_div) * p.kv_stride_h + c * (16 / G::ES)) * G::ES;
+    // this thread's chunk column of head sg.kv_head inside a (page, row)
+    const char* kcol = kb + ((int64_t)(sg.kv_head / p.kv_head_div) * p.kv_stride_h + c * (16 / G::ES)) * G::ES;
     for (int t = sg.tile_begin; t < sg.tile_end; ++t) {
       if (feeds) feeder_step(f, src, k, tiles_issued, lane);
       if (have_nxt) {
@@ -577,9 +591,9 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
       } else {
         const bool pub = feeds ? (k + 1 < f.pub) : seg_peek(src, k + 1);
         if (__shfl_sync(0xffffffffu, pub ? 1 : 0, 0) != 0) {
-          const Segment sn = seg_read(src, k + 1);
-          if (sn.tile_end > sn.tile_begin) {
-            cpasync_tile_pages<KVF, HD>(nxt, p, sn, sn.tile_begin, lane);
+          const Segment sn2 = seg_read(src, k + 1);
+          if (sn2.tile_end > sn2.tile_begin) {
+            cpasync_tile_pages<KVF, HD>(nxt, p, sn2, sn2.tile_begin, lane);
             have_nxt = true;
           }
         }
@@ -588,33 +602,48 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
       const uint32_t sk = ring + stage * G::STAGE_BYTES;
       const int tok0 = t * G::TT;
       const int nvalid = sg.tok_hi - tok0;  // rows of this tile that hold tokens (>= TT: all)
-      const int pit0 = p.page_shift >= 0 ? tok0 >> p.page_shift : tok0 / p.page_size;
+      int pit0 = 0;
+      if (!pow2_page) {
+        if (p.page_shift >= 0) pit0 = tok0 >> p.page_shift;
+        else { pit0 = (int)__umulhi((uint32_t)tok0, magic); pit0 += (tok0 - pit0 * p.page_size >= p.page_size); }
+      }
+      auto issue = [&](auto full_tile) {
 #pragma unroll
-      for (int ps = 0; ps < R::PASSES; ++ps) {
-        const int row = ps * R::RPP + r0;
-        int slot, rip;
-        if (pow2_page) { slot = row >> p.page_shift; rip = row & p.page_mask; }
-        else {
-          const int tok = tok0 + row;
-          const int pit = p.page_shift >= 0 ? tok >> p.page_shift : tok / p.page_size;
-          slot = pit - pit0;
-          rip = tok - pit * p.page_size;
-        }
-        // every lane takes part in the shuffle; rows past the end read a valid lane's (unused) value
-        int page = __shfl_sync(0xffffffffu, cur[0], slot & 31);
-        if constexpr (R::SLOTS > 1) {
+        for (int ps = 0; ps < R::PASSES; ++ps) {
+          const int row = ps * R::RPP + r0;
+          int slot, rip;
+          if (pow2_page) { slot = row >> p.page_shift; rip = row & p.page_mask; }
+          else {
+            const int tok = tok0 + row;
+            int pit;
+            if (p.page_shift >= 0) pit = tok >> p.page_shift;
+            else { pit = (int)__umulhi((uint32_t)tok, magic); pit += (tok - pit * p.page_size >= p.page_size); }
+            slot = pit - pit0;
+            rip = tok - pit * p.page_size;
+          }
+          // every lane takes part in the shuffle; rows past the end read a valid lane's (unused) value
+          int page = __shfl_sync(0xffffffffu, cur[0], slot & 31);
+          if constexpr (R::SLOTS > 1) {
 #pragma unroll
-          for (int i = 1; i < R::SLOTS; ++i) {
-            const int other = __shfl_sync(0xffffffffu, cur[i], slot & 31);
-            page = (slot >> 5) == i ? other : page;
+            for (int i = 1; i < R::SLOTS; ++i) {
+              const int other = __shfl_sync(0xffffffffu, cur[i], slot & 31);
+              page = (slot >> 5) == i ? other : page;
+            }
+          }
+          const char* src_k = kcol + ((uint64_t)(uint32_t)page * spage + (uint64_t)(uint32_t)rip * sn);
+          const uint32_t d = sk + StageRow<G::TT>(row, ~(G::TT - 1)).at(c);
+          if constexpr (decltype(full_tile)::value) {
+            cp_async_16_full(d, src_k);
+            cp_async_16_full(d + G::PANEL_BYTES, src_k + v_minus_k);
+          } else {
+            const bool valid = row < nvalid;
+            cp_async_16(d, valid ? src_k : kb, valid ? 16u : 0u);
+            cp_async_16(d + G::PANEL_BYTES, valid ? src_k + v_minus_k : vb, valid ? 16u : 0u);
           }
         }
-        const bool valid = row < nvalid;
-        const int64_t off = valid ? (int64_t)page * stride_page_b + (int64_t)rip * stride_n_b + col_b : 0;
-        const uint32_t d = sk + StageRow<G::TT>(row, ~(G::TT - 1)).at(c);
-        cp_async_16(d, kb + off, valid ? 16u : 0u);
-        cp_async_16(d + G::PANEL_BYTES, vb + off, valid ? 16u : 0u);
-      }
+      };
+      if (nvalid >= G::TT) issue(std::true_type{});
+      else issue(std::false_type{});
       cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
       if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
       ++tiles_issued;
@@ -1371,7 +1400,7 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   }
   // the work list was written by plan() (a memcpy), not by the preceding kernel, so it
   // may be read before the PDL dependency resolves
-  const SegSource src = seg_source_init(p, G::TT, seg_cache, scratch_ml, LOADER != 0);
+  const SegSource src = seg_source_init(p, G::TT, seg_cache, scratch_ml, LOADER != 0, LOADER != 0);
   __syncthreads();
   FI_TRACE_IF(tid == 0, 1);
   if (seg_source_idle(src)) return;
@@ -1384,12 +1413,17 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
 
   // every role waits for the upstream kernel itself, right before its first access to data an
   // upstream kernel may have produced (q, the KV cache, counters)
+  // cp.async loader with two CTAs per SM: the kernel is compiled for 128 registers per thread
+  // (256 threads x 2 CTAs); the consumer warpgroup grows to 184, the producer warpgroup shrinks to 72
+  constexpr bool kRegSplit = LOADER != 0 && HD <= 128;
   if (tid < kConsumerWarps * 32) {
+    if constexpr (kRegSplit) setmaxnreg_inc<kCpAsyncConsumerRegs>();
     if (p.enable_pdl) pdl_wait();
     consume<QT, KVF, HD, LOADER, ROPE>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
   } else if (LOADER == 0) {
     produce_tma<KVF, HD, true>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);  // waits inside
   } else {
+    if constexpr (kRegSplit) setmaxnreg_dec<kCpAsyncProducerRegs>();
     if (p.enable_pdl) pdl_wait();
     produce_cpasync<KVF, HD>(p, src, tid - kConsumerWarps * 32, ring, full_bar, empty_bar);
   }

@@ -24,7 +24,6 @@ from .utils import (
     PosEncodingMode,
     _get_cache_alibi_slopes_buf,
     _get_cache_buf,
-    _get_range_buf,
     _unpack_paged_kv_cache,
     canonicalize_torch_dtype,
     check_shape_dtype_device,

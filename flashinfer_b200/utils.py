@@ -1,7 +1,11 @@
-"""Host-side helpers of the decode path (same names and behaviour as the small subset of
-the reference's flashinfer/utils.py the path uses: enums :28-45, cache unpacking
-:53-170, cached buffers :183-207, dtype canonicalisation :221-230, dtype / shape checks
-:239-250, :493-511, PDL probe :556)."""
+"""Host-side helpers of the decode path.
+
+Interface names that callers of the reference know (`PosEncodingMode`, `TensorLayout`,
+`_unpack_paged_kv_cache`, `canonicalize_torch_dtype`, `check_shape_dtype_device`,
+`get_alibi_slopes`, reference flashinfer/utils.py:28-45,149-180,221-250,493-511) keep their names,
+argument meaning and exception classes; the implementations are this repo's own, and everything
+the C-ABI path does not need was left out.
+"""
 from __future__ import annotations
 
 import functools
@@ -25,129 +29,86 @@ class TensorLayout(Enum):
     HND = 1
 
 
-log2e = 1.44269504088896340736
+_POS_MODES = frozenset(m.name for m in PosEncodingMode)
+_LAYOUTS = frozenset(m.name for m in TensorLayout)
 
 
 def _check_pos_encoding_mode(pos_encoding_mode: str) -> None:
-    if not hasattr(PosEncodingMode, pos_encoding_mode):
-        raise KeyError("Invalid pos_encoding_mode {}".format(pos_encoding_mode))
+    if pos_encoding_mode not in _POS_MODES:
+        raise KeyError(f"Invalid pos_encoding_mode {pos_encoding_mode}")
 
 
 def _check_kv_layout(kv_layout: str) -> None:
-    if not hasattr(TensorLayout, kv_layout):
-        raise KeyError("Invalid kv_layout {}".format(kv_layout))
+    if kv_layout not in _LAYOUTS:
+        raise KeyError(f"Invalid kv_layout {kv_layout}")
 
 
-def _expand_5d(x: torch.Tensor, kv_layout: str) -> torch.Tensor:
-    if x.ndim not in [4, 5]:
-        raise ValueError("x must be 4D or 5D")
-    if x.ndim == 4:  # page_size == 1
-        if kv_layout == "NHD":
-            return x.unsqueeze(-3)
-        elif kv_layout == "HND":
-            return x.unsqueeze(-2)
-        raise KeyError("Invalid kv_layout {}".format(kv_layout))
-    return x
-
-
-def _expand_4d(x: torch.Tensor, kv_layout: str) -> torch.Tensor:
-    if x.ndim not in [3, 4]:
-        raise ValueError("x must be 3D or 4D")
-    if x.ndim == 3:  # page_size == 1
-        if kv_layout == "NHD":
-            return x.unsqueeze(-3)
-        elif kv_layout == "HND":
-            return x.unsqueeze(-2)
-        raise KeyError("Invalid kv_layout {}".format(kv_layout))
-    return x
+def _with_page_axis(x: torch.Tensor, full_ndim: int, kv_layout: str) -> torch.Tensor:
+    """A cache with `page_size == 1` may come without its page axis (one dimension short of
+    `full_ndim`): put the axis of length one where the layout has it."""
+    if x.ndim == full_ndim:
+        return x
+    if x.ndim != full_ndim - 1:
+        raise ValueError(f"x must be {full_ndim - 1}D or {full_ndim}D")
+    _check_kv_layout(kv_layout)
+    return x.unsqueeze(-3 if kv_layout == "NHD" else -2)
 
 
 def _unpack_paged_kv_cache(
     paged_kv_cache: Union[torch.Tensor, Tuple[torch.Tensor, torch.Tensor]],
     kv_layout: str,
 ) -> Tuple[torch.Tensor, torch.Tensor]:
-    """(k_cache, v_cache) 4-D views; a 5-D cache is split on dim 1 (utils.py:149-170)."""
+    """(k_cache, v_cache) as 4-D views `[pages, page_size, Hkv, D]` (NHD) / `[pages, Hkv, page_size,
+    D]` (HND): a tuple passes through, a single tensor holds K and V as the two halves of dim 1."""
     if isinstance(paged_kv_cache, tuple):
-        paged_k_cache, paged_v_cache = paged_kv_cache
-        return _expand_4d(paged_k_cache, kv_layout), _expand_4d(paged_v_cache, kv_layout)
-    elif torch.is_tensor(paged_kv_cache):
-        paged_kv_cache = _expand_5d(paged_kv_cache, kv_layout)
-        paged_k_cache, paged_v_cache = paged_kv_cache.unbind(dim=1)
-        return paged_k_cache, paged_v_cache
+        k_cache, v_cache = paged_kv_cache
+        return _with_page_axis(k_cache, 4, kv_layout), _with_page_axis(v_cache, 4, kv_layout)
+    if torch.is_tensor(paged_kv_cache):
+        both = _with_page_axis(paged_kv_cache, 5, kv_layout)
+        return both[:, 0], both[:, 1]
     raise KeyError(
-        "Unrecognized paged_kv_cache type {}, expect a single tensor or a tuple of tensor.".format(
-            type(paged_kv_cache)
-        )
+        f"Unrecognized paged_kv_cache type {type(paged_kv_cache)}, expect a single tensor or a tuple of tensor."
     )
 
 
-_cache_buf: Dict[Tuple[str, torch.device], torch.Tensor] = {}
+# scratch tensors that outlive a call, one per (purpose, device)
+_buffers: Dict[Tuple[str, torch.device], torch.Tensor] = {}
 
 
 def _get_cache_buf(name: str, bytes: int, device: torch.device) -> torch.Tensor:
-    key = (name, device)
-    buf = _cache_buf.get(key)
+    """A uint8 scratch tensor of at least `bytes` bytes, grown on demand, never zeroed."""
+    buf = _buffers.get((name, device))
     if buf is None or buf.numel() < bytes:
-        buf = torch.empty(bytes, dtype=torch.uint8, device=device)
-        _cache_buf[key] = buf
+        buf = _buffers[(name, device)] = torch.empty(bytes, dtype=torch.uint8, device=device)
     return buf
 
 
 def get_alibi_slopes(n_heads: int) -> torch.Tensor:
-    """ALiBi head slopes (reference flashinfer/utils.py:172-180): 2^(-8 i / n) for the largest
-    power of two n <= n_heads, interleaved 2^(-4 (2j - 1) / n) for the remaining heads."""
-    n = 2 ** math.floor(math.log2(n_heads))
-    m_0 = 2.0 ** (-8.0 / n)
-    m = torch.pow(m_0, torch.arange(1, 1 + n))
-    if n < n_heads:
-        m_hat_0 = 2.0 ** (-4.0 / n)
-        m_hat = torch.pow(m_hat_0, torch.arange(1, 1 + 2 * (n_heads - n), 2))
-        m = torch.cat([m, m_hat])
-    return m.float()
+    """ALiBi head slopes (Press et al.; the reference's values, flashinfer/utils.py:172-180): with n the
+    largest power of two <= n_heads, head i < n gets 2^(-8 (i + 1) / n); the remaining heads take
+    every other slope of the 2n-head series, 2^(-4 (2 j + 1) / n)."""
+    n = 1 << (max(n_heads, 1).bit_length() - 1)
+    # evaluated in float32 by torch.pow like the reference, so the slopes match it bit for bit
+    slopes = torch.pow(2.0 ** (-8.0 / n), torch.arange(1, n + 1))
+    if n_heads > n:
+        extra = torch.pow(2.0 ** (-4.0 / n), torch.arange(1, 2 * (n_heads - n), 2))
+        slopes = torch.cat([slopes, extra])
+    return slopes.float()
 
 
 def _get_cache_alibi_slopes_buf(num_qo_heads: int, device: torch.device) -> torch.Tensor:
     key = (f"alibi_slopes_{num_qo_heads}", device)
-    buf = _cache_buf.get(key)
-    if buf is None:
-        buf = get_alibi_slopes(num_qo_heads).to(device)
-        _cache_buf[key] = buf
-    return buf
-
-
-def _ceil_pow2(x: int) -> int:
-    return 1 << (x - 1).bit_length()
-
-
-def _get_range_buf(seq_len: int, device) -> torch.Tensor:
-    seq_len_pow2 = _ceil_pow2(max(seq_len, 1))
-    key = (f"range_{seq_len_pow2}", torch.device(device))
-    buf = _cache_buf.get(key)
-    if buf is None:
-        buf = torch.arange(seq_len_pow2, device=device, dtype=torch.int32)
-        _cache_buf[key] = buf
-    return buf[:seq_len]
+    if key not in _buffers:
+        _buffers[key] = get_alibi_slopes(num_qo_heads).to(device)
+    return _buffers[key]
 
 
 def canonicalize_torch_dtype(dtype: Union[torch.dtype, str]) -> torch.dtype:
+    if isinstance(dtype, torch.dtype):
+        return dtype
     if isinstance(dtype, str):
         return getattr(torch, dtype)
-    elif isinstance(dtype, torch.dtype):
-        return dtype
-    raise TypeError("dtype must be a string or torch.dtype, got {}".format(type(dtype)))
-
-
-def _check_cached_qkv_data_type(
-    q: torch.Tensor, k: torch.Tensor, dtype_q: torch.dtype, dtype_kv: torch.dtype
-) -> None:
-    if q.dtype != dtype_q:
-        raise ValueError(
-            f"The dtype of q {q.dtype} does not match the q_data_type {dtype_q} specified in plan function."
-        )
-    if k.dtype != dtype_kv:
-        raise ValueError(
-            f"The dtype of k {k.dtype} does not match the kv_data_type {dtype_kv} specified in plan function."
-        )
+    raise TypeError(f"dtype must be a string or torch.dtype, got {type(dtype)}")
 
 
 def check_shape_dtype_device(
@@ -157,7 +118,7 @@ def check_shape_dtype_device(
     expected_device: Optional[torch.device],
     name: str,
 ) -> None:
-    if expected_shape and x.shape != torch.Size(expected_shape):
+    if expected_shape and tuple(x.shape) != tuple(expected_shape):
         raise ValueError(f"Invalid shape of {name}: expected {expected_shape}, got {x.shape}")
     if expected_dtype and x.dtype != expected_dtype:
         raise ValueError(f"Invalid dtype of {name}: expected {expected_dtype}, got {x.dtype}")
@@ -165,13 +126,10 @@ def check_shape_dtype_device(
         raise ValueError(f"Invalid device of {name}: expected {expected_device}, got {x.device}")
 
 
-@functools.cache
 @functools.lru_cache(maxsize=None)
 def device_support_pdl(device: torch.device) -> bool:
-    if device.type != "cuda":
-        return False
-    major, _ = torch.cuda.get_device_capability(device.index)
-    return major >= 9
+    """Programmatic dependent launch needs sm_90 or later."""
+    return device.type == "cuda" and torch.cuda.get_device_capability(device.index)[0] >= 9
 
 
 def is_float8(x: torch.Tensor) -> bool:
