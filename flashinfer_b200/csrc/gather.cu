@@ -62,7 +62,7 @@ __device__ __forceinline__ unsigned long long global_ns() {
 
 // UNIT: the widest type every address and the row length allow (int4 / uint32_t / uint16_t)
 template <typename UNIT>
-__global__ void __launch_bounds__(256) peer_gather_kernel(const PeerGatherParams p) {
+__global__ void __launch_bounds__(1024) peer_gather_kernel(const PeerGatherParams p) {
   __shared__ int s_last;
   if (p.enable_pdl) pdl_wait();  // o_local is the previous kernel's output
   const int64_t upr = p.row_bytes / (int64_t)sizeof(UNIT);
@@ -87,12 +87,14 @@ __global__ void __launch_bounds__(256) peer_gather_kernel(const PeerGatherParams
   __threadfence_system();
   __syncthreads();
   uint32_t* my = p.ctl[p.rank];
-  if (threadIdx.x == 0)
-    s_last = atom_add_acq_rel_gpu(reinterpret_cast<int*>(my + kCtlCounter), 1) == (int)gridDim.x - 1;
-  __syncthreads();
-  if (!s_last) return;
-  if (threadIdx.x == 0) my[kCtlCounter] = 0;  // re-armed for the next launch
-  __threadfence_system();
+  if (gridDim.x > 1) {  // small payloads run as ONE CTA: no counter round trip, no second fence
+    if (threadIdx.x == 0)
+      s_last = atom_add_acq_rel_gpu(reinterpret_cast<int*>(my + kCtlCounter), 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    if (threadIdx.x == 0) my[kCtlCounter] = 0;  // re-armed for the next launch
+    __threadfence_system();
+  }
   if ((int)threadIdx.x < p.world) {
     const int peer = threadIdx.x;
     st_release_sys_u32(p.ctl[peer] + kCtlFlags + p.rank, p.epoch);
@@ -148,11 +150,15 @@ extern "C" int fi_peer_gather(const void* src, void* const* peer_dst, void* mc_d
   const int unit = (align & 15) == 0 ? 16 : ((align & 3) == 0 ? 4 : 2);
   if (unit != 16) p.mc_dst = nullptr;
   const int64_t total = rows * (row_bytes / unit);
-  int grid = (int)((total + 255) / 256);
-  if (grid > 64) grid = 64;  // 64 KiB .. 256 KiB per rank: a few CTAs saturate the NVLink ports
+  // up to 8192 units (128 KiB of 16-byte chunks: the decode outputs of C2 / C3 / C5 at 4 and 8 ranks)
+  // one CTA of 1024 threads does it all and signals without the CTA counter; larger payloads spread
+  // over up to 64 CTAs of 256 threads
+  const bool one_cta = total <= 8192;
+  int grid = one_cta ? 1 : (int)((total + 255) / 256);
+  if (grid > 64) grid = 64;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(256);
+  cfg.blockDim = dim3(one_cta ? 1024 : 256);
   cfg.stream = static_cast<cudaStream_t>(stream);
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
