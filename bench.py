@@ -488,8 +488,16 @@ def _upstream():
     from flashinfer.jit import env as jit_env
 
     aot = ROOT / "baseline" / "_ref" / "fi_aot"
-    if aot.exists():
-        jit_env.FLASHINFER_AOT_DIR = aot
+    if not aot.exists():
+        raise RuntimeError("baseline/_ref/fi_aot is missing (run scripts/build_upstream_comparators.py where "
+                           "nvcc is; a JIT build inside the bench would take minutes)")
+    jit_env.FLASHINFER_AOT_DIR = aot
+    from flashinfer.jit import core as jit_core
+
+    def _no_jit(self, *a, **k):  # a module that was not pre-built must not start a compile here
+        raise RuntimeError(f"upstream module {self.name} is not pre-built in baseline/_ref/fi_aot")
+
+    jit_core.JitSpec.build = _no_jit
     return up
 
 

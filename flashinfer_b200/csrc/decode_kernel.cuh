@@ -552,6 +552,7 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
   // byte strides fit 32 bits (checked by the launcher): one IMAD.WIDE per row instead of 64 x 64
   const uint32_t spage = (uint32_t)(p.kv_stride_page * G::ES), sn = (uint32_t)(p.kv_stride_n * G::ES);
   const int64_t v_minus_k = vb - kb;
+  const bool wide = p.page_size * 32 < G::TT;  // a tile can touch more than 32 pages
   // floor(2^32 / page_size): tok / page_size = umulhi(tok, magic) or that + 1 (any tok < 2^32)
   const uint32_t magic = p.page_shift >= 0 ? 0u : (uint32_t)(0x100000000ull / (uint32_t)p.page_size);
   Feeder f;
@@ -624,10 +625,12 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
           // every lane takes part in the shuffle; rows past the end read a valid lane's (unused) value
           int page = __shfl_sync(0xffffffffu, cur[0], slot & 31);
           if constexpr (R::SLOTS > 1) {
+            if (wide) {  // warp-uniform: only tiles that touch more than 32 pages (page size 1 or 2)
 #pragma unroll
-            for (int i = 1; i < R::SLOTS; ++i) {
-              const int other = __shfl_sync(0xffffffffu, cur[i], slot & 31);
-              page = (slot >> 5) == i ? other : page;
+              for (int i = 1; i < R::SLOTS; ++i) {
+                const int other = __shfl_sync(0xffffffffu, cur[i], slot & 31);
+                page = (slot >> 5) == i ? other : page;
+              }
             }
           }
           const char* src_k = kcol + ((uint64_t)(uint32_t)page * spage + (uint64_t)(uint32_t)rip * sn);

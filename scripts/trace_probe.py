@@ -95,6 +95,17 @@ def main():
             m = ok & (smid >= lo) & (smid < lo + 20)
             if m.sum():
                 print(f"    SMs {lo:3d}-{lo + 19:3d}: mean duration {dur[m].mean():6.2f} us  (n={m.sum()})")
+    # does a CTA that has an SM to itself finish earlier than one that shares its SM?
+    smid_all = buf[:, 15].astype(np.int64) - 1
+    act = ~np.isnan(rel[:, 6])
+    if act.sum() > 8:
+        per_sm = np.bincount(smid_all[act & (smid_all >= 0)], minlength=160)
+        share = per_sm[np.clip(smid_all, 0, 159)]
+        for n in (1, 2):
+            m = act & (share == n)
+            if m.sum():
+                print(f"CTAs on an SM with {n} active CTA(s): n={m.sum():3d}  last tile done median {np.median(rel[m, 6]):7.2f} "
+                      f"min {rel[m, 6].min():7.2f} max {rel[m, 6].max():7.2f} us")
     print("per-CTA deltas (median / max, us):")
     for a, b in [(0, 1), (1, 2), (2, 3), (3, 4), (4, 5), (5, 6), (6, 10), (10, 11), (11, 7), (6, 7), (7, 8), (7, 9)]:
         dlt = rel[:, b] - rel[:, a]
