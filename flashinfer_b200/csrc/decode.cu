@@ -266,7 +266,22 @@ static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUt
                          cudaStream_t stream) {
   const bool bf = q_dtype == FI_DTYPE_BF16;
   static const bool rope_cuda_core = [] { const char* e = getenv("FI_B200_ROPE_CUDA_CORE"); return e && e[0] == '1'; }();
-  if (p.rope && (kvf != 0 || rope_cuda_core)) {  // fp8 KV (or A/B runs): the CUDA-core variant kernel
+  // fp8 KV with ROPE_LLAMA (or A/B runs), and fp8 KV at head_dim 64 in any mode but ALiBi (64-byte rows do
+  // not fit the 128-byte swizzle atoms of the MMA kernels): the CUDA-core variant kernel; without RoPE it
+  // runs with zero rotation frequencies, i.e. the identity rotation
+  if ((p.rope && (kvf != 0 || rope_cuda_core)) || (kvf != 0 && head_dim == 64)) {
+    if (p.alibi_slopes != nullptr)
+      return fail(FI_ERR_UNSUPPORTED, "ALIBI with fp8 KV at head_dim 64 is not built");
+    if (!p.rope) {
+      DecodeParams p2 = p;
+      p2.rope_rcp_scale = 0.f;
+      p2.rope_rcp_theta = 1.f;
+      switch (kvf) {
+        case 1: return bf ? launch_rope<1, 1>(p2, head_dim, grid, stream) : launch_rope<0, 1>(p2, head_dim, grid, stream);
+        case 2: return bf ? launch_rope<1, 2>(p2, head_dim, grid, stream) : launch_rope<0, 2>(p2, head_dim, grid, stream);
+        default: return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
+      }
+    }
     switch (kvf) {
       case 0: return bf ? launch_rope<1, 0>(p, head_dim, grid, stream) : launch_rope<0, 0>(p, head_dim, grid, stream);
       case 1: return bf ? launch_rope<1, 1>(p, head_dim, grid, stream) : launch_rope<0, 1>(p, head_dim, grid, stream);
@@ -407,8 +422,9 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.alibi_slopes = pos_encoding_mode == FI_POS_ALIBI ? alibi_slopes : nullptr;
   p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
   p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
-  if (p.rope && kvf != 0 && plan_info[kPiNumItems] > plan_info[kPiNumCtas])
-    return fail(FI_ERR_UNSUPPORTED, "ROPE_LLAMA decode needs a static plan (unset FI_B200_SCHED_F0)");
+  if (((p.rope && kvf != 0) || (kvf != 0 && head_dim == 64)) && plan_info[kPiNumItems] > plan_info[kPiNumCtas])
+    return fail(FI_ERR_UNSUPPORTED, "the CUDA-core variant kernel (fp8 KV with ROPE_LLAMA or head_dim 64) needs a "
+                                    "static plan (unset FI_B200_SCHED_F0)");
   // 1: griddepcontrol.launch_dependents right after the kernel's own dependency wait (default);
   // 2: at the very end (FI_B200_PDL_LATE=1, kept for A/B runs)
   static const bool pdl_late = [] { const char* e = getenv("FI_B200_PDL_LATE"); return e && e[0] == '1'; }();
@@ -422,8 +438,9 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.l2_hints = default_l2_hints();
   p.sinks = sinks;
 
-  const bool tma = tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h, kv_stride_page,
-                                page_size, false, 0, TT);
+  const bool cuda_core_only = kvf != 0 && head_dim == 64;
+  const bool tma = !cuda_core_only && tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h,
+                                                   kv_stride_page, page_size, false, 0, TT);
   if (!tma && tuning().loader == 1)
     return fail(FI_ERR_UNSUPPORTED, "TMA loader forced but page geometry is not eligible");
   if (!tma && (kv_stride_page * es >= (int64_t(1) << 32) || kv_stride_n * es >= (int64_t(1) << 32)))
@@ -507,7 +524,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   const int group = num_qo_heads / num_kv_heads;
   const int kvf = kv_format(q_dtype, kv_dtype);
   if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair");
-  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256) || (kvf != 0 && head_dim == 64))
+  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256))
     return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
   if (kv_len < 0) return fail(FI_ERR_INVALID_ARGUMENT, "negative kv_len");
   const int es = dtype_size(kv_dtype);
@@ -556,7 +573,8 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
   p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
 
-  const bool tma = tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
+  const bool tma = !(kvf != 0 && head_dim == 64) &&
+                   tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
   CUtensorMap km, vm;
   memset(&km, 0, sizeof(km));
   memset(&vm, 0, sizeof(vm));

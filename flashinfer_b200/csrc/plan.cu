@@ -152,7 +152,9 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   const int group = num_qo_heads / num_kv_heads;
   const int kvf = kv_format(q_dtype, kv_dtype);
   if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair (%d, %d)", q_dtype, kv_dtype);
-  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256) || (kvf != 0 && head_dim == 64))
+  // fp8 KV at head_dim 64 (64-byte rows, below the 128-byte swizzle atom of the MMA kernels) runs on the
+  // CUDA-core variant kernel (decode_rope_kernel.cuh with zero rotation frequencies)
+  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256))
     return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d for this dtype", head_dim);
   if (indptr_host == nullptr || (last_page_len_host == nullptr && kv_len_host == nullptr))
     return fail(FI_ERR_INVALID_ARGUMENT, "indptr / last_page_len must be host pointers");

@@ -419,9 +419,14 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._rope_scale = rope_scale
         self._rope_theta = rope_theta
         # what run(q_len_per_req > 1) needs to plan the per-row requests on first use
-        self._mtp_children = {}
         self._mtp_src = (indptr, indices, last_page_len, head_dim, page_size, q_data_type, kv_data_type,
                          fixed_split_size, disable_split_kv)
+        if self._use_cuda_graph and self._mtp_children:
+            # captured graphs hold the children's kernels: their work lists follow every re-plan
+            for n, child in self._mtp_children.items():
+                self._plan_mtp_child(child, n)
+        else:
+            self._mtp_children = {}
 
     begin_forward = plan
 
@@ -431,11 +436,12 @@ class BatchDecodeWithPagedKVCacheWrapper:
         and the cache already holds their K / V; token ``t`` of a request attends the request's
         first ``kv_len - (q_len_per_req - 1 - t)`` tokens (causal among the new tokens).  A query
         row that attends a prefix of a page list is a decode request over that prefix, so the
-        rows run as ``batch_size * q_len_per_req`` planned decode requests on the same kernels;
-        the plan of the expanded table is made on the first call (host work, not graph-capturable)
-        and kept until the next ``plan()``."""
-        from .cascade import rows_as_decode_requests
-
+        rows run as ``batch_size * q_len_per_req`` planned decode requests on the same kernels.
+        The plan of the expanded table is made on the first call (host work) and kept until the
+        next ``plan()``.  In CUDA-graph mode the expanded table lives in a child wrapper with its
+        own fixed-size buffers that every later ``plan()`` re-plans, so: call
+        ``run(q_len_per_req=n)`` once outside the capture (the usual warm-up), capture it, and keep
+        re-planning the parent between replays."""
         if self._mtp_src is None:
             raise RuntimeError("q_len_per_req > 1 needs a regular plan() (not fast_decode_plan)")
         if q.shape[0] != self._batch_size * q_len_per_req:
@@ -445,19 +451,42 @@ class BatchDecodeWithPagedKVCacheWrapper:
             )
         child = self._mtp_children.get(q_len_per_req)
         if child is None:
-            (indptr, indices, last_page_len, head_dim, page_size, q_dt, kv_dt, fss, dskv) = self._mtp_src
-            qo_indptr = torch.arange(self._batch_size + 1, dtype=torch.int32) * q_len_per_req
-            r_indptr, r_indices, r_last = rows_as_decode_requests(
-                qo_indptr, indptr, indices, last_page_len, page_size, causal=True)
-            child = BatchDecodeWithPagedKVCacheWrapper(
-                self._float_workspace_buffer, self._kv_layout, use_tensor_cores=self.use_tensor_cores)
-            child.plan(r_indptr, r_indices, r_last, self._num_qo_heads, self._num_kv_heads, head_dim,
-                       page_size, pos_encoding_mode=self._pos_encoding_mode, window_left=self._window_left,
-                       logits_soft_cap=self._logits_soft_cap, q_data_type=q_dt, kv_data_type=kv_dt,
-                       sm_scale=self._sm_scale, rope_scale=self._rope_scale, rope_theta=self._rope_theta,
-                       fixed_split_size=fss, disable_split_kv=dskv)
+            if self._use_cuda_graph and torch.cuda.is_current_stream_capturing():
+                raise RuntimeError(
+                    f"run(q_len_per_req={q_len_per_req}) must be called once before the CUDA-graph capture: "
+                    "its per-row plan is host work")
+            child = self._make_mtp_child(q_len_per_req)
+            self._plan_mtp_child(child, q_len_per_req)
             self._mtp_children[q_len_per_req] = child
         return child.run(q, paged_kv_cache, **run_kw)
+
+    def _make_mtp_child(self, n: int) -> "BatchDecodeWithPagedKVCacheWrapper":
+        if not self._use_cuda_graph:
+            return BatchDecodeWithPagedKVCacheWrapper(
+                self._float_workspace_buffer, self._kv_layout, use_tensor_cores=self.use_tensor_cores)
+        # fixed-size buffers for the n-fold expanded table: row t of a request lists a prefix of
+        # the request's pages, so n times the parent's capacities always suffice
+        bs = self._fixed_batch_size
+        dev = self.device
+        return BatchDecodeWithPagedKVCacheWrapper(
+            self._float_workspace_buffer, self._kv_layout, use_cuda_graph=True,
+            use_tensor_cores=self.use_tensor_cores,
+            paged_kv_indptr_buffer=torch.zeros(bs * n + 1, dtype=torch.int32, device=dev),
+            paged_kv_indices_buffer=torch.zeros(max(len(self._indices_dev) * n, 1), dtype=torch.int32, device=dev),
+            paged_kv_last_page_len_buffer=torch.zeros(bs * n, dtype=torch.int32, device=dev))
+
+    def _plan_mtp_child(self, child, n: int) -> None:
+        from .cascade import rows_as_decode_requests
+
+        (indptr, indices, last_page_len, head_dim, page_size, q_dt, kv_dt, fss, dskv) = self._mtp_src
+        qo_indptr = torch.arange(self._batch_size + 1, dtype=torch.int32) * n
+        r_indptr, r_indices, r_last = rows_as_decode_requests(
+            qo_indptr, indptr, indices, last_page_len, page_size, causal=True)
+        child.plan(r_indptr, r_indices, r_last, self._num_qo_heads, self._num_kv_heads, head_dim,
+                   page_size, pos_encoding_mode=self._pos_encoding_mode, window_left=self._window_left,
+                   logits_soft_cap=self._logits_soft_cap, q_data_type=q_dt, kv_data_type=kv_dt,
+                   sm_scale=self._sm_scale, rope_scale=self._rope_scale, rope_theta=self._rope_theta,
+                   fixed_split_size=fss, disable_split_kv=dskv)
 
     def _bind_workspaces(self) -> None:
         fws, iws, pws = (self._float_workspace_buffer, self._int_workspace_buffer,
@@ -577,8 +606,6 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 raise ValueError("sinks must be a [num_qo_heads] tensor on q's device")
             sinks = sinks.to(torch.float32).contiguous()
         if q_len_per_req not in (None, 1):
-            if self.is_cuda_graph_enabled:
-                raise NotImplementedError("q_len_per_req > 1 is not supported in CUDA-graph mode")
             return self._run_multi_token(
                 q, paged_kv_cache, int(q_len_per_req), q_scale=q_scale, k_scale=k_scale, v_scale=v_scale,
                 out=out, lse=lse, return_lse=return_lse, enable_pdl=enable_pdl, window_left=window_left,

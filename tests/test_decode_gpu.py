@@ -561,6 +561,84 @@ def test_multi_token_decode_q_len_per_req(q_len_per_req, kv_dtype, pos_mode):
         w.run(q[:-1].to(DEV), cache.to(DEV), q_len_per_req=n)
 
 
+@pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+@pytest.mark.parametrize("pos_mode", ["NONE", "ROPE_LLAMA"])
+def test_fp8_kv_at_head_dim_64(kv_dtype, layout, pos_mode):
+    """fp8 KV at head_dim 64 (the reference dispatches it, include/flashinfer/utils.cuh:175-202): 64-byte rows
+    run on the CUDA-core variant kernel; batch and single decode against the oracle, split units included."""
+    fi = _fi()
+    hq, hkv, d, page = 16, 4, 64, 16
+    lens = [1, 54, 97, 512, 9000, 0, 4099, 777]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, layout, torch.float32, seed=91)
+    cache = (cache * 0.5).to(kv_dtype)
+    q = make_q(len(lens), hq, d, torch.bfloat16, seed=92)
+    k_scale, v_scale = 0.5, 0.25
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, pos_encoding_mode=pos_mode, q_data_type=torch.bfloat16,
+           kv_data_type=kv_dtype)
+    o, lse = w.run(q.to(DEV), cache.to(DEV), k_scale=k_scale, v_scale=v_scale, return_lse=True)
+    rope = (1.0, 1e4) if pos_mode == "ROPE_LLAMA" else None
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, layout, k_scale=k_scale,
+                                          v_scale=v_scale, rope=rope)
+    assert (o.float().cpu() - o_ref).abs().max().item() <= O_TOL_FP8
+    assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+    # single decode on request 4 (9000 tokens: the implicit split + merge kernel)
+    k4, v4 = orc.unpack_cache(cache, layout)
+    k, v = orc.gather_paged_kv(k4, v4, indptr, indices, last, 4, layout)
+    kd, vd = (k, v) if layout == "NHD" else (k.transpose(0, 1), v.transpose(0, 1))
+    o1, l1 = fi.single_decode_with_kv_cache(q[4].to(DEV), kd.contiguous().to(DEV), vd.contiguous().to(DEV),
+                                            kv_layout=layout, pos_encoding_mode=pos_mode, k_scale=k_scale,
+                                            v_scale=v_scale, return_lse=True)
+    assert (o1.float().cpu() - o_ref[4]).abs().max().item() <= O_TOL_FP8
+    assert (l1.cpu() - lse_ref[4]).abs().max().item() <= LSE_TOL
+    if pos_mode == "NONE":
+        w.plan(indptr, indices, last, hq, hkv, d, page, pos_encoding_mode="ALIBI", q_data_type=torch.bfloat16,
+               kv_data_type=kv_dtype)
+        with pytest.raises(RuntimeError):
+            w.run(q.to(DEV), cache.to(DEV))
+
+
+@pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn])
+def test_multi_token_decode_in_a_cuda_graph_with_replans(kv_dtype):
+    """run(q_len_per_req = n) captured in a CUDA graph (the reference captures its tensor-core decode,
+    tests/attention/test_tensor_cores_decode.py:200-330): warm-up call outside the capture, then
+    replays after re-plans with different kv lengths — the per-row child plan follows every plan()."""
+    fi = _fi()
+    hq, hkv, d, page, n = 16, 4, 128, 16, 3
+    lens_a, lens_b = [100, 2000, 31, 977, 5], [4000, 7, 64, 1500, 333]
+    is8 = kv_dtype is not None
+    cache, ip_b, ix_b, lp_b = make_paged_case(lens_b, hkv, d, page, "NHD", torch.float32, seed=81)
+    cache = (cache * 0.5 if is8 else cache).to(kv_dtype or torch.float16)
+    _, ip_a, ix_a, lp_a = make_paged_case(lens_a, hkv, d, page, "NHD", torch.float16, seed=82)
+    bs = len(lens_a)
+    max_pages = 4096
+    w = fi.CUDAGraphBatchDecodeWithPagedKVCacheWrapper(
+        _workspace(), torch.zeros(bs + 1, dtype=torch.int32, device=DEV),
+        torch.zeros(max_pages, dtype=torch.int32, device=DEV), torch.zeros(bs, dtype=torch.int32, device=DEV), "NHD")
+    q = make_q(bs * n, hq, d, torch.float16, seed=83).to(DEV)
+    cache_d = cache.to(DEV)
+    out = torch.empty_like(q)
+    kw = dict(q_data_type=torch.float16, kv_data_type=cache.dtype)
+    w.plan(ip_a, ix_a, lp_a, hq, hkv, d, page, **kw)
+    w.run(q, cache_d, out=out, q_len_per_req=n)  # warm-up: creates and plans the per-row child
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        w.run(q, cache_d, out=out, q_len_per_req=n)
+    k4, v4 = orc.unpack_cache(cache, "NHD")
+    for lens, ip, ix, lp in ((lens_a, ip_a, ix_a, lp_a), (lens_b, ip_b, ix_b, lp_b), (lens_a, ip_a, ix_a, lp_a)):
+        w.plan(ip, ix, lp, hq, hkv, d, page, **kw)
+        graph.replay()
+        torch.cuda.synchronize()
+        for b, L in enumerate(lens):
+            k, v = orc.gather_paged_kv(k4, v4, ip, ix, lp, b, "NHD")
+            for t in range(n):
+                Lt = max(L - (n - 1 - t), 0)
+                o_ref, _ = orc.decode_attention_ref(q[b * n + t].cpu(), k[:Lt].float(), v[:Lt].float())
+                assert (out[b * n + t].float().cpu() - o_ref).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+
+
 @pytest.mark.parametrize("kv_dtype,pos_mode,hq", [(None, "NONE", 16), (torch.float8_e4m3fn, "NONE", 32),
                                                   (None, "ROPE_LLAMA", 16), (torch.float8_e4m3fn, "ROPE_LLAMA", 16),
                                                   (None, "NONE", 64)])
