@@ -23,6 +23,8 @@ FI_ERR_INVALID_ARGUMENT = 1
 FI_ERR_WORKSPACE = 2
 FI_ERR_CUDA = 3
 FI_ERR_UNSUPPORTED = 4
+FI_ERR_REPLAN = 5
+PLAN_HEAD_PAIRS = 1
 
 DTYPE_F16, DTYPE_BF16, DTYPE_E4M3, DTYPE_E5M2, DTYPE_F32 = 0, 1, 2, 3, 4
 LAYOUT_NHD, LAYOUT_HND = 0, 1
@@ -40,7 +42,7 @@ class DecodePlanArgs(C.Structure):
                 ("num_kv_heads", _i32), ("head_dim", _i32), ("page_size", _i32), ("q_dtype", _i32),
                 ("kv_dtype", _i32), ("window_left", _i32), ("cuda_graph", _i32),
                 ("fixed_split_pages", _i32), ("disable_split_kv", _i32), ("device", _i32),
-                ("num_ctas_override", _i32), ("pad_", _i32), ("stream", _vp), ("kv_indices_host", _vp),
+                ("num_ctas_override", _i32), ("flags", _i32), ("stream", _vp), ("kv_indices_host", _vp),
                 ("num_indices", _i64), ("plan_info_out", _vp)]
 
 

@@ -46,6 +46,8 @@ static EncodeTiledFn get_encode_fn() {
 // {128 B, rows_per_box, 1, 2, 1} brings the K and the V rows of a token block.
 // A descriptor is a pure function of these arguments; a serving loop calls run() with the same
 // few caches (one per layer), so the last encodings are kept per thread.
+constexpr int64_t kHeadPairMap = -1;  // stride_kv value that selects the head-pair map
+
 struct KvMapKey {
   const void* base;
   int64_t dim_n, dim_h, dim_page, stride_n, stride_h, stride_page, stride_kv;
@@ -94,6 +96,24 @@ static int encode_kv_map(CUtensorMap* map, const void* base, int kv_dtype, int h
   CUtensorMapDataType dt = es == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
                                    : (kv_dtype == FI_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                                 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
+  if (stride_kv == kHeadPairMap) {
+    // (128 B, token % 8, head, token / 8, page), box {128, 8, 2, rows_per_box / 8, 1}: the box lands as
+    // 8-row groups ordered (token / 8, head), 1 KiB each = one 128B-swizzle atom (decode_kernel.cuh
+    // produce_tma HEADPAIR).  fp8 KV at head_dim 128 only.
+    cuuint64_t d5[5] = {128, 8, (cuuint64_t)dim_h, (cuuint64_t)(dim_n / 8), (cuuint64_t)dim_page};
+    cuuint64_t s4[4] = {(cuuint64_t)stride_n, (cuuint64_t)stride_h, (cuuint64_t)(8 * stride_n),
+                        (cuuint64_t)stride_page};
+    cuuint32_t b5[5] = {128, 8, 2, (cuuint32_t)(rows_per_box / 8), 1};
+    cuuint32_t e5[5] = {1, 1, 1, 1, 1};
+    // the pair's two rows are adjacent in an NHD cache: fetch them as one 256-byte request
+    const CUtensorMapL2promotion promo5 = stride_h == 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+                                                          : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    CUresult r5 = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 5, const_cast<void*>(base), d5, s4, b5, e5,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo5,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r5 != CUDA_SUCCESS) return fail(FI_ERR_CUDA, "cuTensorMapEncodeTiled (head pairs) failed with %d", (int)r5);
+    return FI_OK;
+  }
   const bool five = stride_kv > 0;
   cuuint64_t dims[5] = {(cuuint64_t)head_dim, (cuuint64_t)dim_n, (cuuint64_t)dim_h,
                         (cuuint64_t)dim_page, 1};
@@ -201,11 +221,11 @@ static int launch_hd(const DecodeParams& p, const CUtensorMap& km, const CUtenso
 }
 
 // fp8 KV, head_dim 128, TMA-eligible pages: tcgen05 / TMEM kernel (decode_kernel_tc5.cuh)
-template <int QT, int KVF>
+template <int QT, int KVF, bool HP = false>
 static int launch_tc5(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm, int grid,
                       cudaStream_t stream) {
-  auto kern = paged_decode_tc5_kernel<QT, KVF>;
-  const int smem = SmemLayout<KVF, 128>::total(p.num_stages);
+  auto kern = paged_decode_tc5_kernel<QT, KVF, HP>;
+  const int smem = SmemLayout<KVF, 128>::total(p.num_stages) + (HP ? kTc5PairScratchBytes : 0);
   FI_CUDA_TRY(ensure_smem_attr(kern, smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
@@ -288,6 +308,10 @@ static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUt
       case 2: return bf ? launch_rope<1, 2>(p, head_dim, grid, stream) : launch_rope<0, 2>(p, head_dim, grid, stream);
       default: return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
     }
+  }
+  if (p.head_pairs) {  // fi_batch_decode_run checked that this launch fits a head-pair plan
+    if (kvf == 1) return bf ? launch_tc5<1, 1, true>(p, km, vm, grid, stream) : launch_tc5<0, 1, true>(p, km, vm, grid, stream);
+    return bf ? launch_tc5<1, 2, true>(p, km, vm, grid, stream) : launch_tc5<0, 2, true>(p, km, vm, grid, stream);
   }
   if (kvf != 0 && head_dim == 128 && tma && use_tc5()) {
     if (kvf == 1) return bf ? launch_tc5<1, 1>(p, km, vm, grid, stream) : launch_tc5<0, 1>(p, km, vm, grid, stream);
@@ -400,7 +424,8 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.page_size = page_size;
   p.page_shift = is_pow2(page_size) ? ilog2(page_size) : -1;
   p.page_mask = is_pow2(page_size) ? page_size - 1 : 0;
-  const int TT = tile_tokens(kvf);
+  p.head_pairs = plan_info[kPiHeadPairs] != 0;
+  const int TT = p.head_pairs ? tile_tokens(kvf) / 2 : tile_tokens(kvf);
   p.rows_per_box = page_size < TT ? page_size : TT;
   p.tma_h_first = kv_stride_h < kv_stride_n;
   p.header = reinterpret_cast<const PlanHeader*>(iw + plan_info[kPiOffHeader]);
@@ -441,6 +466,9 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   const bool cuda_core_only = kvf != 0 && head_dim == 64;
   const bool tma = !cuda_core_only && tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h,
                                                    kv_stride_page, page_size, false, 0, TT);
+  if (p.head_pairs && (!tma || p.rope || !use_tc5() || es != 1 || head_dim != 128))
+    return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_HEAD_PAIRS, but this run() needs %s: plan "
+                               "again without the flag", p.rope ? "ROPE_LLAMA" : "the gather loader");
   if (!tma && tuning().loader == 1)
     return fail(FI_ERR_UNSUPPORTED, "TMA loader forced but page geometry is not eligible");
   if (!tma && (kv_stride_page * es >= (int64_t(1) << 32) || kv_stride_n * es >= (int64_t(1) << 32)))
@@ -448,7 +476,14 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   CUtensorMap km, vm;
   memset(&km, 0, sizeof(km));
   memset(&vm, 0, sizeof(vm));
-  if (tma) {
+  if (tma && p.head_pairs) {
+    int rc = make_kv_map(&km, k_cache, kv_dtype, head_dim, page_size, 2 * Hkv, num_pages, kv_stride_n,
+                         kv_stride_h, kv_stride_page, p.rows_per_box, kHeadPairMap);
+    if (rc != FI_OK) return rc;
+    rc = make_kv_map(&vm, v_cache, kv_dtype, head_dim, page_size, 2 * Hkv, num_pages, kv_stride_n,
+                     kv_stride_h, kv_stride_page, p.rows_per_box, kHeadPairMap);
+    if (rc != FI_OK) return rc;
+  } else if (tma) {
     const int Hkv_mem = Hkv / p.kv_head_div;  // heads the cache really has
     // K and V of a page interleaved inside the page stride (the 5-D cache every engine allocates):
     // one 5-D map over both, one TMA box per (page, token block) instead of two (mma.sync kernel)

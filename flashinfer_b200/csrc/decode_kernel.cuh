@@ -81,7 +81,7 @@ template <int KVF, int HD>
 struct SmemLayout {
   using G = TileGeom<KVF, HD>;
   static constexpr int SCRATCH_O = (kConsumerWarps - 1) * G::KSTEPS * 4 * 32 * 4;
-  static constexpr int SCRATCH_ML = 768;  // warp (m, l) pairs + merge flag; tcgen05 path: more
+  static constexpr int SCRATCH_ML = kScratchMlBytes;  // warp (m, l) pairs + merge flag; tcgen05 path: more
   static constexpr int SEG_BYTES = kSegCache * (int)sizeof(Segment);
   static constexpr int BAR_BYTES = 2 * kMaxStages * 8 + 128;  // ring + tcgen05-path barriers
   __host__ __device__ static constexpr int ring(int stages) { return stages * G::STAGE_BYTES; }
@@ -132,7 +132,7 @@ constexpr int kQNoReader = 0x3fffffff;
 constexpr int kQueueCtlFloat = 160;  // offset of the control words in the warp scratch (floats)
 constexpr int kMergeDescFloat = 168; // {go, request, kv_head, slot_begin, count} of a posted merge
 constexpr int kHeadPagesFloat = 176; // kItemInlinePages page ids of item blockIdx.x's first tiles
-static_assert((kHeadPagesFloat + kItemInlinePages) * 4 <= 768, "inline pages do not fit the scratch");
+static_assert((kHeadPagesFloat + kItemInlinePages) * 4 <= kScratchMlBytes, "inline pages do not fit the scratch");
 
 // In the implicit mode (single request, header == nullptr) the sequence is static and in closed
 // form: nothing is drawn, the ring holds the first kSegCache segments and later ones are recomputed.
@@ -389,18 +389,25 @@ __device__ __forceinline__ bool feeder_await(Feeder& f, const SegSource& s, int 
 // was removed; see DESIGN.md.)
 // PAIRED (the mma.sync kernel): the StageRow layout; with p.tma_paired the K and V panels of a
 // (page, token block) come in ONE 5-D box through `kmap`, else as a K box and a V box.
-template <int KVF, int HD, bool PAIRED = false>
+// HEADPAIR (the tcgen05 kernel on a head-pair plan, fp8 KV): a tile is G::TT / 2 tokens of TWO
+// adjacent KV heads; kmap / vmap are 5-D (128 B, 8 tokens, head, token / 8, page) and one box
+// {128, 8, 2, rows_per_box / 8, 1} brings rows_per_box tokens of both heads as 8-row groups in the
+// order (token / 8, head) — every 1 KiB group is one swizzle atom of the MMA descriptors, and a
+// token's two 128-byte rows (adjacent in an NHD cache) are requested together.
+template <int KVF, int HD, bool PAIRED = false, bool HEADPAIR = false>
 __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSource& src,
                                             const CUtensorMap* kmap, const CUtensorMap* vmap,
                                             uint32_t ring, uint32_t full_bar, uint32_t empty_bar) {
   using G = TileGeom<KVF, HD>;
+  static_assert(!HEADPAIR || (!PAIRED && G::NP == 1), "head pairs: 128-byte rows, K and V boxes");
+  constexpr int TT = HEADPAIR ? G::TT / 2 : G::TT;
   const int lane = threadIdx.x & 31;
   const int rpb = p.rows_per_box;
-  const int bpt = G::TT / rpb;  // boxes per tile along tokens: a power of two <= 16
+  const int bpt = TT / rpb;  // boxes per tile along tokens: a power of two <= 16
   const bool one_box = PAIRED && p.tma_paired != 0;
   const int nbox = (one_box ? 1 : 2) * G::NP * bpt;
   const int j = lane % bpt;  // same j for every i = lane + 32 k since bpt | 32
-  const uint32_t box_bytes = (uint32_t)rpb * 128u;
+  const uint32_t box_bytes = (uint32_t)rpb * (HEADPAIR ? 256u : 128u);
 
   const bool hints = (p.l2_hints & 1) != 0, keep_meta = (p.l2_hints & 2) != 0;
   const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
@@ -437,14 +444,14 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
       if (!more) break;
       t = sg.tile_begin;
       t_end = sg.tile_end;
-      mem_head = sg.kv_head / p.kv_head_div;
+      mem_head = HEADPAIR ? 2 * sg.kv_head : sg.kv_head / p.kv_head_div;
       npage0 = k == 0 ? src.num_pages : 0;
-      page0 = (sg.tile_begin * G::TT) >> p.page_shift;
+      page0 = (sg.tile_begin * TT) >> p.page_shift;
     }
     // boxes of tile t: page index + first row for this lane's token block j
-    const int tok0 = t * G::TT;
+    const int tok0 = t * TT;
     const int rem = sg.tok_hi - tok0;  // > 0 by construction
-    const int nvb = rem >= G::TT ? bpt : (rem + rpb - 1) / rpb;
+    const int nvb = rem >= TT ? bpt : (rem + rpb - 1) / rpb;
     const int tok = tok0 + j * rpb;
     int page = 0;
     if (j < nvb) {
@@ -466,7 +473,11 @@ __device__ __forceinline__ void produce_tma(const DecodeParams& p, const SegSour
       for (int i = lane; i < nbox; i += 32) {
         const int pn = (i / bpt) % G::NP;
         const int kv = i / (bpt * G::NP);
-        if constexpr (PAIRED) {
+        if constexpr (HEADPAIR) {
+          const uint32_t dst = sbase + kv * G::KV_BYTES;
+          if (hints) tma_load_5d_hint(dst, kv ? vmap : kmap, full_bar + 8 * stage, 0, 0, mem_head, row0 >> 3, page, pol_stream);
+          else tma_load_5d(dst, kv ? vmap : kmap, full_bar + 8 * stage, 0, 0, mem_head, row0 >> 3, page);
+        } else if constexpr (PAIRED) {
           const uint32_t dst = sbase + pn * (2 * G::PANEL_BYTES) + kv * box_bytes;
           if (one_box) {
             if (hints) tma_load_5d_hint(dst, kmap, full_bar + 8 * stage, pn * (128 / G::ES), c1, c2, 0, page, pol_stream);

@@ -21,6 +21,16 @@
 // raised only when the tile maximum exceeds it by more than 2^5; then O is rescaled in TMEM
 // (tcgen05.ld / st).  p = 2^(x - rho + 3) <= 256 fits e4m3; hi + lo keeps ~8 bits.
 // Semantics (base-2 lse, -5e4 sentinel, empty -> o = 0) as in decode_kernel.cuh.
+//
+// HP (head-pair plans, DecodeParams::head_pairs): a unit is a request and a PAIR of adjacent KV heads,
+// a tile 64 tokens of both.  One TMA box brings 8-row groups ordered (token / 8, head), so the 128 rows
+// of a stage's K (and V) part alternate between the heads every 8 rows and softmax thread t owns
+// token 8 (t / 16) + t % 8 of head (t / 8) % 2:
+//   S[128 rows x 64]  = K rows x [Qs(head 0) | Qs(head 1)]^T     (one MMA chain; a row reads only the
+//                        32 columns of its own head, the other 32 are never looked at)
+//   O_h[128 d x 16]  += V rows of head h (8-row groups at twice the stride) x P rows of head h
+// Everything per head — rho, l, the bump vote's maxima — is exchanged among the 64 threads of that head.
+// The query buffer is single (8 KiB); the issuer hands it back through `q_free`.
 #pragma once
 #include "decode_kernel.cuh"
 #include "tc5.cuh"
@@ -28,15 +38,20 @@
 namespace fib200 {
 
 constexpr int kTc5Threads = 192;
-constexpr int kTc5TmemCols = 128;   // S: 2 x 32 columns, O: 16 columns
-constexpr int kTc5ColS = 0;         // S[b] at column 32 b
-constexpr int kTc5ColO = 64;
+// TMEM columns: S[b] at kTc5ColS + sstride b (2 buffers), O after them
+template <bool HP>
+struct Tc5Cols {
+  static constexpr uint32_t kSStride = HP ? 64 : 32;
+  static constexpr uint32_t kO = 2 * kSStride;          // HP: O_h at kO + 16 h
+  static constexpr uint32_t kAlloc = HP ? 256 : 128;    // a power of two >= kO + (HP ? 32 : 16)
+};
+constexpr int kTc5ColS = 0;
 constexpr float kTc5Bump = 5.f;     // raise rho when a tile max exceeds it by more than 2^5
 constexpr float kTc5PShift = 3.f;   // p = 2^(x - rho + 3): <= 2^8 right after a bump
 
 // barrier slots after the ring's full/empty arrays (SmemLayout::BAR_BYTES reserves 128 bytes)
 struct Tc5Bars {
-  uint32_t s_ready[2], s_free[2], p_ready[2], p_free[2], q_ready[2];
+  uint32_t s_ready[2], s_free[2], p_ready[2], p_free[2], q_ready[2], q_free;
 };
 __device__ __forceinline__ Tc5Bars tc5_bars(uint32_t base) {
   Tc5Bars b;
@@ -48,23 +63,28 @@ __device__ __forceinline__ Tc5Bars tc5_bars(uint32_t base) {
     b.p_free[i] = base + 48 + 8 * i;
     b.q_ready[i] = base + 64 + 8 * i;
   }
+  b.q_free = base + 80;
   return b;
 }
 
 // ---- query preparation: 128 softmax threads write Qs (32 rows x 128 B, K-major SW128) ---------
 // thread t: head h = t / 16, dims d0 = 8 (t % 16) .. d0 + 7.  Row 8 term + h holds term `term` of
 // head h; rows 24-31 and heads >= group_size are zero.  dq[h] = amax / 256 is the inverse scale.
-template <int QT>
+// HP: two passes, rows 32 hp + .. and dq[8 hp + h] for head hp of the pair.
+template <int QT, bool HP>
 __device__ __forceinline__ void tc5_prepare_q(const DecodeParams& p, const Segment& sg, uint8_t* qbuf,
                                               float* dq_out, int tid) {
   const int h = tid >> 4, d0 = (tid & 15) * 8;
-  const int GS = p.group_size;
+  const int GS = p.group_size;                // query heads of the unit (both heads of a pair)
+  const int G1 = HP ? GS >> 1 : GS;           // query heads per KV head
+#pragma unroll
+  for (int hp = 0; hp < (HP ? 2 : 1); ++hp) {
   float x[8];
   float amax = 0.f;
-  if (h < GS) {
+  if (h < G1) {
     const char* qrow = static_cast<const char*>(p.q) +
                        ((int64_t)sg.request * p.q_stride_n +
-                        (int64_t)(sg.kv_head * GS + h) * p.q_stride_h) * 2 + d0 * 2;
+                        (int64_t)(sg.kv_head * GS + hp * G1 + h) * p.q_stride_h) * 2 + d0 * 2;
     const uint2 v0 = __ldg(reinterpret_cast<const uint2*>(qrow));
     const uint2 v1 = __ldg(reinterpret_cast<const uint2*>(qrow) + 1);
     const uint32_t w[4] = {v0.x, v0.y, v1.x, v1.y};
@@ -89,14 +109,14 @@ __device__ __forceinline__ void tc5_prepare_q(const DecodeParams& p, const Segme
   for (int s = 1; s < 16; s <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, s));
   const bool nz = amax > 0.f && amax < 3.0e38f;
   const float sq = nz ? 256.f / amax : 1.f;
-  if ((tid & 15) == 0) dq_out[h] = nz ? amax * (1.f / 256.f) : 1.f;
+  if ((tid & 15) == 0) dq_out[8 * hp + h] = nz ? amax * (1.f / 256.f) : 1.f;
   uint32_t t[4][3];
 #pragma unroll
   for (int i = 0; i < 4; ++i) split3_e4m3x2(t[i], x[2 * i] * sq, x[2 * i + 1] * sq);
   const int chunk = d0 >> 4, within = d0 & 15;
 #pragma unroll
   for (int term = 0; term < 4; ++term) {
-    const int row = 8 * term + h;
+    const int row = 32 * hp + 8 * term + h;
     uint2 v = make_uint2(0u, 0u);
     if (term < 3) {
       v.x = t[0][term] | (t[1][term] << 16);
@@ -104,17 +124,19 @@ __device__ __forceinline__ void tc5_prepare_q(const DecodeParams& p, const Segme
     }
     *reinterpret_cast<uint2*>(qbuf + swz<128>(row, chunk) + within) = v;
   }
+  }
 }
 
 // ---- MMA issuer (warp 5; one elected lane issues, the warp stays converged) ---------------------
-template <int KVF>
+template <int KVF, bool HP>
 __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource& src,
                                           uint32_t ring, uint32_t qbufs,
                                           uint32_t pbufs, uint32_t full_bar, uint32_t empty_bar,
                                           const Tc5Bars& bars, uint32_t tmem) {
   using G = TileGeom<KVF, 128>;
   constexpr int AF = (KVF == 2) ? 1 : 0;  // e5m2 : e4m3 storage
-  constexpr uint32_t idesc_qk = tc5::instr_desc_f8(AF, 0, /*a K-major*/ 0, /*b K-major*/ 0, 128, 32);
+  using TC = Tc5Cols<HP>;
+  constexpr uint32_t idesc_qk = tc5::instr_desc_f8(AF, 0, /*a K-major*/ 0, /*b K-major*/ 0, 128, HP ? 64 : 32);
   constexpr uint32_t idesc_pv = tc5::instr_desc_f8(AF, 0, /*a MN-major*/ 1, /*b MN-major*/ 1, 128, 16);
   const bool leader = (threadIdx.x & 31) == 0;
   int stage = 0;
@@ -132,11 +154,24 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
     if (leader) {
       const uint32_t vbase = ring + pend_stage * G::STAGE_BYTES + G::KV_BYTES;
       const uint32_t pb = pbufs + b * 2048u;
+      if constexpr (HP) {
+        // head hp owns every other 8-row group: V groups 2 KiB apart, P groups 256 B apart
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks) {  // 32 tokens per MMA
-        const uint64_t ad = tc5::smem_desc(vbase + ks * 4096u, 1024u, 1024u, tc5::kLayoutSw128);
-        const uint64_t bd = tc5::smem_desc(pb + ks * 512u, 128u, 128u, tc5::kLayoutNone);
-        tc5::mma_f8(tmem + kTc5ColO, ad, bd, idesc_pv, (ks > 0) ? 1u : pend_acc);
+        for (int hp = 0; hp < 2; ++hp) {
+#pragma unroll
+          for (int ks = 0; ks < 2; ++ks) {  // 32 tokens of head hp per MMA
+            const uint64_t ad = tc5::smem_desc(vbase + hp * 1024u + ks * 8192u, 1024u, 2048u, tc5::kLayoutSw128);
+            const uint64_t bd = tc5::smem_desc(pb + hp * 128u + ks * 1024u, 256u, 256u, tc5::kLayoutNone);
+            tc5::mma_f8(tmem + TC::kO + 16u * hp, ad, bd, idesc_pv, (ks > 0) ? 1u : pend_acc);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {  // 32 tokens per MMA
+          const uint64_t ad = tc5::smem_desc(vbase + ks * 4096u, 1024u, 1024u, tc5::kLayoutSw128);
+          const uint64_t bd = tc5::smem_desc(pb + ks * 512u, 128u, 128u, tc5::kLayoutNone);
+          tc5::mma_f8(tmem + TC::kO, ad, bd, idesc_pv, (ks > 0) ? 1u : pend_acc);
+        }
       }
       tc5::commit(empty_bar + 8 * pend_stage);  // K / V stage back to the TMA producer
       tc5::commit(bars.p_free[b]);              // P buffer reusable, O updated
@@ -150,8 +185,11 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
     if (!seg_fetch(src, k, sg)) break;
     __syncwarp();
     if (leader) src.ctl[kQDone1] = k + 1;  // this warp holds its copy of segment k
-    mbar_wait(bars.q_ready[k & 1], (k >> 1) & 1u);  // every segment: never lag a phase behind
-    const uint32_t qb = qbufs + (k & 1) * 4096u;
+    // every segment: never lag a phase behind
+    if constexpr (HP) mbar_wait(bars.q_ready[0], k & 1u);
+    else mbar_wait(bars.q_ready[k & 1], (k >> 1) & 1u);
+    const uint32_t qb = HP ? qbufs : qbufs + (k & 1) * 4096u;
+    if (HP && leader && sg.tile_end <= sg.tile_begin) mbar_arrive(bars.q_free);  // nothing reads this query
     for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
       const uint32_t b = n & 1u;
       // wait for the next K tile (and a free S buffer), but serve the pending P.V the moment its
@@ -176,9 +214,10 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
         for (int ks = 0; ks < 4; ++ks) {  // 32 head dims per MMA: +32 bytes inside the SW128 row
           const uint64_t ad = tc5::smem_desc(kbase + ks * 32u, 16u, 1024u, tc5::kLayoutSw128);
           const uint64_t bd = tc5::smem_desc(qb + ks * 32u, 16u, 1024u, tc5::kLayoutSw128);
-          tc5::mma_f8(tmem + kTc5ColS + 32u * b, ad, bd, idesc_qk, ks > 0 ? 1u : 0u);
+          tc5::mma_f8(tmem + kTc5ColS + TC::kSStride * b, ad, bd, idesc_qk, ks > 0 ? 1u : 0u);
         }
         tc5::commit(bars.s_ready[b]);
+        if (HP && tile == sg.tile_end - 1) tc5::commit(bars.q_free);  // the single query buffer is free again
       }
       __syncwarp();
       if (pend) issue_pv();
@@ -194,9 +233,11 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
 }
 
 
-// ---- softmax warps (0-3): thread tid <-> token tid of each tile, TMEM lane tid ------------------
+// ---- softmax warps (0-3), one KV head per unit: thread tid <-> token tid of each tile, TMEM lane tid ----
+// (kept apart from the head-pair version below: folding the two into one template cost the single-head
+// kernel 1.7 % on C3 through instruction scheduling alone)
 template <int QT, int KVF>
-__device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSource& src,
+__device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const SegSource& src,
                                             uint8_t* smem_ring,
                                             uint8_t* qbufs, uint8_t* pbufs, float* scratch,
                                             const Tc5Bars& bars, uint32_t tmem, int num_stages) {
@@ -227,7 +268,7 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
     Segment sg;
     if (!seg_fetch(src, k, sg)) break;
     if (!have_q) {
-      tc5_prepare_q<QT>(p, sg, qbufs + (k & 1) * 4096, dqs + (k & 1) * 8, tid);
+      tc5_prepare_q<QT, false>(p, sg, qbufs + (k & 1) * 4096, dqs + (k & 1) * 8, tid);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bars.q_ready[k & 1]);
@@ -258,7 +299,7 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
     have_q = src.ctl[kQPeek] != 0;
     if (have_q) {
       const Segment sn = seg_read(src, k + 1);
-      tc5_prepare_q<QT>(p, sn, qbufs + ((k + 1) & 1) * 4096, dqs + ((k + 1) & 1) * 8, tid);
+      tc5_prepare_q<QT, false>(p, sn, qbufs + ((k + 1) & 1) * 4096, dqs + ((k + 1) & 1) * 8, tid);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bars.q_ready[(k + 1) & 1]);
@@ -334,11 +375,11 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
           mbar_wait(bars.p_free[b ^ 1u], ((n - 1) >> 1) & 1u);
           tc5::fence_after_sync();
           float o[16];
-          tc5::ld_x16(tmem + lane_base + kTc5ColO, o);
+          tc5::ld_x16(tmem + lane_base + Tc5Cols<false>::kO, o);
           tc5::wait_ld();
 #pragma unroll
           for (int j = 0; j < 8; ++j) { o[j] *= alpha[j]; o[8 + j] *= alpha[j]; }
-          tc5::st_x16(tmem + lane_base + kTc5ColO, o);
+          tc5::st_x16(tmem + lane_base + Tc5Cols<false>::kO, o);
           tc5::wait_st();
           tc5::fence_before_sync();
         }
@@ -381,7 +422,7 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
       mbar_wait(bars.p_free[(n - 1) & 1u], ((n - 1) >> 1) & 1u);  // P.V of the last tile complete
       tc5::fence_after_sync();
       float o[16];
-      tc5::ld_x16(tmem + lane_base + kTc5ColO, o);
+      tc5::ld_x16(tmem + lane_base + Tc5Cols<false>::kO, o);
       tc5::wait_ld();
       tc5::fence_before_sync();
 #pragma unroll
@@ -444,8 +485,328 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
   FI_TRACE_IF(tid == 0, 8);
 }
 
+// ---- softmax warps (0-3): thread tid <-> row tid of each tile (TMEM lane tid) ------------------
+// row tid = token tid of the tile; HP: token 8 (tid / 16) + tid % 8 of head (tid / 8) % 2.
+// reductions over the threads of one head: all 32 lanes; HP: the 16 lanes with the same bit 3
+template <bool HP>
+__device__ __forceinline__ float tc5_head_max(float m) {
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
+  if constexpr (!HP) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+  return fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+}
+template <bool HP>
+__device__ __forceinline__ float tc5_head_sum(float s) {
+  s += __shfl_xor_sync(0xffffffffu, s, 16);
+  if constexpr (!HP) s += __shfl_xor_sync(0xffffffffu, s, 8);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  return s + __shfl_xor_sync(0xffffffffu, s, 1);
+}
+// v[lane & 7] without a local-memory array index
+__device__ __forceinline__ float tc5_pick8(const float (&v)[8], int lane) {
+  float mine = v[0];
+#pragma unroll
+  for (int j = 1; j < 8; ++j) mine = (lane & 7) == j ? v[j] : mine;
+  return mine;
+}
+
+template <int QT, int KVF, bool HP>
+__device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSource& src,
+                                            uint8_t* smem_ring,
+                                            uint8_t* qbufs, uint8_t* pbufs, float* scratch,
+                                            float* pair_scratch, const Tc5Bars& bars, uint32_t tmem,
+                                            int num_stages) {
+  using G = TileGeom<KVF, 128>;
+  using TC = Tc5Cols<HP>;
+  constexpr int HD = 128;
+  constexpr int TT = HP ? G::TT / 2 : G::TT;  // tokens per tile
+  constexpr int NH = HP ? 2 : 1;              // KV heads per unit
+  constexpr int WS = 8 * NH;                  // per-warp exchange stride (floats)
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int GS = p.group_size;                // query heads of the unit
+  const int G1 = HP ? GS >> 1 : GS;           // query heads per KV head
+  const int hp = HP ? (tid >> 3) & 1 : 0;     // this row's head of the pair
+  const int tok_in_tile = HP ? ((tid >> 4) << 3) | (tid & 7) : tid;
+  const bool use_cap = p.soft_cap > 0.f;
+  const float cap_pre = use_cap ? p.sm_scale / p.soft_cap : 0.f;
+  const float cap_post = use_cap ? p.soft_cap * 1.4426950408889634f : 0.f;
+  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;  // TMEM lane field
+  // scratch (floats): wmax @0 ([2][4][8]; HP: [4][16], single: a bump is followed by the next tile's
+  // vote barrier before wmax is written again), merge flag @64, dq @72 ([2][8]; HP: [16]), lsum @88
+  // ([4][8]), tmem slot @120, vote @124; HP, in pair_scratch: lsum [4][16] @0, alpha @64 [16], rho @80 [16]
+  float* wmax = scratch;
+  float* dqs = scratch + 72;
+  float* lsum = HP ? pair_scratch : scratch + 88;
+  float* alpha_sm = pair_scratch + 64;
+  float* rho_sm = pair_scratch + 80;
+  volatile int* vote = reinterpret_cast<volatile int*>(scratch + 124);  // [2][4]
+
+  int stage = 0;
+  uint32_t n = 0;  // tiles consumed so far: S / P buffer = n & 1
+  PendingMerge pm;
+  pm.mu = -1; pm.old = pm.cnt = pm.slot = pm.req = pm.head = 0;
+  // The query of segment k + 1 is prepared during segment k when that segment is already
+  // published (so the MMA warp can run ahead), else at the top of segment k + 1.  The decision
+  // must be the same in all 128 threads: thread 0 peeks, the barrier broadcasts.
+  // HP (one query buffer): "during" = after the last S tile of segment k has been read, once the
+  // issuer's q_free commit says that every Q.K MMA of segment k is complete.
+  bool have_q = false;
+  for (int k = 0;; ++k) {
+    Segment sg;
+    if (!seg_fetch(src, k, sg)) break;
+    if (!have_q) {
+      if (HP && k > 0) mbar_wait(bars.q_free, (k - 1) & 1u);
+      tc5_prepare_q<QT, HP>(p, sg, HP ? qbufs : qbufs + (k & 1) * 4096, HP ? dqs : dqs + (k & 1) * 8, tid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.q_ready[HP ? 0 : k & 1]);
+    }
+    if (tid == 0) {
+      src.ctl[kQPeek] = seg_peek(src, k + 1) ? 1 : 0;
+      src.ctl[kQDone0] = k;  // every thread is past segment k - 1 (barrier 3 of its epilogue)
+    }
+    named_bar_sync(1, 128);  // dq of segment k visible; scratch of segment k-1 no longer read
+    float mul[8], pre[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = dqs[(HP ? 8 * hp : (k & 1) * 8) + j];
+      mul[j] = d * p.sm_scale_log2;
+      pre[j] = d * cap_pre;
+    }
+    float alc[8];  // ALiBi slope per head, in the units of the expression it is added to
+#pragma unroll
+    for (int j = 0; j < 8; ++j) alc[j] = 0.f;
+    if (p.alibi_slopes != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float a = j < G1 ? __ldg(p.alibi_slopes + sg.kv_head * GS + hp * G1 + j) : 0.f;
+        alc[j] = a * (use_cap ? cap_pre : 1.4426950408889634f);
+        pre[j] *= p.sm_scale;
+      }
+    }
+    have_q = src.ctl[kQPeek] != 0;
+    if (!HP && have_q) {
+      const Segment sn = seg_read(src, k + 1);
+      tc5_prepare_q<QT, HP>(p, sn, qbufs + ((k + 1) & 1) * 4096, dqs + ((k + 1) & 1) * 8, tid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.q_ready[(k + 1) & 1]);
+    }
+    float rho[8], l[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { rho[j] = kNegInf; l[j] = 0.f; }
+
+    for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
+      const uint32_t b = n & 1u;
+      const int tok = tile * TT + tok_in_tile;
+      const bool valid = tok >= sg.tok_lo && tok < sg.tok_hi;
+      float x[8];
+      {
+        mbar_wait(bars.s_ready[b], (n >> 1) & 1u);
+        FI_TRACE_IF(tid == 0 && n == 0, 5);
+        tc5::fence_after_sync();
+        // tcgen05.ld is warp-collective (one address per warp), and a warp holds rows of both heads
+        // of a pair: both heads' 24 term columns are read and every row keeps its own
+        float sd[8];
+        if constexpr (HP) {
+          float c0[16], c1[8], e0[16], e1[8];
+          const uint32_t sb = tmem + lane_base + kTc5ColS + TC::kSStride * b;
+          tc5::ld_x16(sb, c0);
+          tc5::ld_x8(sb + 16u, c1);
+          tc5::ld_x16(sb + 32u, e0);
+          tc5::ld_x8(sb + 48u, e1);
+          tc5::wait_ld();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float s0 = c0[j] + c0[8 + j] + c1[j], s1 = e0[j] + e0[8 + j] + e1[j];
+            sd[j] = hp ? s1 : s0;
+          }
+        } else {
+          float c[32];
+          tc5::ld_x32(tmem + lane_base + kTc5ColS + TC::kSStride * b, c);
+          tc5::wait_ld();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) sd[j] = c[j] + c[8 + j] + c[16 + j];
+        }
+        tc5::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bars.s_free[b]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float sdot = sd[j];
+          const float v = use_cap ? cap_post * tanhf_approx(sdot * pre[j] + alc[j] * (float)tok)
+                                  : sdot * mul[j] + alc[j] * (float)tok;
+          x[j] = valid ? v : kNegInf;
+        }
+      }
+      // Does any logit of this tile exceed rho by more than 2^kTc5Bump?  One vote per warp and one
+      // CTA barrier in the common case; the exact per-head maxima are only reduced when rho moves.
+      bool over = false;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) over |= x[j] > rho[j] + kTc5Bump;
+      const bool wover = __any_sync(0xffffffffu, over);
+      if (lane == 0) vote[b * 4 + warp] = wover ? 1 : 0;
+      named_bar_sync(2, 128);
+      const bool bump = (vote[b * 4] | vote[b * 4 + 1] | vote[b * 4 + 2] | vote[b * 4 + 3]) != 0;
+      if (bump) {  // CTA-uniform: every thread of a head sees the same maxima
+        float mt[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) mt[j] = tc5_head_max<HP>(x[j]);
+        float* wm = HP ? wmax : wmax + b * 32;
+        if (lane < WS) wm[warp * WS + lane] = tc5_pick8(mt, lane);  // HP: lanes 8-15 belong to head 1
+        named_bar_sync(3, 128);
+        float alpha[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int i = 8 * hp + j;
+          const float m = fmaxf(fmaxf(wm[i], wm[WS + i]), fmaxf(wm[2 * WS + i], wm[3 * WS + i]));
+          const float rn = m > rho[j] + kTc5Bump ? m : rho[j];
+          alpha[j] = ex2f(rho[j] - rn);
+          l[j] *= alpha[j];
+          rho[j] = rn;
+        }
+        if (tile != sg.tile_begin) {
+          // O in TMEM is relative to the old rho: wait for P.V of the previous tile, rescale.  This
+          // thread is row d of O^T for ALL heads of the unit.
+          if constexpr (HP) {
+            if (tid < 16) alpha_sm[tid] = tc5_pick8(alpha, tid);  // tid / 8 = that thread's head
+            named_bar_sync(3, 128);
+          }
+          mbar_wait(bars.p_free[b ^ 1u], ((n - 1) >> 1) & 1u);
+          tc5::fence_after_sync();
+#pragma unroll
+          for (int h2 = 0; h2 < NH; ++h2) {
+            float o[16];
+            tc5::ld_x16(tmem + lane_base + TC::kO + 16u * h2, o);
+            tc5::wait_ld();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float a = HP ? alpha_sm[8 * h2 + j] : alpha[j];
+              o[j] *= a;
+              o[8 + j] *= a;
+            }
+            tc5::st_x16(tmem + lane_base + TC::kO + 16u * h2, o);
+          }
+          tc5::wait_st();
+          tc5::fence_before_sync();
+        }
+      }
+      // probabilities -> e4m3 hi / lo, one 16-byte row per token
+      uint32_t w[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float p0 = valid ? ex2f(x[2 * i] - rho[2 * i] + kTc5PShift) : 0.f;
+        const float p1 = valid ? ex2f(x[2 * i + 1] - rho[2 * i + 1] + kTc5PShift) : 0.f;
+        l[2 * i] += p0;
+        l[2 * i + 1] += p1;
+        w[i] = split_e4m3x2(p0, p1);  // hi pair in bits 0-15, lo pair in bits 16-31
+      }
+      uint4 row;
+      row.x = (w[0] & 0xffffu) | (w[1] << 16);
+      row.y = (w[2] & 0xffffu) | (w[3] << 16);
+      row.z = (w[0] >> 16) | (w[1] & 0xffff0000u);
+      row.w = (w[2] >> 16) | (w[3] & 0xffff0000u);
+      mbar_wait(bars.p_free[b], ((n >> 1) & 1u) ^ 1u);  // P.V of tile n-2 done with this buffer
+      *reinterpret_cast<uint4*>(pbufs + b * 2048 + tid * 16) = row;
+      if (tok >= sg.tok_hi) {
+        // this token's V row was not (validly) loaded: zero it so that 0 * junk cannot be NaN
+        uint4* vrow = reinterpret_cast<uint4*>(smem_ring + stage * G::STAGE_BYTES + G::KV_BYTES +
+                                               tid * 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) vrow[i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.p_ready[b]);
+      ++n;
+      if (++stage == num_stages) stage = 0;
+    }
+    if (HP && have_q) {  // CTA-uniform; see the comment at have_q
+      // a segment without tiles has no barrier since dq of segment k was read: it is overwritten below
+      if (sg.tile_end <= sg.tile_begin) named_bar_sync(2, 128);
+      mbar_wait(bars.q_free, k & 1u);
+      const Segment sn = seg_read(src, k + 1);
+      tc5_prepare_q<QT, HP>(p, sn, qbufs, dqs, tid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.q_ready[0]);
+    }
+
+    FI_TRACE_IF(tid == 0, 6);
+    // ---- segment epilogue: thread tid <-> head-dim index d = tid (TMEM lane of O) ---------------
+    float o8[NH * 8];
+    if (sg.tile_end > sg.tile_begin) {
+      mbar_wait(bars.p_free[(n - 1) & 1u], ((n - 1) >> 1) & 1u);  // P.V of the last tile complete
+      tc5::fence_after_sync();
+#pragma unroll
+      for (int h2 = 0; h2 < NH; ++h2) {
+        float o[16];
+        tc5::ld_x16(tmem + lane_base + TC::kO + 16u * h2, o);
+        tc5::wait_ld();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o8[8 * h2 + j] = o[j] + o[8 + j];
+      }
+      tc5::fence_before_sync();
+    } else {
+#pragma unroll
+      for (int i = 0; i < NH * 8; ++i) o8[i] = 0.f;
+    }
+    {
+      float L[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) L[j] = tc5_head_sum<HP>(l[j]);
+      if (lane < WS) lsum[warp * WS + lane] = tc5_pick8(L, lane);
+      if (HP && tid < 16) rho_sm[tid] = tc5_pick8(rho, tid);
+    }
+    if (tid == 0) merge_post(p, pm, scratch);  // arrival of the previous partial
+    named_bar_sync(3, 128);
+    merge_run_posted<QT, HD>(p, scratch, tid);
+
+    const bool direct = sg.slot < 0;
+    const int64_t hq = (int64_t)sg.request * p.num_qo_heads + sg.kv_head * GS;
+#pragma unroll
+    for (int i = 0; i < NH * 8; ++i) {  // i: exchange index = 8 * (head of the pair) + head in its group
+      {
+        const int h2 = i >> 3, j = i & 7;
+        if (j < G1) {
+          const int qh = h2 * G1 + j;      // query head inside the unit
+          float Lj = (lsum[i] + lsum[WS + i]) + (lsum[2 * WS + i] + lsum[3 * WS + i]);
+          const float rj = HP ? rho_sm[i] : rho[j];
+          const bool any = Lj > 0.f;
+          if (direct && any && p.sinks != nullptr)  // L is relative to rho and carries 2^kTc5PShift
+            Lj += ex2f(__ldg(p.sinks + sg.kv_head * GS + qh) * 1.4426950408889634f - rj + kTc5PShift);
+          // numerator and denominator both carry the 2^kTc5PShift scale of p
+          const float val = any ? o8[i] * ((direct ? p.v_scale : 1.f) / Lj) : 0.f;
+          const float lse2 = any ? rj + lg2f(Lj) - kTc5PShift : kNegInf;
+          if (direct) {
+            if (QT == 1) static_cast<__nv_bfloat16*>(p.o)[(hq + qh) * HD + tid] = __float2bfloat16_rn(val);
+            else static_cast<__half*>(p.o)[(hq + qh) * HD + tid] = __float2half_rn(val);
+            if (p.lse != nullptr && tid == i) p.lse[hq + qh] = lse2;
+          } else {
+            p.tmp_o[((int64_t)sg.slot * GS + qh) * HD + tid] = val;
+            if (tid == i) p.tmp_lse[(int64_t)sg.slot * GS + qh] = lse2;
+          }
+        }
+      }
+    }
+    FI_TRACE_IF(tid == 0, 7);
+    if (sg.merge_unit >= 0) {  // CTA-uniform: count the arrival, look at the result later
+      named_bar_sync(2, 128);  // all 128 threads wrote their part of the partial
+      if (tid == 0) merge_arrive(p, pm, sg);
+    }
+  }
+  // end of this CTA's sequence: the last arrival is still unchecked
+  if (tid == 0) merge_post(p, pm, scratch);
+  named_bar_sync(3, 128);
+  merge_run_posted<QT, HD>(p, scratch, tid);
+  FI_TRACE_IF(tid == 0, 8);
+}
+
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 1 = e4m3, 2 = e5m2 KV.  head_dim 128, TMA-eligible pages.
-template <int QT, int KVF>
+// HP: head-pair plan (see the top of this file).
+template <int QT, int KVF, bool HP = false>
 __global__ void __launch_bounds__(kTc5Threads, 2)
     paged_decode_tc5_kernel(const __grid_constant__ DecodeParams p,
                             const __grid_constant__ CUtensorMap kmap,
@@ -459,7 +820,7 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   uint8_t* base = smem_raw + pad;
   const uint32_t ring = raw + pad;
   const int ring_bytes = p.num_stages * G::STAGE_BYTES;
-  uint8_t* qbufs = base + ring_bytes;            // 2 x 4 KiB, 1024-aligned
+  uint8_t* qbufs = base + ring_bytes;            // 2 x 4 KiB (HP: 1 x 8 KiB), 1024-aligned
   uint8_t* pbufs = qbufs + 2 * 4096;             // 2 x 2 KiB
   float* scratch = reinterpret_cast<float*>(base + ring_bytes + L::SCRATCH_O);
   Segment* seg_cache =
@@ -467,12 +828,15 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   const uint32_t full_bar = ring + ring_bytes + L::SCRATCH_O + L::SCRATCH_ML + L::SEG_BYTES;
   const uint32_t empty_bar = full_bar + 8 * kMaxStages;
   const Tc5Bars bars = tc5_bars(empty_bar + 8 * kMaxStages);
+  // HP only (the launch adds kTc5PairScratchBytes): right after the layout every kernel shares
+  float* pair_scratch = reinterpret_cast<float*>(base + ring_bytes + L::SCRATCH_O + L::SCRATCH_ML +
+                                                 L::SEG_BYTES + L::BAR_BYTES);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(scratch + 120);
 
   const int tid = threadIdx.x, warp = tid >> 5;
   FI_TRACE_IF(tid == 0, 0);
   // TMEM allocation (warp 1) overlaps barrier setup (thread 0) and the work-list fetch
-  if (warp == 1) tc5::tmem_alloc(smem_u32(tmem_slot), kTc5TmemCols);
+  if (warp == 1) tc5::tmem_alloc(smem_u32(tmem_slot), Tc5Cols<HP>::kAlloc);
   if (tid == 0) {
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(full_bar + 8 * s, 1);
@@ -485,18 +849,19 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
       mbar_init(bars.p_free[i], 1);
       mbar_init(bars.q_ready[i], 4);
     }
+    mbar_init(bars.q_free, 1);
     fence_mbar_init();
     tma_prefetch_desc(&kmap);
     tma_prefetch_desc(&vmap);
   }
-  const SegSource src = seg_source_init(p, G::TT, seg_cache, scratch, /*has_reader1=*/true);
+  const SegSource src = seg_source_init(p, HP ? G::TT / 2 : G::TT, seg_cache, scratch, /*has_reader1=*/true);
   tc5::fence_before_sync();
   __syncthreads();
   tc5::fence_after_sync();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   FI_TRACE_IF(tid == 0, 1);
   if (seg_source_idle(src)) {
-    if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);
+    if (warp == 1) tc5::tmem_dealloc(tmem, Tc5Cols<HP>::kAlloc);
     return;
   }
   if (p.enable_pdl == 1) pdl_launch_dependents();  // early trigger, see paged_decode_kernel
@@ -506,16 +871,17 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   // requests its first page indices and then waits, the MMA issuer touches no global memory
   if (warp < 4) {
     if (p.enable_pdl) pdl_wait();
-    tc5_softmax<QT, KVF>(p, src, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
+    if constexpr (HP) tc5_softmax<QT, KVF, HP>(p, src, base, qbufs, pbufs, scratch, pair_scratch, bars, tmem, p.num_stages);
+    else tc5_softmax_single<QT, KVF>(p, src, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
   } else if (warp == 4) {
-    produce_tma<KVF, 128>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
+    produce_tma<KVF, 128, false, HP>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
   } else {
-    tc5_issue<KVF>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
+    tc5_issue<KVF, HP>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
   }
   if (p.enable_pdl == 2) pdl_launch_dependents();
   tc5::fence_before_sync();
   __syncthreads();
-  if (warp == 1) tc5::tmem_dealloc(tmem, kTc5TmemCols);
+  if (warp == 1) tc5::tmem_dealloc(tmem, Tc5Cols<HP>::kAlloc);
 }
 
 }  // namespace fib200

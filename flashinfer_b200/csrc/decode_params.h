@@ -19,6 +19,8 @@ constexpr int kConsumerWarps = 4;
 // D = 128 either way.  kvf: 0 = 16-bit KV, 1 = e4m3, 2 = e5m2.
 __host__ __device__ constexpr int tile_tokens(int kvf) { return kvf == 0 ? 64 : 128; }
 constexpr int kMaxStages = 12;
+constexpr int kScratchMlBytes = 768;   // per-CTA scratch (floats 0 .. 191): warp exchange, queue control, inline pages
+constexpr int kTc5PairScratchBytes = 512;  // head-pair tcgen05 kernel only, after the barriers
 constexpr int kSegCache = 32;         // segment queue (ring) in smem per CTA; a power of two
 constexpr int kSegRefill = 8;         // segments the feeder loads from the list at a time
 constexpr float kNegInf = -5e4f;      // finite "-inf", reference math.cuh:32
@@ -124,6 +126,7 @@ enum PlanInfoSlot {
   kPiOffIndices,      // byte offset in the int workspace of plan()'s device copy of kv_indices, or -1
   kPiNumIndices,      // entries of that copy
   kPiIndicesStable,   // 1: kv_indices is written by host copies only (plan() had it on the host)
+  kPiHeadPairs,       // 1: units are (request, PAIR of adjacent KV heads), tiles of 64 tokens (fp8 tcgen05 kernel)
   kPiLen
 };
 constexpr int64_t kPlanMagic = 0xF1B2000001LL;
@@ -180,6 +183,9 @@ struct DecodeParams {
   // with group / kv_head_div (<= kMaxGroup) query heads: Segment::kv_head counts virtual heads
   // (query / output addressing), the cache is addressed with kv_head / kv_head_div
   int32_t kv_head_div;
+  // head-pair plan (fp8 KV on the tcgen05 kernel): Segment::kv_head counts PAIRS of adjacent KV heads,
+  // group_size is twice the real GQA group (the query heads of both), tiles are 64 tokens
+  int32_t head_pairs;
   // attention sinks (reference decode.py:1176, tests/test_helpers/sink_attention_reference.py:23-36):
   // one extra logit per query head that takes part in the softmax denominator only —
   // p_i = exp(s_i) / (sum_j exp(s_j) + exp(sink[head])); natural-log units, not scaled by sm_scale.

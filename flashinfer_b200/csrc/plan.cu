@@ -50,7 +50,7 @@ KernelConfig choose_config(int kvf, int head_dim) {
   const int es = kvf == 0 ? 2 : 1;
   const int stage = 2 * tile_tokens(kvf) * head_dim * es;
   const int fixed = 1024 + (kConsumerWarps - 1) * head_dim * 32 /*scratch o*/ +
-                    768 + kSegCache * (int)sizeof(Segment) + 2 * kMaxStages * 8 + 128;
+                    kScratchMlBytes + kSegCache * (int)sizeof(Segment) + 2 * kMaxStages * 8 + 128;
   const int sm_total = 233472;  // 228 KiB per SM, each resident CTA reserves 1 KiB
   KernelConfig c;
   c.ctas_per_sm = tuning().ctas_per_sm;
@@ -130,14 +130,22 @@ void fi_set_tuning(int stages, int ctas_per_sm, int loader, int min_tiles_per_ct
   t.min_tiles_per_cta = min_tiles_per_cta;
 }
 
-int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, void* pinned_int_ws,
-                         size_t int_ws_bytes, const int32_t* indptr_host,
-                         const int32_t* last_page_len_host, const int32_t* kv_len_host,
-                         int batch_size, int num_qo_heads, int num_kv_heads, int head_dim,
-                         int page_size, int q_dtype, int kv_dtype, int window_left,
-                         int cuda_graph, int fixed_split_pages, int disable_split_kv, int device,
-                         int num_ctas_override, void* stream, const int32_t* kv_indices_host,
-                         int64_t num_indices, int64_t* plan_info_out) {
+// FI_B200_HEAD_PAIRS=0 ignores FI_PLAN_HEAD_PAIRS (A/B runs; read at every plan)
+static bool head_pairs_enabled() {
+  const char* e = getenv("FI_B200_HEAD_PAIRS");
+  if (e != nullptr && e[0] == '0') return false;
+  e = getenv("FI_B200_FP8_TC5");
+  return !(e != nullptr && e[0] == '0');
+}
+
+static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* pinned_int_ws,
+                     size_t int_ws_bytes, const int32_t* indptr_host,
+                     const int32_t* last_page_len_host, const int32_t* kv_len_host,
+                     int batch_size, int num_qo_heads, int num_kv_heads, int head_dim,
+                     int page_size, int q_dtype, int kv_dtype, int window_left,
+                     int cuda_graph, int fixed_split_pages, int disable_split_kv, int device,
+                     int num_ctas_override, void* stream, const int32_t* kv_indices_host,
+                     int64_t num_indices, int64_t* plan_info_out, int flags) {
   static_assert(kPiLen <= FI_PLAN_INFO_LEN, "plan info vector too short");
   (void)float_ws;
   if (batch_size < 0 || num_qo_heads <= 0 || num_kv_heads <= 0 || page_size <= 0)
@@ -149,9 +157,21 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   // reference's CUDA-core decode stops at group 8; its tensor-core decode takes any group)
   const int kv_div = group_split(num_qo_heads / num_kv_heads);
   num_kv_heads *= kv_div;
-  const int group = num_qo_heads / num_kv_heads;
+  int group = num_qo_heads / num_kv_heads;
   const int kvf = kv_format(q_dtype, kv_dtype);
   if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair (%d, %d)", q_dtype, kv_dtype);
+  // Head-pair plan (FI_PLAN_HEAD_PAIRS, fp8 KV, head_dim 128, TMA-sized pages): a unit is a request and a
+  // PAIR of adjacent KV heads, a tile 64 tokens of both — in an NHD cache the two 128-byte rows of a
+  // token are adjacent, so the tcgen05 kernel streams 256 contiguous bytes per token like a 16-bit
+  // cache does.  To everything downstream (items, partial slots, merge) this is a problem with half
+  // the KV heads and twice the GQA group.
+  const bool head_pairs = (flags & FI_PLAN_HEAD_PAIRS) != 0 && head_pairs_enabled() && kvf != 0 &&
+                          head_dim == 128 && kv_div == 1 && num_kv_heads % 2 == 0 && group <= kMaxGroup &&
+                          page_size >= 8 && (page_size & (page_size - 1)) == 0 && tuning().loader != 2;
+  if (head_pairs) {
+    num_kv_heads /= 2;
+    group *= 2;
+  }
   // fp8 KV at head_dim 64 (64-byte rows, below the 128-byte swizzle atom of the MMA kernels) runs on the
   // CUDA-core variant kernel (decode_rope_kernel.cuh with zero rotation frequencies)
   if (!(head_dim == 64 || head_dim == 128 || head_dim == 256))
@@ -171,7 +191,7 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   }
 
   // ---- per-request token / tile ranges --------------------------------------
-  const int TT = tile_tokens(kvf);
+  const int TT = head_pairs ? tile_tokens(kvf) / 2 : tile_tokens(kvf);
   // one scratch allocation per thread, reused across plans (plan() runs once per decode step)
   static thread_local std::vector<int32_t> scratch;
   scratch.resize((size_t)4 * batch_size);
@@ -622,17 +642,33 @@ int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, vo
   // ahead of its programmatic-dependent-launch wait.  Tables the caller keeps on the device
   // (fast_decode_plan, device tensors handed to plan()) may be rewritten by an upstream kernel.
   pi[kPiIndicesStable] = kv_indices_host != nullptr ? 1 : 0;
+  pi[kPiHeadPairs] = head_pairs ? 1 : 0;
   return FI_OK;
+}
+
+int fi_batch_decode_plan(void* float_ws, size_t float_ws_bytes, void* int_ws, void* pinned_int_ws,
+                         size_t int_ws_bytes, const int32_t* indptr_host,
+                         const int32_t* last_page_len_host, const int32_t* kv_len_host,
+                         int batch_size, int num_qo_heads, int num_kv_heads, int head_dim,
+                         int page_size, int q_dtype, int kv_dtype, int window_left,
+                         int cuda_graph, int fixed_split_pages, int disable_split_kv, int device,
+                         int num_ctas_override, void* stream, const int32_t* kv_indices_host,
+                         int64_t num_indices, int64_t* plan_info_out) {
+  return plan_impl(float_ws, float_ws_bytes, int_ws, pinned_int_ws, int_ws_bytes, indptr_host,
+                   last_page_len_host, kv_len_host, batch_size, num_qo_heads, num_kv_heads, head_dim,
+                   page_size, q_dtype, kv_dtype, window_left, cuda_graph, fixed_split_pages,
+                   disable_split_kv, device, num_ctas_override, stream, kv_indices_host, num_indices,
+                   plan_info_out, 0);
 }
 
 int fi_batch_decode_plan_args(const FiDecodePlanArgs* a) {
   if (a == nullptr) return fail(FI_ERR_INVALID_ARGUMENT, "null plan argument block");
-  return fi_batch_decode_plan(a->float_ws, a->float_ws_bytes, a->int_ws, a->pinned_int_ws, a->int_ws_bytes,
-                              a->indptr_host, a->last_page_len_host, a->kv_len_host, a->batch_size,
-                              a->num_qo_heads, a->num_kv_heads, a->head_dim, a->page_size, a->q_dtype,
-                              a->kv_dtype, a->window_left, a->cuda_graph, a->fixed_split_pages,
-                              a->disable_split_kv, a->device, a->num_ctas_override, a->stream,
-                              a->kv_indices_host, a->num_indices, a->plan_info_out);
+  return plan_impl(a->float_ws, a->float_ws_bytes, a->int_ws, a->pinned_int_ws, a->int_ws_bytes,
+                   a->indptr_host, a->last_page_len_host, a->kv_len_host, a->batch_size,
+                   a->num_qo_heads, a->num_kv_heads, a->head_dim, a->page_size, a->q_dtype,
+                   a->kv_dtype, a->window_left, a->cuda_graph, a->fixed_split_pages,
+                   a->disable_split_kv, a->device, a->num_ctas_override, a->stream,
+                   a->kv_indices_host, a->num_indices, a->plan_info_out, a->flags);
 }
 
 }  // extern "C"

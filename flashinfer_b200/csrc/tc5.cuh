@@ -91,6 +91,14 @@ __device__ __forceinline__ void ld_x16(uint32_t taddr, float (&v)[16]) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void ld_x8(uint32_t taddr, float (&v)[8]) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void st_x16(uint32_t taddr, const float (&v)[16]) {
   const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
   asm volatile(

@@ -12,6 +12,7 @@ from __future__ import annotations
 import ctypes as C
 import functools
 import math
+import os
 from typing import Any, List, Optional, Tuple, Union
 
 import torch
@@ -229,6 +230,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._dev_idx = device_index(self.device)
         self._lib = _lib.load()
         self._pdl_default = int(device_support_pdl(self.device))
+        self._head_pairs_ok = True   # cleared when a run() had to fall back (FI_ERR_REPLAN)
+        self._plan_call = None
         self._mtp_children = {}
         self._mtp_src = None
         self._pos_encoding_mode = "NONE"
@@ -404,8 +407,16 @@ class BatchDecodeWithPagedKVCacheWrapper:
             indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads, head_dim,
             page_size, q_data_type, kv_data_type, window_left,
             fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv,
-            indices_host=indices_host,
+            indices_host=indices_host, head_pairs=self._want_head_pairs(pos_encoding_mode),
         )
+        # kept for the one case run() has to plan again (FI_ERR_REPLAN, see _replan_without_head_pairs)
+        self._plan_call = ((indptr, indices, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size),
+                           dict(pos_encoding_mode=pos_encoding_mode, window_left=window_left,
+                                logits_soft_cap=logits_soft_cap, q_data_type=q_data_type,
+                                kv_data_type=kv_data_type, sm_scale=sm_scale, rope_scale=rope_scale,
+                                rope_theta=rope_theta, non_blocking=non_blocking, block_tables=block_tables,
+                                seq_lens=seq_lens, fixed_split_size=fixed_split_size,
+                                disable_split_kv=disable_split_kv))
         if indices_host is not None and not self._use_cuda_graph \
                 and self._plan_info[_PI_OFF_INDICES] < 0:
             # the table did not fit behind the work list in the int workspace: our own device copy
@@ -488,6 +499,27 @@ class BatchDecodeWithPagedKVCacheWrapper:
                    sm_scale=self._sm_scale, rope_scale=self._rope_scale, rope_theta=self._rope_theta,
                    fixed_split_size=fss, disable_split_kv=dskv)
 
+    def _want_head_pairs(self, pos_encoding_mode: str) -> bool:
+        """FI_PLAN_HEAD_PAIRS (include/fi_b200.h): an NHD cache keeps the rows of consecutive KV heads
+        adjacent, which the fp8 tcgen05 kernel streams as pairs; the planner ignores the bit for every
+        shape it does not apply to."""
+        if pos_encoding_mode == "ROPE_LLAMA" or not self._head_pairs_ok:
+            return False
+        # FI_B200_HEAD_PAIRS=2: also for HND caches (A/B runs; the kernel takes any head stride)
+        return self._kv_layout == "NHD" or os.environ.get("FI_B200_HEAD_PAIRS") == "2"
+
+    def _replan_without_head_pairs(self) -> bool:
+        """run() found that the head-pair plan does not fit the cache it was given (strides the TMA
+        loader cannot address) or the mode (forward() switched to ROPE_LLAMA): plan once more without
+        the flag, from the tensors the last plan() was given, and keep it off for this wrapper."""
+        if self._plan_call is None or torch.cuda.is_current_stream_capturing():
+            return False
+        self._head_pairs_ok = False
+        args, kw = self._plan_call
+        kw = dict(kw, pos_encoding_mode=self._pos_encoding_mode)
+        self.plan(*args, **kw)
+        return True
+
     def _bind_workspaces(self) -> None:
         fws, iws, pws = (self._float_workspace_buffer, self._int_workspace_buffer,
                          self._pin_memory_int_workspace_buffer)
@@ -502,7 +534,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
 
     def _run_plan(self, indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
                   head_dim, page_size, q_data_type, kv_data_type, window_left,
-                  fixed_split_size=None, disable_split_kv=False, indices_host=None) -> None:
+                  fixed_split_size=None, disable_split_kv=False, indices_host=None,
+                  head_pairs=False) -> None:
         # fixed_split_size (pages) / disable_split_kv: batch-invariant planning, reference
         # decode.py:880-887; None / -1 mean "off" there as here
         lib = _lib.load()
@@ -518,8 +551,9 @@ class BatchDecodeWithPagedKVCacheWrapper:
         pa.batch_size = batch_size
         # the problem description changes rarely between steps: rewritten only when it does
         sig = (num_qo_heads, num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left,
-               fixed_split_size, disable_split_kv, self._use_cuda_graph)
+               fixed_split_size, disable_split_kv, self._use_cuda_graph, head_pairs)
         if sig != self._plan_sig:
+            pa.flags = _lib.PLAN_HEAD_PAIRS if head_pairs else 0
             pa.num_qo_heads, pa.num_kv_heads = num_qo_heads, num_kv_heads
             pa.head_dim, pa.page_size = head_dim, page_size
             pa.q_dtype, pa.kv_dtype = dtype_code(q_data_type), dtype_code(kv_data_type)
@@ -684,7 +718,10 @@ class BatchDecodeWithPagedKVCacheWrapper:
         ra.stream = current_stream_ptr(dev)
         rc = self._lib.fi_batch_decode_run_args(self._ra_ref)
         if rc:
-            _lib.check(rc)
+            if rc == _lib.FI_ERR_REPLAN and self._replan_without_head_pairs():
+                rc = self._lib.fi_batch_decode_run_args(self._ra_ref)
+            if rc:
+                _lib.check(rc)
         return (out, lse) if return_lse else out
 
     def _bind_cache(self, paged_kv_cache) -> None:
@@ -872,9 +909,11 @@ def fast_decode_plan(
     self._num_qo_heads = num_qo_heads
     self._num_kv_heads = num_kv_heads
     try:
+        self._plan_call = None
         self._run_plan(indptr_ptr, last_page_len_host.data_ptr(), None, batch_size, num_qo_heads,
                        num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left,
-                       fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv)
+                       fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv,
+                       head_pairs=self._want_head_pairs(pos_encoding_mode))
     except Exception as e:
         raise RuntimeError(f"Error in standard plan: {e}") from e
     self._pos_encoding_mode = pos_encoding_mode

@@ -34,6 +34,8 @@ extern "C" {
 #define FI_ERR_WORKSPACE 2        /* workspace too small -> RuntimeError  */
 #define FI_ERR_CUDA 3             /* CUDA runtime failure -> RuntimeError */
 #define FI_ERR_UNSUPPORTED 4      /* shape / dtype not built -> RuntimeError */
+#define FI_ERR_REPLAN 5           /* the plan's unit geometry does not fit this run() (see
+                                     FI_PLAN_HEAD_PAIRS): plan again with flags = 0 and retry */
 
 /* ---- dtype codes -------------------------------------------------------- */
 #define FI_DTYPE_F16 0
@@ -183,13 +185,24 @@ FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan
  * of 26.  Field for field the arguments of fi_batch_decode_plan / fi_batch_decode_run above; no
  * reference counterpart (tvm-ffi packs its arguments per call, csrc/batch_decode_jit_binding.cu:23-40).
  */
+/*
+ * FI_PLAN_HEAD_PAIRS: the caller's cache is NHD (the rows of consecutive KV heads of a token are
+ * adjacent) and run() will not ask for ROPE_LLAMA.  With fp8 KV at head_dim 128, an even number of
+ * KV heads, a GQA group <= 8 and a power-of-two page size >= 8 the planner then makes (request, PAIR
+ * of KV heads) units for the tcgen05 kernel, which streams both heads' 128-byte rows of a token as
+ * one 256-byte run (C3 on one B200: 0.92 -> 0.9x of the measured copy bandwidth); every other shape
+ * ignores the bit.  A head-pair plan run on a cache the TMA loader cannot address (strides that are
+ * not multiples of 16 bytes), or with ROPE_LLAMA, returns FI_ERR_REPLAN.  No reference counterpart:
+ * the reference's planner knows nothing of the cache layout (scheduler.cuh:411-481).
+ */
+#define FI_PLAN_HEAD_PAIRS 1
 typedef struct FiDecodePlanArgs {
   void* float_ws; size_t float_ws_bytes;
   void* int_ws; void* pinned_int_ws; size_t int_ws_bytes;
   const int32_t* indptr_host; const int32_t* last_page_len_host; const int32_t* kv_len_host;
   int32_t batch_size, num_qo_heads, num_kv_heads, head_dim, page_size, q_dtype, kv_dtype;
   int32_t window_left, cuda_graph, fixed_split_pages, disable_split_kv, device, num_ctas_override;
-  int32_t pad_;
+  int32_t flags;   /* FI_PLAN_* bits; the positional fi_batch_decode_plan plans with 0 */
   void* stream;
   const int32_t* kv_indices_host; int64_t num_indices;
   int64_t* plan_info_out;

@@ -96,7 +96,7 @@ PI = dict(magic=0, num_ctas=1, num_segments=2, num_merge=3, num_slots=4, off_hea
           batch_size=11, hq=12, hkv=13, num_kv_heads=13, head_dim=14, page_size=15, q_dtype=16, kv_dtype=17,
           cuda_graph=18, merge_grid=19, total_tiles=20, window_left=21, stages=22, int_bytes=23,
           off_counters=24, off_item_heads=25, off_work_counter=26, kv_head_div=27, off_indices=28,
-          num_indices=29, indices_stable=30)
+          num_indices=29, indices_stable=30, head_pairs=31)
 SEG_BYTES = 48    # sizeof(Segment)
 HEAD_BYTES = 224  # sizeof(ItemHead)
 INLINE_PAGES = 16  # kItemInlinePages
@@ -108,7 +108,7 @@ TILE_FP8 = 128   # ... and for fp8 KV
 def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size,
               num_ctas, q_dtype=1, kv_dtype=1, window_left=-1, cuda_graph=0,
               kv_len=None, int_bytes=8 << 20, float_bytes=128 << 20, fixed_split_pages=0,
-              disable_split_kv=0, indices=None):
+              disable_split_kv=0, indices=None, flags=0):
     """Run fi_batch_decode_plan in host-only mode (device = -1) and decode the work list."""
     from flashinfer_b200 import _lib
 
@@ -119,12 +119,29 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
     kl = None if kv_len is None else np.ascontiguousarray(np.asarray(kv_len, dtype=np.int32))
     info = np.zeros(lib.fi_plan_info_len(), dtype=np.int64)
     ix = None if indices is None else np.ascontiguousarray(np.asarray(indices, dtype=np.int32))
-    rc = lib.fi_batch_decode_plan(
-        None, float_bytes, ws.ctypes.data, ws.ctypes.data, int_bytes, ip.ctypes.data,
-        lp.ctypes.data, None if kl is None else kl.ctypes.data, len(lp), num_qo_heads,
-        num_kv_heads, head_dim, page_size, q_dtype, kv_dtype, window_left, cuda_graph,
-        fixed_split_pages, disable_split_kv, -1, num_ctas, None,
-        None if indices is None else ix.ctypes.data, 0 if indices is None else len(ix), info.ctypes.data)
+    if flags:  # FI_PLAN_* bits exist in the argument-block form only
+        a = _lib.DecodePlanArgs()
+        a.float_ws, a.float_ws_bytes = None, float_bytes
+        a.int_ws = a.pinned_int_ws = ws.ctypes.data
+        a.int_ws_bytes = int_bytes
+        a.indptr_host, a.last_page_len_host = ip.ctypes.data, lp.ctypes.data
+        a.kv_len_host = None if kl is None else kl.ctypes.data
+        a.batch_size, a.num_qo_heads, a.num_kv_heads = len(lp), num_qo_heads, num_kv_heads
+        a.head_dim, a.page_size, a.q_dtype, a.kv_dtype = head_dim, page_size, q_dtype, kv_dtype
+        a.window_left, a.cuda_graph = window_left, cuda_graph
+        a.fixed_split_pages, a.disable_split_kv = fixed_split_pages, disable_split_kv
+        a.device, a.num_ctas_override, a.flags, a.stream = -1, num_ctas, flags, None
+        a.kv_indices_host = None if indices is None else ix.ctypes.data
+        a.num_indices = 0 if indices is None else len(ix)
+        a.plan_info_out = info.ctypes.data
+        rc = lib.fi_batch_decode_plan_args(C.byref(a))
+    else:
+        rc = lib.fi_batch_decode_plan(
+            None, float_bytes, ws.ctypes.data, ws.ctypes.data, int_bytes, ip.ctypes.data,
+            lp.ctypes.data, None if kl is None else kl.ctypes.data, len(lp), num_qo_heads,
+            num_kv_heads, head_dim, page_size, q_dtype, kv_dtype, window_left, cuda_graph,
+            fixed_split_pages, disable_split_kv, -1, num_ctas, None,
+            None if indices is None else ix.ctypes.data, 0 if indices is None else len(ix), info.ctypes.data)
     if rc != 0:
         return rc, _lib.last_error(), None
     hdr = ws[info[PI["off_header"]]:info[PI["off_header"]] + 32].view(np.int32)
@@ -161,6 +178,8 @@ def host_plan(indptr, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_
             assert np.array_equal(inl, seg_full[heads[c, 0] + k]), "inline segment != list segment"
     # inline page ids: exactly the table entries the item's first tiles gather (or none at all)
     tile = TILE if kv_dtype in (0, 1) else TILE_FP8
+    if info[PI["head_pairs"]]:
+        tile //= 2
     for c in range(nheads):
         npg = int(heads[c, 3])
         if ix is None or c >= nitems or heads[c, 1] == 0:

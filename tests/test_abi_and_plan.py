@@ -287,3 +287,37 @@ def test_argument_block_entry_points_match_the_positional_ones():
         subprocess.run(["gcc", "-I", str(ROOT / "include"), "-o", f"{d}/p", f"{d}/p.c"], check=True)
         sizes = subprocess.run([f"{d}/p"], capture_output=True, text=True, check=True).stdout.split()
     assert [int(x) for x in sizes] == [C.sizeof(_lib.DecodePlanArgs), C.sizeof(_lib.DecodeRunArgs)]
+
+
+@pytest.mark.parametrize("page", [8, 16, 64])
+def test_head_pair_plan(page):
+    """FI_PLAN_HEAD_PAIRS (include/fi_b200.h): fp8 KV at head_dim 128 is planned as (request, PAIR of KV
+    heads) units over 64-token tiles — half the heads, every token of every pair visited exactly once —
+    and every shape the flag does not apply to gets the plan it would have got without it."""
+    from flashinfer_b200 import _lib
+
+    kv_lens, hq, hkv, nctas = [4096] * 6 + [77, 0, 5000, 1, 64, 65], 64, 8, 296
+    indptr, last = lens_to_table(kv_lens, page)
+    idx = np.random.default_rng(3).permutation(int(indptr[-1])).astype(np.int32)
+    rc, err, plan = host_plan(indptr, last, hq, hkv, 128, page, nctas, kv_dtype=_lib.DTYPE_E4M3, indices=idx,
+                              flags=_lib.PLAN_HEAD_PAIRS)
+    assert rc == 0, err
+    info = plan["info"]
+    assert info[PI["head_pairs"]] == 1 and info[PI["num_kv_heads"]] == hkv // 2 and info[PI["hq"]] == hq
+    assert info[PI["total_tiles"]] == sum(-(-l // 64) for l in kv_lens) * (hkv // 2)
+    replay_plan(plan, kv_lens, hkv // 2, tile=64)
+    # not applicable: 16-bit KV, other head dims, an odd number of KV heads, groups above 8, tiny pages
+    for kw in (dict(kv_dtype=1), dict(kv_dtype=_lib.DTYPE_E4M3, head_dim=256), dict(kv_dtype=_lib.DTYPE_E4M3, hkv=1),
+               dict(kv_dtype=_lib.DTYPE_E4M3, hq=128, hkv=8)):
+        hd = kw.get("head_dim", 128)
+        args = (indptr, last, kw.get("hq", hq), kw.get("hkv", hkv), hd, page, nctas)
+        rc1, err1, with_flag = host_plan(*args, kv_dtype=kw["kv_dtype"], indices=idx, flags=_lib.PLAN_HEAD_PAIRS)
+        rc0, err0, without = host_plan(*args, kv_dtype=kw["kv_dtype"], indices=idx)
+        assert rc1 == 0 and rc0 == 0, (err1, err0)
+        assert with_flag["info"][PI["head_pairs"]] == 0
+        assert np.array_equal(with_flag["info"], without["info"])
+        assert np.array_equal(with_flag["segments"], without["segments"])
+    indptr4, last4 = lens_to_table(kv_lens, 4)
+    rc, err, small = host_plan(indptr4, last4, hq, hkv, 128, 4, nctas, kv_dtype=_lib.DTYPE_E4M3,
+                               flags=_lib.PLAN_HEAD_PAIRS)
+    assert rc == 0 and small["info"][PI["head_pairs"]] == 0

@@ -599,6 +599,67 @@ def test_fp8_kv_at_head_dim_64(kv_dtype, layout, pos_mode):
             w.run(q.to(DEV), cache.to(DEV))
 
 
+@pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
+@pytest.mark.parametrize("page,hq,hkv", [(16, 64, 8), (8, 16, 2), (32, 8, 8), (64, 12, 4), (128, 32, 4)])
+@pytest.mark.parametrize("variant", ["plain", "window+cap", "alibi", "sinks"])
+def test_fp8_head_pair_plans(kv_dtype, page, hq, hkv, variant):
+    """fp8 KV in an NHD cache: the wrapper plans (request, KV-head pair) units for the tcgen05 kernel
+    (FI_PLAN_HEAD_PAIRS, include/fi_b200.h; plan-info slot 31).  Oracle parity across page sizes, GQA
+    groups 1 / 3 / 8, split units, empty and one-token requests and the logits variants."""
+    fi = _fi()
+    from flashinfer_b200.utils import get_alibi_slopes
+
+    d = 128
+    lens = [1, 54, 97, 512, 9000, 0, 4099, 777, 64, 65, 20000]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=95)
+    cache = (cache * 0.5).to(kv_dtype)
+    q = make_q(len(lens), hq, d, torch.bfloat16, seed=96)
+    kw, okw, rkw = {}, {}, {}
+    if variant == "window+cap":
+        kw, okw = dict(window_left=700, logits_soft_cap=30.0), dict(window_left=700, logits_soft_cap=30.0)
+    elif variant == "alibi":
+        kw, okw = dict(pos_encoding_mode="ALIBI"), dict(alibi_slopes=get_alibi_slopes(hq))
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.bfloat16, kv_data_type=kv_dtype, **kw)
+    assert int(w._plan_info[31]) == 1 and int(w._plan_info[13]) == hkv // 2
+    assert int(w._plan_info[3]) > 0  # split units: the fused merge runs on pair partials
+    sinks = None
+    if variant == "sinks":
+        sinks = torch.linspace(-2.0, 3.0, hq, device=DEV)
+    o, lse = w.run(q.to(DEV), cache.to(DEV), k_scale=0.5, v_scale=0.25, return_lse=True, sinks=sinks)
+    torch.cuda.synchronize()
+    if variant == "sinks":
+        for i in (1, 4, 7, 10):
+            k, v = orc.gather_paged_kv(*orc.unpack_cache(cache, "NHD"), indptr, indices, last, i, "NHD")
+            o_ref, _ = orc.decode_attention_ref(q[i], k.float(), v.float(), 0.5 / math.sqrt(d), sinks=sinks.cpu())
+            assert (o[i].float().cpu() - o_ref * 0.25).abs().max().item() <= O_TOL_FP8
+        return
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, "NHD", k_scale=0.5, v_scale=0.25, **okw)
+    assert (o.float().cpu() - o_ref).abs().max().item() <= O_TOL_FP8
+    if variant == "alibi":
+        assert _alibi_lse_ok(lse.cpu(), lse_ref)
+    else:
+        assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+
+
+def test_fp8_head_pair_plan_falls_back_when_run_needs_rope():
+    """A head-pair plan cannot feed the RoPE variant kernel: forward(pos_encoding_mode="ROPE_LLAMA") after a
+    NONE plan gets FI_ERR_REPLAN from the C-ABI, and the wrapper plans once more without the flag."""
+    fi = _fi()
+    hq, hkv, d, page = 16, 4, 128, 16
+    lens = [300, 5000, 17]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=97)
+    cache = (cache * 0.5).to(torch.float8_e4m3fn)
+    q = make_q(len(lens), hq, d, torch.float16, seed=98)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, kv_data_type=cache.dtype)
+    assert int(w._plan_info[31]) == 1
+    o = w.forward(q.to(DEV), cache.to(DEV), pos_encoding_mode="ROPE_LLAMA")
+    assert int(w._plan_info[31]) == 0 and not w._head_pairs_ok
+    o_ref, _ = orc.batch_decode_ref(q, cache, indptr, indices, last, "NHD", rope=(1.0, 1e4))
+    assert (o.float().cpu() - o_ref).abs().max().item() <= O_TOL_FP8
+
+
 @pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn])
 def test_multi_token_decode_in_a_cuda_graph_with_replans(kv_dtype):
     """run(q_len_per_req = n) captured in a CUDA graph (the reference captures its tensor-core decode,
