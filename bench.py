@@ -238,17 +238,22 @@ def isolated_launch_us(step, n, dev):
     return float(np.median(per)) * 1e3
 
 
-def e2e_us(case, n):
+def e2e_us(case, n, host_out=False):
     """End to end through the public API with HOST buffers: q H2D from pinned memory + plan (page
-    table from pinned host memory) + run + o D2H + sync, every step."""
+    table from pinned host memory) + run + o D2H + sync, every step.  host_out: run(out = the pinned
+    host tensor) — the kernel's epilogue writes o over PCIe, no separate D2H copy."""
     ts = []
     for i in range(n + 2):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         case.q.copy_(case.q_host, non_blocking=True)  # enqueued first: the copy runs while the host plans
         case.plan()
-        case.step(i)
-        case.o_host.copy_(case.out, non_blocking=True)
+        if host_out:
+            case.wrapper.run(case.q, case.caches[i % case.n_copies], k_scale=case.k_scale, v_scale=case.v_scale,
+                             out=case.o_host)
+        else:
+            case.step(i)
+            case.o_host.copy_(case.out, non_blocking=True)
         torch.cuda.synchronize()
         ts.append(time.perf_counter() - t0)
     return float(np.median(ts[2:])) * 1e6
@@ -751,7 +756,14 @@ def run_ours(args):
     kern_us = isolated_launch_us(case.step, min(args.steps, 50), dev)
     clocks = sampler.stop()  # timed region + the isolated-launch leg right after it (same kernel, same load)
     sync_all()
-    e2e = e2e_us(case, max(3, min(args.steps, 20)))
+    # e2e: run(out = pinned host tensor) — the epilogue writes o over PCIe while the kernel is still
+    # streaming; the copy-back form (run into HBM, then o D2H) is measured beside it
+    e2e_copy_back = e2e_us(case, max(3, min(args.steps, 20)))
+    e2e = e2e_us(case, max(3, min(args.steps, 20)), host_out=True)
+    torch.cuda.synchronize()
+    if not torch.equal(case.o_host, case.out.cpu()):
+        raise RuntimeError("run(out = pinned host tensor) differs from run(out = device tensor)")
+    case.e2e_copy_back = e2e_copy_back
     h2d = case.q_host.numel() * 2 + (case.indptr.numel() + case.indices.numel() + case.last.numel()) * 4
     d2h = case.o_host.numel() * 2
 
@@ -898,8 +910,11 @@ def emit(args, wl, world, ms_total, kern_us, e2e, h2d, d2h, launches, clocks, ca
                      "kernel_us": us_step, "kernel_us_isolated": kern_us,
                      "algorithmic_bytes_per_launch": bytes_rank},
         "e2e": {"value": e2e, "unit": "us", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "copy_back_us": getattr(case, "e2e_copy_back", None),
                 "what": "q H2D (pinned, enqueued first so it overlaps the host planner) + plan (page table "
-                        "in pinned host memory -> work list + indices H2D) + run + o D2H, per step"},
+                        "in pinned host memory -> work list + indices H2D) + run(out = pinned host tensor: the "
+                        "kernel epilogue stores o over PCIe, checked bit-equal to the device result) + sync, per "
+                        "step; copy_back_us = the same with run() into HBM followed by an o D2H copy"},
         "gpu_launches": int(launches), "clocks": clocks,
     }
 

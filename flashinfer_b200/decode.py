@@ -695,7 +695,14 @@ class BatchDecodeWithPagedKVCacheWrapper:
         if out is None:
             out = torch.empty(q.shape, dtype=q.dtype, device=dev)
         elif out.shape != q.shape or out.dtype != q.dtype or out.device != dev:
-            check_shape_dtype_device(out, q.shape, q.dtype, dev, "out")
+            # beyond the reference: `out` may be a PINNED host tensor — the kernel's epilogue stores o
+            # straight into it over PCIe (pinned memory is device-addressable under UVA), so the
+            # device-to-host copy of the result overlaps the kernel instead of following it.  The
+            # caller synchronizes the stream before reading it, as after any non_blocking copy.
+            if not (out.device.type == "cpu" and out.shape == q.shape and out.dtype == q.dtype
+                    and out.is_contiguous() and out.is_pinned()):
+                check_shape_dtype_device(out, q.shape, q.dtype, dev, "out")
+                raise ValueError("a host `out` must be pinned and contiguous")
         elif not out.is_contiguous():
             raise ValueError("out must be contiguous")
 

@@ -642,6 +642,30 @@ def test_fp8_head_pair_plans(kv_dtype, page, hq, hkv, variant):
         assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
 
 
+@pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn])
+def test_run_into_a_pinned_host_tensor(kv_dtype):
+    """run(out = pinned host tensor): the epilogue (direct and merged units) stores o over PCIe; bit-equal
+    to the device result after a stream sync.  Pageable host memory is refused."""
+    fi = _fi()
+    hq, hkv, d, page = 32, 8, 128, 16
+    lens = [1, 500, 9000, 0, 4099, 64, 20000]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, "NHD", torch.float32, seed=101)
+    cache = (cache * 0.5 if kv_dtype else cache).to(kv_dtype or torch.bfloat16)
+    q = make_q(len(lens), hq, d, torch.bfloat16, seed=102).to(DEV)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.bfloat16, kv_data_type=cache.dtype)
+    assert int(w._plan_info[3]) > 0
+    cache_d = cache.to(DEV)
+    o_dev = w.run(q, cache_d)
+    o_host = torch.full(q.shape, float("nan"), dtype=q.dtype).pin_memory()
+    ret = w.run(q, cache_d, out=o_host)
+    assert ret is o_host
+    torch.cuda.synchronize()
+    assert torch.equal(o_host, o_dev.cpu())
+    with pytest.raises(ValueError):
+        w.run(q, cache_d, out=torch.empty(q.shape, dtype=q.dtype))
+
+
 def test_fp8_head_pair_plan_falls_back_when_run_needs_rope():
     """A head-pair plan cannot feed the RoPE variant kernel: forward(pos_encoding_mode="ROPE_LLAMA") after a
     NONE plan gets FI_ERR_REPLAN from the C-ABI, and the wrapper plans once more without the flag."""
