@@ -45,6 +45,12 @@ def one(fp8, bs, kv_len, layout="NHD"):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "fp8":  # fp8 only, more shapes (planner A/B runs)
+        for layout in ("NHD", "HND"):
+            for bs, kv in ((32, 8192), (64, 8192), (128, 8192), (192, 8192), (256, 8192), (128, 2048), (128, 4096),
+                           (16, 65536), (37, 20000)):
+                one(True, bs, kv, layout)
+        sys.exit(0)
     for fp8, kv in ((False, 4096), (True, 8192)):
         for bs in (32, 64, 128, 256, 512):
             one(fp8, bs, kv)

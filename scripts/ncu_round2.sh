@@ -18,6 +18,7 @@ TRAFFIC=(--traffic c3); cap r02_decode_c3_fp8_tc5 paged_decode 4 2 $B --workload
 TRAFFIC=()
 cap r02_decode_c2_rank_of_8 paged_decode 4 2 $B --shard-of 8
 cap r02_decode_c3_rank_of_8 paged_decode 4 2 $B --workload c3 --shard-of 8
+cap r02_decode_c3_fp8_page8 paged_decode 4 1 $B --workload c3 --page-size 8
 cap r02_decode_c2_bf16_page1_cpasync paged_decode 4 1 $B --page-size 1
 cap r02_decode_c2_bf16_page5_cpasync paged_decode 4 1 $B --page-size 5
 cap r02_decode_c2_bf16_page8 paged_decode 4 1 $B --page-size 8
