@@ -275,19 +275,22 @@ static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* 
   auto align_chunk = [&](int64_t c0) -> int64_t {
     const int64_t n_u = uniform_tiles;
     if (n_u <= 0 || indivisible || st.f0_pct < 100 || c0 <= 0) return c0;
-    static const int den = env_int("FI_B200_ALIGN_DEN", 6, 1, 1 << 20);  // A/B: 1000 = never align
-    const int64_t hi = c0 + std::max<int64_t>(1, c0 / den);
+    static const int den_short = env_int("FI_B200_ALIGN_DEN", 6, 1, 1 << 20);  // A/B: 1000 = never align
+    static const int den_long = env_int("FI_B200_ALIGN_DEN_LONG", 32, 1, 1 << 20);
+    // Aligned items leave CTA slots idle (C2 / C3: 256 items on 296 slots; head_dim 256, one CTA per SM:
+    // 128 items on 148 SMs).  That pays for short items, where a cut unit costs a merge chain as long as
+    // the item itself, and for 16-bit KV at head_dim 128, which saturates DRAM with 256 CTAs (C2 158.6 vs
+    // 159.3 us).  Every other kernel turns idle slots into lost bytes in flight: with items of >= 2 MiB
+    // they round by <= 1/32 only — C3 on one B200 351.7 -> 326.2 us (NHD, head pairs), 343.6 -> 325.8 us
+    // (HND); 1 GiB probes: bf16 D = 64 209.4 -> 185.6 us, D = 256 166.6 -> 162.5 us, e4m3 D = 256
+    // 264.9 -> 240.9 us.
+    const int64_t tile_bytes = 2LL * TT * head_dim * (kvf == 0 ? 2 : 1) * (head_pairs ? 2 : 1);
+    const bool long_items = c0 * tile_bytes >= (2LL << 20) && !(kvf == 0 && head_dim == 128);
+    const int den = long_items ? den_long : den_short;
+    const int64_t hi = c0 + std::max<int64_t>(long_items ? 0 : 1, c0 / den);
     if (c0 >= n_u) {
-      // Items of whole units leave CTA slots idle (C2 / C3: 256 items on 296 slots).  The 16-bit kernel is
-      // HBM-bound either way (C2 158.6 vs 159.3 us); the tcgen05 fp8 kernel is bound per SM with two
-      // resident CTAs — a lone CTA finishes 12 % earlier — so its idle slots are lost bandwidth: C3 on
-      // one B200 351.7 -> 326.2 us (NHD, head pairs), 343.6 -> 325.8 us (HND) with all 296 items and the
-      // few merges that cutting 128-tile units costs.  fp8 KV at head_dim 128 rounds up by <= 1/32 only
-      // (FI_B200_ALIGN_DEN_FP8 for A/B runs).
-      static const int den8 = env_int("FI_B200_ALIGN_DEN_FP8", 32, 1, 1 << 20);
-      const int64_t hi_u = (kvf != 0 && head_dim == 128) ? c0 + c0 / den8 : hi;
       const int64_t c = (c0 + n_u - 1) / n_u * n_u;
-      return c <= hi_u ? c : c0;
+      return c <= hi ? c : c0;
     }
     for (int64_t c = c0; c <= hi; ++c)
       if (n_u % c == 0) return c;
