@@ -275,6 +275,10 @@ static int launch_rope(const DecodeParams& p, int head_dim, int grid, cudaStream
     FI_ROPE_CASE(64)
     FI_ROPE_CASE(128)
     FI_ROPE_CASE(256)
+    case 512:  // groups above 4 were split into virtual KV heads by the planner (max_group_for)
+      if (p.group_size > 4) return fail(FI_ERR_UNSUPPORTED, "head_dim 512 takes GQA groups of at most 4 per unit");
+      FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 512, 4>, p));
+      break;
     default: return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
   }
 #undef FI_ROPE_CASE
@@ -289,14 +293,15 @@ static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUt
   // fp8 KV with ROPE_LLAMA (or A/B runs), and fp8 KV at head_dim 64 in any mode but ALiBi (64-byte rows do
   // not fit the 128-byte swizzle atoms of the MMA kernels): the CUDA-core variant kernel; without RoPE it
   // runs with zero rotation frequencies, i.e. the identity rotation
-  if ((p.rope && (kvf != 0 || rope_cuda_core)) || (kvf != 0 && head_dim == 64)) {
+  if ((p.rope && (kvf != 0 || rope_cuda_core)) || (kvf != 0 && head_dim == 64) || head_dim == 512) {
     if (p.alibi_slopes != nullptr)
-      return fail(FI_ERR_UNSUPPORTED, "ALIBI with fp8 KV at head_dim 64 is not built");
+      return fail(FI_ERR_UNSUPPORTED, "ALIBI at head_dim 512 or with fp8 KV at head_dim 64 is not built");
     if (!p.rope) {
       DecodeParams p2 = p;
       p2.rope_rcp_scale = 0.f;
       p2.rope_rcp_theta = 1.f;
       switch (kvf) {
+        case 0: return bf ? launch_rope<1, 0>(p2, head_dim, grid, stream) : launch_rope<0, 0>(p2, head_dim, grid, stream);
         case 1: return bf ? launch_rope<1, 1>(p2, head_dim, grid, stream) : launch_rope<0, 1>(p2, head_dim, grid, stream);
         case 2: return bf ? launch_rope<1, 2>(p2, head_dim, grid, stream) : launch_rope<0, 2>(p2, head_dim, grid, stream);
         default: return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
@@ -447,7 +452,8 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.alibi_slopes = pos_encoding_mode == FI_POS_ALIBI ? alibi_slopes : nullptr;
   p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
   p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
-  if (((p.rope && kvf != 0) || (kvf != 0 && head_dim == 64)) && plan_info[kPiNumItems] > plan_info[kPiNumCtas])
+  if (((p.rope && kvf != 0) || (kvf != 0 && head_dim == 64) || head_dim == 512) &&
+      plan_info[kPiNumItems] > plan_info[kPiNumCtas])
     return fail(FI_ERR_UNSUPPORTED, "the CUDA-core variant kernel (fp8 KV with ROPE_LLAMA or head_dim 64) needs a "
                                     "static plan (unset FI_B200_SCHED_F0)");
   // 1: griddepcontrol.launch_dependents right after the kernel's own dependency wait (default);
@@ -463,7 +469,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   p.l2_hints = default_l2_hints();
   p.sinks = sinks;
 
-  const bool cuda_core_only = kvf != 0 && head_dim == 64;
+  const bool cuda_core_only = (kvf != 0 && head_dim == 64) || head_dim == 512;
   const bool tma = !cuda_core_only && tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h,
                                                    kv_stride_page, page_size, false, 0, TT);
   if (p.head_pairs && (!tma || p.rope || !use_tc5() || es != 1 || head_dim != 128))
@@ -553,13 +559,13 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (num_kv_heads <= 0 || num_qo_heads % num_kv_heads)
     return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads must be a multiple of num_kv_heads");
-  const int kv_div = group_split(num_qo_heads / num_kv_heads);
+  const int kv_div = group_split(num_qo_heads / num_kv_heads, max_group_for(head_dim));
   const int num_kv_heads_mem = num_kv_heads;  // heads k / v really have
   num_kv_heads *= kv_div;                     // virtual heads: one unit each (see DecodeParams)
   const int group = num_qo_heads / num_kv_heads;
   const int kvf = kv_format(q_dtype, kv_dtype);
   if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair");
-  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256))
+  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256 || head_dim == 512))
     return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
   if (kv_len < 0) return fail(FI_ERR_INVALID_ARGUMENT, "negative kv_len");
   const int es = dtype_size(kv_dtype);
@@ -608,7 +614,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
   p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
 
-  const bool tma = !(kvf != 0 && head_dim == 64) &&
+  const bool tma = !(kvf != 0 && head_dim == 64) && head_dim != 512 &&
                    tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);
   CUtensorMap km, vm;
   memset(&km, 0, sizeof(km));

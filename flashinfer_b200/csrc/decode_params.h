@@ -25,10 +25,13 @@ constexpr int kSegCache = 32;         // segment queue (ring) in smem per CTA; a
 constexpr int kSegRefill = 8;         // segments the feeder loads from the list at a time
 constexpr float kNegInf = -5e4f;      // finite "-inf", reference math.cuh:32
 constexpr int kMaxGroup = 8;          // GQA group size handled by one MMA N tile
-// smallest d with group % d == 0 and group / d <= kMaxGroup (1 for group <= kMaxGroup)
-__host__ __device__ constexpr int group_split(int group) {
+// query heads one unit may carry: kMaxGroup, 4 at head_dim 512 (the CUDA-core variant kernel keeps the
+// group's accumulators in registers)
+__host__ __device__ constexpr int max_group_for(int head_dim) { return head_dim == 512 ? 4 : kMaxGroup; }
+// smallest d with group % d == 0 and group / d <= max_group (1 for group <= max_group)
+__host__ __device__ constexpr int group_split(int group, int max_group = kMaxGroup) {
   for (int d = 1; d <= group; ++d)
-    if (group % d == 0 && group / d <= kMaxGroup) return d;
+    if (group % d == 0 && group / d <= max_group) return d;
   return group;
 }
 

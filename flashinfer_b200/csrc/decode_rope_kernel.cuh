@@ -29,12 +29,13 @@ __host__ __device__ constexpr int rope_warps(int hd) { return hd <= 128 ? 8 : 4;
 // lanes that share one token: 16 up to D = 128 (a warp works on two tokens), the whole warp at 256
 __host__ __device__ constexpr int rope_lanes_per_token(int hd) { return hd <= 128 ? 16 : 32; }
 // tokens a lane group keeps in flight (registers hold this many K / V rows twice: current + next)
-__host__ __device__ constexpr int rope_unroll(int gb) { return gb <= 4 ? 4 : 2; }
+__host__ __device__ constexpr int rope_unroll(int gb, int hd = 128) { return hd >= 512 ? 1 : (gb <= 4 ? 4 : 2); }
 
 template <int NB> struct RopeRaw;
 template <> struct RopeRaw<2> { using T = uint16_t; static __device__ __forceinline__ uint32_t word(T r, int) { return r; } };
 template <> struct RopeRaw<4> { using T = uint32_t; static __device__ __forceinline__ uint32_t word(T r, int) { return r; } };
 template <> struct RopeRaw<8> { using T = uint2; static __device__ __forceinline__ uint32_t word(T r, int i) { return i == 0 ? r.x : r.y; } };
+template <> struct RopeRaw<16> { using T = uint4; static __device__ __forceinline__ uint32_t word(T r, int i) { return i == 0 ? r.x : (i == 1 ? r.y : (i == 2 ? r.z : r.w)); } };
 
 // elements 2i, 2i + 1 of a packed row fragment.  FMT: 0 f16, 1 bf16, 2 e4m3, 3 e5m2
 template <int FMT, int NB>
@@ -67,14 +68,14 @@ __global__ void __launch_bounds__(rope_warps(HD) * 32)
   constexpr int LPT = rope_lanes_per_token(HD);
   constexpr int TPW = 32 / LPT;        // tokens a warp works on at once
   constexpr int C = HD / (2 * LPT);    // dims a lane owns in EACH half of the head
-  constexpr int U = rope_unroll(GB);
+  constexpr int U = rope_unroll(GB, HD);
   constexpr int STEP = NW * TPW;       // tokens the CTA covers per unrolled step
   constexpr int ES = KVF == 0 ? 2 : 1;
   constexpr int KFMT = KVF == 0 ? QT : (KVF == 1 ? 2 : 3);
   using RR = RopeRaw<C * ES>;
   using Raw = typename RR::T;
   __shared__ float sm_m[NW][kMaxGroup], sm_l[NW][kMaxGroup];
-  __shared__ __align__(16) float sm_o[NW][kMaxGroup][HD];
+  __shared__ __align__(16) float sm_o[NW][GB][HD];  // 32 KiB at most (HD 256 x 8 heads, HD 512 x 4 heads)
   __shared__ int sm_last;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;

@@ -155,7 +155,7 @@ static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* 
                 num_qo_heads, num_kv_heads);
   // a GQA group larger than one MMA N tile becomes kv_div virtual KV heads per real one (the
   // reference's CUDA-core decode stops at group 8; its tensor-core decode takes any group)
-  const int kv_div = group_split(num_qo_heads / num_kv_heads);
+  const int kv_div = group_split(num_qo_heads / num_kv_heads, max_group_for(head_dim));
   num_kv_heads *= kv_div;
   int group = num_qo_heads / num_kv_heads;
   const int kvf = kv_format(q_dtype, kv_dtype);
@@ -172,9 +172,9 @@ static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* 
     num_kv_heads /= 2;
     group *= 2;
   }
-  // fp8 KV at head_dim 64 (64-byte rows, below the 128-byte swizzle atom of the MMA kernels) runs on the
-  // CUDA-core variant kernel (decode_rope_kernel.cuh with zero rotation frequencies)
-  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256))
+  // fp8 KV at head_dim 64 (64-byte rows, below the 128-byte swizzle atom of the MMA kernels) and head_dim
+  // 512 run on the CUDA-core variant kernel (decode_rope_kernel.cuh with zero rotation frequencies)
+  if (!(head_dim == 64 || head_dim == 128 || head_dim == 256 || head_dim == 512))
     return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d for this dtype", head_dim);
   if (indptr_host == nullptr || (last_page_len_host == nullptr && kv_len_host == nullptr))
     return fail(FI_ERR_INVALID_ARGUMENT, "indptr / last_page_len must be host pointers");

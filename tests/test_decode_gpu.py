@@ -642,6 +642,44 @@ def test_fp8_head_pair_plans(kv_dtype, page, hq, hkv, variant):
         assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
 
 
+@pytest.mark.parametrize("q_dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn, torch.float8_e5m2])
+@pytest.mark.parametrize("hq,hkv", [(4, 4), (8, 2), (16, 2)])
+@pytest.mark.parametrize("variant", ["plain", "rope", "window+cap"])
+def test_head_dim_512(q_dtype, kv_dtype, hq, hkv, variant):
+    """head_dim 512 (the reference dispatches it, include/flashinfer/utils.cuh:192): runs on the CUDA-core
+    variant kernel, groups above 4 as virtual KV heads; batch (split units, merge) and single decode
+    against the oracle; ALiBi is refused."""
+    fi = _fi()
+    d, page, layout = 512, 16, "NHD"
+    lens = [1, 130, 3000, 0, 64, 9000]
+    is8 = kv_dtype is not None
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, layout, torch.float32, seed=111)
+    cache = (cache * 0.5 if is8 else cache).to(kv_dtype or q_dtype)
+    q = make_q(len(lens), hq, d, q_dtype, seed=112)
+    kw, okw = {}, {}
+    if variant == "rope":
+        kw, okw = dict(pos_encoding_mode="ROPE_LLAMA"), dict(rope=(1.0, 1e4))
+    elif variant == "window+cap":
+        kw, okw = dict(window_left=500, logits_soft_cap=20.0), dict(window_left=500, logits_soft_cap=20.0)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=q_dtype, kv_data_type=cache.dtype, **kw)
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True)
+    o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, layout, **okw)
+    assert (o.float().cpu() - o_ref).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+    assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+    if variant != "window+cap":
+        k, v = orc.gather_paged_kv(*orc.unpack_cache(cache, layout), indptr, indices, last, 2, layout)
+        o1 = fi.single_decode_with_kv_cache(q[2].to(DEV), k.contiguous().to(DEV), v.contiguous().to(DEV),
+                                            pos_encoding_mode=kw.get("pos_encoding_mode", "NONE"))
+        assert (o1.float().cpu() - o_ref[2]).abs().max().item() <= (O_TOL_FP8 if is8 else O_TOL)
+    if variant == "plain":
+        w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=q_dtype, kv_data_type=cache.dtype,
+               pos_encoding_mode="ALIBI")
+        with pytest.raises(RuntimeError):
+            w.run(q.to(DEV), cache.to(DEV))
+
+
 @pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn])
 def test_run_into_a_pinned_host_tensor(kv_dtype):
     """run(out = pinned host tensor): the epilogue (direct and merged units) stores o over PCIe; bit-equal
