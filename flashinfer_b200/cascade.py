@@ -212,6 +212,12 @@ class MultiLevelCascadeAttentionWrapper:
     :class:`BatchDecodeWithPagedKVCacheWrapper` with one decode request per query row (see the
     note above), and the levels are combined with :func:`merge_state_in_place` in the
     reference's order (last level first, cascade.py:534-543).
+
+    ``use_cuda_graph=True`` (reference cascade.py:313-330 takes per-level fixed buffers): ``run`` can
+    be captured, ``plan`` stays host work between replays.  The caller's ``paged_kv_indices_buf_arr``
+    gives the page capacity of every level; the per-ROW tables live in buffers of this wrapper
+    (rows x that capacity entries, created by the first ``plan``), and the total number of query
+    rows is fixed by that first ``plan`` (a captured graph holds the launch shapes).
     """
 
     def __init__(
@@ -227,15 +233,19 @@ class MultiLevelCascadeAttentionWrapper:
     ) -> None:
         from .decode import BatchDecodeWithPagedKVCacheWrapper
 
+        self._use_cuda_graph = bool(use_cuda_graph)
+        self._float_workspace_buffer = float_workspace_buffer
+        self._page_capacity = None
         if use_cuda_graph:
-            # the per-row page tables are rebuilt by plan(); the reference's fixed user buffers
-            # describe per-group tables and cannot hold them
-            raise NotImplementedError("use_cuda_graph is not supported by the cascade wrappers")
-        self._use_cuda_graph = False
-        self._batch_decode_wrappers = [
-            BatchDecodeWithPagedKVCacheWrapper(float_workspace_buffer, kv_layout)
-            for _ in range(num_levels)
-        ]
+            if paged_kv_indices_buf_arr is None or len(paged_kv_indices_buf_arr) != num_levels:
+                raise ValueError("use_cuda_graph needs paged_kv_indices_buf_arr with one buffer per level")
+            self._page_capacity = [int(b.numel()) for b in paged_kv_indices_buf_arr]
+            self._batch_decode_wrappers = [None] * num_levels  # fixed-size wrappers, made by the first plan()
+        else:
+            self._batch_decode_wrappers = [
+                BatchDecodeWithPagedKVCacheWrapper(float_workspace_buffer, kv_layout)
+                for _ in range(num_levels)
+            ]
         self._num_levels = num_levels
         self._kv_layout = kv_layout
         self._num_rows = None
@@ -246,8 +256,10 @@ class MultiLevelCascadeAttentionWrapper:
 
     def reset_workspace_buffer(self, float_workspace_buffer: torch.Tensor,
                                int_workspace_buffers) -> None:
+        self._float_workspace_buffer = float_workspace_buffer
         for wrapper, int_ws in zip(self._batch_decode_wrappers, int_workspace_buffers):
-            wrapper.reset_workspace_buffer(float_workspace_buffer, int_ws)
+            if wrapper is not None:
+                wrapper.reset_workspace_buffer(float_workspace_buffer, int_ws)
 
     def plan(
         self,
@@ -287,6 +299,8 @@ class MultiLevelCascadeAttentionWrapper:
                 num_rows = indptr.numel() - 1
             elif num_rows != indptr.numel() - 1:
                 raise ValueError("the last element of every qo_indptr must be the total number of queries")
+            if self._use_cuda_graph:
+                wrapper = self._graph_level_wrapper(i, num_rows, indices)
             wrapper.plan(
                 indptr, indices, last, num_qo_heads, num_kv_heads, head_dim, page_size,
                 pos_encoding_mode="NONE", window_left=window_left, logits_soft_cap=logits_soft_cap,
@@ -296,6 +310,27 @@ class MultiLevelCascadeAttentionWrapper:
         self._num_rows = num_rows
 
     begin_forward = plan
+
+    def _graph_level_wrapper(self, level: int, num_rows: int, indices: torch.Tensor):
+        """CUDA-graph mode: level `level`'s decode wrapper with fixed buffers for `num_rows` per-row
+        requests and rows x (the level's page capacity) table entries."""
+        from .decode import BatchDecodeWithPagedKVCacheWrapper
+
+        if self._num_rows is not None and num_rows != self._num_rows:
+            raise ValueError(f"the number of query rows is fixed in CUDA-graph mode ({self._num_rows}, got {num_rows})")
+        capacity = max(num_rows * self._page_capacity[level], 1)
+        if indices.numel() > capacity:
+            raise ValueError("a level's page table exceeds the capacity of its paged_kv_indices buffer")
+        w = self._batch_decode_wrappers[level]
+        if w is None:
+            dev = self._float_workspace_buffer.device
+            w = BatchDecodeWithPagedKVCacheWrapper(
+                self._float_workspace_buffer, self._kv_layout, use_cuda_graph=True,
+                paged_kv_indptr_buffer=torch.zeros(num_rows + 1, dtype=torch.int32, device=dev),
+                paged_kv_indices_buffer=torch.zeros(capacity, dtype=torch.int32, device=dev),
+                paged_kv_last_page_len_buffer=torch.zeros(num_rows, dtype=torch.int32, device=dev))
+            self._batch_decode_wrappers[level] = w
+        return w
 
     def run(self, q: torch.Tensor, paged_kv_cache):
         if self._num_rows is None:

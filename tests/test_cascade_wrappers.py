@@ -169,7 +169,7 @@ def test_cascade_wrapper_contract():
     import flashinfer_b200 as fi
 
     ws = torch.zeros(8 << 20, dtype=torch.uint8, device="cuda:0")
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(ValueError):  # graph mode needs the per-level page-capacity buffers
         fi.MultiLevelCascadeAttentionWrapper(2, ws, "NHD", use_cuda_graph=True)
     w = fi.MultiLevelCascadeAttentionWrapper(2, ws, "NHD")
     assert w.is_cuda_graph_enabled is False
@@ -181,3 +181,62 @@ def test_cascade_wrapper_contract():
                pos_encoding_mode="ROPE_LLAMA")
     with pytest.raises(ValueError):
         w.plan([i32([0, 1])], [i32([0, 1])], [i32([0])], [i32([1])], 8, 8, 128, 16)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("causal,rows_per_req", [(False, 1), (True, 2)])
+def test_multi_level_cascade_in_a_cuda_graph(causal, rows_per_req):
+    """use_cuda_graph=True (reference cascade.py:313-330): run() captured once, replayed after re-plans
+    with other unique-level lengths; every replay against full attention over the concatenated KV."""
+    import flashinfer_b200 as fi
+    from oracle.attention_ref import gather_paged_kv, unpack_cache
+
+    dev, dtype = "cuda:0", torch.float16
+    bs, Hq, Hkv, D, page, n = 4, 16, 4, 128, 16, rows_per_req
+    need = lambda L: -(-L // page)
+    g = torch.Generator().manual_seed(21)
+    pool = 200
+    cache = torch.randn(pool, 2, page, Hkv, D, generator=g).to(dtype).to(dev)
+    q = torch.randn(bs * n, Hq, D, generator=g).to(dtype).to(dev)
+    ws = torch.zeros(32 << 20, dtype=torch.uint8, device=dev)
+    cap = [torch.zeros(64, dtype=torch.int32, device=dev) for _ in range(2)]
+    w = fi.MultiLevelCascadeAttentionWrapper(2, ws, "NHD", use_cuda_graph=True, paged_kv_indices_buf_arr=cap)
+    assert w.is_cuda_graph_enabled
+    qo = [torch.tensor([0, bs * n], dtype=torch.int32), torch.arange(bs + 1, dtype=torch.int32) * n]
+
+    def tables(shared_len, lens, seed):
+        perm = torch.randperm(pool, generator=torch.Generator().manual_seed(seed)).tolist()
+        take = lambda k: [perm.pop() for _ in range(k)]
+        lv = [[take(need(shared_len))], [take(need(L)) for L in lens]]
+        last = [[(shared_len - 1) % page + 1], [(L - 1) % page + 1 for L in lens]]
+        return [_level_tables(p, l) for p, l in zip(lv, last)]
+
+    def check(o, tb, shared_len, lens):
+        kc, vc = unpack_cache(cache.cpu(), "NHD")
+        ks, vs = gather_paged_kv(kc, vc, tb[0][0].tolist(), tb[0][1].tolist(), tb[0][2].tolist(), 0, "NHD")
+        for r in range(bs):
+            k2, v2 = gather_paged_kv(kc, vc, tb[1][0].tolist(), tb[1][1].tolist(), tb[1][2].tolist(), r, "NHD")
+            for t in range(n):
+                keep = lens[r] - (n - 1 - t) if causal else lens[r]
+                ref = _full_attention(q[r * n + t], torch.cat([ks, k2[:keep]]), torch.cat([vs, v2[:keep]]),
+                                      1.0 / math.sqrt(D))
+                assert (o[r * n + t].float().cpu() - ref).abs().max().item() <= O_TOL, (r, t)
+
+    cases = [(100, [n + 5, 40, n, 130], 1), (333, [64, n + 1, 200, 17], 2), (16, [n, n, n + 30, 90], 3)]
+    graph, out = None, None
+    for shared_len, lens, seed in cases:
+        tb = tables(shared_len, lens, seed)
+        w.plan(qo, [t[0] for t in tb], [t[1] for t in tb], [t[2] for t in tb], Hq, Hkv, D, page, causal=causal,
+               q_data_type=dtype)
+        if graph is None:
+            w.run(q, cache)  # warm-up outside the capture
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = w.run(q, cache)
+        graph.replay()
+        torch.cuda.synchronize()
+        check(out, tb, shared_len, lens)
+    with pytest.raises(ValueError):  # another number of query rows cannot reuse the captured shapes
+        w.plan([torch.tensor([0, bs * n + 1], dtype=torch.int32), torch.arange(bs + 2, dtype=torch.int32)],
+               [t[0] for t in tb], [t[1] for t in tb], [t[2] for t in tb], Hq, Hkv, D, page, q_data_type=dtype)
