@@ -221,11 +221,11 @@ static int launch_hd(const DecodeParams& p, const CUtensorMap& km, const CUtenso
 }
 
 // fp8 KV, head_dim 128, TMA-eligible pages: tcgen05 / TMEM kernel (decode_kernel_tc5.cuh)
-template <int QT, int KVF, bool HP = false>
+template <int QT, int KVF, bool HP = false, int HD = 128>
 static int launch_tc5(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm, int grid,
                       cudaStream_t stream) {
-  auto kern = paged_decode_tc5_kernel<QT, KVF, HP>;
-  const int smem = SmemLayout<KVF, 128>::total(p.num_stages) + (HP ? kTc5PairScratchBytes : 0);
+  auto kern = paged_decode_tc5_kernel<QT, KVF, HP, HD>;
+  const int smem = SmemLayout<KVF, HD>::total(p.num_stages) + (HP ? kTc5PairScratchBytes : 0);
   FI_CUDA_TRY(ensure_smem_attr(kern, smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
@@ -317,6 +317,10 @@ static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUt
   if (p.head_pairs) {  // fi_batch_decode_run checked that this launch fits a head-pair plan
     if (kvf == 1) return bf ? launch_tc5<1, 1, true>(p, km, vm, grid, stream) : launch_tc5<0, 1, true>(p, km, vm, grid, stream);
     return bf ? launch_tc5<1, 2, true>(p, km, vm, grid, stream) : launch_tc5<0, 2, true>(p, km, vm, grid, stream);
+  }
+  if (kvf != 0 && head_dim == 256 && tma && use_tc5()) {
+    if (kvf == 1) return bf ? launch_tc5<1, 1, false, 256>(p, km, vm, grid, stream) : launch_tc5<0, 1, false, 256>(p, km, vm, grid, stream);
+    return bf ? launch_tc5<1, 2, false, 256>(p, km, vm, grid, stream) : launch_tc5<0, 2, false, 256>(p, km, vm, grid, stream);
   }
   if (kvf != 0 && head_dim == 128 && tma && use_tc5()) {
     if (kvf == 1) return bf ? launch_tc5<1, 1>(p, km, vm, grid, stream) : launch_tc5<0, 1>(p, km, vm, grid, stream);
@@ -495,7 +499,7 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
     // one 5-D map over both, one TMA box per (page, token block) instead of two (mma.sync kernel)
     const int64_t kv_gap = (static_cast<const char*>(v_cache) - static_cast<const char*>(k_cache)) / es;
     static const bool pair_env = [] { const char* e = getenv("FI_B200_TMA_PAIRED"); return !(e && e[0] == '0'); }();
-    const bool tc5 = kvf != 0 && head_dim == 128 && use_tc5() && !p.rope;
+    const bool tc5 = kvf != 0 && (head_dim == 128 || head_dim == 256) && use_tc5() && !p.rope;
     p.tma_paired = pair_env && !tc5 && v_cache > k_cache && kv_gap * es % 16 == 0 && kv_gap < kv_stride_page &&
                    (static_cast<const char*>(v_cache) - static_cast<const char*>(k_cache)) % es == 0;
     int rc = make_kv_map(&km, k_cache, kv_dtype, head_dim, page_size, Hkv_mem, num_pages, kv_stride_n,

@@ -127,13 +127,72 @@ __device__ __forceinline__ void tc5_prepare_q(const DecodeParams& p, const Segme
   }
 }
 
+// head_dim 256: thread t: head h = t / 16, dims d0 = 16 (t % 16) .. d0 + 15 = one 16-byte chunk of fp8 terms.
+// Qs is two 128-byte panels of 32 rows each (dims 0-127 | 128-255, 4 KiB apart).
+template <int QT>
+__device__ __forceinline__ void tc5_prepare_q256(const DecodeParams& p, const Segment& sg, uint8_t* qbuf,
+                                                 float* dq_out, int tid) {
+  const int h = tid >> 4, d0 = (tid & 15) * 16;
+  const int GS = p.group_size;
+  float x[16];
+  float amax = 0.f;
+  if (h < GS) {
+    const char* qrow = static_cast<const char*>(p.q) +
+                       ((int64_t)sg.request * p.q_stride_n +
+                        (int64_t)(sg.kv_head * GS + h) * p.q_stride_h) * 2 + d0 * 2;
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      const uint2 w2 = __ldg(reinterpret_cast<const uint2*>(qrow) + v);
+      const uint32_t w[2] = {w2.x, w2.y};
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        if constexpr (QT == 1) {
+          x[4 * v + 2 * i] = __uint_as_float(w[i] << 16);
+          x[4 * v + 2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        } else {
+          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+          x[4 * v + 2 * i] = f.x;
+          x[4 * v + 2 * i + 1] = f.y;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fabsf(x[i]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = 0.f;
+  }
+#pragma unroll
+  for (int s2 = 1; s2 < 16; s2 <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, s2));
+  const bool nz = amax > 0.f && amax < 3.0e38f;
+  const float sq = nz ? 256.f / amax : 1.f;
+  if ((tid & 15) == 0) dq_out[h] = nz ? amax * (1.f / 256.f) : 1.f;
+  uint32_t t[8][3];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) split3_e4m3x2(t[i], x[2 * i] * sq, x[2 * i + 1] * sq);
+  const int chunk = tid & 15;
+#pragma unroll
+  for (int term = 0; term < 4; ++term) {
+    const int row = 8 * term + h;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (term < 3) {
+      v.x = t[0][term] | (t[1][term] << 16);
+      v.y = t[2][term] | (t[3][term] << 16);
+      v.z = t[4][term] | (t[5][term] << 16);
+      v.w = t[6][term] | (t[7][term] << 16);
+    }
+    *reinterpret_cast<uint4*>(qbuf + swz<32>(row, chunk)) = v;
+  }
+}
+
 // ---- MMA issuer (warp 5; one elected lane issues, the warp stays converged) ---------------------
-template <int KVF, bool HP>
+template <int KVF, bool HP, int HD = 128>
 __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource& src,
                                           uint32_t ring, uint32_t qbufs,
                                           uint32_t pbufs, uint32_t full_bar, uint32_t empty_bar,
                                           const Tc5Bars& bars, uint32_t tmem) {
-  using G = TileGeom<KVF, 128>;
+  using G = TileGeom<KVF, HD>;
+  static_assert(!HP || HD == 128, "head pairs: head_dim 128");
   constexpr int AF = (KVF == 2) ? 1 : 0;  // e5m2 : e4m3 storage
   using TC = Tc5Cols<HP>;
   constexpr uint32_t idesc_qk = tc5::instr_desc_f8(AF, 0, /*a K-major*/ 0, /*b K-major*/ 0, 128, HP ? 64 : 32);
@@ -167,10 +226,14 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
         }
       } else {
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {  // 32 tokens per MMA
-          const uint64_t ad = tc5::smem_desc(vbase + ks * 4096u, 1024u, 1024u, tc5::kLayoutSw128);
-          const uint64_t bd = tc5::smem_desc(pb + ks * 512u, 128u, 128u, tc5::kLayoutNone);
-          tc5::mma_f8(tmem + TC::kO, ad, bd, idesc_pv, (ks > 0) ? 1u : pend_acc);
+        for (int mh = 0; mh < HD / 128; ++mh) {  // 128 output dims per accumulator (one V panel)
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {  // 32 tokens per MMA
+            const uint64_t ad = tc5::smem_desc(vbase + mh * G::PANEL_BYTES + ks * 4096u, 1024u, 1024u,
+                                               tc5::kLayoutSw128);
+            const uint64_t bd = tc5::smem_desc(pb + ks * 512u, 128u, 128u, tc5::kLayoutNone);
+            tc5::mma_f8(tmem + TC::kO + 16u * mh, ad, bd, idesc_pv, (ks > 0) ? 1u : pend_acc);
+          }
         }
       }
       tc5::commit(empty_bar + 8 * pend_stage);  // K / V stage back to the TMA producer
@@ -188,7 +251,7 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
     // every segment: never lag a phase behind
     if constexpr (HP) mbar_wait(bars.q_ready[0], k & 1u);
     else mbar_wait(bars.q_ready[k & 1], (k >> 1) & 1u);
-    const uint32_t qb = HP ? qbufs : qbufs + (k & 1) * 4096u;
+    const uint32_t qb = HP ? qbufs : qbufs + (k & 1) * (32u * HD);
     if (HP && leader && sg.tile_end <= sg.tile_begin) mbar_arrive(bars.q_free);  // nothing reads this query
     for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
       const uint32_t b = n & 1u;
@@ -211,9 +274,10 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
       if (leader) {
         const uint32_t kbase = ring + stage * G::STAGE_BYTES;
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {  // 32 head dims per MMA: +32 bytes inside the SW128 row
-          const uint64_t ad = tc5::smem_desc(kbase + ks * 32u, 16u, 1024u, tc5::kLayoutSw128);
-          const uint64_t bd = tc5::smem_desc(qb + ks * 32u, 16u, 1024u, tc5::kLayoutSw128);
+        for (int ks = 0; ks < HD / 32; ++ks) {  // 32 head dims per MMA: +32 bytes inside the SW128 row
+          const uint32_t pn = ks >> 2, off = (ks & 3) * 32u;  // 128-dim panel (K: PANEL_BYTES, Qs: 4 KiB apart)
+          const uint64_t ad = tc5::smem_desc(kbase + pn * G::PANEL_BYTES + off, 16u, 1024u, tc5::kLayoutSw128);
+          const uint64_t bd = tc5::smem_desc(qb + pn * 4096u + off, 16u, 1024u, tc5::kLayoutSw128);
           tc5::mma_f8(tmem + kTc5ColS + TC::kSStride * b, ad, bd, idesc_qk, ks > 0 ? 1u : 0u);
         }
         tc5::commit(bars.s_ready[b]);
@@ -236,13 +300,13 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
 // ---- softmax warps (0-3), one KV head per unit: thread tid <-> token tid of each tile, TMEM lane tid ----
 // (kept apart from the head-pair version below: folding the two into one template cost the single-head
 // kernel 1.7 % on C3 through instruction scheduling alone)
-template <int QT, int KVF>
+template <int QT, int KVF, int HD = 128>
 __device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const SegSource& src,
                                             uint8_t* smem_ring,
                                             uint8_t* qbufs, uint8_t* pbufs, float* scratch,
                                             const Tc5Bars& bars, uint32_t tmem, int num_stages) {
-  using G = TileGeom<KVF, 128>;
-  constexpr int HD = 128;
+  using G = TileGeom<KVF, HD>;
+  constexpr int NA = HD / 128;  // O accumulators of 128 dims each (thread tid: dims tid, 128 + tid)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int GS = p.group_size;
   const bool use_cap = p.soft_cap > 0.f;
@@ -268,7 +332,8 @@ __device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const 
     Segment sg;
     if (!seg_fetch(src, k, sg)) break;
     if (!have_q) {
-      tc5_prepare_q<QT, false>(p, sg, qbufs + (k & 1) * 4096, dqs + (k & 1) * 8, tid);
+      if constexpr (HD == 256) tc5_prepare_q256<QT>(p, sg, qbufs + (k & 1) * 8192, dqs + (k & 1) * 8, tid);
+      else tc5_prepare_q<QT, false>(p, sg, qbufs + (k & 1) * 4096, dqs + (k & 1) * 8, tid);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bars.q_ready[k & 1]);
@@ -299,7 +364,8 @@ __device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const 
     have_q = src.ctl[kQPeek] != 0;
     if (have_q) {
       const Segment sn = seg_read(src, k + 1);
-      tc5_prepare_q<QT, false>(p, sn, qbufs + ((k + 1) & 1) * 4096, dqs + ((k + 1) & 1) * 8, tid);
+      if constexpr (HD == 256) tc5_prepare_q256<QT>(p, sn, qbufs + ((k + 1) & 1) * 8192, dqs + ((k + 1) & 1) * 8, tid);
+      else tc5_prepare_q<QT, false>(p, sn, qbufs + ((k + 1) & 1) * 4096, dqs + ((k + 1) & 1) * 8, tid);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bars.q_ready[(k + 1) & 1]);
@@ -374,12 +440,15 @@ __device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const 
           // O in TMEM is relative to the old rho: wait for P.V of the previous tile, rescale
           mbar_wait(bars.p_free[b ^ 1u], ((n - 1) >> 1) & 1u);
           tc5::fence_after_sync();
-          float o[16];
-          tc5::ld_x16(tmem + lane_base + Tc5Cols<false>::kO, o);
-          tc5::wait_ld();
 #pragma unroll
-          for (int j = 0; j < 8; ++j) { o[j] *= alpha[j]; o[8 + j] *= alpha[j]; }
-          tc5::st_x16(tmem + lane_base + Tc5Cols<false>::kO, o);
+          for (int a = 0; a < NA; ++a) {
+            float o[16];
+            tc5::ld_x16(tmem + lane_base + Tc5Cols<false>::kO + 16u * a, o);
+            tc5::wait_ld();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { o[j] *= alpha[j]; o[8 + j] *= alpha[j]; }
+            tc5::st_x16(tmem + lane_base + Tc5Cols<false>::kO + 16u * a, o);
+          }
           tc5::wait_st();
           tc5::fence_before_sync();
         }
@@ -403,10 +472,13 @@ __device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const 
       *reinterpret_cast<uint4*>(pbufs + b * 2048 + tid * 16) = row;
       if (tok >= sg.tok_hi) {
         // this token's V row was not (validly) loaded: zero it so that 0 * junk cannot be NaN
-        uint4* vrow = reinterpret_cast<uint4*>(smem_ring + stage * G::STAGE_BYTES + G::KV_BYTES +
-                                               tid * 128);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) vrow[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int pn = 0; pn < G::NP; ++pn) {
+          uint4* vrow = reinterpret_cast<uint4*>(smem_ring + stage * G::STAGE_BYTES + G::KV_BYTES +
+                                                 pn * G::PANEL_BYTES + tid * 128);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) vrow[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
       }
       fence_proxy_async_smem();
       __syncwarp();
@@ -417,19 +489,22 @@ __device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const 
 
     FI_TRACE_IF(tid == 0, 6);
     // ---- segment epilogue: thread tid <-> head-dim index d = tid (TMEM lane of O) ---------------
-    float o8[8];
+    float o8[NA * 8];
     if (sg.tile_end > sg.tile_begin) {
       mbar_wait(bars.p_free[(n - 1) & 1u], ((n - 1) >> 1) & 1u);  // P.V of the last tile complete
       tc5::fence_after_sync();
-      float o[16];
-      tc5::ld_x16(tmem + lane_base + Tc5Cols<false>::kO, o);
-      tc5::wait_ld();
-      tc5::fence_before_sync();
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o8[j] = o[j] + o[8 + j];
+      for (int a = 0; a < NA; ++a) {
+        float o[16];
+        tc5::ld_x16(tmem + lane_base + Tc5Cols<false>::kO + 16u * a, o);
+        tc5::wait_ld();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o8[8 * a + j] = o[j] + o[8 + j];
+      }
+      tc5::fence_before_sync();
     } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o8[j] = 0.f;
+      for (int j = 0; j < NA * 8; ++j) o8[j] = 0.f;
     }
     float L[8];
 #pragma unroll
@@ -460,15 +535,23 @@ __device__ __forceinline__ void tc5_softmax_single(const DecodeParams& p, const 
         if (direct && any && p.sinks != nullptr)  // L is relative to rho and carries 2^kTc5PShift
           L[j] += ex2f(__ldg(p.sinks + sg.kv_head * GS + j) * 1.4426950408889634f - rho[j] + kTc5PShift);
         // numerator and denominator both carry the 2^kTc5PShift scale of p
-        const float val = any ? o8[j] * ((direct ? p.v_scale : 1.f) / L[j]) : 0.f;
+        const float nrm = (direct ? p.v_scale : 1.f) / L[j];
         const float lse2 = any ? rho[j] + lg2f(L[j]) - kTc5PShift : kNegInf;
+#pragma unroll
+        for (int a = 0; a < NA; ++a) {
+          const float val = any ? o8[8 * a + j] * nrm : 0.f;
+          const int d = 128 * a + tid;
+          if (direct) {
+            if (QT == 1) static_cast<__nv_bfloat16*>(p.o)[(hq + j) * HD + d] = __float2bfloat16_rn(val);
+            else static_cast<__half*>(p.o)[(hq + j) * HD + d] = __float2half_rn(val);
+          } else {
+            p.tmp_o[((int64_t)sg.slot * GS + j) * HD + d] = val;
+          }
+        }
         if (direct) {
-          if (QT == 1) static_cast<__nv_bfloat16*>(p.o)[(hq + j) * HD + tid] = __float2bfloat16_rn(val);
-          else static_cast<__half*>(p.o)[(hq + j) * HD + tid] = __float2half_rn(val);
           if (p.lse != nullptr && tid == j) p.lse[hq + j] = lse2;
-        } else {
-          p.tmp_o[((int64_t)sg.slot * GS + j) * HD + tid] = val;
-          if (tid == j) p.tmp_lse[(int64_t)sg.slot * GS + j] = lse2;
+        } else if (tid == j) {
+          p.tmp_lse[(int64_t)sg.slot * GS + j] = lse2;
         }
       }
     }
@@ -805,15 +888,17 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
 }
 
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 1 = e4m3, 2 = e5m2 KV.  head_dim 128, TMA-eligible pages.
-// HP: head-pair plan (see the top of this file).
-template <int QT, int KVF, bool HP = false>
-__global__ void __launch_bounds__(kTc5Threads, 2)
+// HP: head-pair plan (see the top of this file).  HD: 128, or 256 (one CTA per SM: 64 KiB stages, two K / V /
+// Qs panels per row, two O accumulators; single-head units only).
+template <int QT, int KVF, bool HP = false, int HD = 128>
+__global__ void __launch_bounds__(kTc5Threads, HD == 128 ? 2 : 1)
     paged_decode_tc5_kernel(const __grid_constant__ DecodeParams p,
                             const __grid_constant__ CUtensorMap kmap,
                             const __grid_constant__ CUtensorMap vmap) {
-  using G = TileGeom<KVF, 128>;
-  using L = SmemLayout<KVF, 128>;
-  static_assert(L::SCRATCH_O >= 2 * 4096 + 2 * 2048, "Q / P buffers do not fit the scratch region");
+  using G = TileGeom<KVF, HD>;
+  using L = SmemLayout<KVF, HD>;
+  static_assert(L::SCRATCH_O >= 2 * 32 * HD + 2 * 2048, "Q / P buffers do not fit the scratch region");
+  static_assert(!HP || HD == 128, "head pairs: head_dim 128");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t pad = ((raw + 1023u) & ~1023u) - raw;
@@ -821,7 +906,7 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   const uint32_t ring = raw + pad;
   const int ring_bytes = p.num_stages * G::STAGE_BYTES;
   uint8_t* qbufs = base + ring_bytes;            // 2 x 4 KiB (HP: 1 x 8 KiB), 1024-aligned
-  uint8_t* pbufs = qbufs + 2 * 4096;             // 2 x 2 KiB
+  uint8_t* pbufs = qbufs + 2 * 32 * HD;          // 2 x 2 KiB
   float* scratch = reinterpret_cast<float*>(base + ring_bytes + L::SCRATCH_O);
   Segment* seg_cache =
       reinterpret_cast<Segment*>(base + ring_bytes + L::SCRATCH_O + L::SCRATCH_ML);
@@ -854,7 +939,7 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
     tma_prefetch_desc(&kmap);
     tma_prefetch_desc(&vmap);
   }
-  const SegSource src = seg_source_init(p, HP ? G::TT / 2 : G::TT, seg_cache, scratch, /*has_reader1=*/true);
+  const SegSource src = seg_source_init(p, HP ? G::TT / 2 : G::TT, seg_cache, scratch, /*has_reader1=*/true);  // TT: 128 tokens at either head_dim
   tc5::fence_before_sync();
   __syncthreads();
   tc5::fence_after_sync();
@@ -872,11 +957,11 @@ __global__ void __launch_bounds__(kTc5Threads, 2)
   if (warp < 4) {
     if (p.enable_pdl) pdl_wait();
     if constexpr (HP) tc5_softmax<QT, KVF, HP>(p, src, base, qbufs, pbufs, scratch, pair_scratch, bars, tmem, p.num_stages);
-    else tc5_softmax_single<QT, KVF>(p, src, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
+    else tc5_softmax_single<QT, KVF, HD>(p, src, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
   } else if (warp == 4) {
-    produce_tma<KVF, 128, false, HP>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
+    produce_tma<KVF, HD, false, HP>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
   } else {
-    tc5_issue<KVF, HP>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
+    tc5_issue<KVF, HP, HD>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
   }
   if (p.enable_pdl == 2) pdl_launch_dependents();
   tc5::fence_before_sync();
