@@ -1,5 +1,5 @@
 """Streaming rate of the 16-bit decode kernel at head_dim 64 / 128 / 256 (1 GiB of KV each, Hkv = 8, G = 4).
-python scripts/head_dim_probe.py [fp8]"""
+python scripts/head_dim_probe.py [fp8 [head_dim]]"""
 import sys
 from pathlib import Path
 
@@ -11,7 +11,8 @@ import flashinfer_b200 as fi  # noqa: E402
 
 DEV = "cuda:0"
 fp8 = len(sys.argv) > 1 and sys.argv[1] == "fp8"
-for d in ((128, 256) if fp8 else (64, 128, 256)):
+only = int(sys.argv[2]) if len(sys.argv) > 2 else 0  # e.g. `fp8 256`: that head_dim only (ncu captures)
+for d in ((only,) if only else ((128, 256) if fp8 else (64, 128, 256))):
     hkv, hq, page, bs = 8, 32, 16, 64
     es = 1 if fp8 else 2
     kv_len = (1 << 30) // (bs * hkv * d * 2 * es)
