@@ -71,6 +71,7 @@ PROTOTYPES = {
                                  _vp, _vp, _vp, _vp, _f, _f, _f, _i, _vp, _f, _f, _vp, _i, _i, _vp]),
     "fi_batch_decode_plan_args": (_i, [C.POINTER(DecodePlanArgs)]),
     "fi_batch_decode_run_args": (_i, [C.POINTER(DecodeRunArgs)]),
+    "fi_batch_decode_step": (_i, [C.POINTER(DecodePlanArgs), C.POINTER(DecodeRunArgs)]),
     "fi_single_decode_run": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _i, _i, _i, _i, _i, _i,
                                   _i, _f, _f, _f, _i, _vp, _f, _f, _i, _vp]),
     "fi_single_decode_tmp_bytes": (_sz, [_i, _i, _i, _i]),

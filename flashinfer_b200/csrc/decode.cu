@@ -545,6 +545,18 @@ int fi_batch_decode_run_args(const FiDecodeRunArgs* a) {
                              a->rope_scale, a->rope_theta, a->sinks, a->enable_pdl, a->device, a->stream);
 }
 
+int fi_batch_decode_step(const FiDecodePlanArgs* plan, const FiDecodeRunArgs* run) {
+  if (plan == nullptr || run == nullptr) return fail(FI_ERR_INVALID_ARGUMENT, "null argument block");
+  if (run->plan_info != plan->plan_info_out)
+    return fail(FI_ERR_INVALID_ARGUMENT, "fi_batch_decode_step: run->plan_info must be plan->plan_info_out");
+  if (int rc = fi_batch_decode_plan_args(plan)) return rc;
+  if (plan->kv_indices_host != nullptr && run->kv_indices == nullptr && !plan->cuda_graph &&
+      plan->plan_info_out[kPiOffIndices] < 0)
+    return fail(FI_ERR_WORKSPACE, "fi_batch_decode_step: the page table does not fit the int workspace and no "
+                                  "device copy was given");
+  return fi_batch_decode_run_args(run);
+}
+
 size_t fi_single_decode_tmp_bytes(int num_qo_heads, int num_kv_heads, int head_dim, int device) {
   int sms = 148;
   if (device >= 0) device_sm_count(device, &sms);

@@ -231,6 +231,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._lib = _lib.load()
         self._pdl_default = int(device_support_pdl(self.device))
         self._head_pairs_ok = True   # cleared when a run() had to fall back (FI_ERR_REPLAN)
+        self._ran_once = False       # step(): the run argument block holds a complete run()
+        self._run_kw = (None, None, None, None, None)
         self._plan_call = None
         self._mtp_children = {}
         self._mtp_src = None
@@ -429,6 +431,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._sm_scale = sm_scale
         self._rope_scale = rope_scale
         self._rope_theta = rope_theta
+        self._ran_once = False  # step(): the next run() refreshes the run argument block
         # what run(q_len_per_req > 1) needs to plan the per-row requests on first use
         self._mtp_src = (indptr, indices, last_page_len, head_dim, page_size, q_data_type, kv_data_type,
                          fixed_split_size, disable_split_kv)
@@ -729,7 +732,83 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 rc = self._lib.fi_batch_decode_run_args(self._ra_ref)
             if rc:
                 _lib.check(rc)
+        self._ran_once = True
+        self._run_kw = (q_scale, k_scale, v_scale, enable_pdl, sinks)
         return (out, lse) if return_lse else out
+
+    def step(self, indptr: torch.Tensor, indices: torch.Tensor, last_page_len: torch.Tensor,
+             q: torch.Tensor, paged_kv_cache, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        r"""One decode step of a serving loop in ONE library call (beyond the reference, whose wrapper
+        plans and runs through separate calls): ``plan(indptr, indices, last_page_len, <everything
+        else as in the last plan()>)`` followed by ``run(q, paged_kv_cache, out=out)`` with the
+        scales, soft cap, sinks and PDL setting of the last ``run()``.
+
+        The fast path needs what a serving loop has anyway: a previous ``plan()`` and ``run()`` on this
+        wrapper, the same cache tensor as that ``run()``, and the page table as contiguous int32 CPU
+        tensors (pinned or not; the planner reads them during the call).  Anything else — CUDA-graph
+        mode, device tables, another cache — takes ``plan()`` + ``run()``.
+        """
+        kv = self._kv_key
+        call = self._plan_call
+        i32 = torch.int32
+        if (call is None or self._use_cuda_graph or kv is None or not self._ran_once
+                or kv[0]() is not paged_kv_cache or kv[1] != paged_kv_cache.data_ptr()
+                or indptr.device.type != "cpu" or indices.device.type != "cpu" or last_page_len.device.type != "cpu"
+                or indptr.dtype != i32 or indices.dtype != i32 or last_page_len.dtype != i32
+                or not (indptr.is_contiguous() and indices.is_contiguous() and last_page_len.is_contiguous())):
+            if call is None:
+                raise RuntimeError("step() needs a previous plan() on this wrapper")
+            self.plan(indptr, indices, last_page_len, *call[0][3:], **dict(call[1], seq_lens=None, block_tables=None))
+            rk = self._run_kw  # the last run()'s scales, as on the fast path
+            return self.run(q, paged_kv_cache, out=out, q_scale=rk[0], k_scale=rk[1], v_scale=rk[2],
+                            enable_pdl=rk[3], sinks=rk[4])
+        batch_size = last_page_len.shape[0]
+        if indptr.shape[0] != batch_size + 1:
+            raise ValueError("indptr must have batch_size + 1 entries")
+        if q.dtype != self._cached_q_data_type:
+            raise ValueError(
+                f"The dtype of q {q.dtype} does not match the q_data_type {self._cached_q_data_type} "
+                "specified in plan function.")
+        shape = (batch_size, self._num_qo_heads, self._head_dim)
+        qs = q.stride()
+        if q.shape != shape or qs[2] != 1 or q.device != self.device:
+            raise ValueError(f"q must be a [{batch_size}, {self._num_qo_heads}, {self._head_dim}] tensor on the "
+                             "wrapper's device with a contiguous last dimension")
+        if out is None:
+            out = torch.empty(shape, dtype=q.dtype, device=q.device)
+        elif out.shape != q.shape or out.dtype != q.dtype or not out.is_contiguous() or \
+                not (out.device == q.device or (out.device.type == "cpu" and out.is_pinned())):
+            raise ValueError("out must be a contiguous tensor of q's shape and dtype on q's device or in pinned host memory")
+        pa, ra = self._pa, self._ra
+        info = _PlanInfo()
+        pa.indptr_host, pa.last_page_len_host, pa.kv_len_host = indptr.data_ptr(), last_page_len.data_ptr(), None
+        pa.kv_indices_host, pa.num_indices = indices.data_ptr(), indices.numel()
+        pa.batch_size = batch_size
+        pa.plan_info_out = ra.plan_info = C.addressof(info)
+        pa.stream = ra.stream = current_stream_ptr(self.device)
+        ra.q, ra.q_stride_n, ra.q_stride_h = q.data_ptr(), qs[0], qs[1]
+        ra.o, ra.lse = out.data_ptr(), None
+        ra.kv_indices = ra.kv_indptr = None  # the planner ships the table behind the work list
+        rc = self._lib.fi_batch_decode_step(self._pa_ref, self._ra_ref)
+        self._plan_info = info
+        if rc:
+            if rc in (_lib.FI_ERR_REPLAN, _lib.FI_ERR_WORKSPACE):  # head pairs / table too large: the long way
+                self._ran_once = False
+                try:
+                    return self.step(indptr, indices, last_page_len, q, paged_kv_cache, out=out)
+                finally:
+                    self._ran_once = True
+            _lib.check(rc)
+        # what plan() leaves behind for the other entry points
+        self._indices_dev, self._indices_src = None, indices
+        self._indptr_dev, self._indptr_src = None, indptr
+        self._last_page_len_dev, self._last_page_len_src = None, last_page_len
+        self._batch_size, self._q_shape = batch_size, shape
+        self._plan_call = ((indptr, indices, last_page_len) + call[0][3:], call[1])
+        self._mtp_src = (indptr, indices, last_page_len) + self._mtp_src[3:]
+        if self._mtp_children:
+            self._mtp_children = {}
+        return out
 
     def _bind_cache(self, paged_kv_cache) -> None:
         """Validate the cache against the plan and write its geometry into the run argument block."""

@@ -223,6 +223,16 @@ typedef struct FiDecodeRunArgs {
   void* stream;
 } FiDecodeRunArgs;
 FI_API int fi_batch_decode_run_args(const FiDecodeRunArgs* a);
+/*
+ * fi_batch_decode_step — fi_batch_decode_plan_args(plan) followed by fi_batch_decode_run_args(run) in ONE call:
+ * a decode step of a serving loop (new page table, same problem shape) costs the binding a single
+ * foreign call.  run->plan_info must be plan->plan_info_out.  When the planner could not place its copy
+ * of kv_indices_host behind the work list (int workspace too small) and run->kv_indices is NULL the
+ * call fails with FI_ERR_WORKSPACE before anything is launched (NULL would mean "identity table").
+ * No reference counterpart: its wrapper calls plan and run through separate tvm-ffi functions
+ * (flashinfer/decode.py:1086-1102, 1286-1330).
+ */
+FI_API int fi_batch_decode_step(const FiDecodePlanArgs* plan, const FiDecodeRunArgs* run);
 
 /*
  * fi_single_decode_run — one request, contiguous K/V.

@@ -704,6 +704,57 @@ def test_run_into_a_pinned_host_tensor(kv_dtype):
         w.run(q, cache_d, out=torch.empty(q.shape, dtype=q.dtype))
 
 
+@pytest.mark.parametrize("kv_dtype", [None, torch.float8_e4m3fn])
+def test_step_is_plan_plus_run(kv_dtype):
+    """wrapper.step(table, q, cache): plan + run through ONE library call (fi_batch_decode_step) with the
+    problem description of the last plan() and the scales of the last run() — bit-equal to plan() + run()
+    for new page tables and batch sizes, into device or pinned host memory; device tables and a
+    different cache tensor take the two-call path."""
+    fi = _fi()
+    hq, hkv, d, page = 32, 8, 128, 16
+    is8 = kv_dtype is not None
+    lens_all = [[300, 5000, 17, 0, 9000], [301, 5001, 18, 1, 9001], [64, 128, 7000], [12000, 1, 2, 3, 4, 5, 6]]
+    big = max(sum(-(-l // page) for l in lens) for lens in lens_all) + 8
+    g = torch.Generator().manual_seed(121)
+    cache = torch.randn(big, 2, page, hkv, d, generator=g)
+    cache = (cache * 0.5 if is8 else cache).to(kv_dtype or torch.bfloat16).to(DEV)
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), "NHD")
+    ref = fi.BatchDecodeWithPagedKVCacheWrapper(torch.empty(64 << 20, dtype=torch.uint8, device=DEV), "NHD")
+    kw = dict(q_data_type=torch.bfloat16, kv_data_type=cache.dtype, logits_soft_cap=30.0)
+    rkw = dict(k_scale=0.5, v_scale=2.0)
+
+    def table(lens, seed):
+        pages = [-(-l // page) for l in lens]
+        perm = torch.randperm(big, generator=torch.Generator().manual_seed(seed))[: sum(pages)].to(torch.int32)
+        indptr = torch.tensor([0] + list(np.cumsum(pages)), dtype=torch.int32)
+        last = torch.tensor([(l - 1) % page + 1 if l else 0 for l in lens], dtype=torch.int32)
+        return indptr, perm.contiguous(), last
+
+    with pytest.raises(RuntimeError):
+        w.step(*table(lens_all[0], 1), make_q(5, hq, d, torch.bfloat16).to(DEV), cache)  # no plan() yet
+    for it, lens in enumerate(lens_all):
+        indptr, indices, last = table(lens, 10 + it)
+        q = make_q(len(lens), hq, d, torch.bfloat16, seed=130 + it).to(DEV)
+        ref.plan(indptr, indices, last, hq, hkv, d, page, **kw)
+        o_ref = ref.run(q, cache, **rkw)
+        if it == 0:  # what a serving loop has done before its first step()
+            w.plan(indptr, indices, last, hq, hkv, d, page, **kw)
+            w.run(q, cache, **rkw)
+        if it == 2:
+            o = torch.empty(q.shape, dtype=q.dtype).pin_memory()
+            assert w.step(indptr, indices, last, q, cache, out=o) is o
+        elif it == 3:  # device tables: plan() + run() underneath
+            o = w.step(indptr.to(DEV), indices.to(DEV), last.to(DEV), q, cache)
+        else:
+            o = w.step(indptr, indices, last, q, cache)
+        torch.cuda.synchronize()
+        assert torch.equal(o.cpu(), o_ref.cpu()), it
+        # the wrapper is left as after plan(): run() alone gives the same again
+        assert torch.equal(w.run(q, cache, **rkw).cpu(), o_ref.cpu())
+    other = cache.clone()
+    assert torch.equal(w.step(indptr, indices, last, q, other).cpu(), o_ref.cpu())
+
+
 def test_fp8_head_pair_plan_falls_back_when_run_needs_rope():
     """A head-pair plan cannot feed the RoPE variant kernel: forward(pos_encoding_mode="ROPE_LLAMA") after a
     NONE plan gets FI_ERR_REPLAN from the C-ABI, and the wrapper plans once more without the flag."""
