@@ -619,7 +619,7 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
         if (p.page_shift >= 0) pit0 = tok0 >> p.page_shift;
         else { pit0 = (int)__umulhi((uint32_t)tok0, magic); pit0 += (tok0 - pit0 * p.page_size >= p.page_size); }
       }
-      auto issue = [&](auto full_tile) {
+      auto issue = [&](auto full_tile, auto wide_tile) {
 #pragma unroll
         for (int ps = 0; ps < R::PASSES; ++ps) {
           const int row = ps * R::RPP + r0;
@@ -635,13 +635,13 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
           }
           // every lane takes part in the shuffle; rows past the end read a valid lane's (unused) value
           int page = __shfl_sync(0xffffffffu, cur[0], slot & 31);
-          if constexpr (R::SLOTS > 1) {
-            if (wide) {  // warp-uniform: only tiles that touch more than 32 pages (page size 1 or 2)
+          if constexpr (R::SLOTS > 1 && decltype(wide_tile)::value) {
+            // only tiles that touch more than 32 pages (page size 1): compiled as its own copy of the loop,
+            // a warp-uniform branch per row in here cost page size 1 ten per cent
 #pragma unroll
-              for (int i = 1; i < R::SLOTS; ++i) {
-                const int other = __shfl_sync(0xffffffffu, cur[i], slot & 31);
-                page = (slot >> 5) == i ? other : page;
-              }
+            for (int i = 1; i < R::SLOTS; ++i) {
+              const int other = __shfl_sync(0xffffffffu, cur[i], slot & 31);
+              page = (slot >> 5) == i ? other : page;
             }
           }
           const char* src_k = kcol + ((uint64_t)(uint32_t)page * spage + (uint64_t)(uint32_t)rip * sn);
@@ -656,8 +656,13 @@ __device__ __forceinline__ void produce_cpasync(const DecodeParams& p, const Seg
           }
         }
       };
-      if (nvalid >= G::TT) issue(std::true_type{});
-      else issue(std::false_type{});
+      if (wide) {
+        if (nvalid >= G::TT) issue(std::true_type{}, std::true_type{});
+        else issue(std::false_type{}, std::true_type{});
+      } else {
+        if (nvalid >= G::TT) issue(std::true_type{}, std::false_type{});
+        else issue(std::false_type{}, std::false_type{});
+      }
       cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
       if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
       ++tiles_issued;
