@@ -175,10 +175,10 @@ static cudaError_t ensure_smem_attr(K kern, int smem) {
   return e;
 }
 
-template <int QT, int KVF, int HD, int LOADER, bool ROPE = false>
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, bool MROWS = false>
 static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                       int grid, cudaStream_t stream) {
-  auto kern = paged_decode_kernel<QT, KVF, HD, LOADER, ROPE>;
+  auto kern = paged_decode_kernel<QT, KVF, HD, LOADER, ROPE, MROWS>;
   const int smem = SmemLayout<KVF, HD>::total(p.num_stages);
   FI_CUDA_TRY(ensure_smem_attr(kern, smem));
   cudaLaunchConfig_t cfg = {};
@@ -198,7 +198,11 @@ static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtens
 template <int QT, int KVF, int HD>
 static int launch_loader(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                          int grid, bool tma, cudaStream_t stream) {
-  if constexpr (KVF == 0) {  // ROPE_LLAMA on 16-bit KV: K rotated in registers (decode_kernel.cuh)
+  if constexpr (KVF == 0) {
+    if (p.q_rows > 1)  // multi-row units (fi_batch_decode_run_args q_rows): checked by the caller
+      return tma ? launch_one<QT, KVF, HD, 0, false, true>(p, km, vm, grid, stream)
+                 : launch_one<QT, KVF, HD, 1, false, true>(p, km, vm, grid, stream);
+    // ROPE_LLAMA on 16-bit KV: K rotated in registers (decode_kernel.cuh)
     if (p.rope)
       return tma ? launch_one<QT, KVF, HD, 0, true>(p, km, vm, grid, stream)
                  : launch_one<QT, KVF, HD, 1, true>(p, km, vm, grid, stream);
@@ -389,14 +393,14 @@ FI_API int fi_debug_trace(unsigned long long* dst, int n_ctas) {
 int fi_last_loader(void) { return g_last_loader; }
 long long fi_launch_count(void) { return g_launch_count; }
 
-int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, const void* q,
-                        int64_t q_stride_n, int64_t q_stride_h, const void* k_cache,
-                        const void* v_cache, int64_t num_pages, int64_t kv_stride_page,
-                        int64_t kv_stride_n, int64_t kv_stride_h, const int32_t* kv_indices,
-                        const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
-                        float v_scale, float logits_soft_cap, int pos_encoding_mode,
-                        const float* alibi_slopes, float rope_scale, float rope_theta,
-                        const float* sinks, int enable_pdl, int device, void* stream_) {
+static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* plan_info, const void* q,
+                                 int64_t q_stride_n, int64_t q_stride_h, const void* k_cache,
+                                 const void* v_cache, int64_t num_pages, int64_t kv_stride_page,
+                                 int64_t kv_stride_n, int64_t kv_stride_h, const int32_t* kv_indices,
+                                 const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
+                                 float v_scale, float logits_soft_cap, int pos_encoding_mode,
+                                 const float* alibi_slopes, float rope_scale, float rope_theta,
+                                 const float* sinks, int enable_pdl, int device, void* stream_, int q_rows) {
   if (int rc = check_pos_mode(pos_encoding_mode, alibi_slopes, rope_scale, rope_theta)) return rc;
   if (plan_info == nullptr || plan_info[kPiMagic] != kPlanMagic)
     return fail(FI_ERR_INVALID_ARGUMENT, "plan info is not initialized");
@@ -472,6 +476,16 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   // the L2 full of DIRTY lines (a 256 MB memset right before it) is slower (C2 +4 %, C4 +10 %).
   p.l2_hints = default_l2_hints();
   p.sinks = sinks;
+  if (q_rows > 1) {
+    // multi-row units: the plan was made with num_qo_heads = q_rows x the model's query heads
+    const int Hkv_mem = Hkv / p.kv_head_div;
+    if (kvf != 0 || p.rope || Hq % q_rows != 0 || (Hq / q_rows) % Hkv_mem != 0 || p.head_pairs ||
+        plan_info[kPiMergeGrid] > 0 || plan_info[kPiWindowLeft] >= 0 || head_dim == 512)
+      return fail(FI_ERR_UNSUPPORTED, "q_rows > 1 needs 16-bit KV, no ROPE_LLAMA, no sliding window, the fused "
+                                      "merge and a plan made with num_qo_heads = q_rows x query heads");
+    p.q_rows = q_rows;
+    p.q_group = (Hq / q_rows) / Hkv_mem;
+  }
 
   const bool cuda_core_only = (kvf != 0 && head_dim == 64) || head_dim == 512;
   const bool tma = !cuda_core_only && tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h,
@@ -536,13 +550,28 @@ int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, 
   return FI_OK;
 }
 
+int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan_info, const void* q,
+                        int64_t q_stride_n, int64_t q_stride_h, const void* k_cache,
+                        const void* v_cache, int64_t num_pages, int64_t kv_stride_page,
+                        int64_t kv_stride_n, int64_t kv_stride_h, const int32_t* kv_indices,
+                        const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
+                        float v_scale, float logits_soft_cap, int pos_encoding_mode,
+                        const float* alibi_slopes, float rope_scale, float rope_theta,
+                        const float* sinks, int enable_pdl, int device, void* stream_) {
+  return batch_decode_run_impl(float_ws, int_ws, plan_info, q, q_stride_n, q_stride_h, k_cache, v_cache,
+                               num_pages, kv_stride_page, kv_stride_n, kv_stride_h, kv_indices, kv_indptr, o,
+                               lse, sm_scale, v_scale, logits_soft_cap, pos_encoding_mode, alibi_slopes,
+                               rope_scale, rope_theta, sinks, enable_pdl, device, stream_, 1);
+}
+
 int fi_batch_decode_run_args(const FiDecodeRunArgs* a) {
   if (a == nullptr) return fail(FI_ERR_INVALID_ARGUMENT, "null run argument block");
-  return fi_batch_decode_run(a->float_ws, a->int_ws, a->plan_info, a->q, a->q_stride_n, a->q_stride_h,
-                             a->k_cache, a->v_cache, a->num_pages, a->kv_stride_page, a->kv_stride_n,
-                             a->kv_stride_h, a->kv_indices, a->kv_indptr, a->o, a->lse, a->sm_scale,
-                             a->v_scale, a->logits_soft_cap, a->pos_encoding_mode, a->alibi_slopes,
-                             a->rope_scale, a->rope_theta, a->sinks, a->enable_pdl, a->device, a->stream);
+  return batch_decode_run_impl(a->float_ws, a->int_ws, a->plan_info, a->q, a->q_stride_n, a->q_stride_h,
+                               a->k_cache, a->v_cache, a->num_pages, a->kv_stride_page, a->kv_stride_n,
+                               a->kv_stride_h, a->kv_indices, a->kv_indptr, a->o, a->lse, a->sm_scale,
+                               a->v_scale, a->logits_soft_cap, a->pos_encoding_mode, a->alibi_slopes,
+                               a->rope_scale, a->rope_theta, a->sinks, a->enable_pdl, a->device, a->stream,
+                               a->q_rows > 1 ? a->q_rows : 1);
 }
 
 int fi_batch_decode_step(const FiDecodePlanArgs* plan, const FiDecodeRunArgs* run) {

@@ -940,9 +940,29 @@ __device__ __forceinline__ float4 ldcg_f32x4(const float* p) {
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
 }
+// ---- multi-row units (DecodeParams::q_rows = n > 1, run(q_len_per_req = n)) -------------------
+// A request's n new query tokens share its KV stream: the unit's GS query "heads" are (row, head)
+// pairs.  Column c of virtual KV head vh is column cc = (vh % div) * GS + c of the real KV head
+// kv = vh / div, i.e. row cc / G of the n rows and query head kv * G + cc % G (G = q_group, the
+// model's GQA group).  Row r is query token r of the request and attends all but the last
+// n - 1 - r tokens of the cache (causal among the new tokens).
+struct RowHead {
+  int row, head;  // row of the request's n query rows; real query head
+  __device__ __forceinline__ int64_t token(const DecodeParams& p, int request) const {
+    return (int64_t)request * p.q_rows + row;  // row of q / o / lse
+  }
+};
+__device__ __forceinline__ RowHead row_head(const DecodeParams& p, int kv_head, int c) {
+  const int cc = (kv_head % p.kv_head_div) * p.group_size + c;
+  RowHead r;
+  r.row = cc / p.q_group;
+  r.head = (kv_head / p.kv_head_div) * p.q_group + (cc - r.row * p.q_group);
+  return r;
+}
+
 // ctid: 0 .. 127 (the four consumer warps).  One item = (head, 4 dims); loads are issued in
 // batches of four independent .cg reads so that the unit costs ~two L2 round trips.
-template <int QT, int HD>
+template <int QT, int HD, bool MROWS = false>
 __device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int request, int kv_head,
                                                int slot_begin, int count, int ctid) {
   const int GS = p.group_size;
@@ -981,8 +1001,14 @@ __device__ __forceinline__ void merge_unit_cta(const DecodeParams& p, int reques
         acc.x += w * x4[j].x; acc.y += w * x4[j].y; acc.z += w * x4[j].z; acc.w += w * x4[j].w;
       }
     }
-    const int64_t hq = (int64_t)request * p.num_qo_heads + kv_head * GS + h;
-    if (p.sinks != nullptr && mx > kNegInf) d += ex2f(__ldg(p.sinks + kv_head * GS + h) * 1.4426950408889634f - mx);
+    int64_t hq = (int64_t)request * p.num_qo_heads + kv_head * GS + h;
+    int sink_head = kv_head * GS + h;
+    if constexpr (MROWS) {
+      const RowHead rh = row_head(p, kv_head, h);
+      sink_head = rh.head;
+      hq = rh.token(p, request) * (p.num_qo_heads / p.q_rows) + rh.head;
+    }
+    if (p.sinks != nullptr && mx > kNegInf) d += ex2f(__ldg(p.sinks + sink_head) * 1.4426950408889634f - mx);
     const float inv = p.v_scale / d;
     uint2 u;
     u.x = pack2<QT == 1>(acc.x * inv, acc.y * inv);
@@ -1018,12 +1044,12 @@ __device__ __forceinline__ void merge_post(const DecodeParams& p, PendingMerge& 
   pm.mu = -1;
 }
 // all consumer threads, after that barrier (and before the next one)
-template <int QT, int HD>
+template <int QT, int HD, bool MROWS = false>
 __device__ __forceinline__ void merge_run_posted(const DecodeParams& p, const float* scratch, int ctid) {
   const volatile int* d = reinterpret_cast<const volatile int*>(scratch + kMergeDescFloat);
   if (d[0]) {
     __threadfence();
-    merge_unit_cta<QT, HD>(p, d[1], d[2], d[3], d[4], ctid);
+    merge_unit_cta<QT, HD, MROWS>(p, d[1], d[2], d[3], d[4], ctid);
     FI_TRACE_IF(ctid == 0, 9);
   }
 }
@@ -1034,7 +1060,7 @@ __device__ __forceinline__ void merge_run_posted(const DecodeParams& p, const fl
 //         running max - 20), so that probabilities quantised to e4m3 are scaled by their own
 //         32-token block's maximum and nothing within 2^-18 of it is flushed),
 //   l[j]  sum of exp2(x - m[j]),  o[..] = sum of exp2(x - m[j]) v  (x 256 for fp8 KV).
-template <int QT, int KVF, int HD, int LOADER, bool ROPE = false>
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, bool MROWS = false>
 __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& src, uint32_t ring,
                                         uint32_t full_bar, uint32_t empty_bar, float* scratch_o,
                                         float* scratch_ml) {
@@ -1056,6 +1082,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
   const int rmask = ~(rpb - 1);
   const uint32_t vdelta = (uint32_t)rpb * 128u;
   static_assert(!ROPE || KVF == 0, "in-register RoPE is built for 16-bit KV");
+  static_assert(!MROWS || (KVF == 0 && !ROPE), "multi-row units: 16-bit KV, no RoPE");
   [[maybe_unused]] float freq[ROPE ? HD / 8 : 1];
   if constexpr (ROPE) rope_freqs<HD>(freq, p, t);
 
@@ -1073,10 +1100,19 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
     uint32_t qf[NQ][2];
     uint32_t ql[KVF == 0 ? 1 : NQ][2], ql2[KVF == 0 ? 1 : NQ][2];  // fp8: residual query terms
     float mul[2], pre[2];               // logit scale per head column (2t, 2t+1)
+    // multi-row units: tokens at the end of the cache that head column 2t + j does not see
+    [[maybe_unused]] int hid[2] = {0, 0};
     {
       const char* qrow = static_cast<const char*>(p.q) +
                          ((int64_t)sg.request * p.q_stride_n +
                           (int64_t)(sg.kv_head * GS + g) * p.q_stride_h) * 2;
+      if constexpr (MROWS) {
+        const RowHead rh = row_head(p, sg.kv_head, g);
+        qrow = static_cast<const char*>(p.q) +
+               (rh.token(p, sg.request) * p.q_stride_n + (int64_t)rh.head * p.q_stride_h) * 2;
+        hid[0] = p.q_rows - 1 - row_head(p, sg.kv_head, 2 * t).row;
+        hid[1] = p.q_rows - 1 - row_head(p, sg.kv_head, 2 * t + 1).row;
+      }
       if constexpr (KVF == 0) {
         if (have_qn) {
 #pragma unroll
@@ -1091,6 +1127,11 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
           const char* nrow = static_cast<const char*>(p.q) +
                              ((int64_t)sn.request * p.q_stride_n +
                               (int64_t)(sn.kv_head * GS + g) * p.q_stride_h) * 2;
+          if constexpr (MROWS) {
+            const RowHead rn = row_head(p, sn.kv_head, g);
+            nrow = static_cast<const char*>(p.q) +
+                   (rn.token(p, sn.request) * p.q_stride_n + (int64_t)rn.head * p.q_stride_h) * 2;
+          }
           load_q_frags16<HD>(qn, nrow, g < GS, t);
           if constexpr (ROPE) rope_rotate_q<BF, HD>(qn, freq, sn.kv_len - 1);
         }
@@ -1115,7 +1156,8 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         const int h = 2 * t + j;
-        const float a = h < GS ? __ldg(p.alibi_slopes + sg.kv_head * GS + h) : 0.f;
+        const int ah = MROWS ? row_head(p, sg.kv_head, h).head : sg.kv_head * GS + h;
+        const float a = h < GS ? __ldg(p.alibi_slopes + ah) : 0.f;
         alc[j] = a * (use_cap ? cap_pre : 1.4426950408889634f);
         pre[j] *= p.sm_scale;
       }
@@ -1158,8 +1200,16 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
           for (int i = 0; i < 4; ++i)
             x[i] = use_cap ? cap_post * tanhf_approx(s[i] * pre[i & 1] + alc[i & 1] * pf[i >> 1])
                            : s[i] * mul[i & 1] + alc[i & 1] * pf[i >> 1];
+          [[maybe_unused]] bool vc[4] = {va, va, vb, vb};  // per (token, head column)
+          if constexpr (MROWS) {
+            vc[0] = va && ta < sg.tok_hi - hid[0]; vc[1] = va && ta < sg.tok_hi - hid[1];
+            vc[2] = vb && tb < sg.tok_hi - hid[0]; vc[3] = vb && tb < sg.tok_hi - hid[1];
+            x[0] = vc[0] ? x[0] : kNegInf; x[1] = vc[1] ? x[1] : kNegInf;
+            x[2] = vc[2] ? x[2] : kNegInf; x[3] = vc[3] ? x[3] : kNegInf;
+          } else {
           x[0] = va ? x[0] : kNegInf; x[1] = va ? x[1] : kNegInf;
           x[2] = vb ? x[2] : kNegInf; x[3] = vb ? x[3] : kNegInf;
+          }
           float mx[2] = {fmaxf(x[0], x[2]), fmaxf(x[1], x[3])};
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
@@ -1175,10 +1225,17 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
             m[j] = mn;
           }
           float pr[4];
+          if constexpr (MROWS) {
+            pr[0] = vc[0] ? ex2f(x[0] - m[0]) : 0.f;
+            pr[1] = vc[1] ? ex2f(x[1] - m[1]) : 0.f;
+            pr[2] = vc[2] ? ex2f(x[2] - m[0]) : 0.f;
+            pr[3] = vc[3] ? ex2f(x[3] - m[1]) : 0.f;
+          } else {
           pr[0] = va ? ex2f(x[0] - m[0]) : 0.f;
           pr[1] = va ? ex2f(x[1] - m[1]) : 0.f;
           pr[2] = vb ? ex2f(x[2] - m[0]) : 0.f;
           pr[3] = vb ? ex2f(x[3] - m[1]) : 0.f;
+          }
           l[0] = l[0] * sc[0] + pr[0] + pr[2];
           l[1] = l[1] * sc[1] + pr[1] + pr[3];
 #pragma unroll
@@ -1272,7 +1329,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
     named_bar_sync(1, kConsumerWarps * 32);
     if (threadIdx.x == 0) src.ctl[kQDone0] = k + 1;  // every warp holds its copy of segment k
     FI_TRACE_IF(threadIdx.x == 0, 10);
-    merge_run_posted<QT, HD>(p, scratch_ml, threadIdx.x);
+    merge_run_posted<QT, HD, MROWS>(p, scratch_ml, threadIdx.x);
     float M[2], L[2], f[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -1314,8 +1371,10 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         const bool any = L[j] > 0.f;
-        if (direct && any && p.sinks != nullptr && 2 * t + j < GS)
-          L[j] += ex2f(__ldg(p.sinks + sg.kv_head * GS + 2 * t + j) * 1.4426950408889634f - M[j]);
+        if (direct && any && p.sinks != nullptr && 2 * t + j < GS) {
+          const int sh = MROWS ? row_head(p, sg.kv_head, 2 * t + j).head : sg.kv_head * GS + 2 * t + j;
+          L[j] += ex2f(__ldg(p.sinks + sh) * 1.4426950408889634f - M[j]);
+        }
         // fp8 KV: the accumulator carries the x256 scale of the quantised probabilities
         inv[j] = any ? (direct ? p.v_scale : 1.f) * (KVF == 0 ? 1.f : 1.f / 256.f) / L[j] : 0.f;
         lse2[j] = any ? M[j] + lg2f(L[j]) : kNegInf;
@@ -1326,22 +1385,27 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
           if (h0 + j < GS) {
+            int64_t oh = hq + h0 + j;  // row of o / lse: (request, query head)
+            if constexpr (MROWS) {
+              const RowHead rh = row_head(p, sg.kv_head, h0 + j);
+              oh = rh.token(p, sg.request) * (p.num_qo_heads / p.q_rows) + rh.head;
+            }
             if (QT == 1) {
-              __nv_bfloat16* orow = static_cast<__nv_bfloat16*>(p.o) + (hq + h0 + j) * HD;
+              __nv_bfloat16* orow = static_cast<__nv_bfloat16*>(p.o) + oh * HD;
 #pragma unroll
               for (int i = 0; i < MT; ++i) {
                 orow[o_dim<KVF>(i, 0, g)] = __float2bfloat16_rn(o[i][j] * inv[j]);
                 orow[o_dim<KVF>(i, 1, g)] = __float2bfloat16_rn(o[i][2 + j] * inv[j]);
               }
             } else {
-              __half* orow = static_cast<__half*>(p.o) + (hq + h0 + j) * HD;
+              __half* orow = static_cast<__half*>(p.o) + oh * HD;
 #pragma unroll
               for (int i = 0; i < MT; ++i) {
                 orow[o_dim<KVF>(i, 0, g)] = __float2half_rn(o[i][j] * inv[j]);
                 orow[o_dim<KVF>(i, 1, g)] = __float2half_rn(o[i][2 + j] * inv[j]);
               }
             }
-            if (p.lse != nullptr && g == 0) p.lse[hq + h0 + j] = lse2[j];
+            if (p.lse != nullptr && g == 0) p.lse[oh] = lse2[j];
           }
         }
       } else {
@@ -1368,7 +1432,7 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
   // end of this CTA's sequence: the last arrival is still unchecked
   if (threadIdx.x == 0) merge_post(p, pm, scratch_ml);
   named_bar_sync(1, kConsumerWarps * 32);
-  merge_run_posted<QT, HD>(p, scratch_ml, threadIdx.x);
+  merge_run_posted<QT, HD, MROWS>(p, scratch_ml, threadIdx.x);
   FI_TRACE_IF(threadIdx.x == 0, 8);
 }
 
@@ -1381,7 +1445,8 @@ struct BlockDim {
 
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 0 = KV has q's dtype, 1 = e4m3, 2 = e5m2.
 // LOADER: 0 = TMA boxes, 1 = cp.async gathers.
-template <int QT, int KVF, int HD, int LOADER, bool ROPE = false>
+// MROWS: multi-row units (see row_head): n query rows of a request share its KV stream.
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, bool MROWS = false>
 __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
     paged_decode_kernel(const __grid_constant__ DecodeParams p,
                         const __grid_constant__ CUtensorMap kmap,
@@ -1438,7 +1503,7 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   if (tid < kConsumerWarps * 32) {
     if constexpr (kRegSplit) setmaxnreg_inc<kCpAsyncConsumerRegs>();
     if (p.enable_pdl) pdl_wait();
-    consume<QT, KVF, HD, LOADER, ROPE>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
+    consume<QT, KVF, HD, LOADER, ROPE, MROWS>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
   } else if (LOADER == 0) {
     produce_tma<KVF, HD, true>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);  // waits inside
   } else {

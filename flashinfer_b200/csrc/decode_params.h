@@ -189,6 +189,10 @@ struct DecodeParams {
   // head-pair plan (fp8 KV on the tcgen05 kernel): Segment::kv_head counts PAIRS of adjacent KV heads,
   // group_size is twice the real GQA group (the query heads of both), tiles are 64 tokens
   int32_t head_pairs;
+  // multi-row units (run(q_len_per_req = n), 16-bit KV): q / o hold q_rows consecutive rows per request
+  // and num_qo_heads = q_rows x the model's query heads; q_group = the model's GQA group; the unit's
+  // group_size columns are (row, head) pairs (decode_kernel.cuh row_head).  q_rows <= 1: off
+  int32_t q_rows, q_group;
   // attention sinks (reference decode.py:1176, tests/test_helpers/sink_attention_reference.py:23-36):
   // one extra logit per query head that takes part in the softmax denominator only —
   // p_i = exp(s_i) / (sum_j exp(s_j) + exp(sink[head])); natural-log units, not scaled by sm_scale.

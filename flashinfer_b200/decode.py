@@ -232,6 +232,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._pdl_default = int(device_support_pdl(self.device))
         self._head_pairs_ok = True   # cleared when a run() had to fall back (FI_ERR_REPLAN)
         self._ran_once = False       # step(): the run argument block holds a complete run()
+        self._q_rows = 1             # > 1: a multi-token child whose rows share the KV stream (q_rows)
         self._run_kw = (None, None, None, None, None)
         self._plan_call = None
         self._mtp_children = {}
@@ -474,7 +475,30 @@ class BatchDecodeWithPagedKVCacheWrapper:
             self._mtp_children[q_len_per_req] = child
         return child.run(q, paged_kv_cache, **run_kw)
 
+    def _mtp_rows_share_the_stream(self) -> bool:
+        """Multi-token decode as multi-row units (FiDecodeRunArgs.q_rows): the n rows of a request ride
+        its KV stream as extra columns of the GQA group instead of re-reading it once per row — 16-bit
+        KV without ROPE_LLAMA / sliding window (the rest takes one decode request per row)."""
+        kv_dt = self._mtp_src[6]
+        return (kv_dt in (torch.float16, torch.bfloat16) and self._pos_encoding_mode != "ROPE_LLAMA"
+                and self._window_left < 0 and self._mtp_src[3] != 512
+                and os.environ.get("FI_B200_MTP_ROWS", "1") != "0")
+
     def _make_mtp_child(self, n: int) -> "BatchDecodeWithPagedKVCacheWrapper":
+        if self._mtp_rows_share_the_stream():
+            if not self._use_cuda_graph:
+                child = BatchDecodeWithPagedKVCacheWrapper(
+                    self._float_workspace_buffer, self._kv_layout, use_tensor_cores=self.use_tensor_cores)
+            else:  # the request's own table: the parent's capacities
+                bs, dev = self._fixed_batch_size, self.device
+                child = BatchDecodeWithPagedKVCacheWrapper(
+                    self._float_workspace_buffer, self._kv_layout, use_cuda_graph=True,
+                    use_tensor_cores=self.use_tensor_cores,
+                    paged_kv_indptr_buffer=torch.zeros(bs + 1, dtype=torch.int32, device=dev),
+                    paged_kv_indices_buffer=torch.zeros(max(len(self._indices_dev), 1), dtype=torch.int32, device=dev),
+                    paged_kv_last_page_len_buffer=torch.zeros(bs, dtype=torch.int32, device=dev))
+            child._q_rows = n
+            return child
         if not self._use_cuda_graph:
             return BatchDecodeWithPagedKVCacheWrapper(
                 self._float_workspace_buffer, self._kv_layout, use_tensor_cores=self.use_tensor_cores)
@@ -493,6 +517,13 @@ class BatchDecodeWithPagedKVCacheWrapper:
         from .cascade import rows_as_decode_requests
 
         (indptr, indices, last_page_len, head_dim, page_size, q_dt, kv_dt, fss, dskv) = self._mtp_src
+        if child._q_rows > 1:  # n x the query heads on the request's own page table
+            child.plan(indptr, indices, last_page_len, n * self._num_qo_heads, self._num_kv_heads, head_dim,
+                       page_size, pos_encoding_mode=self._pos_encoding_mode, window_left=self._window_left,
+                       logits_soft_cap=self._logits_soft_cap, q_data_type=q_dt, kv_data_type=kv_dt,
+                       sm_scale=self._sm_scale, rope_scale=self._rope_scale, rope_theta=self._rope_theta,
+                       fixed_split_size=fss, disable_split_kv=dskv)
+            return
         qo_indptr = torch.arange(self._batch_size + 1, dtype=torch.int32) * n
         r_indptr, r_indices, r_last = rows_as_decode_requests(
             qo_indptr, indptr, indices, last_page_len, page_size, causal=True)
@@ -639,7 +670,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
             raise RuntimeError("plan() must be called before run()")
         if sinks is not None:
             # one extra logit per query head in the softmax denominator (reference decode.py:1176)
-            if sinks.dim() != 1 or sinks.shape[0] != self._num_qo_heads or sinks.device != q.device:
+            if sinks.dim() != 1 or sinks.shape[0] != self._num_qo_heads // self._q_rows or sinks.device != q.device:
                 raise ValueError("sinks must be a [num_qo_heads] tensor on q's device")
             sinks = sinks.to(torch.float32).contiguous()
         if q_len_per_req not in (None, 1):
@@ -660,10 +691,12 @@ class BatchDecodeWithPagedKVCacheWrapper:
                 "specified in plan function.")
         qs = q.stride()
         if q.shape != self._q_shape:
-            raise ValueError(
-                f"q must have shape [{self._batch_size}, {self._num_qo_heads}, {self._head_dim}], "
-                f"got {list(q.shape)}"
-            )
+            rows = self._q_rows  # a multi-token child: [batch * rows, Hq, D] against a plan of rows * Hq heads
+            if rows == 1 or q.shape != (self._batch_size * rows, self._num_qo_heads // rows, self._head_dim):
+                raise ValueError(
+                    f"q must have shape [{self._batch_size * rows}, {self._num_qo_heads // rows}, {self._head_dim}], "
+                    f"got {list(q.shape)}"
+                )
         if qs[2] != 1:
             raise ValueError("the last dimension of q / k / v must be contiguous")
         dev = q.device
@@ -725,6 +758,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         ra.logits_soft_cap = logits_soft_cap if logits_soft_cap is not None else 0.0
         ra.sinks = sinks.data_ptr() if sinks is not None else None
         ra.enable_pdl = self._pdl_default if enable_pdl is None else int(bool(enable_pdl))
+        ra.q_rows = self._q_rows
         ra.stream = current_stream_ptr(dev)
         rc = self._lib.fi_batch_decode_run_args(self._ra_ref)
         if rc:

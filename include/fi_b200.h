@@ -221,6 +221,15 @@ typedef struct FiDecodeRunArgs {
   const float* sinks;
   int32_t enable_pdl, device;
   void* stream;
+  /* Multi-token decode (argument-block form only; <= 1: one query row per request).  q / o hold
+   * q_rows consecutive rows per request ([batch * q_rows, Hq, D], q_stride_n = the row stride; lse
+   * [batch * q_rows, Hq]); row r of a request attends all but the last q_rows - 1 - r tokens of its
+   * cache (causal among the new tokens, whose K / V the cache already holds).  The plan must have
+   * been made with num_qo_heads = q_rows * Hq on the request's own page table: the rows then share
+   * one KV stream as extra columns of the GQA group instead of re-reading it once per row.
+   * 16-bit KV, NONE / ALIBI, no sliding window; anything else returns FI_ERR_UNSUPPORTED.  Reference:
+   * q_len_per_req of BatchDecodeWithPagedKVCacheWrapper.run (flashinfer/decode.py:1177,1278). */
+  int32_t q_rows, reserved_;
 } FiDecodeRunArgs;
 FI_API int fi_batch_decode_run_args(const FiDecodeRunArgs* a);
 /*

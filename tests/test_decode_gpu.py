@@ -561,6 +561,60 @@ def test_multi_token_decode_q_len_per_req(q_len_per_req, kv_dtype, pos_mode):
         w.run(q[:-1].to(DEV), cache.to(DEV), q_len_per_req=n)
 
 
+@pytest.mark.parametrize("n", [2, 3, 4, 8])
+@pytest.mark.parametrize("hq,hkv", [(8, 8), (8, 4), (16, 4), (32, 4), (24, 2)])
+@pytest.mark.parametrize("d,page,layout", [(128, 16, "NHD"), (128, 1, "NHD"), (64, 16, "HND"), (256, 8, "NHD")])
+@pytest.mark.parametrize("variant", ["plain", "alibi+cap", "sinks"])
+def test_multi_token_rows_share_the_kv_stream(n, hq, hkv, d, page, layout, variant):
+    """run(q_len_per_req = n) with 16-bit KV: the n rows of a request are extra columns of its GQA group
+    (FiDecodeRunArgs.q_rows; plan with n x the query heads on the request's own table) — every (row, head)
+    against the oracle on the row's causal prefix, for groups 1 .. 12 (virtual KV heads above 8 columns),
+    both loaders, split units, empty rows (kv_len < n), ALiBi + soft cap, sinks; the per-row-request path
+    (FI_B200_MTP_ROWS=0) gives the same."""
+    import os
+
+    from flashinfer_b200.utils import get_alibi_slopes
+
+    fi = _fi()
+    lens = [5, 97, 3000, 2, 64, 1, 7000]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, layout, torch.float32, seed=141)
+    cache = cache.to(torch.float16)
+    q = make_q(len(lens) * n, hq, d, torch.float16, seed=142)
+    kw, okw, rkw = {}, {}, {}
+    if variant == "alibi+cap":
+        kw = dict(pos_encoding_mode="ALIBI", logits_soft_cap=30.0)
+        okw = dict(alibi_slopes=get_alibi_slopes(hq), logits_soft_cap=30.0)
+    elif variant == "sinks":
+        rkw = dict(sinks=torch.linspace(-1.0, 2.0, hq, device=DEV))
+        okw = dict(sinks=rkw["sinks"].cpu())
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, kv_data_type=cache.dtype, **kw)
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True, q_len_per_req=n, **rkw)
+    assert w._mtp_children[n]._q_rows == n and o.shape == q.shape and lse.shape == (len(lens) * n, hq)
+    torch.cuda.synchronize()
+    k4, v4 = orc.unpack_cache(cache, layout)
+    for b, L in enumerate(lens):
+        k, v = orc.gather_paged_kv(k4, v4, indptr, indices, last, b, layout)
+        for t in range(n):
+            Lt = max(L - (n - 1 - t), 0)
+            o_ref, lse_ref = orc.decode_attention_ref(q[b * n + t], k[:Lt].float(), v[:Lt].float(), **okw)
+            assert (o[b * n + t].float().cpu() - o_ref).abs().max().item() <= O_TOL, (b, t)
+            if variant == "alibi+cap":
+                assert _alibi_lse_ok(lse[b * n + t].cpu(), lse_ref)
+            elif Lt > 0 or variant != "sinks":
+                assert (lse[b * n + t].cpu() - lse_ref).abs().max().item() <= LSE_TOL, (b, t)
+    if variant == "plain" and n in (2, 4):
+        os.environ["FI_B200_MTP_ROWS"] = "0"
+        try:
+            w2 = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+            w2.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, kv_data_type=cache.dtype)
+            o2 = w2.run(q.to(DEV), cache.to(DEV), q_len_per_req=n)
+            assert w2._mtp_children[n]._q_rows == 1
+        finally:
+            del os.environ["FI_B200_MTP_ROWS"]
+        assert (o2.float() - o.float()).abs().max().item() <= 4e-3
+
+
 @pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
 @pytest.mark.parametrize("layout", ["NHD", "HND"])
 @pytest.mark.parametrize("pos_mode", ["NONE", "ROPE_LLAMA"])
