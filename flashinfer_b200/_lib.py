@@ -54,7 +54,7 @@ class DecodeRunArgs(C.Structure):
                 ("kv_stride_h", _i64), ("kv_indices", _vp), ("kv_indptr", _vp), ("o", _vp), ("lse", _vp),
                 ("sm_scale", _f), ("v_scale", _f), ("logits_soft_cap", _f), ("pos_encoding_mode", _i32),
                 ("alibi_slopes", _vp), ("rope_scale", _f), ("rope_theta", _f), ("sinks", _vp),
-                ("enable_pdl", _i32), ("device", _i32), ("stream", _vp), ("q_rows", _i32), ("reserved_", _i32)]
+                ("enable_pdl", _i32), ("device", _i32), ("stream", _vp), ("q_rows", _i32), ("q_rows_noncausal", _i32)]
 
 
 # name -> (restype, argtypes); must list every symbol include/fi_b200.h declares

@@ -7,12 +7,13 @@ A state is (v, s): v the normalised partial attention output, s its log-sum-exp 
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
 
 from . import _lib
-from .utils import current_stream_ptr, device_index, dtype_code
+from .utils import canonicalize_torch_dtype, current_stream_ptr, device_index, dtype_code
 
 
 def _check_vs(v: torch.Tensor, s: torch.Tensor, name: str) -> None:
@@ -294,13 +295,30 @@ class MultiLevelCascadeAttentionWrapper:
                 self._batch_decode_wrappers, qo_indptr_arr, paged_kv_indptr_arr,
                 paged_kv_indices_arr, paged_kv_last_page_len)):
             level_causal = causal if i == self._num_levels - 1 else False
-            indptr, indices, last = rows_as_decode_requests(qo, kvp, kvi, lpl, page_size, level_causal)
+            rows = self._uniform_rows(qo)
+            kv_dt = canonicalize_torch_dtype(kv_data_type if kv_data_type is not None else q_data_type)
+            level_rows = int(qo[-1])
             if num_rows is None:
-                num_rows = indptr.numel() - 1
-            elif num_rows != indptr.numel() - 1:
+                num_rows = level_rows
+            elif num_rows != level_rows:
                 raise ValueError("the last element of every qo_indptr must be the total number of queries")
+            if (rows > 1 and not self._use_cuda_graph and window_left < 0 and head_dim != 512
+                    and kv_dt in (torch.float16, torch.bfloat16) and os.environ.get("FI_B200_MTP_ROWS", "1") != "0"):
+                # every group of the level has `rows` query rows: they share the group's KV stream as extra
+                # columns of the GQA group (FiDecodeRunArgs.q_rows) instead of one decode request per row
+                wrapper._q_rows, wrapper._q_rows_noncausal = rows, int(not level_causal)
+                wrapper.plan(
+                    kvp, kvi, lpl, rows * num_qo_heads, num_kv_heads, head_dim, page_size,
+                    pos_encoding_mode="NONE", window_left=window_left, logits_soft_cap=logits_soft_cap,
+                    q_data_type=q_data_type, kv_data_type=kv_data_type, sm_scale=sm_scale,
+                    rope_scale=rope_scale, rope_theta=rope_theta,
+                )
+                continue
+            indptr, indices, last = rows_as_decode_requests(qo, kvp, kvi, lpl, page_size, level_causal)
             if self._use_cuda_graph:
                 wrapper = self._graph_level_wrapper(i, num_rows, indices)
+            else:
+                wrapper._q_rows, wrapper._q_rows_noncausal = 1, 0
             wrapper.plan(
                 indptr, indices, last, num_qo_heads, num_kv_heads, head_dim, page_size,
                 pos_encoding_mode="NONE", window_left=window_left, logits_soft_cap=logits_soft_cap,
@@ -310,6 +328,16 @@ class MultiLevelCascadeAttentionWrapper:
         self._num_rows = num_rows
 
     begin_forward = plan
+
+    @staticmethod
+    def _uniform_rows(qo_indptr) -> int:
+        """Query rows per group when every group of the level has the same number (else 0)."""
+        qo = qo_indptr.detach().cpu()
+        if qo.numel() < 2:
+            return 0
+        d = qo[1:] - qo[:-1]
+        n = int(d[0])
+        return n if n > 0 and bool((d == n).all()) else 0
 
     def _graph_level_wrapper(self, level: int, num_rows: int, indices: torch.Tensor):
         """CUDA-graph mode: level `level`'s decode wrapper with fixed buffers for `num_rows` per-row

@@ -400,7 +400,8 @@ static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* pl
                                  const int32_t* kv_indptr, void* o, float* lse, float sm_scale,
                                  float v_scale, float logits_soft_cap, int pos_encoding_mode,
                                  const float* alibi_slopes, float rope_scale, float rope_theta,
-                                 const float* sinks, int enable_pdl, int device, void* stream_, int q_rows) {
+                                 const float* sinks, int enable_pdl, int device, void* stream_, int q_rows,
+                                 int q_rows_noncausal = 0) {
   if (int rc = check_pos_mode(pos_encoding_mode, alibi_slopes, rope_scale, rope_theta)) return rc;
   if (plan_info == nullptr || plan_info[kPiMagic] != kPlanMagic)
     return fail(FI_ERR_INVALID_ARGUMENT, "plan info is not initialized");
@@ -484,6 +485,7 @@ static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* pl
       return fail(FI_ERR_UNSUPPORTED, "q_rows > 1 needs 16-bit KV, no ROPE_LLAMA, no sliding window, the fused "
                                       "merge and a plan made with num_qo_heads = q_rows x query heads");
     p.q_rows = q_rows;
+    p.q_rows_noncausal = q_rows_noncausal != 0;
     p.q_group = (Hq / q_rows) / Hkv_mem;
   }
 
@@ -571,7 +573,7 @@ int fi_batch_decode_run_args(const FiDecodeRunArgs* a) {
                                a->kv_stride_h, a->kv_indices, a->kv_indptr, a->o, a->lse, a->sm_scale,
                                a->v_scale, a->logits_soft_cap, a->pos_encoding_mode, a->alibi_slopes,
                                a->rope_scale, a->rope_theta, a->sinks, a->enable_pdl, a->device, a->stream,
-                               a->q_rows > 1 ? a->q_rows : 1);
+                               a->q_rows > 1 ? a->q_rows : 1, a->q_rows_noncausal);
 }
 
 int fi_batch_decode_step(const FiDecodePlanArgs* plan, const FiDecodeRunArgs* run) {

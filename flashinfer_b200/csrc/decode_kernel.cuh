@@ -1110,8 +1110,10 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
         const RowHead rh = row_head(p, sg.kv_head, g);
         qrow = static_cast<const char*>(p.q) +
                (rh.token(p, sg.request) * p.q_stride_n + (int64_t)rh.head * p.q_stride_h) * 2;
-        hid[0] = p.q_rows - 1 - row_head(p, sg.kv_head, 2 * t).row;
-        hid[1] = p.q_rows - 1 - row_head(p, sg.kv_head, 2 * t + 1).row;
+        if (!p.q_rows_noncausal) {
+          hid[0] = p.q_rows - 1 - row_head(p, sg.kv_head, 2 * t).row;
+          hid[1] = p.q_rows - 1 - row_head(p, sg.kv_head, 2 * t + 1).row;
+        }
       }
       if constexpr (KVF == 0) {
         if (have_qn) {

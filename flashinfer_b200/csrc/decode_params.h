@@ -193,6 +193,7 @@ struct DecodeParams {
   // and num_qo_heads = q_rows x the model's query heads; q_group = the model's GQA group; the unit's
   // group_size columns are (row, head) pairs (decode_kernel.cuh row_head).  q_rows <= 1: off
   int32_t q_rows, q_group;
+  int32_t q_rows_noncausal;  // 1: no causal mask among the rows (cascade attention's shared levels)
   // attention sinks (reference decode.py:1176, tests/test_helpers/sink_attention_reference.py:23-36):
   // one extra logit per query head that takes part in the softmax denominator only —
   // p_i = exp(s_i) / (sum_j exp(s_j) + exp(sink[head])); natural-log units, not scaled by sm_scale.

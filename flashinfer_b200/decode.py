@@ -233,6 +233,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         self._head_pairs_ok = True   # cleared when a run() had to fall back (FI_ERR_REPLAN)
         self._ran_once = False       # step(): the run argument block holds a complete run()
         self._q_rows = 1             # > 1: a multi-token child whose rows share the KV stream (q_rows)
+        self._q_rows_noncausal = 0   # cascade levels below the last: no mask among the rows
         self._run_kw = (None, None, None, None, None)
         self._plan_call = None
         self._mtp_children = {}
@@ -759,6 +760,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         ra.sinks = sinks.data_ptr() if sinks is not None else None
         ra.enable_pdl = self._pdl_default if enable_pdl is None else int(bool(enable_pdl))
         ra.q_rows = self._q_rows
+        ra.q_rows_noncausal = self._q_rows_noncausal
         ra.stream = current_stream_ptr(dev)
         rc = self._lib.fi_batch_decode_run_args(self._ra_ref)
         if rc:

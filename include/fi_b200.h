@@ -228,8 +228,10 @@ typedef struct FiDecodeRunArgs {
    * been made with num_qo_heads = q_rows * Hq on the request's own page table: the rows then share
    * one KV stream as extra columns of the GQA group instead of re-reading it once per row.
    * 16-bit KV, NONE / ALIBI, no sliding window; anything else returns FI_ERR_UNSUPPORTED.  Reference:
-   * q_len_per_req of BatchDecodeWithPagedKVCacheWrapper.run (flashinfer/decode.py:1177,1278). */
-  int32_t q_rows, reserved_;
+   * q_len_per_req of BatchDecodeWithPagedKVCacheWrapper.run (flashinfer/decode.py:1177,1278).
+   * q_rows_noncausal = 1: every row sees the whole cache (the shared levels of cascade attention,
+   * flashinfer/cascade.py:498-543: the rows of a group attend the group's pages without a mask). */
+  int32_t q_rows, q_rows_noncausal;
 } FiDecodeRunArgs;
 FI_API int fi_batch_decode_run_args(const FiDecodeRunArgs* a);
 /*
