@@ -445,14 +445,26 @@ class BatchDecodeWithSharedPrefixPagedKVCacheWrapper:
         if key == self._shared_key:
             return
         num_qo_heads, num_kv_heads, head_dim = self._shape
-        indptr = torch.arange(batch_size + 1, dtype=torch.int32) * pages
-        indices = torch.arange(pages, dtype=torch.int32).repeat(batch_size)
-        last = torch.full((batch_size,), page if pages else 0, dtype=torch.int32)
-        self._shared_wrapper.plan(
-            indptr, indices, last, num_qo_heads, num_kv_heads, head_dim, page,
-            pos_encoding_mode="NONE", q_data_type=q_dtype, kv_data_type=kv_dtype,
-            sm_scale=self._batch_decode_wrapper._sm_scale,
-        )
+        w = self._shared_wrapper
+        if (batch_size > 1 and kv_dtype in (torch.float16, torch.bfloat16) and head_dim != 512
+                and os.environ.get("FI_B200_MTP_ROWS", "1") != "0"):
+            # ONE request over the shared pages whose query rows are the batch (FiDecodeRunArgs.q_rows,
+            # no mask among the rows): the prefix is streamed once per 8 (row, head) columns, not per request
+            w._q_rows, w._q_rows_noncausal = batch_size, 1
+            w.plan(torch.tensor([0, pages], dtype=torch.int32), torch.arange(pages, dtype=torch.int32),
+                   torch.tensor([page if pages else 0], dtype=torch.int32), batch_size * num_qo_heads,
+                   num_kv_heads, head_dim, page, pos_encoding_mode="NONE", q_data_type=q_dtype,
+                   kv_data_type=kv_dtype, sm_scale=self._batch_decode_wrapper._sm_scale)
+        else:
+            w._q_rows, w._q_rows_noncausal = 1, 0
+            indptr = torch.arange(batch_size + 1, dtype=torch.int32) * pages
+            indices = torch.arange(pages, dtype=torch.int32).repeat(batch_size)
+            last = torch.full((batch_size,), page if pages else 0, dtype=torch.int32)
+            w.plan(
+                indptr, indices, last, num_qo_heads, num_kv_heads, head_dim, page,
+                pos_encoding_mode="NONE", q_data_type=q_dtype, kv_data_type=kv_dtype,
+                sm_scale=self._batch_decode_wrapper._sm_scale,
+            )
         self._shared_key = key
 
     def forward(self, q: torch.Tensor, k_shared: torch.Tensor, v_shared: torch.Tensor,
