@@ -25,6 +25,7 @@ FI_ERR_CUDA = 3
 FI_ERR_UNSUPPORTED = 4
 FI_ERR_REPLAN = 5
 PLAN_HEAD_PAIRS = 1
+PLAN_WIDE_UNITS = 2
 
 DTYPE_F16, DTYPE_BF16, DTYPE_E4M3, DTYPE_E5M2, DTYPE_F32 = 0, 1, 2, 3, 4
 LAYOUT_NHD, LAYOUT_HND = 0, 1

@@ -175,7 +175,7 @@ static cudaError_t ensure_smem_attr(K kern, int smem) {
   return e;
 }
 
-template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, bool MROWS = false>
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, int MROWS = 0>
 static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                       int grid, cudaStream_t stream) {
   auto kern = paged_decode_kernel<QT, KVF, HD, LOADER, ROPE, MROWS>;
@@ -199,9 +199,15 @@ template <int QT, int KVF, int HD>
 static int launch_loader(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                          int grid, bool tma, cudaStream_t stream) {
   if constexpr (KVF == 0) {
+    if (p.q_rows > 1 && p.group_size > kMaxGroup) {  // wide units: two N tiles per warp (TMA loader, D <= 128)
+      if constexpr (HD <= 128) {
+        if (tma) return launch_one<QT, KVF, HD, 0, false, 2>(p, km, vm, grid, stream);
+      }
+      return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_WIDE_UNITS, but this run() needs the gather loader");
+    }
     if (p.q_rows > 1)  // multi-row units (fi_batch_decode_run_args q_rows): checked by the caller
-      return tma ? launch_one<QT, KVF, HD, 0, false, true>(p, km, vm, grid, stream)
-                 : launch_one<QT, KVF, HD, 1, false, true>(p, km, vm, grid, stream);
+      return tma ? launch_one<QT, KVF, HD, 0, false, 1>(p, km, vm, grid, stream)
+                 : launch_one<QT, KVF, HD, 1, false, 1>(p, km, vm, grid, stream);
     // ROPE_LLAMA on 16-bit KV: K rotated in registers (decode_kernel.cuh)
     if (p.rope)
       return tma ? launch_one<QT, KVF, HD, 0, true>(p, km, vm, grid, stream)
@@ -477,6 +483,8 @@ static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* pl
   // the L2 full of DIRTY lines (a 256 MB memset right before it) is slower (C2 +4 %, C4 +10 %).
   p.l2_hints = default_l2_hints();
   p.sinks = sinks;
+  if (q_rows <= 1 && !p.head_pairs && p.group_size > kMaxGroup)
+    return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_WIDE_UNITS: it needs q_rows > 1");
   if (q_rows > 1) {
     // multi-row units: the plan was made with num_qo_heads = q_rows x the model's query heads
     const int Hkv_mem = Hkv / p.kv_head_div;

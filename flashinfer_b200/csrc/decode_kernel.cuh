@@ -1438,6 +1438,274 @@ __device__ __forceinline__ void consume(const DecodeParams& p, const SegSource& 
   FI_TRACE_IF(threadIdx.x == 0, 8);
 }
 
+// ---- consumer for multi-row units of up to 16 (row, head) columns: TWO N tiles per warp ----------
+// (FI_PLAN_WIDE_UNITS plans, 16-bit KV, TMA loader.)  The warp's 16 tokens meet both 8-column tiles per
+// ldmatrix: one K fragment feeds two Q.K MMAs, one V fragment two P.V MMAs, so 16 columns cost the KV
+// stream once.  A separate function on purpose: the single-tile consumer above is the headline kernel
+// and must not move by a register.  Structure and epilogue as in consume(); no query prefetch across
+// segments (its fragments would hold 32 more registers).
+template <int QT, int HD, int LOADER>
+__device__ __forceinline__ void consume_rows2(const DecodeParams& p, const SegSource& src, uint32_t ring,
+                                              uint32_t full_bar, uint32_t empty_bar, float* scratch_o,
+                                              float* scratch_ml) {
+  using G = TileGeom<0, HD>;
+  constexpr bool BF = (QT == 1);
+  constexpr int MT = HD / 16, KS = HD / 16, TPW = G::TPW, NT = 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int GS = p.group_size;  // 9 .. 16 columns
+  const bool use_cap = p.soft_cap > 0.f;
+  const float cap_pre = use_cap ? p.sm_scale / p.soft_cap : 0.f;
+  const float cap_post = use_cap ? p.soft_cap * 1.4426950408889634f : 0.f;
+  const int row0 = warp * TPW;
+  const int rpb = LOADER == 0 ? p.rows_per_box : G::TT;
+  const int rmask = ~(rpb - 1);
+  const uint32_t vdelta = (uint32_t)rpb * 128u;
+  const int hq_real = p.num_qo_heads / p.q_rows;
+
+  int stage = 0;
+  uint32_t phase = 0;
+  PendingMerge pm;
+  pm.mu = -1; pm.old = pm.cnt = pm.slot = pm.req = pm.head = 0;
+  for (int k = 0;; ++k) {
+    Segment sg;
+    if (!seg_fetch(src, k, sg)) break;
+    uint32_t qf[NT][KS][2];
+    int hid[NT][2];
+    float alc[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int col = 8 * nt + g;
+      const RowHead rh = row_head(p, sg.kv_head, col);
+      const char* qrow = static_cast<const char*>(p.q) +
+                         (rh.token(p, sg.request) * p.q_stride_n + (int64_t)rh.head * p.q_stride_h) * 2;
+      load_q_frags16<HD>(qf[nt], qrow, col < GS, t);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int c = 8 * nt + 2 * t + j;
+        const RowHead rc = row_head(p, sg.kv_head, c);
+        hid[nt][j] = p.q_rows_noncausal ? 0 : p.q_rows - 1 - rc.row;
+        alc[nt][j] = 0.f;
+        if (p.alibi_slopes != nullptr && c < GS)
+          alc[nt][j] = __ldg(p.alibi_slopes + rc.head) * (use_cap ? cap_pre : 1.4426950408889634f);
+      }
+    }
+    const float mul = p.sm_scale_log2;
+    const float pre = p.alibi_slopes != nullptr ? cap_pre * p.sm_scale : cap_pre;
+    float o[NT][MT][4];
+    float m[NT][2], l[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+      for (int i = 0; i < MT; ++i) o[nt][i][0] = o[nt][i][1] = o[nt][i][2] = o[nt][i][3] = 0.f;
+      m[nt][0] = m[nt][1] = kNegInf;
+      l[nt][0] = l[nt][1] = 0.f;
+    }
+
+    for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
+      mbar_wait(full_bar + 8 * stage, phase);
+      const int tok0 = tile * G::TT + row0;
+      const int vcount = min(TPW, sg.tok_hi - tok0);
+      if (vcount > 0 && tok0 + TPW > sg.tok_lo) {  // warp-uniform
+        const uint32_t kbase = ring + stage * G::STAGE_BYTES;
+        const uint32_t vbase = kbase + vdelta;
+        if constexpr (LOADER == 0) {
+          if (vcount < TPW) {  // rows the TMA did not (validly) fill: zero V so 0 * junk != NaN
+            for (int i = lane; i < (TPW - vcount) * G::CHUNKS; i += 32) {
+              const int row = row0 + vcount + i / G::CHUNKS;
+              const uint32_t a = vbase + StageRow<G::TT>(row, rmask).at(i % G::CHUNKS);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(a), "r"(0u) : "memory");
+            }
+            __syncwarp();
+          }
+        }
+        // S^T (16 tokens x 16 columns): one K fragment per k-step, two MMAs
+        float s[NT][4];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        {
+          const int kch = lane >> 4;
+          const StageRow<64> kr(row0 + (lane & 7) + 8 * ((lane >> 3) & 1), rmask);
+#pragma unroll
+          for (int ks = 0; ks < KS; ++ks) {
+            uint32_t a[4];
+            ldmatrix_x4(a, kbase + kr.at(2 * ks + kch));
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) mma_16816<BF>(s[nt], a, qf[nt][ks][0], qf[nt][ks][1]);
+          }
+        }
+        const int ta = tok0 + g, tb = ta + 8;
+        const bool va = ta >= sg.tok_lo, vb = tb >= sg.tok_lo;
+        const float pf[2] = {(float)ta, (float)tb};
+        uint32_t pb[NT][2];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+          bool vc[4];
+          vc[0] = va && ta < sg.tok_hi - hid[nt][0]; vc[1] = va && ta < sg.tok_hi - hid[nt][1];
+          vc[2] = vb && tb < sg.tok_hi - hid[nt][0]; vc[3] = vb && tb < sg.tok_hi - hid[nt][1];
+          float x[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float v = use_cap ? cap_post * tanhf_approx(s[nt][i] * pre + alc[nt][i & 1] * pf[i >> 1])
+                                    : s[nt][i] * mul + alc[nt][i & 1] * pf[i >> 1];
+            x[i] = vc[i] ? v : kNegInf;
+          }
+          float mx[2] = {fmaxf(x[0], x[2]), fmaxf(x[1], x[3])};
+          float sc[2];
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 4));
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 8));
+            mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 16));
+            const float mn = fmaxf(m[nt][j], mx[j]);
+            sc[j] = ex2f(m[nt][j] - mn);
+            m[nt][j] = mn;
+          }
+          float pr[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) pr[i] = vc[i] ? ex2f(x[i] - m[nt][i & 1]) : 0.f;
+          l[nt][0] = l[nt][0] * sc[0] + pr[0] + pr[2];
+          l[nt][1] = l[nt][1] * sc[1] + pr[1] + pr[3];
+#pragma unroll
+          for (int i = 0; i < MT; ++i) {
+            o[nt][i][0] *= sc[0]; o[nt][i][1] *= sc[1]; o[nt][i][2] *= sc[0]; o[nt][i][3] *= sc[1];
+          }
+          pb[nt][0] = movmatrix_trans(pack2<BF>(pr[0], pr[1]));
+          pb[nt][1] = movmatrix_trans(pack2<BF>(pr[2], pr[3]));
+        }
+        {  // O^T += V^T . P^T: one V fragment per 16 output dims, two MMAs
+          const int vch = (lane >> 3) & 1;
+          const StageRow<64> vr(row0 + (lane & 7) + 8 * (lane >> 4), rmask);
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            uint32_t a[4];
+            ldmatrix_x4_trans(a, vbase + vr.at(2 * mt + vch));
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) mma_16816<BF>(o[nt][mt], a, pb[nt][0], pb[nt][1]);
+          }
+        }
+        if constexpr (LOADER == 0) {
+          if (vcount < TPW) fence_proxy_async_smem();  // generic zero-fill before next TMA write
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_bar + 8 * stage);
+      if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+    }
+
+    // ---- segment epilogue: 4 warp states -> one (o, lse) per column; 16 columns in scratch_ml ----
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        l[nt][j] += __shfl_xor_sync(0xffffffffu, l[nt][j], 4);
+        l[nt][j] += __shfl_xor_sync(0xffffffffu, l[nt][j], 8);
+        l[nt][j] += __shfl_xor_sync(0xffffffffu, l[nt][j], 16);
+      }
+    if (g == 0) {
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          scratch_ml[(warp * 16 + 8 * nt + 2 * t + j) * 2 + 0] = m[nt][j];
+          scratch_ml[(warp * 16 + 8 * nt + 2 * t + j) * 2 + 1] = l[nt][j];
+        }
+    }
+    if (threadIdx.x == 0) merge_post(p, pm, scratch_ml);  // arrival of the previous partial
+    named_bar_sync(1, kConsumerWarps * 32);
+    if (threadIdx.x == 0) src.ctl[kQDone0] = k + 1;
+    merge_run_posted<QT, HD, true>(p, scratch_ml, threadIdx.x);
+    float M[NT][2], L[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int c = 8 * nt + 2 * t + j;
+        float mm = kNegInf;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) mm = fmaxf(mm, scratch_ml[(w * 16 + c) * 2]);
+        float ll = 0.f;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w)
+          ll += scratch_ml[(w * 16 + c) * 2 + 1] * ex2f(scratch_ml[(w * 16 + c) * 2] - mm);
+        M[nt][j] = mm; L[nt][j] = ll;
+        const float f = ex2f(m[nt][j] - mm);
+#pragma unroll
+        for (int i = 0; i < MT; ++i) { o[nt][i][j] *= f; o[nt][i][2 + j] *= f; }
+      }
+    const bool direct = sg.slot < 0;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {  // the cross-warp sum of o goes through scratch_o one N tile at a time
+      if (warp != 0) {
+        float* dst = scratch_o + (warp - 1) * (MT * 4 * 32) + lane;
+#pragma unroll
+        for (int i = 0; i < MT; ++i)
+#pragma unroll
+          for (int r = 0; r < 4; ++r) dst[(i * 4 + r) * 32] = o[nt][i][r];
+      }
+      named_bar_sync(2, kConsumerWarps * 32);
+      if (warp == 0) {
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps - 1; ++w) {
+          const float* s2 = scratch_o + w * (MT * 4 * 32) + lane;
+#pragma unroll
+          for (int i = 0; i < MT; ++i)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) o[nt][i][r] += s2[(i * 4 + r) * 32];
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int c = 8 * nt + 2 * t + j;
+          if (c < GS) {
+            const RowHead rh = row_head(p, sg.kv_head, c);
+            float Lc = L[nt][j];
+            const bool any = Lc > 0.f;
+            if (direct && any && p.sinks != nullptr)
+              Lc += ex2f(__ldg(p.sinks + rh.head) * 1.4426950408889634f - M[nt][j]);
+            const float inv = any ? (direct ? p.v_scale : 1.f) / Lc : 0.f;
+            const float lse2 = any ? M[nt][j] + lg2f(Lc) : kNegInf;
+            if (direct) {
+              const int64_t oh = rh.token(p, sg.request) * hq_real + rh.head;
+              if (QT == 1) {
+                __nv_bfloat16* orow = static_cast<__nv_bfloat16*>(p.o) + oh * HD;
+#pragma unroll
+                for (int i = 0; i < MT; ++i) {
+                  orow[o_dim<0>(i, 0, g)] = __float2bfloat16_rn(o[nt][i][j] * inv);
+                  orow[o_dim<0>(i, 1, g)] = __float2bfloat16_rn(o[nt][i][2 + j] * inv);
+                }
+              } else {
+                __half* orow = static_cast<__half*>(p.o) + oh * HD;
+#pragma unroll
+                for (int i = 0; i < MT; ++i) {
+                  orow[o_dim<0>(i, 0, g)] = __float2half_rn(o[nt][i][j] * inv);
+                  orow[o_dim<0>(i, 1, g)] = __float2half_rn(o[nt][i][2 + j] * inv);
+                }
+              }
+              if (p.lse != nullptr && g == 0) p.lse[oh] = lse2;
+            } else {
+              float* orow = p.tmp_o + ((int64_t)sg.slot * GS + c) * HD;
+#pragma unroll
+              for (int i = 0; i < MT; ++i) {
+                orow[o_dim<0>(i, 0, g)] = o[nt][i][j] * inv;
+                orow[o_dim<0>(i, 1, g)] = o[nt][i][2 + j] * inv;
+              }
+              if (g == 0) p.tmp_lse[(int64_t)sg.slot * GS + c] = lse2;
+            }
+          }
+        }
+      }
+      named_bar_sync(2, kConsumerWarps * 32);  // scratch_o is free for the next N tile / segment
+    }
+    if (warp == 0 && !direct && sg.merge_unit >= 0) {  // publish the partial: count the arrival, look later
+      __syncwarp();
+      if (lane == 0) merge_arrive(p, pm, sg);
+    }
+  }
+  if (threadIdx.x == 0) merge_post(p, pm, scratch_ml);
+  named_bar_sync(1, kConsumerWarps * 32);
+  merge_run_posted<QT, HD, true>(p, scratch_ml, threadIdx.x);
+}
+
 // threads per CTA: 4 consumer warps + 1 (TMA) or 4 (cp.async) producer warps
 template <int LOADER>
 struct BlockDim {
@@ -1448,7 +1716,8 @@ struct BlockDim {
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 0 = KV has q's dtype, 1 = e4m3, 2 = e5m2.
 // LOADER: 0 = TMA boxes, 1 = cp.async gathers.
 // MROWS: multi-row units (see row_head): n query rows of a request share its KV stream.
-template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, bool MROWS = false>
+// (MROWS as int: 1 = one N tile of 8 columns per unit, 2 = two: consume_rows2.)
+template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, int MROWS = 0>
 __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
     paged_decode_kernel(const __grid_constant__ DecodeParams p,
                         const __grid_constant__ CUtensorMap kmap,
@@ -1505,7 +1774,8 @@ __global__ void __launch_bounds__(BlockDim<LOADER>::kThreads, HD <= 128 ? 2 : 1)
   if (tid < kConsumerWarps * 32) {
     if constexpr (kRegSplit) setmaxnreg_inc<kCpAsyncConsumerRegs>();
     if (p.enable_pdl) pdl_wait();
-    consume<QT, KVF, HD, LOADER, ROPE, MROWS>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
+    if constexpr (MROWS == 2) consume_rows2<QT, HD, LOADER>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
+    else consume<QT, KVF, HD, LOADER, ROPE, MROWS == 1>(p, src, ring, full_bar, empty_bar, scratch_o, scratch_ml);
   } else if (LOADER == 0) {
     produce_tma<KVF, HD, true>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);  // waits inside
   } else {

@@ -412,6 +412,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
             page_size, q_data_type, kv_data_type, window_left,
             fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv,
             indices_host=indices_host, head_pairs=self._want_head_pairs(pos_encoding_mode),
+            wide_units=self._q_rows > 1 and self._head_pairs_ok,  # FI_PLAN_WIDE_UNITS: 16 (row, head) columns per unit
         )
         # kept for the one case run() has to plan again (FI_ERR_REPLAN, see _replan_without_head_pairs)
         self._plan_call = ((indptr, indices, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size),
@@ -570,7 +571,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
     def _run_plan(self, indptr_ptr, lpl_ptr, kv_len_ptr, batch_size, num_qo_heads, num_kv_heads,
                   head_dim, page_size, q_data_type, kv_data_type, window_left,
                   fixed_split_size=None, disable_split_kv=False, indices_host=None,
-                  head_pairs=False) -> None:
+                  head_pairs=False, wide_units=False) -> None:
         # fixed_split_size (pages) / disable_split_kv: batch-invariant planning, reference
         # decode.py:880-887; None / -1 mean "off" there as here
         lib = _lib.load()
@@ -586,9 +587,9 @@ class BatchDecodeWithPagedKVCacheWrapper:
         pa.batch_size = batch_size
         # the problem description changes rarely between steps: rewritten only when it does
         sig = (num_qo_heads, num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left,
-               fixed_split_size, disable_split_kv, self._use_cuda_graph, head_pairs)
+               fixed_split_size, disable_split_kv, self._use_cuda_graph, head_pairs, wide_units)
         if sig != self._plan_sig:
-            pa.flags = _lib.PLAN_HEAD_PAIRS if head_pairs else 0
+            pa.flags = (_lib.PLAN_HEAD_PAIRS if head_pairs else 0) | (_lib.PLAN_WIDE_UNITS if wide_units else 0)
             pa.num_qo_heads, pa.num_kv_heads = num_qo_heads, num_kv_heads
             pa.head_dim, pa.page_size = head_dim, page_size
             pa.q_dtype, pa.kv_dtype = dtype_code(q_data_type), dtype_code(kv_data_type)

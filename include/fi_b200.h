@@ -196,6 +196,14 @@ FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan
  * the reference's planner knows nothing of the cache layout (scheduler.cuh:411-481).
  */
 #define FI_PLAN_HEAD_PAIRS 1
+/*
+ * FI_PLAN_WIDE_UNITS: units of up to 16 query-head columns instead of 8 (16-bit KV, head_dim <= 128,
+ * power-of-two pages >= 8).  For plans that run with FiDecodeRunArgs.q_rows > 1 (multi-token decode,
+ * cascade levels): a unit's columns are (row, head) pairs, and the 16-bit kernel carries two 8-column
+ * MMA tiles per KV pass.  Such a plan run with q_rows <= 1 or through the gather loader returns
+ * FI_ERR_REPLAN.  No reference counterpart.
+ */
+#define FI_PLAN_WIDE_UNITS 2
 typedef struct FiDecodePlanArgs {
   void* float_ws; size_t float_ws_bytes;
   void* int_ws; void* pinned_int_ws; size_t int_ws_bytes;
