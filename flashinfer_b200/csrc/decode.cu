@@ -199,7 +199,7 @@ template <int QT, int KVF, int HD>
 static int launch_loader(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                          int grid, bool tma, cudaStream_t stream) {
   if constexpr (KVF == 0) {
-    if (p.q_rows > 1 && p.group_size > kMaxGroup) {  // wide units: two N tiles per warp (TMA loader, D <= 128)
+    if (p.q_rows >= 1 && p.group_size > kMaxGroup) {  // wide units: two N tiles per warp (TMA loader, D <= 128)
       if constexpr (HD <= 128) {
         if (tma) return launch_one<QT, KVF, HD, 0, false, 2>(p, km, vm, grid, stream);
       }
@@ -483,8 +483,14 @@ static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* pl
   // the L2 full of DIRTY lines (a 256 MB memset right before it) is slower (C2 +4 %, C4 +10 %).
   p.l2_hints = default_l2_hints();
   p.sinks = sinks;
-  if (q_rows <= 1 && !p.head_pairs && p.group_size > kMaxGroup)
-    return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_WIDE_UNITS: it needs q_rows > 1");
+  const bool wide_plan = !p.head_pairs && p.group_size > kMaxGroup;  // FI_PLAN_WIDE_UNITS took effect
+  if (wide_plan && (kvf != 0 || p.rope))
+    return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_WIDE_UNITS, but this run() needs ROPE_LLAMA");
+  if (wide_plan && q_rows <= 1) {
+    // a GQA group of 9 .. 16 as ONE unit: the multi-row consumer with a single row per request
+    p.q_rows = 1;
+    p.q_group = Hq / (Hkv / p.kv_head_div);
+  }
   if (q_rows > 1) {
     // multi-row units: the plan was made with num_qo_heads = q_rows x the model's query heads
     const int Hkv_mem = Hkv / p.kv_head_div;

@@ -412,7 +412,8 @@ class BatchDecodeWithPagedKVCacheWrapper:
             page_size, q_data_type, kv_data_type, window_left,
             fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv,
             indices_host=indices_host, head_pairs=self._want_head_pairs(pos_encoding_mode),
-            wide_units=self._q_rows > 1 and self._head_pairs_ok,  # FI_PLAN_WIDE_UNITS: 16 (row, head) columns per unit
+            # FI_PLAN_WIDE_UNITS: 16 columns per unit (GQA groups of 9 .. 16, multi-row units); same promises as above
+            wide_units=pos_encoding_mode != "ROPE_LLAMA" and self._head_pairs_ok,
         )
         # kept for the one case run() has to plan again (FI_ERR_REPLAN, see _replan_without_head_pairs)
         self._plan_call = ((indptr, indices, last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size),
@@ -1036,7 +1037,8 @@ def fast_decode_plan(
         self._run_plan(indptr_ptr, last_page_len_host.data_ptr(), None, batch_size, num_qo_heads,
                        num_kv_heads, head_dim, page_size, q_data_type, kv_data_type, window_left,
                        fixed_split_size=fixed_split_size, disable_split_kv=disable_split_kv,
-                       head_pairs=self._want_head_pairs(pos_encoding_mode))
+                       head_pairs=self._want_head_pairs(pos_encoding_mode),
+                       wide_units=pos_encoding_mode != "ROPE_LLAMA" and self._head_pairs_ok)
     except Exception as e:
         raise RuntimeError(f"Error in standard plan: {e}") from e
     self._pos_encoding_mode = pos_encoding_mode

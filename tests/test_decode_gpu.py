@@ -615,6 +615,64 @@ def test_multi_token_rows_share_the_kv_stream(n, hq, hkv, d, page, layout, varia
         assert (o2.float() - o.float()).abs().max().item() <= 4e-3
 
 
+@pytest.mark.parametrize("hq,hkv", [(16, 1), (12, 1), (40, 4), (128, 8), (36, 4), (24, 1)])
+@pytest.mark.parametrize("d,page,layout", [(128, 16, "NHD"), (64, 32, "HND"), (128, 8, "NHD")])
+@pytest.mark.parametrize("variant", ["plain", "window+cap", "alibi", "sinks"])
+def test_gqa_groups_of_9_to_16_are_one_unit(hq, hkv, d, page, layout, variant):
+    """GQA groups of 9 .. 16 (Llama-3-405B: 128 / 8) with 16-bit KV: one unit of up to 16 columns
+    (FI_PLAN_WIDE_UNITS, two MMA N tiles per KV pass) instead of two virtual KV heads; group 24 splits
+    into two units of 12.  Oracle parity incl. split units, empty requests, the logits variants; the
+    plan without the flag (FI_B200_WIDE_UNITS=0) gives the same; ROPE_LLAMA through forward() re-plans."""
+    import os
+
+    from flashinfer_b200.utils import get_alibi_slopes
+
+    fi = _fi()
+    lens = [1, 97, 3000, 0, 64, 9000, 513]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, layout, torch.float32, seed=151)
+    cache = cache.to(torch.float16)
+    q = make_q(len(lens), hq, d, torch.float16, seed=152)
+    kw, okw, rkw = {}, {}, {}
+    if variant == "window+cap":
+        kw, okw = dict(window_left=700, logits_soft_cap=30.0), dict(window_left=700, logits_soft_cap=30.0)
+    elif variant == "alibi":
+        kw, okw = dict(pos_encoding_mode="ALIBI"), dict(alibi_slopes=get_alibi_slopes(hq))
+    elif variant == "sinks":
+        rkw = dict(sinks=torch.linspace(-1.0, 2.0, hq, device=DEV))
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, kv_data_type=cache.dtype, **kw)
+    group = hq // hkv
+    assert int(w._plan_info[13]) == hkv * (1 if group <= 16 else 2)  # (virtual) KV heads of the plan
+    o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True, **rkw)
+    torch.cuda.synchronize()
+    if variant == "sinks":
+        for i in (1, 2, 5):
+            k, v = orc.gather_paged_kv(*orc.unpack_cache(cache, layout), indptr, indices, last, i, layout)
+            o_ref, _ = orc.decode_attention_ref(q[i], k.float(), v.float(), sinks=rkw["sinks"].cpu())
+            assert (o[i].float().cpu() - o_ref).abs().max().item() <= O_TOL
+    else:
+        o_ref, lse_ref = orc.batch_decode_ref(q, cache, indptr, indices, last, layout, **okw)
+        assert (o.float().cpu() - o_ref).abs().max().item() <= O_TOL
+        if variant == "alibi":
+            assert _alibi_lse_ok(lse.cpu(), lse_ref)
+        else:
+            assert (lse.cpu() - lse_ref).abs().max().item() <= LSE_TOL
+    if variant in ("plain", "window+cap"):
+        os.environ["FI_B200_WIDE_UNITS"] = "0"
+        try:
+            w2 = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+            w2.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, kv_data_type=cache.dtype, **kw)
+            assert int(w2._plan_info[13]) > int(w._plan_info[13])
+            o2 = w2.run(q.to(DEV), cache.to(DEV))
+        finally:
+            del os.environ["FI_B200_WIDE_UNITS"]
+        assert (o2.float() - o.float()).abs().max().item() <= 4e-3
+    if variant == "plain":
+        o3 = w.forward(q.to(DEV), cache.to(DEV), pos_encoding_mode="ROPE_LLAMA")  # FI_ERR_REPLAN underneath
+        o3_ref, _ = orc.batch_decode_ref(q, cache, indptr, indices, last, layout, rope=(1.0, 1e4))
+        assert (o3.float().cpu() - o3_ref).abs().max().item() <= O_TOL
+
+
 @pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
 @pytest.mark.parametrize("layout", ["NHD", "HND"])
 @pytest.mark.parametrize("pos_mode", ["NONE", "ROPE_LLAMA"])
