@@ -24,6 +24,7 @@ cap r02_decode_c2_bf16_page5_cpasync paged_decode 4 1 $B --page-size 5
 cap r02_decode_c2_bf16_page8 paged_decode 4 1 $B --page-size 8
 cap r02_decode_c2_bf16_rope paged_decode 40 1 python scripts/rope_probe.py ours
 cap r02_decode_fp8_d256_tc5 paged_decode_tc5 4 1 python scripts/head_dim_probe.py fp8 256
+cap r02_decode_gqa16_rows2 paged_decode 4 1 python scripts/gqa_group_probe.py 128 8
 FI_PROBE_ONCE=1 cap r02_kernels_misc 'decode_merge|merge_state|merge_states|append_paged|batch_indices|paged_decode' 0 40 python scripts/misc_kernels_probe.py
 case "launches" in *"${ONLY:-}"*)
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file profiles/r02_launches_c2_bf16.csv \
