@@ -620,12 +620,18 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (num_kv_heads <= 0 || num_qo_heads % num_kv_heads)
     return fail(FI_ERR_INVALID_ARGUMENT, "num_qo_heads must be a multiple of num_kv_heads");
-  const int kv_div = group_split(num_qo_heads / num_kv_heads, max_group_for(head_dim));
+  const int kvf = kv_format(q_dtype, kv_dtype);
+  if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair");
+  // GQA groups of 9 .. 16 as one 16-column unit (consume_rows2) where the batch path does it too:
+  // 16-bit KV, head_dim <= 128, TMA loader (K / V 16-byte aligned, at least one tile), no ROPE_LLAMA
+  const int full_group = num_qo_heads / num_kv_heads;
+  const bool wide = kvf == 0 && head_dim <= 128 && pos_encoding_mode != FI_POS_ROPE_LLAMA && full_group > kMaxGroup &&
+                    tuning().loader != 2 && kv_len >= tile_tokens(kvf) &&
+                    ((reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+  const int kv_div = group_split(full_group, wide ? 2 * kMaxGroup : max_group_for(head_dim));
   const int num_kv_heads_mem = num_kv_heads;  // heads k / v really have
   num_kv_heads *= kv_div;                     // virtual heads: one unit each (see DecodeParams)
   const int group = num_qo_heads / num_kv_heads;
-  const int kvf = kv_format(q_dtype, kv_dtype);
-  if (kvf < 0) return fail(FI_ERR_UNSUPPORTED, "unsupported q/kv dtype pair");
   if (!(head_dim == 64 || head_dim == 128 || head_dim == 256 || head_dim == 512))
     return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
   if (kv_len < 0) return fail(FI_ERR_INVALID_ARGUMENT, "negative kv_len");
@@ -674,6 +680,7 @@ int fi_single_decode_run(const void* q, const void* k, const void* v, void* tmp,
   p.alibi_slopes = pos_encoding_mode == FI_POS_ALIBI ? alibi_slopes : nullptr;
   p.rope = pos_encoding_mode == FI_POS_ROPE_LLAMA;
   p.rope_rcp_scale = 1.f / rope_scale; p.rope_rcp_theta = 1.f / rope_theta;
+  if (group > kMaxGroup) { p.q_rows = 1; p.q_group = full_group; }  // wide units (see above)
 
   const bool tma = !(kvf != 0 && head_dim == 64) && head_dim != 512 &&
                    tma_eligible(k, v, es, p.kv_stride_n, p.kv_stride_h, 0, 0, true, kv_len, TT);

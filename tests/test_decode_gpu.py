@@ -668,6 +668,13 @@ def test_gqa_groups_of_9_to_16_are_one_unit(hq, hkv, d, page, layout, variant):
             del os.environ["FI_B200_WIDE_UNITS"]
         assert (o2.float() - o.float()).abs().max().item() <= 4e-3
     if variant == "plain":
+        for i in (1, 2, 5):  # single decode takes the same 16-column units (request 1: shorter than a tile, it does not)
+            k, v = orc.gather_paged_kv(*orc.unpack_cache(cache, layout), indptr, indices, last, i, layout)
+            kd, vd = (k, v) if layout == "NHD" else (k.transpose(0, 1), v.transpose(0, 1))
+            o1, l1 = fi.single_decode_with_kv_cache(q[i].to(DEV), kd.contiguous().to(DEV), vd.contiguous().to(DEV),
+                                                    kv_layout=layout, return_lse=True)
+            assert (o1.float().cpu() - o_ref[i]).abs().max().item() <= O_TOL
+            assert (l1.cpu() - lse_ref[i]).abs().max().item() <= LSE_TOL
         o3 = w.forward(q.to(DEV), cache.to(DEV), pos_encoding_mode="ROPE_LLAMA")  # FI_ERR_REPLAN underneath
         o3_ref, _ = orc.batch_decode_ref(q, cache, indptr, indices, last, layout, rope=(1.0, 1e4))
         assert (o3.float().cpu() - o3_ref).abs().max().item() <= O_TOL
