@@ -13,6 +13,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib
+from .decode import rows_can_share_the_stream
 from .utils import canonicalize_torch_dtype, current_stream_ptr, device_index, dtype_code
 
 
@@ -302,8 +303,8 @@ class MultiLevelCascadeAttentionWrapper:
                 num_rows = level_rows
             elif num_rows != level_rows:
                 raise ValueError("the last element of every qo_indptr must be the total number of queries")
-            if (rows > 1 and not self._use_cuda_graph and window_left < 0 and head_dim != 512
-                    and kv_dt in (torch.float16, torch.bfloat16) and os.environ.get("FI_B200_MTP_ROWS", "1") != "0"):
+            if (rows > 1 and not self._use_cuda_graph and window_left < 0
+                    and rows_can_share_the_stream(kv_dt, head_dim, page_size)):
                 # every group of the level has `rows` query rows: they share the group's KV stream as extra
                 # columns of the GQA group (FiDecodeRunArgs.q_rows) instead of one decode request per row
                 wrapper._q_rows, wrapper._q_rows_noncausal = rows, int(not level_causal)
@@ -446,8 +447,7 @@ class BatchDecodeWithSharedPrefixPagedKVCacheWrapper:
             return
         num_qo_heads, num_kv_heads, head_dim = self._shape
         w = self._shared_wrapper
-        if (batch_size > 1 and kv_dtype in (torch.float16, torch.bfloat16) and head_dim != 512
-                and os.environ.get("FI_B200_MTP_ROWS", "1") != "0"):
+        if batch_size > 1 and rows_can_share_the_stream(kv_dtype, head_dim, page):
             # ONE request over the shared pages whose query rows are the batch (FiDecodeRunArgs.q_rows,
             # no mask among the rows): the prefix is streamed once per 8 (row, head) columns, not per request
             w._q_rows, w._q_rows_noncausal = batch_size, 1

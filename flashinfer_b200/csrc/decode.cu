@@ -231,11 +231,11 @@ static int launch_hd(const DecodeParams& p, const CUtensorMap& km, const CUtenso
 }
 
 // fp8 KV, head_dim 128, TMA-eligible pages: tcgen05 / TMEM kernel (decode_kernel_tc5.cuh)
-template <int QT, int KVF, bool HP = false, int HD = 128>
+template <int QT, int KVF, int MODE = kTc5Single, int HD = 128>
 static int launch_tc5(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm, int grid,
                       cudaStream_t stream) {
-  auto kern = paged_decode_tc5_kernel<QT, KVF, HP, HD>;
-  const int smem = SmemLayout<KVF, HD>::total(p.num_stages) + (HP ? kTc5PairScratchBytes : 0);
+  auto kern = paged_decode_tc5_kernel<QT, KVF, MODE, HD>;
+  const int smem = SmemLayout<KVF, HD>::total(p.num_stages) + (MODE != kTc5Single ? kTc5PairScratchBytes : 0);
   FI_CUDA_TRY(ensure_smem_attr(kern, smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
@@ -325,12 +325,16 @@ static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUt
     }
   }
   if (p.head_pairs) {  // fi_batch_decode_run checked that this launch fits a head-pair plan
-    if (kvf == 1) return bf ? launch_tc5<1, 1, true>(p, km, vm, grid, stream) : launch_tc5<0, 1, true>(p, km, vm, grid, stream);
-    return bf ? launch_tc5<1, 2, true>(p, km, vm, grid, stream) : launch_tc5<0, 2, true>(p, km, vm, grid, stream);
+    if (kvf == 1) return bf ? launch_tc5<1, 1, kTc5Pairs>(p, km, vm, grid, stream) : launch_tc5<0, 1, kTc5Pairs>(p, km, vm, grid, stream);
+    return bf ? launch_tc5<1, 2, kTc5Pairs>(p, km, vm, grid, stream) : launch_tc5<0, 2, kTc5Pairs>(p, km, vm, grid, stream);
+  }
+  if (kvf != 0 && p.q_rows >= 1) {  // wide units / multi-row units with fp8 KV (checked by the caller: D 128, TMA, tcgen05)
+    if (kvf == 1) return bf ? launch_tc5<1, 1, kTc5Wide>(p, km, vm, grid, stream) : launch_tc5<0, 1, kTc5Wide>(p, km, vm, grid, stream);
+    return bf ? launch_tc5<1, 2, kTc5Wide>(p, km, vm, grid, stream) : launch_tc5<0, 2, kTc5Wide>(p, km, vm, grid, stream);
   }
   if (kvf != 0 && head_dim == 256 && tma && use_tc5()) {
-    if (kvf == 1) return bf ? launch_tc5<1, 1, false, 256>(p, km, vm, grid, stream) : launch_tc5<0, 1, false, 256>(p, km, vm, grid, stream);
-    return bf ? launch_tc5<1, 2, false, 256>(p, km, vm, grid, stream) : launch_tc5<0, 2, false, 256>(p, km, vm, grid, stream);
+    if (kvf == 1) return bf ? launch_tc5<1, 1, kTc5Single, 256>(p, km, vm, grid, stream) : launch_tc5<0, 1, kTc5Single, 256>(p, km, vm, grid, stream);
+    return bf ? launch_tc5<1, 2, kTc5Single, 256>(p, km, vm, grid, stream) : launch_tc5<0, 2, kTc5Single, 256>(p, km, vm, grid, stream);
   }
   if (kvf != 0 && head_dim == 128 && tma && use_tc5()) {
     if (kvf == 1) return bf ? launch_tc5<1, 1>(p, km, vm, grid, stream) : launch_tc5<0, 1>(p, km, vm, grid, stream);
@@ -484,8 +488,11 @@ static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* pl
   p.l2_hints = default_l2_hints();
   p.sinks = sinks;
   const bool wide_plan = !p.head_pairs && p.group_size > kMaxGroup;  // FI_PLAN_WIDE_UNITS took effect
-  if (wide_plan && (kvf != 0 || p.rope))
-    return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_WIDE_UNITS, but this run() needs ROPE_LLAMA");
+  // fp8 KV: the tcgen05 kernel's wide mode (head_dim 128, TMA pages: checked below with `tma`)
+  const bool fp8_wide_ok = kvf != 0 && head_dim == 128 && use_tc5() && !p.head_pairs;
+  if (wide_plan && (p.rope || (kvf != 0 && !fp8_wide_ok)))
+    return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_WIDE_UNITS, but this run() needs %s",
+                p.rope ? "ROPE_LLAMA" : "the register path");
   if (wide_plan && q_rows <= 1) {
     // a GQA group of 9 .. 16 as ONE unit: the multi-row consumer with a single row per request
     p.q_rows = 1;
@@ -494,10 +501,10 @@ static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* pl
   if (q_rows > 1) {
     // multi-row units: the plan was made with num_qo_heads = q_rows x the model's query heads
     const int Hkv_mem = Hkv / p.kv_head_div;
-    if (kvf != 0 || p.rope || Hq % q_rows != 0 || (Hq / q_rows) % Hkv_mem != 0 || p.head_pairs ||
+    if ((kvf != 0 && !fp8_wide_ok) || p.rope || Hq % q_rows != 0 || (Hq / q_rows) % Hkv_mem != 0 || p.head_pairs ||
         plan_info[kPiMergeGrid] > 0 || plan_info[kPiWindowLeft] >= 0 || head_dim == 512)
-      return fail(FI_ERR_UNSUPPORTED, "q_rows > 1 needs 16-bit KV, no ROPE_LLAMA, no sliding window, the fused "
-                                      "merge and a plan made with num_qo_heads = q_rows x query heads");
+      return fail(FI_ERR_UNSUPPORTED, "q_rows > 1 needs 16-bit KV or fp8 KV at head_dim 128, no ROPE_LLAMA, no sliding "
+                                      "window, the fused merge and a plan made with num_qo_heads = q_rows x query heads");
     p.q_rows = q_rows;
     p.q_rows_noncausal = q_rows_noncausal != 0;
     p.q_group = (Hq / q_rows) / Hkv_mem;
@@ -506,6 +513,9 @@ static int batch_decode_run_impl(void* float_ws, void* int_ws, const int64_t* pl
   const bool cuda_core_only = (kvf != 0 && head_dim == 64) || head_dim == 512;
   const bool tma = !cuda_core_only && tma_eligible(k_cache, v_cache, es, kv_stride_n, kv_stride_h,
                                                    kv_stride_page, page_size, false, 0, TT);
+  if (kvf != 0 && p.q_rows >= 1 && !tma)  // fp8 wide / multi-row units exist on the tcgen05 kernel only
+    return fail(wide_plan ? FI_ERR_REPLAN : FI_ERR_UNSUPPORTED,
+                "fp8 KV with wide or multi-row units needs TMA-addressable pages (a power of two >= 8)");
   if (p.head_pairs && (!tma || p.rope || !use_tc5() || es != 1 || head_dim != 128))
     return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_HEAD_PAIRS, but this run() needs %s: plan "
                                "again without the flag", p.rope ? "ROPE_LLAMA" : "the gather loader");

@@ -39,12 +39,15 @@ namespace fib200 {
 
 constexpr int kTc5Threads = 192;
 // TMEM columns: S[b] at kTc5ColS + sstride b (2 buffers), O after them
-template <bool HP>
+template <bool HP>  // true: 64 logit columns per row (head pairs, wide units)
 struct Tc5Cols {
   static constexpr uint32_t kSStride = HP ? 64 : 32;
   static constexpr uint32_t kO = 2 * kSStride;          // HP: O_h at kO + 16 h
   static constexpr uint32_t kAlloc = HP ? 256 : 128;    // a power of two >= kO + (HP ? 32 : 16)
 };
+// kernel modes: one KV head and <= 8 query columns per unit; a PAIR of KV heads; one KV head and <= 16
+// (row, head) columns (FI_PLAN_WIDE_UNITS, FiDecodeRunArgs.q_rows)
+constexpr int kTc5Single = 0, kTc5Pairs = 1, kTc5Wide = 2;
 constexpr int kTc5ColS = 0;
 constexpr float kTc5Bump = 5.f;     // raise rho when a tile max exceeds it by more than 2^5
 constexpr float kTc5PShift = 3.f;   // p = 2^(x - rho + 3): <= 2^8 right after a bump
@@ -186,17 +189,19 @@ __device__ __forceinline__ void tc5_prepare_q256(const DecodeParams& p, const Se
 }
 
 // ---- MMA issuer (warp 5; one elected lane issues, the warp stays converged) ---------------------
-template <int KVF, bool HP, int HD = 128>
+template <int KVF, int MODE, int HD = 128>
 __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource& src,
                                           uint32_t ring, uint32_t qbufs,
                                           uint32_t pbufs, uint32_t full_bar, uint32_t empty_bar,
                                           const Tc5Bars& bars, uint32_t tmem) {
   using G = TileGeom<KVF, HD>;
-  static_assert(!HP || HD == 128, "head pairs: head_dim 128");
+  constexpr bool HP = MODE == kTc5Pairs, WIDE = MODE == kTc5Wide;
+  constexpr bool Q1 = MODE != kTc5Single;  // 64-row query buffer, single, handed back through q_free
+  static_assert(MODE == kTc5Single || HD == 128, "head pairs / wide units: head_dim 128");
   constexpr int AF = (KVF == 2) ? 1 : 0;  // e5m2 : e4m3 storage
-  using TC = Tc5Cols<HP>;
-  constexpr uint32_t idesc_qk = tc5::instr_desc_f8(AF, 0, /*a K-major*/ 0, /*b K-major*/ 0, 128, HP ? 64 : 32);
-  constexpr uint32_t idesc_pv = tc5::instr_desc_f8(AF, 0, /*a MN-major*/ 1, /*b MN-major*/ 1, 128, 16);
+  using TC = Tc5Cols<Q1>;
+  constexpr uint32_t idesc_qk = tc5::instr_desc_f8(AF, 0, /*a K-major*/ 0, /*b K-major*/ 0, 128, Q1 ? 64 : 32);
+  constexpr uint32_t idesc_pv = tc5::instr_desc_f8(AF, 0, /*a MN-major*/ 1, /*b MN-major*/ 1, 128, WIDE ? 32 : 16);
   const bool leader = (threadIdx.x & 31) == 0;
   int stage = 0;
   uint32_t phase = 0;
@@ -207,13 +212,22 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
   uint32_t pend_n = 0, pend_acc = 0;
 
   auto issue_pv = [&]() {
-    const uint32_t b = pend_n & 1u;
-    mbar_wait(bars.p_ready[b], (pend_n >> 1) & 1u);
+    // WIDE: ONE probability buffer (4 KiB: 128 rows x [columns 0-7 hi lo | columns 8-15 hi lo]), phase = tile
+    const uint32_t b = WIDE ? 0u : pend_n & 1u;
+    mbar_wait(bars.p_ready[b], WIDE ? pend_n & 1u : (pend_n >> 1) & 1u);
     tc5::fence_after_sync();
     if (leader) {
       const uint32_t vbase = ring + pend_stage * G::STAGE_BYTES + G::KV_BYTES;
       const uint32_t pb = pbufs + b * 2048u;
-      if constexpr (HP) {
+      if constexpr (WIDE) {
+        // N = 32: the two 16-byte column groups of a row are 2 KiB apart (SBO), 8-token groups 128 B (LBO)
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint64_t ad = tc5::smem_desc(vbase + ks * 4096u, 1024u, 1024u, tc5::kLayoutSw128);
+          const uint64_t bd = tc5::smem_desc(pb + ks * 512u, 128u, 2048u, tc5::kLayoutNone);
+          tc5::mma_f8(tmem + TC::kO, ad, bd, idesc_pv, (ks > 0) ? 1u : pend_acc);
+        }
+      } else if constexpr (HP) {
         // head hp owns every other 8-row group: V groups 2 KiB apart, P groups 256 B apart
 #pragma unroll
         for (int hp = 0; hp < 2; ++hp) {
@@ -249,10 +263,10 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
     __syncwarp();
     if (leader) src.ctl[kQDone1] = k + 1;  // this warp holds its copy of segment k
     // every segment: never lag a phase behind
-    if constexpr (HP) mbar_wait(bars.q_ready[0], k & 1u);
+    if constexpr (Q1) mbar_wait(bars.q_ready[0], k & 1u);
     else mbar_wait(bars.q_ready[k & 1], (k >> 1) & 1u);
-    const uint32_t qb = HP ? qbufs : qbufs + (k & 1) * (32u * HD);
-    if (HP && leader && sg.tile_end <= sg.tile_begin) mbar_arrive(bars.q_free);  // nothing reads this query
+    const uint32_t qb = Q1 ? qbufs : qbufs + (k & 1) * (32u * HD);
+    if (Q1 && leader && sg.tile_end <= sg.tile_begin) mbar_arrive(bars.q_free);  // nothing reads this query
     for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
       const uint32_t b = n & 1u;
       // wait for the next K tile (and a free S buffer), but serve the pending P.V the moment its
@@ -260,7 +274,8 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
       {
         const long long t0 = clock64();
         while (true) {
-          if (pend && mbar_try_wait(bars.p_ready[pend_n & 1u], (pend_n >> 1) & 1u)) issue_pv();
+          if (pend && mbar_try_wait(bars.p_ready[WIDE ? 0u : pend_n & 1u], WIDE ? pend_n & 1u : (pend_n >> 1) & 1u))
+            issue_pv();
           if (mbar_try_wait(full_bar + 8 * stage, phase) &&
               mbar_try_wait(bars.s_free[b], ((n >> 1) & 1u) ^ 1u))
             break;
@@ -281,7 +296,7 @@ __device__ __forceinline__ void tc5_issue(const DecodeParams& p, const SegSource
           tc5::mma_f8(tmem + kTc5ColS + TC::kSStride * b, ad, bd, idesc_qk, ks > 0 ? 1u : 0u);
         }
         tc5::commit(bars.s_ready[b]);
-        if (HP && tile == sg.tile_end - 1) tc5::commit(bars.q_free);  // the single query buffer is free again
+        if (Q1 && tile == sg.tile_end - 1) tc5::commit(bars.q_free);  // the single query buffer is free again
       }
       __syncwarp();
       if (pend) issue_pv();
@@ -887,18 +902,332 @@ __device__ __forceinline__ void tc5_softmax(const DecodeParams& p, const SegSour
   FI_TRACE_IF(tid == 0, 8);
 }
 
+// ---- wide units (kTc5Wide): ONE KV head, up to 16 (row, head) query columns per unit ------------
+// Columns map to (row, head) through row_head (decode_kernel.cuh); the query buffer holds two
+// 32-row groups (columns 0-7, 8-15), S has 64 columns per token, and a softmax thread — still one
+// token — works through the two column groups one after the other (rho / l for 16 columns stay in
+// registers, the per-column scales and causal cuts come from shared memory).  P is ONE 4 KiB buffer:
+// the thread waits for P.V of the previous tile before it overwrites its row.
+template <int QT>
+__device__ __forceinline__ void tc5_prepare_q_wide(const DecodeParams& p, const Segment& sg, uint8_t* qbuf,
+                                                   float* dq_out, int tid) {
+  const int h = tid >> 4, d0 = (tid & 15) * 8;
+  const int GS = p.group_size;
+#pragma unroll
+  for (int cg = 0; cg < 2; ++cg) {
+    const int col = 8 * cg + h;
+    float x[8];
+    float amax = 0.f;
+    if (col < GS) {
+      const RowHead rh = row_head(p, sg.kv_head, col);
+      const char* qrow = static_cast<const char*>(p.q) +
+                         (rh.token(p, sg.request) * p.q_stride_n + (int64_t)rh.head * p.q_stride_h) * 2 + d0 * 2;
+      const uint2 v0 = __ldg(reinterpret_cast<const uint2*>(qrow));
+      const uint2 v1 = __ldg(reinterpret_cast<const uint2*>(qrow) + 1);
+      const uint32_t w[4] = {v0.x, v0.y, v1.x, v1.y};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if constexpr (QT == 1) {
+          x[2 * i] = __uint_as_float(w[i] << 16);
+          x[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        } else {
+          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+          x[2 * i] = f.x;
+          x[2 * i + 1] = f.y;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(x[i]));
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) x[i] = 0.f;
+    }
+#pragma unroll
+    for (int s2 = 1; s2 < 16; s2 <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, s2));
+    const bool nz = amax > 0.f && amax < 3.0e38f;
+    const float sq = nz ? 256.f / amax : 1.f;
+    if ((tid & 15) == 0) dq_out[col] = nz ? amax * (1.f / 256.f) : 1.f;
+    uint32_t t[4][3];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) split3_e4m3x2(t[i], x[2 * i] * sq, x[2 * i + 1] * sq);
+    const int chunk = d0 >> 4, within = d0 & 15;
+#pragma unroll
+    for (int term = 0; term < 4; ++term) {
+      const int row = 32 * cg + 8 * term + h;
+      uint2 v = make_uint2(0u, 0u);
+      if (term < 3) {
+        v.x = t[0][term] | (t[1][term] << 16);
+        v.y = t[2][term] | (t[3][term] << 16);
+      }
+      *reinterpret_cast<uint2*>(qbuf + swz<128>(row, chunk) + within) = v;
+    }
+  }
+}
+
+// v[lane >> 3][lane & 7] for lane < 16, without a local-memory array index
+__device__ __forceinline__ float tc5_pick16(const float (&v)[2][8], int lane) {
+  float mine = v[0][0];
+#pragma unroll
+  for (int c = 0; c < 2; ++c)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mine = (lane & 15) == 8 * c + j ? v[c][j] : mine;
+  return mine;
+}
+
+template <int QT, int KVF>
+__device__ __forceinline__ void tc5_softmax_wide(const DecodeParams& p, const SegSource& src,
+                                                 uint8_t* smem_ring, uint8_t* qbuf, uint8_t* pbuf,
+                                                 float* scratch, float* pair_scratch, const Tc5Bars& bars,
+                                                 uint32_t tmem, int num_stages) {
+  using G = TileGeom<KVF, 128>;
+  using TC = Tc5Cols<true>;
+  constexpr int HD = 128;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int GS = p.group_size;  // <= 16 columns
+  const int hq_real = p.num_qo_heads / p.q_rows;
+  const bool use_cap = p.soft_cap > 0.f;
+  const float cap_pre = use_cap ? p.sm_scale / p.soft_cap : 0.f;
+  const float cap_post = use_cap ? p.soft_cap * 1.4426950408889634f : 0.f;
+  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;  // TMEM lane field
+  // scratch (floats): wmax [4][16] @0, dq [16] @72, tmem slot @120, vote [2][4] @124;
+  // pair_scratch: lsum [4][16] @0, per column: causal cut (int) @64, ALiBi slope @80
+  float* wmax = scratch;
+  float* dqs = scratch + 72;
+  float* lsum = pair_scratch;
+  int* hid_sm = reinterpret_cast<int*>(pair_scratch + 64);
+  float* slope_sm = pair_scratch + 80;
+  volatile int* vote = reinterpret_cast<volatile int*>(scratch + 124);
+
+  int stage = 0;
+  uint32_t n = 0;  // tiles consumed so far: S buffer = n & 1
+  PendingMerge pm;
+  pm.mu = -1; pm.old = pm.cnt = pm.slot = pm.req = pm.head = 0;
+  bool have_q = false;
+  for (int k = 0;; ++k) {
+    Segment sg;
+    if (!seg_fetch(src, k, sg)) break;
+    if (!have_q) {
+      if (k > 0) mbar_wait(bars.q_free, (k - 1) & 1u);
+      tc5_prepare_q_wide<QT>(p, sg, qbuf, dqs, tid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.q_ready[0]);
+    }
+    if (tid == 0) {
+      src.ctl[kQPeek] = seg_peek(src, k + 1) ? 1 : 0;
+      src.ctl[kQDone0] = k;
+    }
+    if (tid < 16) {
+      const RowHead rh = row_head(p, sg.kv_head, tid);
+      hid_sm[tid] = p.q_rows_noncausal ? 0 : p.q_rows - 1 - rh.row;
+      float a = 0.f;
+      if (p.alibi_slopes != nullptr && tid < GS)
+        a = __ldg(p.alibi_slopes + rh.head) * (use_cap ? cap_pre : 1.4426950408889634f);
+      slope_sm[tid] = a;
+    }
+    named_bar_sync(1, 128);
+    have_q = src.ctl[kQPeek] != 0;
+    const float pre_scale = p.alibi_slopes != nullptr ? cap_pre * p.sm_scale : cap_pre;
+    float rho[2][8], l[2][8];
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { rho[c][j] = kNegInf; l[c][j] = 0.f; }
+
+    for (int tile = sg.tile_begin; tile < sg.tile_end; ++tile) {
+      const uint32_t b = n & 1u;
+      const int tok = tile * G::TT + tid;
+      const bool inwin = tok >= sg.tok_lo && tok < sg.tok_hi;
+      float x[2][8];
+      bool vcol[2][8];
+      mbar_wait(bars.s_ready[b], (n >> 1) & 1u);
+      tc5::fence_after_sync();
+      {
+        const uint32_t sb = tmem + lane_base + kTc5ColS + TC::kSStride * b;
+        float c0[16], c1[8], e0[16], e1[8];
+        tc5::ld_x16(sb, c0);
+        tc5::ld_x8(sb + 16u, c1);
+        tc5::ld_x16(sb + 32u, e0);
+        tc5::ld_x8(sb + 48u, e1);
+        tc5::wait_ld();
+        tc5::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bars.s_free[b]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          x[0][j] = c0[j] + c0[8 + j] + c1[j];
+          x[1][j] = e0[j] + e0[8 + j] + e1[j];
+        }
+      }
+      bool over = false;
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int col = 8 * c + j;
+          const float d = dqs[col];
+          const float v = use_cap ? cap_post * tanhf_approx(x[c][j] * (d * pre_scale) + slope_sm[col] * (float)tok)
+                                  : x[c][j] * (d * p.sm_scale_log2) + slope_sm[col] * (float)tok;
+          vcol[c][j] = inwin && tok < sg.tok_hi - hid_sm[col];
+          x[c][j] = vcol[c][j] ? v : kNegInf;
+          over |= x[c][j] > rho[c][j] + kTc5Bump;
+        }
+      const bool wover = __any_sync(0xffffffffu, over);
+      if (lane == 0) vote[b * 4 + warp] = wover ? 1 : 0;
+      named_bar_sync(2, 128);
+      const bool bump = (vote[b * 4] | vote[b * 4 + 1] | vote[b * 4 + 2] | vote[b * 4 + 3]) != 0;
+      if (bump) {  // CTA-uniform
+        float mt[2][8];
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) mt[c][j] = tc5_head_max<false>(x[c][j]);
+        if (lane < 16) wmax[warp * 16 + lane] = tc5_pick16(mt, lane);
+        named_bar_sync(3, 128);
+        float alpha[2][8];
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int i = 8 * c + j;
+            const float m = fmaxf(fmaxf(wmax[i], wmax[16 + i]), fmaxf(wmax[32 + i], wmax[48 + i]));
+            const float rn = m > rho[c][j] + kTc5Bump ? m : rho[c][j];
+            alpha[c][j] = ex2f(rho[c][j] - rn);
+            l[c][j] *= alpha[c][j];
+            rho[c][j] = rn;
+          }
+        if (tile != sg.tile_begin) {  // O is relative to the old rho: wait for P.V of the previous tile, rescale
+          mbar_wait(bars.p_free[0], (n - 1) & 1u);
+          tc5::fence_after_sync();
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            float o[16];
+            tc5::ld_x16(tmem + lane_base + TC::kO + 16u * c, o);
+            tc5::wait_ld();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { o[j] *= alpha[c][j]; o[8 + j] *= alpha[c][j]; }
+            tc5::st_x16(tmem + lane_base + TC::kO + 16u * c, o);
+          }
+          tc5::wait_st();
+          tc5::fence_before_sync();
+        }
+      }
+      if (n > 0) mbar_wait(bars.p_free[0], (n - 1) & 1u);  // P.V of the previous tile is done with the buffer
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float p0 = vcol[c][2 * i] ? ex2f(x[c][2 * i] - rho[c][2 * i] + kTc5PShift) : 0.f;
+          const float p1 = vcol[c][2 * i + 1] ? ex2f(x[c][2 * i + 1] - rho[c][2 * i + 1] + kTc5PShift) : 0.f;
+          l[c][2 * i] += p0;
+          l[c][2 * i + 1] += p1;
+          w[i] = split_e4m3x2(p0, p1);  // hi pair in bits 0-15, lo pair in bits 16-31
+        }
+        uint4 row;
+        row.x = (w[0] & 0xffffu) | (w[1] << 16);
+        row.y = (w[2] & 0xffffu) | (w[3] << 16);
+        row.z = (w[0] >> 16) | (w[1] & 0xffff0000u);
+        row.w = (w[2] >> 16) | (w[3] & 0xffff0000u);
+        *reinterpret_cast<uint4*>(pbuf + c * 2048 + tid * 16) = row;
+      }
+      if (tok >= sg.tok_hi) {  // this token's V row was not (validly) loaded: 0 * junk must not be NaN
+        uint4* vrow = reinterpret_cast<uint4*>(smem_ring + stage * G::STAGE_BYTES + G::KV_BYTES + tid * 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) vrow[i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.p_ready[0]);
+      ++n;
+      if (++stage == num_stages) stage = 0;
+    }
+    if (have_q) {  // CTA-uniform: the next segment's query, once every Q.K MMA of this one is complete
+      if (sg.tile_end <= sg.tile_begin) named_bar_sync(2, 128);  // dq of this segment is still being read
+      mbar_wait(bars.q_free, k & 1u);
+      const Segment sn = seg_read(src, k + 1);
+      tc5_prepare_q_wide<QT>(p, sn, qbuf, dqs, tid);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars.q_ready[0]);
+    }
+
+    // ---- segment epilogue: thread tid <-> head-dim index d = tid (TMEM lane of O) ---------------
+    float o8[16];
+    if (sg.tile_end > sg.tile_begin) {
+      mbar_wait(bars.p_free[0], (n - 1) & 1u);  // P.V of the last tile complete
+      tc5::fence_after_sync();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float o[16];
+        tc5::ld_x16(tmem + lane_base + TC::kO + 16u * c, o);
+        tc5::wait_ld();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o8[8 * c + j] = o[j] + o[8 + j];
+      }
+      tc5::fence_before_sync();
+    } else {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) o8[i] = 0.f;
+    }
+    {
+      float L[2][8];
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) L[c][j] = tc5_head_sum<false>(l[c][j]);
+      if (lane < 16) lsum[warp * 16 + lane] = tc5_pick16(L, lane);
+    }
+    if (tid == 0) merge_post(p, pm, scratch);
+    named_bar_sync(3, 128);
+    merge_run_posted<QT, HD, true>(p, scratch, tid);
+
+    const bool direct = sg.slot < 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      if (i < GS) {
+        const RowHead rh = row_head(p, sg.kv_head, i);
+        float Lj = (lsum[i] + lsum[16 + i]) + (lsum[32 + i] + lsum[48 + i]);
+        const float rj = rho[i >> 3][i & 7];
+        const bool any = Lj > 0.f;
+        if (direct && any && p.sinks != nullptr)
+          Lj += ex2f(__ldg(p.sinks + rh.head) * 1.4426950408889634f - rj + kTc5PShift);
+        const float val = any ? o8[i] * ((direct ? p.v_scale : 1.f) / Lj) : 0.f;
+        const float lse2 = any ? rj + lg2f(Lj) - kTc5PShift : kNegInf;
+        if (direct) {
+          const int64_t oh = rh.token(p, sg.request) * hq_real + rh.head;
+          if (QT == 1) static_cast<__nv_bfloat16*>(p.o)[oh * HD + tid] = __float2bfloat16_rn(val);
+          else static_cast<__half*>(p.o)[oh * HD + tid] = __float2half_rn(val);
+          if (p.lse != nullptr && tid == i) p.lse[oh] = lse2;
+        } else {
+          p.tmp_o[((int64_t)sg.slot * GS + i) * HD + tid] = val;
+          if (tid == i) p.tmp_lse[(int64_t)sg.slot * GS + i] = lse2;
+        }
+      }
+    }
+    if (sg.merge_unit >= 0) {
+      named_bar_sync(2, 128);
+      if (tid == 0) merge_arrive(p, pm, sg);
+    }
+  }
+  if (tid == 0) merge_post(p, pm, scratch);
+  named_bar_sync(3, 128);
+  merge_run_posted<QT, HD, true>(p, scratch, tid);
+}
+
 // QT: 0 f16, 1 bf16 (q / o dtype).  KVF: 1 = e4m3, 2 = e5m2 KV.  head_dim 128, TMA-eligible pages.
 // HP: head-pair plan (see the top of this file).  HD: 128, or 256 (one CTA per SM: 64 KiB stages, two K / V /
 // Qs panels per row, two O accumulators; single-head units only).
-template <int QT, int KVF, bool HP = false, int HD = 128>
+template <int QT, int KVF, int MODE = kTc5Single, int HD = 128>
 __global__ void __launch_bounds__(kTc5Threads, HD == 128 ? 2 : 1)
     paged_decode_tc5_kernel(const __grid_constant__ DecodeParams p,
                             const __grid_constant__ CUtensorMap kmap,
                             const __grid_constant__ CUtensorMap vmap) {
   using G = TileGeom<KVF, HD>;
   using L = SmemLayout<KVF, HD>;
+  constexpr bool HP = MODE == kTc5Pairs, WIDE = MODE == kTc5Wide, Q1 = MODE != kTc5Single;
   static_assert(L::SCRATCH_O >= 2 * 32 * HD + 2 * 2048, "Q / P buffers do not fit the scratch region");
-  static_assert(!HP || HD == 128, "head pairs: head_dim 128");
+  static_assert(MODE == kTc5Single || HD == 128, "head pairs / wide units: head_dim 128");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t pad = ((raw + 1023u) & ~1023u) - raw;
@@ -921,7 +1250,7 @@ __global__ void __launch_bounds__(kTc5Threads, HD == 128 ? 2 : 1)
   const int tid = threadIdx.x, warp = tid >> 5;
   FI_TRACE_IF(tid == 0, 0);
   // TMEM allocation (warp 1) overlaps barrier setup (thread 0) and the work-list fetch
-  if (warp == 1) tc5::tmem_alloc(smem_u32(tmem_slot), Tc5Cols<HP>::kAlloc);
+  if (warp == 1) tc5::tmem_alloc(smem_u32(tmem_slot), Tc5Cols<Q1>::kAlloc);
   if (tid == 0) {
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(full_bar + 8 * s, 1);
@@ -946,7 +1275,7 @@ __global__ void __launch_bounds__(kTc5Threads, HD == 128 ? 2 : 1)
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
   FI_TRACE_IF(tid == 0, 1);
   if (seg_source_idle(src)) {
-    if (warp == 1) tc5::tmem_dealloc(tmem, Tc5Cols<HP>::kAlloc);
+    if (warp == 1) tc5::tmem_dealloc(tmem, Tc5Cols<Q1>::kAlloc);
     return;
   }
   if (p.enable_pdl == 1) pdl_launch_dependents();  // early trigger, see paged_decode_kernel
@@ -956,17 +1285,18 @@ __global__ void __launch_bounds__(kTc5Threads, HD == 128 ? 2 : 1)
   // requests its first page indices and then waits, the MMA issuer touches no global memory
   if (warp < 4) {
     if (p.enable_pdl) pdl_wait();
-    if constexpr (HP) tc5_softmax<QT, KVF, HP>(p, src, base, qbufs, pbufs, scratch, pair_scratch, bars, tmem, p.num_stages);
+    if constexpr (WIDE) tc5_softmax_wide<QT, KVF>(p, src, base, qbufs, pbufs, scratch, pair_scratch, bars, tmem, p.num_stages);
+    else if constexpr (HP) tc5_softmax<QT, KVF, HP>(p, src, base, qbufs, pbufs, scratch, pair_scratch, bars, tmem, p.num_stages);
     else tc5_softmax_single<QT, KVF, HD>(p, src, base, qbufs, pbufs, scratch, bars, tmem, p.num_stages);
   } else if (warp == 4) {
     produce_tma<KVF, HD, false, HP>(p, src, &kmap, &vmap, ring, full_bar, empty_bar);
   } else {
-    tc5_issue<KVF, HP, HD>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
+    tc5_issue<KVF, MODE, HD>(p, src, ring, smem_u32(qbufs), smem_u32(pbufs), full_bar, empty_bar, bars, tmem);
   }
   if (p.enable_pdl == 2) pdl_launch_dependents();
   tc5::fence_before_sync();
   __syncthreads();
-  if (warp == 1) tc5::tmem_dealloc(tmem, Tc5Cols<HP>::kAlloc);
+  if (warp == 1) tc5::tmem_dealloc(tmem, Tc5Cols<Q1>::kAlloc);
 }
 
 }  // namespace fib200

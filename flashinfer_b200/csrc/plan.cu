@@ -158,7 +158,10 @@ static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* 
   const int kvf0 = kv_format(q_dtype, kv_dtype);
   // FI_PLAN_WIDE_UNITS: 16 columns per unit (two MMA N tiles, decode_kernel.cuh consume_rows2)
   const char* wide_env = getenv("FI_B200_WIDE_UNITS");  // 0: ignore the flag (A/B runs; read at every plan)
-  const bool wide_units = (flags & FI_PLAN_WIDE_UNITS) != 0 && kvf0 == 0 && head_dim <= 128 && page_size >= 8 &&
+  const char* tc5_env = getenv("FI_B200_FP8_TC5");
+  const bool wide_shape = kvf0 == 0 ? head_dim <= 128
+                                    : (kvf0 > 0 && head_dim == 128 && !(tc5_env != nullptr && tc5_env[0] == '0'));
+  const bool wide_units = (flags & FI_PLAN_WIDE_UNITS) != 0 && wide_shape && page_size >= 8 &&
                           (page_size & (page_size - 1)) == 0 && tuning().loader != 2 &&
                           !(wide_env != nullptr && wide_env[0] == '0');
   const int kv_div = group_split(num_qo_heads / num_kv_heads, wide_units ? 2 * kMaxGroup : max_group_for(head_dim));

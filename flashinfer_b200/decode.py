@@ -49,6 +49,17 @@ def _host_i32_ptr(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
     return h, h.data_ptr()
 
 
+def rows_can_share_the_stream(kv_dtype: torch.dtype, head_dim: int, page_size: int) -> bool:
+    """Shapes with multi-row units (FiDecodeRunArgs.q_rows): 16-bit KV on the mma.sync kernel, fp8 KV on the
+    tcgen05 kernel's wide mode (head_dim 128, TMA-sized pages)."""
+    if os.environ.get("FI_B200_MTP_ROWS", "1") == "0" or head_dim == 512:
+        return False
+    if kv_dtype in (torch.float16, torch.bfloat16):
+        return True
+    return (kv_dtype in (torch.float8_e4m3fn, torch.float8_e5m2) and head_dim == 128 and page_size >= 8
+            and page_size & (page_size - 1) == 0 and os.environ.get("FI_B200_FP8_TC5", "1") != "0")
+
+
 def _unsupported_variant(pos_encoding_mode: str) -> None:
     _check_pos_encoding_mode(pos_encoding_mode)
     # all three reference modes are built: "NONE" and "ALIBI" on the tuned kernels, "ROPE_LLAMA"
@@ -482,10 +493,9 @@ class BatchDecodeWithPagedKVCacheWrapper:
         """Multi-token decode as multi-row units (FiDecodeRunArgs.q_rows): the n rows of a request ride
         its KV stream as extra columns of the GQA group instead of re-reading it once per row — 16-bit
         KV without ROPE_LLAMA / sliding window (the rest takes one decode request per row)."""
-        kv_dt = self._mtp_src[6]
-        return (kv_dt in (torch.float16, torch.bfloat16) and self._pos_encoding_mode != "ROPE_LLAMA"
-                and self._window_left < 0 and self._mtp_src[3] != 512
-                and os.environ.get("FI_B200_MTP_ROWS", "1") != "0")
+        head_dim, page_size, kv_dt = self._mtp_src[3], self._mtp_src[4], self._mtp_src[6]
+        return (rows_can_share_the_stream(kv_dt, head_dim, page_size) and self._pos_encoding_mode != "ROPE_LLAMA"
+                and self._window_left < 0)
 
     def _make_mtp_child(self, n: int) -> "BatchDecodeWithPagedKVCacheWrapper":
         if self._mtp_rows_share_the_stream():
@@ -540,7 +550,7 @@ class BatchDecodeWithPagedKVCacheWrapper:
         """FI_PLAN_HEAD_PAIRS (include/fi_b200.h): an NHD cache keeps the rows of consecutive KV heads
         adjacent, which the fp8 tcgen05 kernel streams as pairs; the planner ignores the bit for every
         shape it does not apply to."""
-        if pos_encoding_mode == "ROPE_LLAMA" or not self._head_pairs_ok:
+        if pos_encoding_mode == "ROPE_LLAMA" or not self._head_pairs_ok or self._q_rows > 1:
             return False
         # FI_B200_HEAD_PAIRS=2: also for HND caches (A/B runs; the kernel takes any head stride)
         return self._kv_layout == "NHD" or os.environ.get("FI_B200_HEAD_PAIRS") == "2"

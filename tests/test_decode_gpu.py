@@ -681,6 +681,53 @@ def test_gqa_groups_of_9_to_16_are_one_unit(hq, hkv, d, page, layout, variant):
 
 
 @pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
+@pytest.mark.parametrize("n,hq,hkv", [(1, 128, 8), (1, 12, 1), (1, 40, 4), (2, 8, 8), (2, 16, 4), (2, 32, 4), (3, 16, 4),
+                                      (4, 32, 8), (4, 8, 1), (8, 24, 2)])
+@pytest.mark.parametrize("page,layout", [(16, "NHD"), (8, "HND"), (64, "NHD")])
+@pytest.mark.parametrize("variant", ["plain", "alibi+cap", "sinks"])
+def test_fp8_wide_units(kv_dtype, n, hq, hkv, page, layout, variant):
+    """fp8 KV on the tcgen05 kernel's wide mode: up to 16 (row, head) columns per unit — GQA groups of
+    9 .. 16 as one unit (n = 1) and run(q_len_per_req = n) with the rows sharing the KV stream — against
+    the oracle on every row's causal prefix; split units, empty rows, ALiBi + soft cap, sinks."""
+    from flashinfer_b200.utils import get_alibi_slopes
+
+    fi = _fi()
+    d = 128
+    lens = [5, 97, 3000, 2, 64, 1, 7000, 0]
+    cache, indptr, indices, last = make_paged_case(lens, hkv, d, page, layout, torch.float32, seed=161)
+    cache = (cache * 0.5).to(kv_dtype)
+    q = make_q(len(lens) * n, hq, d, torch.float16, seed=162)
+    kw, okw, rkw = {}, {}, {}
+    if variant == "alibi+cap":
+        kw = dict(pos_encoding_mode="ALIBI", logits_soft_cap=30.0)
+        okw = dict(alibi_slopes=get_alibi_slopes(hq), logits_soft_cap=30.0)
+    elif variant == "sinks":
+        rkw = dict(sinks=torch.linspace(-1.0, 2.0, hq, device=DEV))
+        okw = dict(sinks=rkw["sinks"].cpu())
+    w = fi.BatchDecodeWithPagedKVCacheWrapper(_workspace(), layout)
+    w.plan(indptr, indices, last, hq, hkv, d, page, q_data_type=torch.float16, kv_data_type=kv_dtype, **kw)
+    if n == 1:
+        assert int(w._plan_info[13]) == hkv  # one unit per KV head: no virtual heads
+        o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True, k_scale=0.5, v_scale=2.0, **rkw)
+    else:
+        o, lse = w.run(q.to(DEV), cache.to(DEV), return_lse=True, q_len_per_req=n, k_scale=0.5, v_scale=2.0, **rkw)
+        assert w._mtp_children[n]._q_rows == n
+    torch.cuda.synchronize()
+    k4, v4 = orc.unpack_cache(cache, layout)
+    for b, L in enumerate(lens):
+        k, v = orc.gather_paged_kv(k4, v4, indptr, indices, last, b, layout)
+        for t in range(n):
+            Lt = max(L - (n - 1 - t), 0)
+            o_ref, lse_ref = orc.decode_attention_ref(q[b * n + t], k[:Lt].float(), v[:Lt].float(),
+                                                      0.5 / math.sqrt(d), **okw)
+            assert (o[b * n + t].float().cpu() - 2.0 * o_ref).abs().max().item() <= O_TOL_FP8, (b, t)
+            if variant == "alibi+cap":
+                assert _alibi_lse_ok(lse[b * n + t].cpu(), lse_ref)
+            elif Lt > 0 or variant != "sinks":
+                assert (lse[b * n + t].cpu() - lse_ref).abs().max().item() <= LSE_TOL, (b, t)
+
+
+@pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.float8_e5m2])
 @pytest.mark.parametrize("layout", ["NHD", "HND"])
 @pytest.mark.parametrize("pos_mode", ["NONE", "ROPE_LLAMA"])
 def test_fp8_kv_at_head_dim_64(kv_dtype, layout, pos_mode):
