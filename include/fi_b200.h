@@ -197,7 +197,7 @@ FI_API int fi_batch_decode_run(void* float_ws, void* int_ws, const int64_t* plan
  */
 #define FI_PLAN_HEAD_PAIRS 1
 /*
- * FI_PLAN_WIDE_UNITS: units of up to 16 query-head columns instead of 8 (16-bit KV, head_dim <= 128,
+ * FI_PLAN_WIDE_UNITS: units of up to 16 query-head columns instead of 8 (16-bit KV at head_dim <= 128 or fp8 KV at 128,
  * power-of-two pages >= 8; the caller promises that run() will not ask for ROPE_LLAMA).  The 16-bit
  * kernel then carries two 8-column MMA tiles per KV pass: GQA groups of 9 .. 16 (Llama-3-405B: 16)
  * stream their KV head once instead of once per 8 query heads, and plans that run with
