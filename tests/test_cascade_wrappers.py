@@ -240,3 +240,43 @@ def test_multi_level_cascade_in_a_cuda_graph(causal, rows_per_req):
     with pytest.raises(ValueError):  # another number of query rows cannot reuse the captured shapes
         w.plan([torch.tensor([0, bs * n + 1], dtype=torch.int32), torch.arange(bs + 2, dtype=torch.int32)],
                [t[0] for t in tb], [t[1] for t in tb], [t[2] for t in tb], Hq, Hkv, D, page, q_data_type=dtype)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kv_dtype", [torch.float8_e4m3fn, torch.bfloat16])
+def test_two_level_cascade_shared_prefix_rows_share_the_stream(kv_dtype):
+    """Shared prefix (one group, every request a row) + unique suffixes with 3 appended rows each: both levels
+    run as multi-row units (fp8 KV: the tcgen05 kernel's wide mode, non-causal below the last level) —
+    against full attention over the concatenated KV."""
+    import flashinfer_b200 as fi
+    from oracle.attention_ref import gather_paged_kv, unpack_cache
+
+    dev, dtype = "cuda:0", torch.bfloat16
+    bs, Hq, Hkv, D, page, n = 5, 16, 4, 128, 16, 3
+    shared_len, lens = 777, [n + 40, n, 300, n + 1, 2000]
+    need = lambda L: -(-L // page)
+    g = torch.Generator().manual_seed(31)
+    pool = need(shared_len) + sum(need(L) for L in lens) + 4
+    cache = (torch.randn(pool, 2, page, Hkv, D, generator=g) * 0.5).to(kv_dtype).to(dev)
+    q = torch.randn(bs * n, Hq, D, generator=g).to(dtype).to(dev)
+    perm = torch.randperm(pool, generator=g).tolist()
+    take = lambda k: [perm.pop() for _ in range(k)]
+    tb = [_level_tables([take(need(shared_len))], [(shared_len - 1) % page + 1]),
+          _level_tables([take(need(L)) for L in lens], [(L - 1) % page + 1 for L in lens])]
+    qo = [torch.tensor([0, bs * n], dtype=torch.int32), torch.arange(bs + 1, dtype=torch.int32) * n]
+    w = fi.MultiLevelCascadeAttentionWrapper(2, torch.zeros(32 << 20, dtype=torch.uint8, device=dev), "NHD")
+    w.plan(qo, [t[0] for t in tb], [t[1] for t in tb], [t[2] for t in tb], Hq, Hkv, D, page, causal=True,
+           q_data_type=dtype, kv_data_type=kv_dtype)
+    assert [x._q_rows for x in w._batch_decode_wrappers] == [bs * n, n]
+    assert [x._q_rows_noncausal for x in w._batch_decode_wrappers] == [1, 0]
+    o = w.run(q, cache)
+    kc, vc = unpack_cache(cache.cpu(), "NHD")
+    ks, vs = gather_paged_kv(kc, vc, tb[0][0].tolist(), tb[0][1].tolist(), tb[0][2].tolist(), 0, "NHD")
+    tol = 3e-2 if kv_dtype != torch.bfloat16 else O_TOL
+    for r in range(bs):
+        k2, v2 = gather_paged_kv(kc, vc, tb[1][0].tolist(), tb[1][1].tolist(), tb[1][2].tolist(), r, "NHD")
+        for t in range(n):
+            keep = lens[r] - (n - 1 - t)
+            ref = _full_attention(q[r * n + t], torch.cat([ks, k2[:keep]]).float(), torch.cat([vs, v2[:keep]]).float(),
+                                  1.0 / math.sqrt(D))
+            assert (o[r * n + t].float().cpu() - ref).abs().max().item() <= tol, (r, t)
