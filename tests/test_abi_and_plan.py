@@ -321,3 +321,35 @@ def test_head_pair_plan(page):
     rc, err, small = host_plan(indptr4, last4, hq, hkv, 128, 4, nctas, kv_dtype=_lib.DTYPE_E4M3,
                                flags=_lib.PLAN_HEAD_PAIRS)
     assert rc == 0 and small["info"][PI["head_pairs"]] == 0
+
+
+def test_wide_unit_plans():
+    """FI_PLAN_WIDE_UNITS (include/fi_b200.h): up to 16 query columns per unit — GQA groups of 9 .. 16 are one
+    unit per KV head instead of two virtual heads (16-bit KV at head_dim <= 128, fp8 KV at 128, TMA-sized pages);
+    groups above 16 split into units of <= 16; every other shape gets the plan it would have got without the flag."""
+    from flashinfer_b200 import _lib
+
+    kv_lens, page, nctas = [4096] * 6 + [77, 0, 5000, 1], 16, 296
+    indptr, last = lens_to_table(kv_lens, page)
+
+    def plan(hq, hkv, d=128, kvd=1, flags=_lib.PLAN_WIDE_UNITS, pg=page, ip=indptr, lp=last):
+        rc, err, pl = host_plan(ip, lp, hq, hkv, d, pg, nctas, kv_dtype=kvd, flags=flags)
+        assert rc == 0, err
+        return pl
+
+    for hq, hkv, kvd, d in ((128, 8, 1, 128), (12, 1, 1, 64), (40, 4, 1, 128), (128, 8, _lib.DTYPE_E4M3, 128)):
+        pl = plan(hq, hkv, d=d, kvd=kvd)
+        info = pl["info"]
+        assert info[PI["num_kv_heads"]] == hkv and info[PI["kv_head_div"]] == 1
+        replay_plan(pl, kv_lens, hkv, tile=64 if kvd == 1 else 128)
+    # 24 / 1 heads: two units of 12 columns; 64 / 1: four of 16
+    assert plan(24, 1)["info"][PI["kv_head_div"]] == 2 and plan(64, 1)["info"][PI["kv_head_div"]] == 4
+    # not applicable: head_dim 256, fp8 at head_dim 256, small pages -> as without the flag
+    indptr4, last4 = lens_to_table(kv_lens, 4)
+    for kw in (dict(d=256), dict(d=256, kvd=_lib.DTYPE_E4M3), dict(pg=4, ip=indptr4, lp=last4)):
+        a, b = plan(128, 8, **kw), plan(128, 8, flags=0, **kw)
+        assert a["info"][PI["kv_head_div"]] == 2
+        assert np.array_equal(a["info"], b["info"]) and np.array_equal(a["segments"], b["segments"])
+    # groups of <= 8 are untouched by the flag
+    a, b = plan(32, 8), plan(32, 8, flags=0)
+    assert np.array_equal(a["info"], b["info"]) and np.array_equal(a["segments"], b["segments"])
