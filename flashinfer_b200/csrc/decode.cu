@@ -12,9 +12,13 @@
 #include <mutex>
 #include <utility>
 
-#include "decode_kernel.cuh"
-#include "decode_kernel_tc5.cuh"
-#include "decode_rope_kernel.cuh"
+#ifdef FI_B200_TRACE
+// the trace build (build.py --trace) is one translation unit: the kernels share g_fi_trace
+#include "decode_mma.cu"
+#include "decode_tc5.cu"
+#include "decode_variant.cu"
+#endif
+#include "decode_launch.h"
 #include "host_common.h"
 #include "merge_kernels.cuh"
 
@@ -159,98 +163,7 @@ static bool tma_eligible(const void* k, const void* v, int es, int64_t sn, int64
 }
 
 // ---- kernel launch ---------------------------------------------------------------
-// The opt-in dynamic shared memory limit is a per-(function, device) attribute: set it when it
-// has to grow (or the device changed), not on every launch.
-template <typename K>
-static cudaError_t ensure_smem_attr(K kern, int smem) {
-  // all kernels share one pointer type, so the cache is keyed by (function, device)
-  static thread_local std::map<std::pair<const void*, int>, int> cache;
-  int dev = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return e;
-  int& cur = cache[{reinterpret_cast<const void*>(kern), dev}];
-  if (smem <= cur) return cudaSuccess;
-  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e == cudaSuccess) cur = smem;
-  return e;
-}
-
-template <int QT, int KVF, int HD, int LOADER, bool ROPE = false, int MROWS = 0>
-static int launch_one(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
-                      int grid, cudaStream_t stream) {
-  auto kern = paged_decode_kernel<QT, KVF, HD, LOADER, ROPE, MROWS>;
-  const int smem = SmemLayout<KVF, HD>::total(p.num_stages);
-  FI_CUDA_TRY(ensure_smem_attr(kern, smem));
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(BlockDim<LOADER>::kThreads);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = p.enable_pdl ? 1 : 0;
-  FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p, km, vm));
-  return FI_OK;
-}
-
-template <int QT, int KVF, int HD>
-static int launch_loader(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
-                         int grid, bool tma, cudaStream_t stream) {
-  if constexpr (KVF == 0) {
-    if (p.q_rows >= 1 && p.group_size > kMaxGroup) {  // wide units: two N tiles per warp (TMA loader, D <= 128)
-      if constexpr (HD <= 128) {
-        if (tma) return launch_one<QT, KVF, HD, 0, false, 2>(p, km, vm, grid, stream);
-      }
-      return fail(FI_ERR_REPLAN, "the plan was made with FI_PLAN_WIDE_UNITS, but this run() needs the gather loader");
-    }
-    if (p.q_rows > 1)  // multi-row units (fi_batch_decode_run_args q_rows): checked by the caller
-      return tma ? launch_one<QT, KVF, HD, 0, false, 1>(p, km, vm, grid, stream)
-                 : launch_one<QT, KVF, HD, 1, false, 1>(p, km, vm, grid, stream);
-    // ROPE_LLAMA on 16-bit KV: K rotated in registers (decode_kernel.cuh)
-    if (p.rope)
-      return tma ? launch_one<QT, KVF, HD, 0, true>(p, km, vm, grid, stream)
-                 : launch_one<QT, KVF, HD, 1, true>(p, km, vm, grid, stream);
-  }
-  return tma ? launch_one<QT, KVF, HD, 0>(p, km, vm, grid, stream)
-             : launch_one<QT, KVF, HD, 1>(p, km, vm, grid, stream);
-}
-
-template <int QT, int KVF>
-static int launch_hd(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
-                     int head_dim, int grid, bool tma, cudaStream_t stream) {
-  switch (head_dim) {
-    case 128: return launch_loader<QT, KVF, 128>(p, km, vm, grid, tma, stream);
-    case 256: return launch_loader<QT, KVF, 256>(p, km, vm, grid, tma, stream);
-    case 64:
-      if constexpr (KVF == 0) return launch_loader<QT, KVF, 64>(p, km, vm, grid, tma, stream);
-    default: break;
-  }
-  return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
-}
-
-// fp8 KV, head_dim 128, TMA-eligible pages: tcgen05 / TMEM kernel (decode_kernel_tc5.cuh)
-template <int QT, int KVF, int MODE = kTc5Single, int HD = 128>
-static int launch_tc5(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm, int grid,
-                      cudaStream_t stream) {
-  auto kern = paged_decode_tc5_kernel<QT, KVF, MODE, HD>;
-  const int smem = SmemLayout<KVF, HD>::total(p.num_stages) + (MODE != kTc5Single ? kTc5PairScratchBytes : 0);
-  FI_CUDA_TRY(ensure_smem_attr(kern, smem));
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kTc5Threads);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = p.enable_pdl ? 1 : 0;
-  FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p, km, vm));
-  return FI_OK;
-}
-
+// The kernels are instantiated in decode_mma.cu / decode_tc5.cu / decode_variant.cu (decode_launch.h).
 static int default_l2_hints() {
   static const int l2_env = [] { const char* e = getenv("FI_B200_L2_HINTS"); return e ? atoi(e) : -1; }();
   return l2_env >= 0 ? l2_env : 3;
@@ -264,92 +177,38 @@ static bool use_tc5() {
   return on;
 }
 
-// pos_encoding_mode = ROPE_LLAMA: the CUDA-core variant kernel (decode_rope_kernel.cuh)
-template <int QT, int KVF>
-static int launch_rope(const DecodeParams& p, int head_dim, int grid, cudaStream_t stream) {
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(rope_warps(head_dim) * 32);
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = p.enable_pdl ? 1 : 0;
-#define FI_ROPE_CASE(HD_)                                                                          \
-  case HD_:                                                                                        \
-    if (p.group_size <= 4) FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, HD_, 4>, p)); \
-    else FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, HD_, 8>, p));      \
-    break;
-  switch (head_dim) {
-    FI_ROPE_CASE(64)
-    FI_ROPE_CASE(128)
-    FI_ROPE_CASE(256)
-    case 512:  // groups above 4 were split into virtual KV heads by the planner (max_group_for)
-      if (p.group_size > 4) return fail(FI_ERR_UNSUPPORTED, "head_dim 512 takes GQA groups of at most 4 per unit");
-      FI_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_decode_rope_kernel<QT, KVF, 512, 4>, p));
-      break;
-    default: return fail(FI_ERR_UNSUPPORTED, "unsupported head_dim %d", head_dim);
-  }
-#undef FI_ROPE_CASE
-  return FI_OK;
-}
-
 static int launch_decode(const DecodeParams& p, const CUtensorMap& km, const CUtensorMap& vm,
                          int q_dtype, int kvf, int head_dim, int grid, bool tma,
                          cudaStream_t stream) {
   const bool bf = q_dtype == FI_DTYPE_BF16;
   static const bool rope_cuda_core = [] { const char* e = getenv("FI_B200_ROPE_CUDA_CORE"); return e && e[0] == '1'; }();
   // fp8 KV with ROPE_LLAMA (or A/B runs), and fp8 KV at head_dim 64 in any mode but ALiBi (64-byte rows do
-  // not fit the 128-byte swizzle atoms of the MMA kernels): the CUDA-core variant kernel; without RoPE it
-  // runs with zero rotation frequencies, i.e. the identity rotation
+  // not fit the 128-byte swizzle atoms of the MMA kernels): the CUDA-core variant kernel
+  // (decode_rope_kernel.cuh); without RoPE it runs with zero rotation frequencies, i.e. the identity rotation
   if ((p.rope && (kvf != 0 || rope_cuda_core)) || (kvf != 0 && head_dim == 64) || head_dim == 512) {
     if (p.alibi_slopes != nullptr)
       return fail(FI_ERR_UNSUPPORTED, "ALIBI at head_dim 512 or with fp8 KV at head_dim 64 is not built");
+    DecodeParams p2 = p;
     if (!p.rope) {
-      DecodeParams p2 = p;
       p2.rope_rcp_scale = 0.f;
       p2.rope_rcp_theta = 1.f;
-      switch (kvf) {
-        case 0: return bf ? launch_rope<1, 0>(p2, head_dim, grid, stream) : launch_rope<0, 0>(p2, head_dim, grid, stream);
-        case 1: return bf ? launch_rope<1, 1>(p2, head_dim, grid, stream) : launch_rope<0, 1>(p2, head_dim, grid, stream);
-        case 2: return bf ? launch_rope<1, 2>(p2, head_dim, grid, stream) : launch_rope<0, 2>(p2, head_dim, grid, stream);
-        default: return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
-      }
     }
-    switch (kvf) {
-      case 0: return bf ? launch_rope<1, 0>(p, head_dim, grid, stream) : launch_rope<0, 0>(p, head_dim, grid, stream);
-      case 1: return bf ? launch_rope<1, 1>(p, head_dim, grid, stream) : launch_rope<0, 1>(p, head_dim, grid, stream);
-      case 2: return bf ? launch_rope<1, 2>(p, head_dim, grid, stream) : launch_rope<0, 2>(p, head_dim, grid, stream);
-      default: return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
-    }
+    return bf ? launch_variant_slice<1>(p2, kvf, head_dim, grid, stream)
+              : launch_variant_slice<0>(p2, kvf, head_dim, grid, stream);
   }
-  if (p.head_pairs) {  // fi_batch_decode_run checked that this launch fits a head-pair plan
-    if (kvf == 1) return bf ? launch_tc5<1, 1, kTc5Pairs>(p, km, vm, grid, stream) : launch_tc5<0, 1, kTc5Pairs>(p, km, vm, grid, stream);
-    return bf ? launch_tc5<1, 2, kTc5Pairs>(p, km, vm, grid, stream) : launch_tc5<0, 2, kTc5Pairs>(p, km, vm, grid, stream);
-  }
-  if (kvf != 0 && p.q_rows >= 1) {  // wide units / multi-row units with fp8 KV (checked by the caller: D 128, TMA, tcgen05)
-    if (kvf == 1) return bf ? launch_tc5<1, 1, kTc5Wide>(p, km, vm, grid, stream) : launch_tc5<0, 1, kTc5Wide>(p, km, vm, grid, stream);
-    return bf ? launch_tc5<1, 2, kTc5Wide>(p, km, vm, grid, stream) : launch_tc5<0, 2, kTc5Wide>(p, km, vm, grid, stream);
-  }
-  if (kvf != 0 && head_dim == 256 && tma && use_tc5()) {
-    if (kvf == 1) return bf ? launch_tc5<1, 1, kTc5Single, 256>(p, km, vm, grid, stream) : launch_tc5<0, 1, kTc5Single, 256>(p, km, vm, grid, stream);
-    return bf ? launch_tc5<1, 2, kTc5Single, 256>(p, km, vm, grid, stream) : launch_tc5<0, 2, kTc5Single, 256>(p, km, vm, grid, stream);
-  }
-  if (kvf != 0 && head_dim == 128 && tma && use_tc5()) {
-    if (kvf == 1) return bf ? launch_tc5<1, 1>(p, km, vm, grid, stream) : launch_tc5<0, 1>(p, km, vm, grid, stream);
-    return bf ? launch_tc5<1, 2>(p, km, vm, grid, stream) : launch_tc5<0, 2>(p, km, vm, grid, stream);
-  }
-  switch (kvf) {
-    case 0: return bf ? launch_hd<1, 0>(p, km, vm, head_dim, grid, tma, stream)
-                      : launch_hd<0, 0>(p, km, vm, head_dim, grid, tma, stream);
-    case 1: return bf ? launch_hd<1, 1>(p, km, vm, head_dim, grid, tma, stream)
-                      : launch_hd<0, 1>(p, km, vm, head_dim, grid, tma, stream);
-    case 2: return bf ? launch_hd<1, 2>(p, km, vm, head_dim, grid, tma, stream)
-                      : launch_hd<0, 2>(p, km, vm, head_dim, grid, tma, stream);
-    default: break;
-  }
-  return fail(FI_ERR_UNSUPPORTED, "unsupported kv format");
+  // fp8 KV on the tcgen05 / TMEM kernels (decode_kernel_tc5.cuh)
+  int tc5_mode = -1;
+  if (p.head_pairs) tc5_mode = kTc5Pairs;  // fi_batch_decode_run checked that this launch fits a head-pair plan
+  else if (kvf != 0 && p.q_rows >= 1) tc5_mode = kTc5Wide;  // wide / multi-row units (checked by the caller: D 128, TMA, tcgen05)
+  else if (kvf != 0 && (head_dim == 256 || head_dim == 128) && tma && use_tc5()) tc5_mode = kTc5Single;
+  if (tc5_mode >= 0)
+    return bf ? launch_tc5_slice<1>(p, km, vm, kvf, tc5_mode, head_dim, grid, stream)
+              : launch_tc5_slice<0>(p, km, vm, kvf, tc5_mode, head_dim, grid, stream);
+  if (kvf == 0)
+    return bf ? launch_mma_slice<1, false>(p, km, vm, kvf, head_dim, grid, tma, stream)
+              : launch_mma_slice<0, false>(p, km, vm, kvf, head_dim, grid, tma, stream);
+  return bf ? launch_mma_slice<1, true>(p, km, vm, kvf, head_dim, grid, tma, stream)
+            : launch_mma_slice<0, true>(p, km, vm, kvf, head_dim, grid, tma, stream);
 }
 
 static int launch_merge(const MergeParams& mp, int grid, cudaStream_t stream) {

@@ -45,9 +45,7 @@ struct Tc5Cols {
   static constexpr uint32_t kO = 2 * kSStride;          // HP: O_h at kO + 16 h
   static constexpr uint32_t kAlloc = HP ? 256 : 128;    // a power of two >= kO + (HP ? 32 : 16)
 };
-// kernel modes: one KV head and <= 8 query columns per unit; a PAIR of KV heads; one KV head and <= 16
-// (row, head) columns (FI_PLAN_WIDE_UNITS, FiDecodeRunArgs.q_rows)
-constexpr int kTc5Single = 0, kTc5Pairs = 1, kTc5Wide = 2;
+// kernel modes kTc5Single / kTc5Pairs / kTc5Wide: decode_params.h
 constexpr int kTc5ColS = 0;
 constexpr float kTc5Bump = 5.f;     // raise rho when a tile max exceeds it by more than 2^5
 constexpr float kTc5PShift = 3.f;   // p = 2^(x - rho + 3): <= 2^8 right after a bump

@@ -21,6 +21,9 @@ __host__ __device__ constexpr int tile_tokens(int kvf) { return kvf == 0 ? 64 : 
 constexpr int kMaxStages = 12;
 constexpr int kScratchMlBytes = 768;   // per-CTA scratch (floats 0 .. 191): warp exchange, queue control, inline pages
 constexpr int kTc5PairScratchBytes = 512;  // head-pair tcgen05 kernel only, after the barriers
+// tcgen05 kernel modes: one KV head and <= 8 query columns per unit; a PAIR of KV heads (FI_PLAN_HEAD_PAIRS);
+// one KV head and <= 16 (row, head) columns (FI_PLAN_WIDE_UNITS, FiDecodeRunArgs.q_rows)
+constexpr int kTc5Single = 0, kTc5Pairs = 1, kTc5Wide = 2;
 constexpr int kSegCache = 32;         // segment queue (ring) in smem per CTA; a power of two
 constexpr int kSegRefill = 8;         // segments the feeder loads from the list at a time
 constexpr float kNegInf = -5e4f;      // finite "-inf", reference math.cuh:32
