@@ -353,3 +353,89 @@ def test_wide_unit_plans():
     # groups of <= 8 are untouched by the flag
     a, b = plan(32, 8), plan(32, 8, flags=0)
     assert np.array_equal(a["info"], b["info"]) and np.array_equal(a["segments"], b["segments"])
+
+
+def _fuzz_plan_case(data):
+    from hypothesis import strategies as st
+    from flashinfer_b200 import _lib
+
+    bs = data.draw(st.integers(1, 24), label="bs")
+    len_st = st.one_of(st.sampled_from([0, 1, 63, 64, 65, 127, 128, 129, 4096]), st.integers(0, 9000))
+    if data.draw(st.booleans(), label="uniform"):
+        kv_lens = [data.draw(len_st, label="len")] * bs
+    else:
+        kv_lens = [data.draw(len_st, label="len") for _ in range(bs)]
+    page = data.draw(st.sampled_from([1, 2, 4, 5, 8, 16, 32, 64, 128]), label="page")
+    hkv = data.draw(st.sampled_from([1, 2, 3, 4, 8]), label="hkv")
+    group = data.draw(st.sampled_from([1, 2, 3, 4, 5, 6, 7, 8, 9, 12, 16, 24, 32]), label="group")
+    head_dim = data.draw(st.sampled_from([64, 128, 256, 512]), label="head_dim")
+    fp8 = data.draw(st.booleans(), label="fp8")
+    nctas = data.draw(st.sampled_from([1, 7, 31, 148, 296, 600]), label="nctas")
+    window = data.draw(st.sampled_from([-1, -1, 0, 17, 1000]), label="window_left")
+    mode = data.draw(st.sampled_from(["default", "default", "fixed", "nosplit"]), label="mode")
+    flags = data.draw(st.sampled_from([0, _lib.PLAN_HEAD_PAIRS, _lib.PLAN_WIDE_UNITS,
+                                       _lib.PLAN_HEAD_PAIRS | _lib.PLAN_WIDE_UNITS]), label="flags")
+    graph = data.draw(st.booleans(), label="cuda_graph")
+    with_indices = data.draw(st.booleans(), label="with_indices")
+    return dict(kv_lens=kv_lens, page=page, hkv=hkv, hq=hkv * group, head_dim=head_dim,
+                kv_dtype=_lib.DTYPE_E4M3 if fp8 else 1, nctas=nctas, window=window, mode=mode, flags=flags,
+                graph=int(graph), with_indices=with_indices,
+                fixed=data.draw(st.sampled_from([1, 3, 16]), label="fixed_split_pages") if mode == "fixed" else 0)
+
+
+def _check_fuzzed_plan(c):
+    from flashinfer_b200 import _lib
+
+    indptr, last = lens_to_table(c["kv_lens"], c["page"])
+    indices = None
+    if c["with_indices"]:
+        indices = np.random.default_rng(len(c["kv_lens"])).permutation(int(indptr[-1]) + 3)[: int(indptr[-1])]
+    rc, err, plan = host_plan(indptr, last, c["hq"], c["hkv"], c["head_dim"], c["page"], c["nctas"],
+                              kv_dtype=c["kv_dtype"], window_left=c["window"], cuda_graph=c["graph"],
+                              fixed_split_pages=c["fixed"], disable_split_kv=int(c["mode"] == "nosplit"),
+                              indices=indices, flags=c["flags"], int_bytes=32 << 20, float_bytes=1 << 36)
+    assert rc == 0, err
+    info = plan["info"]
+    fp8 = c["kv_dtype"] == _lib.DTYPE_E4M3
+    pairs = int(info[PI["head_pairs"]])
+    div = int(info[PI["kv_head_div"]])
+    tile = (TILE_FP8 if fp8 else TILE) // (2 if pairs else 1)
+    unit_heads = int(info[PI["num_kv_heads"]])
+    # what a unit is: a KV head, `div` virtual heads of one, or a pair of KV heads — never two of those at once
+    assert unit_heads == (c["hkv"] // 2 if pairs else c["hkv"] * div) and not (pairs and div > 1)
+    group = c["hq"] // c["hkv"]
+    cols = group * 2 if pairs else group // div
+    assert group % div == 0 and info[PI["hq"]] == c["hq"]
+    wide = bool(c["flags"] & _lib.PLAN_WIDE_UNITS)
+    assert cols <= (16 if wide or pairs else 8), (cols, div, pairs)
+    if c["head_dim"] == 512:
+        assert cols <= 4
+    if pairs:
+        assert fp8 and c["head_dim"] == 128 and c["flags"] & _lib.PLAN_HEAD_PAIRS and c["hkv"] % 2 == 0 \
+            and group <= 8 and c["page"] >= 8 and c["page"] & (c["page"] - 1) == 0
+    replay_plan(plan, c["kv_lens"], unit_heads, window_left=c["window"], tile=tile, chunked=c["mode"] == "fixed")
+    if c["mode"] == "nosplit":
+        assert len(plan["merges"]) == 0 and np.all(plan["segments"][:, 4] < 0)
+    # a plan is a pure function of its arguments
+    rc2, _, again = host_plan(indptr, last, c["hq"], c["hkv"], c["head_dim"], c["page"], c["nctas"],
+                              kv_dtype=c["kv_dtype"], window_left=c["window"], cuda_graph=c["graph"],
+                              fixed_split_pages=c["fixed"], disable_split_kv=int(c["mode"] == "nosplit"),
+                              indices=indices, flags=c["flags"], int_bytes=32 << 20, float_bytes=1 << 36)
+    assert rc2 == 0 and np.array_equal(again["info"], info) and np.array_equal(again["segments"], plan["segments"]) \
+        and np.array_equal(again["item_heads"], plan["item_heads"]) and np.array_equal(again["merges"], plan["merges"])
+
+
+def test_plan_fuzz():
+    """Property test over the whole planner argument space (lengths incl. empty and tile-edge requests, page sizes,
+    head shapes, GQA groups 1 .. 32, head dims, fp8 / 16-bit KV, grid sizes, sliding windows, fixed_split_size /
+    disable_split_kv, FI_PLAN_* flags, CUDA-graph layout, with and without the host page table): every plan is
+    replayed — each attended token of each unit exactly once, each unit written once, each partial slot owned by
+    one merge, inline segments / page ids equal to the lists — and planned twice (bit-identical)."""
+    from hypothesis import given, settings, HealthCheck, strategies as st
+
+    @settings(max_examples=250, deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))
+    @given(st.data())
+    def run(data):
+        _check_fuzzed_plan(_fuzz_plan_case(data))
+
+    run()
