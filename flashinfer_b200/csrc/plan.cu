@@ -305,9 +305,15 @@ static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* 
       if (n_u % c == 0) return c;
     return c0;
   };
+  // Head-grouped order (static divisible plans, Hkv > 1): the REQUEST tile stream is cut into
+  // num_ctas / Hkv ranges and the Hkv CTAs of a group walk the same range, one KV head each, in
+  // step.  In an NHD cache the Hkv head rows of a token are adjacent in memory, so the group
+  // sweeps whole pages at about the same time (DRAM row locality) instead of a 1-in-Hkv comb.
+  const bool head_group = head_group_enabled() && !indivisible && num_kv_heads > 1 &&
+                          num_ctas % num_kv_heads == 0 && st.f0_pct >= 100 && total_tiles > 0;
   static thread_local std::vector<int64_t> item_end;  // exclusive end (stream position) of every item
   item_end.clear();
-  {
+  if (!head_group) {  // (the head-grouped walk below has its own, regular item boundaries)
     int64_t pos = 0;
     bool first = true;
     while (pos < total_tiles) {
@@ -325,20 +331,13 @@ static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* 
     }
     if (item_end.empty()) item_end.push_back(0);  // only zero-tile segments (or none at all)
   }
-  // Head-grouped order (static divisible plans, Hkv > 1): the REQUEST tile stream is cut into
-  // num_ctas / Hkv ranges and the Hkv CTAs of a group walk the same range, one KV head each, in
-  // step.  In an NHD cache the Hkv head rows of a token are adjacent in memory, so the group
-  // sweeps whole pages at about the same time (DRAM row locality) instead of a 1-in-Hkv comb.
-  const bool head_group = head_group_enabled() && !indivisible && num_kv_heads > 1 &&
-                          num_ctas % num_kv_heads == 0 && st.f0_pct >= 100 && total_tiles > 0;
   int64_t hg_chunk = 0, hg_groups = 0;
   if (head_group) {
     const int64_t tr = total_tiles / num_kv_heads, groups = num_ctas / num_kv_heads;
     hg_chunk = align_chunk(std::max<int64_t>((tr + groups - 1) / groups, min_tiles));
     hg_groups = (tr + hg_chunk - 1) / hg_chunk;
-    item_end.assign((size_t)(hg_groups * num_kv_heads), 0);  // only the count is used below
   }
-  const int64_t num_items = (int64_t)item_end.size();
+  const int64_t num_items = head_group ? hg_groups * num_kv_heads : (int64_t)item_end.size();
   const int64_t* const item_end_p = item_end.data();  // not through the TLS wrapper in the hot loop
 
   // ---- layout: offsets of everything the kernels get as launch parameters depend only on
@@ -577,7 +576,7 @@ static int plan_impl(void* float_ws, size_t float_ws_bytes, void* int_ws, void* 
       const int64_t first_page = (int64_t)s0.tile_begin * TT / page_size;
       const int64_t req_pages = (int64_t)indptr_host[s0.request + 1] - indptr_host[s0.request];
       const int64_t n = std::min<int64_t>(kItemInlinePages, req_pages - first_page);
-      for (int64_t j = 0; j < n; ++j) hd.pages[j] = kv_indices_host[s0.page_base + first_page + j];
+      if (n > 0) memcpy(hd.pages, kv_indices_host + s0.page_base + first_page, (size_t)n * sizeof(int32_t));
       hd.num_pages = (int32_t)std::max<int64_t>(n, 0);
     }
   }
